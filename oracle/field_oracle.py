@@ -1,0 +1,520 @@
+"""CPU oracle for the Few-TensoRF per-ray hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file restates, in plain functional PyTorch (CPU, fp32), the algorithm of the
+reference's per-ray path so that it can travel to the GPU box (where
+/root/reference does not exist).  Only tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py may import it.  The product
+package (fewtensorf_b200) never does.
+
+Parity status: the reference ships no tests or golden vectors of its own
+(SURVEY.md section 4), so this oracle is pinned against OUTPUTS OF THE REFERENCE ITSELF:
+tests/golden/make_golden.py imports the unmodified reference `models/` package
+from /root/reference in the build container, runs it on seeded inputs and
+commits the results under tests/golden/*.npz; tests/test_oracle_golden.py
+checks every function here against those vectors.
+
+Each function cites the reference file:line it follows (paths relative to the
+reference root).  Parameters travel as a flat dict keyed by the reference's
+state_dict names ("density_plane.0", "app_line.2", "basis_mat.weight",
+"renderModule.mlp.0.weight", ...), in the reference layout.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn.functional as F
+
+MAT_MODE = ((0, 1), (0, 2), (1, 2))   # models/tensorBase.py:60
+VEC_MODE = (2, 1, 0)                  # models/tensorBase.py:61
+
+
+@dataclass
+class FieldConfig:
+    """Hyper-parameters reaching the hot path (models/tensorBase.py:52-87)."""
+    model: str = "VM"                 # "VM" (TensorVMSplit) | "CP" (TensorCP)
+    shading: str = "MLP_Fea"          # MLP_Fea | MLP_PE | MLP | SH
+    grid: tuple = (128, 128, 128)
+    aabb: tuple = ((-1.5, -1.5, -1.5), (1.5, 1.5, 1.5))
+    near_far: tuple = (2.0, 6.0)
+    density_n_comp: tuple = (16, 16, 16)
+    app_n_comp: tuple = (48, 48, 48)
+    app_dim: int = 27
+    step_ratio: float = 0.5
+    density_shift: float = -10.0
+    distance_scale: float = 25.0
+    alpha_mask_thres: float = 0.001
+    fea2dense: str = "softplus"
+    weight_thres: float = 1e-4
+    pos_pe: int = 2
+    view_pe: int = 2
+    fea_pe: int = 2
+    feature_c: int = 128
+
+
+@dataclass
+class AlphaMask:
+    """Occupancy volume + its own aabb (models/tensorBase.py:30-48)."""
+    volume: torch.Tensor              # (Z, Y, X) float {0,1}
+    aabb: torch.Tensor                # (2, 3)
+
+    @property
+    def inv_grid(self):               # models/tensorBase.py:36-37
+        return 1.0 / (self.aabb[1] - self.aabb[0]) * 2
+
+
+@dataclass
+class Field:
+    cfg: FieldConfig
+    params: Dict[str, torch.Tensor]
+    alpha_mask: Optional[AlphaMask] = None
+    # derived, filled by derive_steps()
+    aabb: torch.Tensor = field(default=None)
+    inv_aabb: torch.Tensor = field(default=None)
+    step_size: torch.Tensor = field(default=None)
+    n_samples: int = 0
+
+    def __post_init__(self):
+        derive_steps(self)
+
+
+def derive_steps(f: Field) -> None:
+    """Step size / sample count — models/tensorBase.py:104-111."""
+    f.aabb = torch.tensor(f.cfg.aabb, dtype=torch.float32)
+    size = f.aabb[1] - f.aabb[0]
+    f.inv_aabb = 2.0 / size
+    g = torch.LongTensor(list(f.cfg.grid))
+    units = size / (g - 1)
+    f.step_size = torch.mean(units) * f.cfg.step_ratio
+    diag = torch.sqrt(torch.sum(torch.square(size)))
+    f.n_samples = int((diag / f.step_size).item()) + 1
+
+
+def mlp_in_dim(cfg: FieldConfig) -> int:
+    """models/mlp.py:31, :75, :113."""
+    d = cfg.app_dim + 3
+    if cfg.shading == "MLP_Fea":
+        return d + 2 * cfg.view_pe * 3 + 2 * cfg.fea_pe * cfg.app_dim
+    if cfg.shading == "MLP_PE":
+        return d + 2 * cfg.view_pe * 3 + 2 * cfg.pos_pe * 3
+    if cfg.shading == "MLP":
+        return d + 2 * cfg.view_pe * 3 + 2 * cfg.pos_pe * 3 + 2 * cfg.fea_pe * cfg.app_dim
+    raise ValueError(cfg.shading)
+
+
+def init_params(cfg: FieldConfig, seed: int = 0, scale: Optional[float] = None) -> Dict[str, torch.Tensor]:
+    """Random factors in the reference's shapes (models/tensoRF.py:146-162, :335-347;
+    models/mlp.py:28-39).  The draw ORDER is this oracle's own, not the reference's
+    (golden fixtures store the reference's parameters explicitly)."""
+    g = torch.Generator().manual_seed(seed)
+    G = cfg.grid
+    p: Dict[str, torch.Tensor] = {}
+    if cfg.model == "VM":
+        s = 0.1 if scale is None else scale
+        for name, comps in (("density", cfg.density_n_comp), ("app", cfg.app_n_comp)):
+            for k in range(3):
+                m0, m1 = MAT_MODE[k]
+                p[f"{name}_plane.{k}"] = s * torch.randn(1, comps[k], G[m1], G[m0], generator=g)
+                p[f"{name}_line.{k}"] = s * torch.randn(1, comps[k], G[VEC_MODE[k]], 1, generator=g)
+        n_app = sum(cfg.app_n_comp)
+    else:
+        s = 0.2 if scale is None else scale
+        for name, comps in (("density", cfg.density_n_comp), ("app", cfg.app_n_comp)):
+            for k in range(3):
+                p[f"{name}_line.{k}"] = s * torch.randn(1, comps[0], G[VEC_MODE[k]], 1, generator=g)
+        n_app = cfg.app_n_comp[0]
+    bound = 1.0 / math.sqrt(n_app)
+    p["basis_mat.weight"] = (torch.rand(cfg.app_dim, n_app, generator=g) * 2 - 1) * bound
+    if cfg.shading != "SH":
+        dims = [(mlp_in_dim(cfg), cfg.feature_c), (cfg.feature_c, cfg.feature_c), (cfg.feature_c, 3)]
+        for li, (fan_in, fan_out) in zip((0, 2, 4), dims):
+            b = 1.0 / math.sqrt(fan_in)
+            p[f"renderModule.mlp.{li}.weight"] = (torch.rand(fan_out, fan_in, generator=g) * 2 - 1) * b
+            p[f"renderModule.mlp.{li}.bias"] = (torch.rand(fan_out, generator=g) * 2 - 1) * b
+        p["renderModule.mlp.4.bias"].zero_()      # models/mlp.py:39
+    return p
+
+
+def plant_box(cfg: FieldConfig, p: Dict[str, torch.Tensor], half: float = 0.6, amp: float = 11.0) -> None:
+    """Planted-box density of SURVEY.md section 8(d): sigma ~ 1.3 inside a cube so that the
+    shading branch is exercised (reference-scale init never reaches it)."""
+    G = cfg.grid
+    lo, hi = cfg.aabb
+    def ind(axis):
+        return (torch.linspace(lo[axis], hi[axis], G[axis]).abs() < half).float()
+    if cfg.model == "VM":
+        m0, m1 = MAT_MODE[0]
+        p["density_plane.0"][0, 0] = amp * ind(m1)[:, None] * ind(m0)[None, :]
+        p["density_line.0"][0, 0, :, 0] = ind(VEC_MODE[0])
+    else:
+        p["density_line.0"][0, 0, :, 0] = amp * ind(VEC_MODE[0])
+        p["density_line.1"][0, 0, :, 0] = ind(VEC_MODE[1])
+        p["density_line.2"][0, 0, :, 0] = ind(VEC_MODE[2])
+
+
+# --------------------------------------------------------------------------- stage 1
+def march(f: Field, rays_o, rays_d, jitter: Optional[torch.Tensor], n_samples: int):
+    """AABB ray sampling — models/tensorBase.py:189-208 (sample_ray).
+    `jitter` is the per-ray U[0,1) column the reference draws at :201 (None = eval)."""
+    near, far = f.cfg.near_far
+    vec = torch.where(rays_d == 0, torch.full_like(rays_d, 1e-6), rays_d)
+    ra = (f.aabb[1] - rays_o) / vec
+    rb = (f.aabb[0] - rays_o) / vec
+    t_min = torch.minimum(ra, rb).amax(-1).clamp(min=near, max=far)
+    rng = torch.arange(n_samples)[None].float()
+    if jitter is not None:
+        rng = rng.repeat(rays_d.shape[-2], 1)
+        rng += jitter
+    z = t_min[..., None] + f.step_size * rng
+    pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., None]
+    outside = ((f.aabb[0] > pts) | (pts > f.aabb[1])).any(dim=-1)
+    return pts, z, ~outside
+
+
+def march_ndc(f: Field, rays_o, rays_d, z_jitter: Optional[torch.Tensor], n_samples: int):
+    """NDC sampling — models/tensorBase.py:178-187.  `z_jitter` is the [1,S] U[0,1) row of :183."""
+    near, far = f.cfg.near_far
+    z = torch.linspace(near, far, n_samples).unsqueeze(0)
+    if z_jitter is not None:
+        z = z + z_jitter * ((far - near) / n_samples)
+    pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., None]
+    outside = ((f.aabb[0] > pts) | (pts > f.aabb[1])).any(dim=-1)
+    return pts, z, ~outside
+
+
+def alpha_mask_values(m: AlphaMask, pts):
+    """models/tensorBase.py:41-48 (sample_alpha + its own normalize_coord)."""
+    c = (pts - m.aabb[0]) * m.inv_grid - 1
+    vol = m.volume.view(1, 1, *m.volume.shape[-3:])
+    return F.grid_sample(vol, c.view(1, -1, 1, 1, 3), align_corners=True).view(-1)
+
+
+def normalize(f: Field, pts):
+    """models/tensorBase.py:130-131."""
+    return (pts - f.aabb[0]) * f.inv_aabb - 1
+
+
+# --------------------------------------------------------------------------- stage 2
+def _line_coords(xn):
+    cl = torch.stack([xn[..., VEC_MODE[k]] for k in range(3)])
+    return torch.stack((torch.zeros_like(cl), cl), dim=-1).detach().view(3, -1, 1, 2)
+
+
+def _plane_coords(xn):
+    return torch.stack([xn[..., list(MAT_MODE[k])] for k in range(3)]).detach().view(3, -1, 1, 2)
+
+
+def _gs(t, coords):
+    return F.grid_sample(t, coords, align_corners=True).view(t.shape[1], -1)
+
+
+def density_feature(f: Field, xn, dmask=None):
+    """VM: models/tensoRF.py:207-227; CP: models/tensoRF.py:358-386."""
+    p = f.params
+    cl = _line_coords(xn)
+    if f.cfg.model == "VM":
+        cp = _plane_coords(xn)
+        out = torch.zeros((xn.shape[0],))
+        for k in range(3):
+            pl = _gs(p[f"density_plane.{k}"], cp[[k]])
+            ln = _gs(p[f"density_line.{k}"], cl[[k]])
+            if dmask is None:
+                out = out + torch.sum(pl * ln, dim=0)
+            else:
+                mk = dmask[k][..., None]
+                out = out + torch.sum((pl * mk) * (ln * mk), dim=0)
+        return out
+    prod = _gs(p["density_line.0"], cl[[0]])
+    prod = prod * _gs(p["density_line.1"], cl[[1]])
+    prod = prod * _gs(p["density_line.2"], cl[[2]])
+    if dmask is not None:
+        prod = prod * dmask[0][..., None]
+    return torch.sum(prod, dim=0)
+
+
+def app_feature(f: Field, xn, amask=None):
+    """VM: models/tensoRF.py:230-263; CP: models/tensoRF.py:388-415."""
+    p = f.params
+    cl = _line_coords(xn)
+    if f.cfg.model == "VM":
+        cp = _plane_coords(xn)
+        pls, lns = [], []
+        for k in range(3):
+            pl = _gs(p[f"app_plane.{k}"], cp[[k]])
+            ln = _gs(p[f"app_line.{k}"], cl[[k]])
+            if amask is not None:
+                pl = pl * amask[k][..., None]
+                ln = ln * amask[k][..., None]
+            pls.append(pl)
+            lns.append(ln)
+        prod = torch.cat(pls) * torch.cat(lns)
+    else:
+        prod = _gs(p["app_line.0"], cl[[0]])
+        prod = prod * _gs(p["app_line.1"], cl[[1]])
+        prod = prod * _gs(p["app_line.2"], cl[[2]])
+        if amask is not None:
+            prod = prod * amask[0][..., None]
+    return F.linear(prod.T, p["basis_mat.weight"])
+
+
+def feature2density(f: Field, x):
+    """models/tensorBase.py:291-295."""
+    if f.cfg.fea2dense == "softplus":
+        return F.softplus(x + f.cfg.density_shift)
+    return F.relu(x)
+
+
+# --------------------------------------------------------------------------- stage 3
+def posenc(x, freqs: int):
+    """models/mlp.py:8-13 — channel-major, frequency-minor; [sin | cos]."""
+    bands = 2 ** torch.arange(freqs).float()
+    a = (x[..., None] * bands).reshape(x.shape[:-1] + (freqs * x.shape[-1],))
+    return torch.cat([torch.sin(a), torch.cos(a)], dim=-1)
+
+
+_SH_C0 = 0.28209479177387814
+_SH_C1 = 0.4886025119029199
+_SH_C2 = (1.0925484305920792, -1.0925484305920792, 0.31539156525252005,
+          -1.0925484305920792, 0.5462742152960396)
+
+
+def sh_basis_deg2(d):
+    """models/sh.py:87-112 with deg = 2 (9 coefficients)."""
+    out = torch.empty((*d.shape[:-1], 9), dtype=d.dtype)
+    x, y, z = d.unbind(-1)
+    out[..., 0] = _SH_C0
+    out[..., 1] = -_SH_C1 * y
+    out[..., 2] = _SH_C1 * z
+    out[..., 3] = -_SH_C1 * x
+    xx, yy, zz = x * x, y * y, z * z
+    out[..., 4] = _SH_C2[0] * (x * y)
+    out[..., 5] = _SH_C2[1] * (y * z)
+    out[..., 6] = _SH_C2[2] * (2.0 * zz - xx - yy)
+    out[..., 7] = _SH_C2[3] * (x * z)
+    out[..., 8] = _SH_C2[4] * (xx - yy)
+    return out
+
+
+def shade(f: Field, xn, view, feat, enc_mask=None):
+    """MLP_Fea models/mlp.py:41-69; MLP_PE :88-107; MLP :127-155; SH :15-19."""
+    cfg = f.cfg
+    if cfg.shading == "SH":
+        basis = sh_basis_deg2(view)[:, None]
+        return torch.relu(torch.sum(basis * feat.view(-1, 3, 9), dim=-1) + 0.5)
+    em = enc_mask or {"pos": None, "view": None, "fea": None}
+
+    def blk(src, n, key):
+        e = posenc(src, n)
+        return e if em[key] is None else e * em[key]
+
+    cols = [feat, view]
+    if cfg.shading == "MLP_Fea":
+        if cfg.fea_pe > 0:
+            cols.append(blk(feat, cfg.fea_pe, "fea"))
+        if cfg.view_pe > 0:
+            cols.append(blk(view, cfg.view_pe, "view"))
+    elif cfg.shading == "MLP_PE":
+        if cfg.pos_pe > 0:
+            cols.append(blk(xn, cfg.pos_pe, "pos"))
+        if cfg.view_pe > 0:
+            cols.append(blk(view, cfg.view_pe, "view"))
+    else:
+        if cfg.pos_pe > 0:
+            cols.append(blk(xn, cfg.pos_pe, "pos"))
+        if cfg.view_pe > 0:
+            cols.append(blk(view, cfg.view_pe, "view"))
+        if cfg.fea_pe > 0:
+            cols.append(blk(feat, cfg.fea_pe, "fea"))
+    x = torch.cat(cols, dim=-1)
+    p = f.params
+    h = torch.relu(F.linear(x, p["renderModule.mlp.0.weight"], p["renderModule.mlp.0.bias"]))
+    h = torch.relu(F.linear(h, p["renderModule.mlp.2.weight"], p["renderModule.mlp.2.bias"]))
+    return torch.sigmoid(F.linear(h, p["renderModule.mlp.4.weight"], p["renderModule.mlp.4.bias"]))
+
+
+# --------------------------------------------------------------------------- stage 4
+def raw2alpha(sigma, dist):
+    """models/tensorBase.py:21-28."""
+    alpha = 1.0 - torch.exp(-sigma * dist)
+    T = torch.cumprod(torch.cat([torch.ones(alpha.shape[0], 1), 1.0 - alpha + 1e-10], -1), -1)
+    return alpha, alpha * T[:, :-1], T[:, -1:]
+
+
+# --------------------------------------------------------------------------- the path
+def render_chunk(f: Field, rays, mask=None, white_bg=True, is_train=False, ndc_ray=False,
+                 n_samples=-1, jitter=None, bg_coin: Optional[bool] = None, keep=None):
+    """One call of the field on a ray chunk — models/tensorBase.py:321-395 (TensorBase.forward).
+
+    RNG inputs are explicit so the CUDA path can be fed the same draws:
+      jitter  : [N,1] U[0,1) (non-ndc train, :201) or [1,S] (ndc train, :183); None when not training.
+      bg_coin : outcome of `torch.rand((1,)) < 0.5` at :380 (only read if is_train and not white_bg).
+    `keep`, if a dict, receives the stage intermediates used by the stage-level parity tests.
+    """
+    if mask is None:
+        enc, dmask, amask = None, None, None
+    else:
+        enc, dmask, amask = mask["encoding"], mask["decomp"]["den"], mask["decomp"]["app"]
+    S = n_samples if n_samples > 0 else f.n_samples
+    o, view = rays[:, :3], rays[:, 3:6]
+    if ndc_ray:
+        pts, z, valid = march_ndc(f, o, view, jitter if is_train else None, S)
+        dists = torch.cat((z[:, 1:] - z[:, :-1], torch.zeros_like(z[:, :1])), dim=-1)
+        norm = torch.norm(view, dim=-1, keepdim=True)
+        dists = dists * norm
+        view = view / norm
+        z = z.expand(rays.shape[0], -1)
+    else:
+        pts, z, valid = march(f, o, view, jitter if is_train else None, S)
+        dists = torch.cat((z[:, 1:] - z[:, :-1], torch.zeros_like(z[:, :1])), dim=-1)
+    viewdirs = view.view(-1, 1, 3).expand(pts.shape)
+
+    if f.alpha_mask is not None:
+        a = alpha_mask_values(f.alpha_mask, pts[valid])
+        invalid = ~valid
+        invalid[valid] |= ~(a > 0)
+        valid = ~invalid
+
+    sigma = torch.zeros(pts.shape[:-1])
+    rgb = torch.zeros((*pts.shape[:2], 3))
+    xn = pts
+    if valid.any():
+        xn = normalize(f, pts)
+        sigma[valid] = feature2density(f, density_feature(f, xn[valid], dmask))
+
+    alpha, weight, _ = raw2alpha(sigma, dists * f.cfg.distance_scale)
+    app = weight > f.cfg.weight_thres
+    if app.any():
+        feat = app_feature(f, xn[app], amask)
+        rgb[app] = shade(f, xn[app], viewdirs[app], feat, enc)
+
+    acc = torch.sum(weight, -1)
+    rgb_map = torch.sum(weight[..., None] * rgb, -2)
+    if white_bg or (is_train and bool(bg_coin)):
+        rgb_map = rgb_map + (1.0 - acc[..., None])
+    rgb_map = rgb_map.clamp(0, 1)
+    with torch.no_grad():
+        depth = torch.sum(weight * z, -1)
+        depth = depth + (1.0 - acc) * rays[..., -1]
+    if keep is not None:
+        keep.update(z=z, valid=valid, sigma=sigma, alpha=alpha, weight=weight, app=app, acc=acc)
+    return rgb_map, depth, app.long().sum()
+
+
+def octree_render(rays, f: Field, mask=None, chunk=4096, N_samples=-1, ndc_ray=False,
+                  white_bg=True, is_train=False, jitter=None, bg_coins=None):
+    """renderer.py:13-26 (OctreeRender_trilinear_fast): chunk loop, cat, float-summed counts.
+    `jitter` is a list with one entry per chunk (the reference draws per call of the field)."""
+    rgbs, depths, count = [], [], []
+    n = rays.shape[0]
+    for ci in range(n // chunk + int(n % chunk > 0)):
+        rc = rays[ci * chunk:(ci + 1) * chunk]
+        r, d, nv = render_chunk(f, rc, mask, white_bg=white_bg, is_train=is_train, ndc_ray=ndc_ray,
+                                n_samples=N_samples,
+                                jitter=None if jitter is None else jitter[ci],
+                                bg_coin=None if bg_coins is None else bg_coins[ci])
+        rgbs.append(r)
+        depths.append(d)
+        count.append(float(nv))
+    return torch.cat(rgbs), None, torch.cat(depths), None, None, sum(count)
+
+
+def draw_jitter(n_rays: int, n_samples: int, ndc_ray: bool):
+    """Draw order of the reference's CPU RNG for one field call (tensorBase.py:183 / :201)."""
+    return torch.rand(1, n_samples) if ndc_ray else torch.rand(n_rays, 1)
+
+
+# --------------------------------------------------------------------------- producers of inputs
+def build_alpha_mask(f: Field, grid=(200, 200, 200), dmask=None) -> torch.Tensor:
+    """Occupancy rebuild — models/tensorBase.py:215-256 (getDenseAlpha + updateAlphaMask) and
+    compute_alpha :298-318.  Sets f.alpha_mask and returns the tight aabb the reference returns."""
+    gx, gy, gz = grid
+    lin = [torch.linspace(0, 1, g) for g in grid]
+    samples = torch.stack(torch.meshgrid(*lin, indexing="ij"), -1)
+    dense = f.aabb[0] * (1 - samples) + f.aabb[1] * samples
+    alpha = torch.zeros_like(dense[..., 0])
+    with torch.no_grad():
+        for i in range(gx):
+            loc = dense[i].view(-1, 3)
+            if f.alpha_mask is not None:
+                ok = alpha_mask_values(f.alpha_mask, loc) > 0
+            else:
+                ok = torch.ones_like(loc[:, 0], dtype=bool)
+            sg = torch.zeros(loc.shape[:-1])
+            if ok.any():
+                sg[ok] = feature2density(f, density_feature(f, normalize(f, loc[ok]), dmask))
+            alpha[i] = (1 - torch.exp(-sg * f.step_size)).view(gy, gz)
+        dense = dense.transpose(0, 2).contiguous()
+        alpha = alpha.clamp(0, 1).transpose(0, 2).contiguous()[None, None]
+        alpha = F.max_pool3d(alpha, kernel_size=3, padding=1, stride=1).view(grid[::-1])
+        alpha[alpha >= f.cfg.alpha_mask_thres] = 1
+        alpha[alpha < f.cfg.alpha_mask_thres] = 0
+        f.alpha_mask = AlphaMask(alpha, f.aabb.clone())
+        occ = dense[alpha > 0.5]
+        return torch.stack((occ.amin(0), occ.amax(0)))
+
+
+def freq_mask_shipped(lengths, it, total, ratio):
+    """utils.py:11-36 AS SHIPPED: returns from inside the loop, i.e. ONE tensor for lengths[0]."""
+    n = lengths[0]
+    if it < total:
+        m = torch.zeros(n)
+        ln = n * ratio
+        ptr = ln / 4 * it / total + 1
+        ptr = ptr if ptr < ln / 4 else ln / 4
+        ip = int(ptr)
+        m[: ip * 4] = 1.0
+        m[ip * 4: ip * 4 + 4] = ptr - ip
+        return torch.clamp(m, 1e-8, 1 - 1e-8)
+    return torch.ones(n)
+
+
+def freq_mask_intended(lengths, it, total, ratio):
+    """The FreeNeRF schedule the reference evidently intended: one vector per entry of `lengths`."""
+    return [freq_mask_shipped([n], it, total, ratio) for n in lengths]
+
+
+def free_mask(pos_bl=(0,), view_bl=(0,), fea_bl=(0,), den_bl=(), app_bl=(), step=-1, total_step=1,
+              ratio=1, using_decomp_mask=True, intended=False):
+    """utils.py:38-70 (get_free_mask).  intended=False reproduces the shipped indexing quirk
+    ([0] of a 1-D tensor = 0-dim scalar; decomposition masks = one tensor indexed per plane)."""
+    def enc(bl):
+        if bl[0] <= 0:
+            return None
+        m = freq_mask_shipped(list(bl), step, total_step, ratio)
+        return m if intended else m[0]
+    den = app = None
+    if using_decomp_mask:
+        fn = freq_mask_intended if intended else freq_mask_shipped
+        if len(den_bl) > 0:
+            den = fn(list(den_bl), step, total_step, ratio)
+        if len(app_bl) > 0:
+            app = fn(list(app_bl), step, total_step, ratio)
+    return {"encoding": {"pos": enc(pos_bl), "view": enc(view_bl), "fea": enc(fea_bl)},
+            "decomp": {"den": den, "app": app}}
+
+
+# --------------------------------------------------------------------------- gradients
+def loss_and_grads(f: Field, rays, target, **kw):
+    """MSE training step — train.py:338 (`mean((rgb_map-rgb_train)**2)`) then backward (:374-376).
+    Returns (loss, rgb_map, depth, n_valid, {name: grad})."""
+    leaves = {k: v.detach().clone().requires_grad_(True) for k, v in f.params.items()}
+    g = Field(f.cfg, leaves, f.alpha_mask)
+    rgb, depth, nv = render_chunk(g, rays, **kw)
+    loss = torch.mean((rgb - target) ** 2)
+    loss.backward()
+    grads = {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in leaves.items()}
+    return loss.detach(), rgb.detach(), depth, nv, grads
+
+
+# --------------------------------------------------------------------------- synthetic inputs
+def synthetic_rays(n: int, seed: int = 0, radius: float = 4.0):
+    """SURVEY.md section 8(d) synthetic training rays: origins on a sphere, aimed into the box."""
+    g = torch.Generator().manual_seed(seed)
+    o = torch.randn(n, 3, generator=g)
+    o = radius * o / o.norm(dim=-1, keepdim=True)
+    tgt = (torch.rand(n, 3, generator=g) - 0.5) * 2
+    d = tgt - o
+    d = d / d.norm(dim=-1, keepdim=True)
+    return torch.cat([o, d], -1)

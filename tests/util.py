@@ -1,0 +1,70 @@
+"""Shared helpers for the parity tests: golden-fixture loading and comparison metrics."""
+import ast
+import glob
+import os
+
+import numpy as np
+import torch
+
+from oracle import field_oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
+
+
+class Golden:
+    def __init__(self, name):
+        d = np.load(os.path.join(GOLDEN, name + ".npz"))
+        self.name = name
+        self.meta = ast.literal_eval(str(d["meta"]))
+        self.t = {k: torch.from_numpy(np.asarray(d[k])) for k in d.files if k != "meta"}
+        self.params = {k[2:]: v for k, v in self.t.items() if k.startswith("p:")}
+        self.grads = {k[2:]: v for k, v in self.t.items() if k.startswith("g:")}
+        self.rays, self.target = self.t["rays"], self.t["target"]
+        self.jitter = self.t.get("jitter")
+        self.coin = bool(self.t["coin"])
+
+    # -- reference-shaped mask dict (None when the case has no mask)
+    def mask(self):
+        keys = [k for k in self.t if k.startswith("m:")]
+        if not keys:
+            return None
+        m = {"encoding": {"pos": None, "view": None, "fea": None}, "decomp": {"den": None, "app": None}}
+        lists = {}
+        for k in keys:
+            parts = k.split(":")
+            if len(parts) == 4:
+                lists.setdefault((parts[1], parts[2]), {})[int(parts[3])] = self.t[k]
+            else:
+                m[parts[1]][parts[2]] = self.t[k]
+        for (g, n), dd in lists.items():
+            m[g][n] = [dd[i] for i in sorted(dd)]
+        return m
+
+    def config(self) -> O.FieldConfig:
+        a, mt = self.meta["args"], self.meta
+        return O.FieldConfig(model=mt["kind"], shading=mt["shading"], grid=tuple(mt["grid"]),
+                             near_far=tuple(mt["near_far"]), density_n_comp=tuple(a["density_n_comp"]),
+                             app_n_comp=tuple(a["app_n_comp"]), app_dim=a["app_dim"], step_ratio=a["step_ratio"],
+                             density_shift=a["density_shift"], distance_scale=a["distance_scale"],
+                             alpha_mask_thres=a["alphaMask_thres"], fea2dense=a["fea2denseAct"],
+                             pos_pe=a["pos_pe"], view_pe=a["view_pe"], fea_pe=a["fea_pe"], feature_c=a["featureC"])
+
+    def field(self) -> O.Field:
+        am = None
+        if "am_volume" in self.t:
+            am = O.AlphaMask(self.t["am_volume"].float(), self.t["am_aabb"])
+        return O.Field(self.config(), {k: v.clone() for k, v in self.params.items()}, am)
+
+    def call_kwargs(self):
+        mt = self.meta
+        return dict(mask=self.mask(), white_bg=mt["white_bg"], is_train=mt["is_train"], ndc_ray=mt["ndc"],
+                    n_samples=mt["S"], jitter=self.jitter, bg_coin=self.coin)
+
+
+def rel_inf(a: torch.Tensor, b: torch.Tensor, eps: float = 1e-12) -> float:
+    """||a-b||_inf / max(||b||_inf, eps) — the per-tensor relative metric of SURVEY section 8(c)."""
+    a, b = a.double().flatten(), b.double().flatten()
+    if a.numel() == 0:
+        return 0.0
+    return float((a - b).abs().max() / max(float(b.abs().max()), eps))
