@@ -1,0 +1,117 @@
+"""ctypes binding of include/fewtensorf.h (libfewtensorf_b200.so).
+
+There is NO fallback: if the shared library is missing or does not export a symbol the
+import raises, and every compute entry point needs a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfewtensorf_b200.so")
+
+MODEL_VM, MODEL_CP = 0, 1
+SHADE_MLP_FEA, SHADE_MLP_PE, SHADE_MLP, SHADE_SH = 0, 1, 2, 3
+ACT_SOFTPLUS, ACT_RELU = 0, 1
+SHADING_KINDS = {"MLP_Fea": SHADE_MLP_FEA, "MLP_PE": SHADE_MLP_PE, "MLP": SHADE_MLP, "SH": SHADE_SH}
+
+WS_NAMES = ["COUNTERS", "TMIN", "RAY_OFF", "RAY_CNT", "ACC", "RGB_PRE", "S_RAY", "S_IDX", "S_SIGMA", "S_W", "S_T",
+            "S_APP", "S_GSIG", "A_SLOT", "A_FEAT", "A_RGB", "A_H1", "A_H2", "A_GRGB", "A_GH1", "A_GH2", "A_GFEAT"]
+WS_COUNT = len(WS_NAMES)
+WS = {n: i for i, n in enumerate(WS_NAMES)}
+
+_f32p = C.c_void_p   # device pointers travel as integers
+
+
+class FtrfFactorSet(C.Structure):
+    _fields_ = [
+        ("n_comp", C.c_int32 * 3),
+        ("plane_w", C.c_int32 * 3),
+        ("plane_h", C.c_int32 * 3),
+        ("line_len", C.c_int32 * 3),
+        ("plane", _f32p * 3),
+        ("line", _f32p * 3),
+        ("g_plane", _f32p * 3),
+        ("g_line", _f32p * 3),
+        ("mask", _f32p * 3),
+        ("mask_stride", C.c_int32 * 3),
+    ]
+
+
+class FtrfField(C.Structure):
+    _fields_ = [
+        ("model", C.c_int32), ("shading", C.c_int32), ("act", C.c_int32), ("app_dim", C.c_int32),
+        ("feature_c", C.c_int32), ("pos_pe", C.c_int32), ("view_pe", C.c_int32), ("fea_pe", C.c_int32),
+        ("in_dim", C.c_int32),
+        ("aabb", C.c_float * 6), ("inv_aabb", C.c_float * 3), ("step_size", C.c_float),
+        ("near_", C.c_float), ("far_", C.c_float),
+        ("distance_scale", C.c_float), ("density_shift", C.c_float), ("weight_thres", C.c_float),
+        ("has_alpha_mask", C.c_int32), ("am_dim", C.c_int32 * 3), ("am_aabb0", C.c_float * 3),
+        ("am_inv", C.c_float * 3), ("am_bits", C.c_void_p),
+        ("den", FtrfFactorSet), ("app", FtrfFactorSet),
+        ("basis", _f32p), ("g_basis", _f32p),
+        ("w1", _f32p), ("b1", _f32p), ("w2", _f32p), ("b2", _f32p), ("w3", _f32p), ("b3", _f32p),
+        ("g_w1", _f32p), ("g_b1", _f32p), ("g_w2", _f32p), ("g_b2", _f32p), ("g_w3", _f32p), ("g_b3", _f32p),
+        ("enc_mask", _f32p * 3), ("enc_mask_len", C.c_int32 * 3),
+    ]
+
+
+class FtrfCall(C.Structure):
+    _fields_ = [
+        ("n_rays", C.c_int64), ("ray_cols", C.c_int32), ("n_samples", C.c_int32), ("is_train", C.c_int32),
+        ("ndc", C.c_int32), ("add_bg", C.c_int32), ("save_for_backward", C.c_int32),
+        ("rays", _f32p), ("jitter", _f32p), ("rgb_map", _f32p), ("depth_map", _f32p), ("g_rgb_map", _f32p),
+        ("cap_samples", C.c_int64), ("cap_app", C.c_int64),
+    ]
+
+
+# every symbol include/fewtensorf.h declares
+EXPORTS = [
+    "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward",
+    "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
+    "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
+    "ftrf_pack_alpha_mask", "ftrf_density_at",
+]
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C fewtensorf_b200/csrc`). fewtensorf_b200 has no CPU or PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise ImportError(f"{LIB_PATH} does not export {name}")
+    lib.ftrf_abi_version.restype = C.c_int
+    lib.ftrf_last_error.restype = C.c_char_p
+    lib.ftrf_workspace_layout.restype = C.c_size_t
+    lib.ftrf_workspace_layout.argtypes = [C.POINTER(FtrfField), C.POINTER(FtrfCall), C.POINTER(C.c_int64)]
+    stage_args = [C.POINTER(FtrfField), C.POINTER(FtrfCall), C.c_void_p, C.c_size_t, C.c_void_p]
+    for name in ("ftrf_forward", "ftrf_backward", "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate",
+                 "ftrf_stage_appearance", "ftrf_stage_shade", "ftrf_stage_composite"):
+        fn = getattr(lib, name)
+        fn.restype = C.c_int
+        fn.argtypes = stage_args
+    lib.ftrf_mse_loss.restype = C.c_int
+    lib.ftrf_mse_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ftrf_alpha_mask_words.restype = C.c_size_t
+    lib.ftrf_alpha_mask_words.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    lib.ftrf_pack_alpha_mask.restype = C.c_int
+    lib.ftrf_pack_alpha_mask.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.ftrf_density_at.restype = C.c_int
+    lib.ftrf_density_at.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    if lib.ftrf_abi_version() != 1:
+        raise ImportError("libfewtensorf_b200.so ABI version mismatch")
+    return lib
+
+
+lib = _load()
+
+
+def check(code: int, what: str = "") -> None:
+    """Error convention of the boundary: non-zero return code -> RuntimeError(ftrf_last_error())."""
+    if code != 0:
+        msg = lib.ftrf_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"fewtensorf {what} failed ({code}): {msg}")

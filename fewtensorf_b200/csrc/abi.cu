@@ -1,0 +1,216 @@
+// abi.cu — the extern "C" boundary: argument checks, workspace carving, stage sequencing.
+// No torch types, no global mutable state besides the thread-local error string.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace ftrf {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return FTRF_E_CUDA;
+  }
+  return FTRF_OK;
+}
+
+static inline size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+
+size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws* ws) {
+  const size_t N = (size_t)c.n_rays, V = (size_t)c.cap_samples, A = (size_t)c.cap_app;
+  const size_t D = (size_t)f.app_dim, H = (size_t)f.feature_c;
+  const bool train = c.save_for_backward != 0;
+  const bool mlp = f.shading != FTRF_SHADE_SH;
+  size_t sz[FTRF_WS_COUNT];
+  sz[FTRF_WS_COUNTERS] = 8 * 4;
+  sz[FTRF_WS_TMIN] = N * 4;
+  sz[FTRF_WS_RAY_OFF] = N * 4;
+  sz[FTRF_WS_RAY_CNT] = N * 4;
+  sz[FTRF_WS_ACC] = N * 4;
+  sz[FTRF_WS_RGB_PRE] = N * 12;
+  sz[FTRF_WS_S_RAY] = V * 4;
+  sz[FTRF_WS_S_IDX] = V * 4;
+  sz[FTRF_WS_S_SIGMA] = V * 4;
+  sz[FTRF_WS_S_W] = V * 4;
+  sz[FTRF_WS_S_T] = train ? V * 4 : 0;
+  sz[FTRF_WS_S_APP] = V * 4;
+  sz[FTRF_WS_S_GSIG] = train ? V * 4 : 0;
+  sz[FTRF_WS_A_SLOT] = A * 4;
+  sz[FTRF_WS_A_FEAT] = A * D * 4;
+  sz[FTRF_WS_A_RGB] = A * 12;
+  sz[FTRF_WS_A_H1] = (train && mlp) ? A * H * 4 : 0;
+  sz[FTRF_WS_A_H2] = (train && mlp) ? A * H * 4 : 0;
+  sz[FTRF_WS_A_GRGB] = train ? A * 12 : 0;
+  sz[FTRF_WS_A_GH1] = (train && mlp) ? A * H * 4 : 0;
+  sz[FTRF_WS_A_GH2] = (train && mlp) ? A * H * 4 : 0;
+  sz[FTRF_WS_A_GFEAT] = train ? A * D * 4 : 0;
+  size_t cur = 0, offs[FTRF_WS_COUNT];
+  for (int i = 0; i < FTRF_WS_COUNT; ++i) {
+    offs[i] = cur;
+    cur += align_up(sz[i]);
+    if (off) off[i] = (int64_t)offs[i];
+  }
+  if (ws && base) {
+    char* b = (char*)base;
+    ws->counters = (int32_t*)(b + offs[FTRF_WS_COUNTERS]);
+    ws->tmin = (float*)(b + offs[FTRF_WS_TMIN]);
+    ws->ray_off = (int32_t*)(b + offs[FTRF_WS_RAY_OFF]);
+    ws->ray_cnt = (int32_t*)(b + offs[FTRF_WS_RAY_CNT]);
+    ws->acc = (float*)(b + offs[FTRF_WS_ACC]);
+    ws->rgb_pre = (float*)(b + offs[FTRF_WS_RGB_PRE]);
+    ws->s_ray = (int32_t*)(b + offs[FTRF_WS_S_RAY]);
+    ws->s_idx = (int32_t*)(b + offs[FTRF_WS_S_IDX]);
+    ws->s_sigma = (float*)(b + offs[FTRF_WS_S_SIGMA]);
+    ws->s_w = (float*)(b + offs[FTRF_WS_S_W]);
+    ws->s_T = (float*)(b + offs[FTRF_WS_S_T]);
+    ws->s_app = (int32_t*)(b + offs[FTRF_WS_S_APP]);
+    ws->s_gsig = (float*)(b + offs[FTRF_WS_S_GSIG]);
+    ws->a_slot = (int32_t*)(b + offs[FTRF_WS_A_SLOT]);
+    ws->a_feat = (float*)(b + offs[FTRF_WS_A_FEAT]);
+    ws->a_rgb = (float*)(b + offs[FTRF_WS_A_RGB]);
+    ws->a_h1 = (float*)(b + offs[FTRF_WS_A_H1]);
+    ws->a_h2 = (float*)(b + offs[FTRF_WS_A_H2]);
+    ws->a_grgb = (float*)(b + offs[FTRF_WS_A_GRGB]);
+    ws->a_gh1 = (float*)(b + offs[FTRF_WS_A_GH1]);
+    ws->a_gh2 = (float*)(b + offs[FTRF_WS_A_GH2]);
+    ws->a_gfeat = (float*)(b + offs[FTRF_WS_A_GFEAT]);
+  }
+  return cur;
+}
+
+static int check_factor_set(const FtrfFactorSet& s, int model, const char* name, bool need_grad) {
+  for (int k = 0; k < 3; ++k) {
+    if (s.n_comp[k] <= 0 || s.n_comp[k] % 4) { set_error("%s: n_comp[%d]=%d must be a positive multiple of 4", name, k, s.n_comp[k]); return FTRF_E_ARG; }
+    if (!s.line[k] || s.line_len[k] < 1) { set_error("%s: line %d missing", name, k); return FTRF_E_ARG; }
+    if (model == FTRF_MODEL_VM && (!s.plane[k] || s.plane_w[k] < 1 || s.plane_h[k] < 1)) { set_error("%s: plane %d missing", name, k); return FTRF_E_ARG; }
+    if (model == FTRF_MODEL_CP && s.n_comp[k] != s.n_comp[0]) { set_error("%s: CP needs equal n_comp", name); return FTRF_E_ARG; }
+    if (need_grad && (!s.g_line[k] || (model == FTRF_MODEL_VM && !s.g_plane[k]))) { set_error("%s: gradient pointer %d missing", name, k); return FTRF_E_ARG; }
+  }
+  return FTRF_OK;
+}
+
+static int check_args(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, bool backward, Ws* ws) {
+  if (!f || !c || !wsb) { set_error("null argument"); return FTRF_E_ARG; }
+  if (f->model != FTRF_MODEL_VM && f->model != FTRF_MODEL_CP) { set_error("unknown model kind %d", f->model); return FTRF_E_ARG; }
+  if (f->shading < 0 || f->shading > FTRF_SHADE_SH) { set_error("unknown shading kind %d", f->shading); return FTRF_E_ARG; }
+  if (c->n_rays < 0 || c->n_rays > 0x7fffffff || c->ray_cols < 6 || c->n_samples < 1) { set_error("bad ray batch (n_rays %lld, cols %d, S %d)", (long long)c->n_rays, c->ray_cols, c->n_samples); return FTRF_E_ARG; }
+  if (c->cap_samples < 0 || c->cap_samples > 0x7fffffff || c->cap_app < 0 || c->cap_app > 0x7fffffff) { set_error("capacity out of range"); return FTRF_E_ARG; }
+  if (c->n_rays && (!c->rays || !c->rgb_map || !c->depth_map)) { set_error("null ray/output pointer"); return FTRF_E_ARG; }
+  if ((c->ndc || c->is_train) && !c->jitter) { set_error("jitter / z table missing"); return FTRF_E_ARG; }
+  if (f->has_alpha_mask && !f->am_bits) { set_error("alpha mask bits missing"); return FTRF_E_ARG; }
+  if (f->app_dim < 1 || f->app_dim > 64) { set_error("app_dim %d unsupported", f->app_dim); return FTRF_E_ARG; }
+  if (int e = check_factor_set(f->den, f->model, "density", backward)) return e;
+  if (int e = check_factor_set(f->app, f->model, "appearance", backward)) return e;
+  if (!f->basis || (backward && !f->g_basis)) { set_error("basis_mat missing"); return FTRF_E_ARG; }
+  if (f->shading != FTRF_SHADE_SH) {
+    if (!f->w1 || !f->b1 || !f->w2 || !f->b2 || !f->w3 || !f->b3) { set_error("MLP weights missing"); return FTRF_E_ARG; }
+    if (backward && (!f->g_w1 || !f->g_b1 || !f->g_w2 || !f->g_b2 || !f->g_w3 || !f->g_b3)) { set_error("MLP gradient pointers missing"); return FTRF_E_ARG; }
+  }
+  if (backward && (!c->save_for_backward || !c->g_rgb_map)) { set_error("backward needs save_for_backward and g_rgb_map"); return FTRF_E_ARG; }
+  size_t need = carve(*f, *c, nullptr, wsb, ws);
+  if (ws_bytes < need) { set_error("workspace too small: %zu < %zu", ws_bytes, need); return FTRF_E_WORKSPACE; }
+  return FTRF_OK;
+}
+
+__global__ void mse_kernel(const float* __restrict__ rgb, const float* __restrict__ tgt, int64_t n, float inv_n,
+                           float* __restrict__ loss, float* __restrict__ g) {
+  float acc = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float d = rgb[i] - tgt[i];
+    acc = fmaf(d, d, acc);
+    if (g) g[i] = 2.f * d * inv_n;
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, d);
+  __shared__ float part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += part[w];
+    atomicAdd(loss, s * inv_n);
+  }
+}
+
+}  // namespace ftrf
+
+using namespace ftrf;
+
+extern "C" int ftrf_abi_version(void) { return FTRF_ABI_VERSION; }
+extern "C" const char* ftrf_last_error(void) { return g_err; }
+
+extern "C" size_t ftrf_workspace_layout(const FtrfField* f, const FtrfCall* c, int64_t* offsets_out) {
+  if (!f || !c) { set_error("null argument"); return 0; }
+  return carve(*f, *c, offsets_out, nullptr, nullptr);
+}
+
+#define STAGE_FN(name, launcher)                                                                          \
+  extern "C" int name(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {   \
+    Ws ws;                                                                                                 \
+    if (int e = check_args(f, c, wsb, ws_bytes, false, &ws)) return e;                                     \
+    return launcher(*f, *c, ws, (cudaStream_t)stream);                                                     \
+  }
+
+static int march_with_reset(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (cudaMemsetAsync(ws.counters, 0, 32, st) != cudaSuccess) return check_launch("memset counters");
+  return launch_march(f, c, ws, st);
+}
+
+STAGE_FN(ftrf_stage_march, march_with_reset)
+STAGE_FN(ftrf_stage_density, launch_density)
+STAGE_FN(ftrf_stage_integrate, launch_integrate)
+STAGE_FN(ftrf_stage_appearance, launch_appearance)
+STAGE_FN(ftrf_stage_shade, launch_shade)
+STAGE_FN(ftrf_stage_composite, launch_composite)
+
+extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+  Ws ws;
+  if (int e = check_args(f, c, wsb, ws_bytes, false, &ws)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int e = march_with_reset(*f, *c, ws, st)) return e;
+  if (int e = launch_density(*f, *c, ws, st)) return e;
+  if (int e = launch_integrate(*f, *c, ws, st)) return e;
+  if (int e = launch_appearance(*f, *c, ws, st)) return e;
+  if (int e = launch_shade(*f, *c, ws, st)) return e;
+  return launch_composite(*f, *c, ws, st);
+}
+
+extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+  Ws ws;
+  if (int e = check_args(f, c, wsb, ws_bytes, true, &ws)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
+  if (int e = launch_shade_bwd(*f, *c, ws, st)) return e;
+  if (int e = launch_appearance_bwd(*f, *c, ws, st)) return e;
+  return launch_density_bwd(*f, *c, ws, st);
+}
+
+extern "C" int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, float* loss_out, float* g_rgb_out,
+                             void* stream) {
+  if (!rgb || !target || !loss_out || n <= 0) { set_error("mse_loss: bad argument"); return FTRF_E_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemsetAsync(loss_out, 0, sizeof(float), st) != cudaSuccess) return check_launch("memset loss");
+  int64_t blocks = (n + 255) / 256;
+  int grid = (int)(blocks < FTRF_SMS ? blocks : FTRF_SMS);
+  mse_kernel<<<grid, 256, 0, st>>>(rgb, target, n, 1.f / (float)n, loss_out, g_rgb_out);
+  return check_launch("mse_loss");
+}
+
+extern "C" int ftrf_density_at(const FtrfField* f, const float* xyz, int64_t n, float* sigma_out, void* stream) {
+  if (!f || !xyz || !sigma_out || n < 0) { set_error("density_at: bad argument"); return FTRF_E_ARG; }
+  if (int e = check_factor_set(f->den, f->model, "density", false)) return e;
+  if (f->has_alpha_mask && !f->am_bits) { set_error("alpha mask bits missing"); return FTRF_E_ARG; }
+  return launch_density_at(*f, xyz, n, sigma_out, (cudaStream_t)stream);
+}

@@ -1,0 +1,250 @@
+// k_appearance.cu — stage 2b: VM / CP appearance gather + basis_mat projection on the packed
+// shaded-sample list, and its backward.  Replaces TensorVMSplit/TensorCP.compute_appfeature
+// (models/tensoRF.py:230-263, :388-415; basis_mat :149/:338).
+//
+// A CTA of 256 threads owns a tile of 64 shaded samples, 4 lanes per sample (same channel-chunk
+// split as k_density.cu).  The plane*line products (144 for VM 48x3, n_comp for CP) go to shared
+// memory, then every 4-lane group does its sample's app_dim x NP mat-vec against the basis matrix
+// held in shared memory.  Algorithmic bytes per shaded sample (VM 48x3): 3*48*(4+2)*4 = 3456 B
+// forward, 6912 B backward (re-read + gradient reduction).
+#include "common.cuh"
+
+namespace ftrf {
+
+constexpr int AGS = 4;          // lanes per sample
+constexpr int ATILE = 64;       // samples per CTA tile
+
+__host__ __device__ inline int app_np(const FtrfField& f) {
+  return f.model == FTRF_MODEL_VM ? f.app.n_comp[0] + f.app.n_comp[1] + f.app.n_comp[2] : f.app.n_comp[0];
+}
+
+__device__ __forceinline__ void app_point(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t s, float xn[3]) {
+  int slot = ws.a_slot[s];
+  Ray ray = load_ray(f, c, ws.s_ray[slot]);
+  float p[3];
+  sample_pt(ray, sample_z(f, c, ray, ws.s_idx[slot]), p);
+  normalize_pt(f, p, xn);
+}
+
+// products of this lane's channel chunks -> P row (shared)
+__device__ __forceinline__ void app_products(const FtrfField& f, const float xn[3], int sub, float* prow) {
+  const FtrfFactorSet& a = f.app;
+  if (f.model == FTRF_MODEL_VM) {
+    int base = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int C = a.n_comp[k];
+      Tap tx = make_tap(xn[mat0(k)], a.plane_w[k]);
+      Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
+      Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+      for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+        float4 p = plane4(a.plane[k], a.plane_w[k], C, tx, ty, ch);
+        float4 l = line4(a.line[k], C, tl, ch);
+        if (a.mask[k]) {                                   // tensoRF.py:250, :257
+          float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+          p = mul4(p, m);
+          l = mul4(l, m);
+        }
+        *reinterpret_cast<float4*>(prow + base + ch) = mul4(p, l);
+      }
+      base += C;
+    }
+  } else {
+    const int C = a.n_comp[0];
+    Tap t0 = make_tap(xn[vecm(0)], a.line_len[0]);
+    Tap t1 = make_tap(xn[vecm(1)], a.line_len[1]);
+    Tap t2 = make_tap(xn[vecm(2)], a.line_len[2]);
+    for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+      float4 v = mul4(mul4(line4(a.line[0], C, t0, ch), line4(a.line[1], C, t1, ch)), line4(a.line[2], C, t2, ch));
+      if (a.mask[0]) v = mul4(v, mask4(a.mask[0], a.mask_stride[0], ch));   // tensoRF.py:415
+      *reinterpret_cast<float4*>(prow + ch) = v;
+    }
+  }
+}
+
+// smem: Wb [D][NPs] | P [ATILE][NPs] | G [ATILE][Dp] (backward only)
+__global__ void __launch_bounds__(256)
+app_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  extern __shared__ __align__(16) float smem[];
+  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim;
+  float* Wb = smem;
+  float* P = Wb + (size_t)D * NPs;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
+  const int sl = threadIdx.x / AGS, sub = threadIdx.x % AGS;
+  for (int64_t t0 = (int64_t)blockIdx.x * ATILE; t0 < n; t0 += (int64_t)gridDim.x * ATILE) {
+    const int64_t s = t0 + sl;
+    __syncthreads();                     // Wb visible / previous tile's P consumed
+    if (s < n) {
+      float xn[3];
+      app_point(f, c, ws, s, xn);
+      app_products(f, xn, sub, P + (size_t)sl * NPs);
+    }
+    __syncthreads();
+    if (s < n) {
+      const float* prow = P + (size_t)sl * NPs;
+      for (int o = sub; o < D; o += AGS) {
+        const float* wrow = Wb + (size_t)o * NPs;
+        float acc = 0.f;
+        for (int k = 0; k < NP; k += 4) {
+          float4 pv = *reinterpret_cast<const float4*>(prow + k);
+          float4 wv = *reinterpret_cast<const float4*>(wrow + k);
+          acc = fmaf(pv.x, wv.x, acc); acc = fmaf(pv.y, wv.y, acc);
+          acc = fmaf(pv.z, wv.z, acc); acc = fmaf(pv.w, wv.w, acc);
+        }
+        ws.a_feat[s * D + o] = acc;
+      }
+    }
+  }
+}
+
+// Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
+constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thread
+
+__global__ void __launch_bounds__(256)
+app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  extern __shared__ __align__(16) float smem[];
+  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, Dp = (D + 3) & ~3;
+  float* Wb = smem;
+  float* P = Wb + (size_t)D * NPs;
+  float* G = P + (size_t)ATILE * NPs;
+  const FtrfFactorSet& a = f.app;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
+  const int sl = threadIdx.x / AGS, sub = threadIdx.x % AGS;
+  const int n_og = Dp / 4, n_kg = NP / 4, n_tt = n_og * n_kg;
+  float dW[BW_TT][16];
+#pragma unroll
+  for (int t = 0; t < BW_TT; ++t)
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dW[t][i] = 0.f;
+
+  for (int64_t t0 = (int64_t)blockIdx.x * ATILE; t0 < n; t0 += (int64_t)gridDim.x * ATILE) {
+    const int64_t s = t0 + sl;
+    __syncthreads();
+    float xn[3] = {0.f, 0.f, 0.f};
+    if (s < n) {
+      app_point(f, c, ws, s, xn);
+      app_products(f, xn, sub, P + (size_t)sl * NPs);
+      for (int o = sub; o < Dp; o += AGS) G[sl * Dp + o] = o < D ? ws.a_gfeat[s * D + o] : 0.f;
+    } else {
+      for (int k = sub * 4; k < NP; k += AGS * 4) *reinterpret_cast<float4*>(P + (size_t)sl * NPs + k) = make_float4(0, 0, 0, 0);
+      for (int o = sub; o < Dp; o += AGS) G[sl * Dp + o] = 0.f;
+    }
+    __syncthreads();
+    // (a) basis gradient: 4x4 register tiles over (output group, component group)
+#pragma unroll
+    for (int t = 0; t < BW_TT; ++t) {
+      int tt = threadIdx.x + t * 256;
+      if (tt < n_tt) {
+        int og = tt / n_kg, kg = tt % n_kg;
+        for (int r = 0; r < ATILE; ++r) {
+          float4 gv = *reinterpret_cast<const float4*>(G + r * Dp + og * 4);
+          float4 pv = *reinterpret_cast<const float4*>(P + (size_t)r * NPs + kg * 4);
+          const float gg[4] = {gv.x, gv.y, gv.z, gv.w}, pp[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dW[t][i * 4 + j] = fmaf(gg[i], pp[j], dW[t][i * 4 + j]);
+        }
+      }
+    }
+    // (b) gradient w.r.t. the products, then scatter into plane / line gradients
+    if (s < n) {
+      const float* grow = G + sl * Dp;
+      if (f.model == FTRF_MODEL_VM) {
+        int base = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int C = a.n_comp[k], W = a.plane_w[k];
+          Tap tx = make_tap(xn[mat0(k)], W);
+          Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
+          Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+          for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+            float4 gq = make_float4(0, 0, 0, 0);
+            for (int o = 0; o < D; ++o) gq = fma4(grow[o], *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + base + ch), gq);
+            if (a.mask[k]) {
+              float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+              gq = mul4(gq, mul4(m, m));
+            }
+            float4 pv = plane4(a.plane[k], W, C, tx, ty, ch);
+            float4 lv = line4(a.line[k], C, tl, ch);
+            float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
+            float* gp0 = a.g_plane[k] + ((size_t)ty.i0 * W) * C + ch;
+            float* gp1 = a.g_plane[k] + ((size_t)ty.i1 * W) * C + ch;
+            float w;
+            if ((w = tx.w0 * ty.w0) != 0.f) red4(gp0 + (size_t)tx.i0 * C, scale4(w, gp));
+            if ((w = tx.w1 * ty.w0) != 0.f) red4(gp0 + (size_t)tx.i1 * C, scale4(w, gp));
+            if ((w = tx.w0 * ty.w1) != 0.f) red4(gp1 + (size_t)tx.i0 * C, scale4(w, gp));
+            if ((w = tx.w1 * ty.w1) != 0.f) red4(gp1 + (size_t)tx.i1 * C, scale4(w, gp));
+            if (tl.w0 != 0.f) red4(a.g_line[k] + (size_t)tl.i0 * C + ch, scale4(tl.w0, gl));
+            if (tl.w1 != 0.f) red4(a.g_line[k] + (size_t)tl.i1 * C + ch, scale4(tl.w1, gl));
+          }
+          base += C;
+        }
+      } else {
+        const int C = a.n_comp[0];
+        Tap t[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) t[k] = make_tap(xn[vecm(k)], a.line_len[k]);
+        for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+          float4 gq = make_float4(0, 0, 0, 0);
+          for (int o = 0; o < D; ++o) gq = fma4(grow[o], *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + ch), gq);
+          if (a.mask[0]) gq = mul4(gq, mask4(a.mask[0], a.mask_stride[0], ch));
+          float4 l0 = line4(a.line[0], C, t[0], ch), l1 = line4(a.line[1], C, t[1], ch), l2 = line4(a.line[2], C, t[2], ch);
+          float4 gk[3] = {mul4(gq, mul4(l1, l2)), mul4(gq, mul4(l0, l2)), mul4(gq, mul4(l0, l1))};
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            if (t[k].w0 != 0.f) red4(a.g_line[k] + (size_t)t[k].i0 * C + ch, scale4(t[k].w0, gk[k]));
+            if (t[k].w1 != 0.f) red4(a.g_line[k] + (size_t)t[k].i1 * C + ch, scale4(t[k].w1, gk[k]));
+          }
+        }
+      }
+    }
+  }
+  // flush the basis gradient tiles
+#pragma unroll
+  for (int t = 0; t < BW_TT; ++t) {
+    int tt = threadIdx.x + t * 256;
+    if (tt < n_tt) {
+      int og = tt / n_kg, kg = tt % n_kg;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        int o = og * 4 + i;
+        if (o < D)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float v = dW[t][i * 4 + j];
+            if (v != 0.f) atomicAdd(f.g_basis + (size_t)o * NP + kg * 4 + j, v);
+          }
+      }
+    }
+  }
+}
+
+static int app_check(const FtrfField& f, size_t smem) {
+  int NP = app_np(f), Dp = (f.app_dim + 3) & ~3;
+  if (NP % 4 || (Dp / 4) * (NP / 4) > BW_TT * 256) { set_error("appearance: unsupported component count %d", NP); return FTRF_E_ARG; }
+  if (smem > 220 * 1024) { set_error("appearance: shared memory %zu B too large", smem); return FTRF_E_ARG; }
+  return FTRF_OK;
+}
+
+int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  int NPs = app_np(f) + 4;
+  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs) * sizeof(float);
+  if (int e = app_check(f, smem)) return e;
+  cudaFuncSetAttribute(app_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  app_fwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);
+  return check_launch("app_fwd");
+}
+
+int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  int NPs = app_np(f) + 4, Dp = (f.app_dim + 3) & ~3;
+  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp) * sizeof(float);
+  if (int e = app_check(f, smem)) return e;
+  cudaFuncSetAttribute(app_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);
+  return check_launch("app_bwd");
+}
+
+}  // namespace ftrf

@@ -1,0 +1,199 @@
+// k_density.cu — stage 2a: VM / CP density gather + sigma activation on the packed sample list,
+// and its scatter-add backward.  Replaces TensorVMSplit/TensorCP.compute_densityfeature
+// (models/tensoRF.py:207-227, :358-386) and feature2density (models/tensorBase.py:291-295).
+//
+// Layout: factors are channel-last, so the C channels of one texel are one contiguous 4C-byte
+// vector.  A group of GS=4 lanes owns one sample; lane `sub` handles float4 channel chunks
+// sub, sub+4, ...  (C=16: one 16-byte load per lane per corner, the 4 lanes cover one 64-byte
+// texel).  Consecutive packed samples of a ray are half a texel apart, so neighbouring groups hit
+// the same or adjacent texels: the working set is L1/L2 resident.
+// Algorithmic bytes per sample (VM, C=16x3): 3*16*(4+2)*4 = 1152 B forward;
+// backward re-reads them and reduces 1152 B of gradient (2304 B).
+#include "common.cuh"
+
+namespace ftrf {
+
+constexpr int GS = 4;   // lanes per sample
+
+__device__ __forceinline__ float group_sum(float v) {
+  v += __shfl_xor_sync(FULL_MASK, v, 1);
+  v += __shfl_xor_sync(FULL_MASK, v, 2);
+  return v;
+}
+
+// Partial (this lane's channel chunks) density feature of one normalised point.
+__device__ __forceinline__ float density_partial(const FtrfField& f, const float xn[3], int sub) {
+  const FtrfFactorSet& d = f.den;
+  float acc = 0.f;
+  if (f.model == FTRF_MODEL_VM) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int C = d.n_comp[k];
+      Tap tx = make_tap(xn[mat0(k)], d.plane_w[k]);
+      Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
+      Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+      for (int c = sub * 4; c < C; c += GS * 4) {
+        float4 p = plane4(d.plane[k], d.plane_w[k], C, tx, ty, c);
+        float4 l = line4(d.line[k], C, tl, c);
+        if (d.mask[k]) {                       // (plane*m)*(line*m), tensoRF.py:224-225
+          float4 m = mask4(d.mask[k], d.mask_stride[k], c);
+          p = mul4(p, m);
+          l = mul4(l, m);
+        }
+        acc += sum4(mul4(p, l));
+      }
+    }
+  } else {
+    const int C = d.n_comp[0];
+    Tap t0 = make_tap(xn[vecm(0)], d.line_len[0]);
+    Tap t1 = make_tap(xn[vecm(1)], d.line_len[1]);
+    Tap t2 = make_tap(xn[vecm(2)], d.line_len[2]);
+    for (int c = sub * 4; c < C; c += GS * 4) {
+      float4 v = mul4(mul4(line4(d.line[0], C, t0, c), line4(d.line[1], C, t1, c)), line4(d.line[2], C, t2, c));
+      if (d.mask[0]) v = mul4(v, mask4(d.mask[0], d.mask_stride[0], c));     // tensoRF.py:384
+      acc += sum4(v);
+    }
+  }
+  return acc;
+}
+
+__device__ __forceinline__ float activate(const FtrfField& f, float feat) {
+  return f.act == FTRF_ACT_SOFTPLUS ? softplus_f(feat + f.density_shift) : fmaxf(feat, 0.f);
+}
+
+__global__ void __launch_bounds__(256)
+density_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
+  const int sub = threadIdx.x & (GS - 1);
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  // all lanes of a warp run the same trip count so the group shuffles stay converged
+  const int64_t n_pad = (n + 7) & ~(int64_t)7;
+  for (int64_t s = g0; s < n_pad; s += gstride) {
+    float part = 0.f;
+    if (s < n) {
+      Ray ray = load_ray(f, c, ws.s_ray[s]);
+      float p[3], xn[3];
+      sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+      normalize_pt(f, p, xn);
+      part = density_partial(f, xn, sub);
+    }
+    float feat = group_sum(part);
+    if (s < n && sub == 0) ws.s_sigma[s] = activate(f, feat);
+  }
+}
+
+// sigma at arbitrary world-space points (compute_alpha's inner part, tensorBase.py:298-313)
+__global__ void __launch_bounds__(256)
+density_at_kernel(const FtrfField f, const float* __restrict__ xyz, int64_t n, float* __restrict__ out) {
+  const int sub = threadIdx.x & (GS - 1);
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  const int64_t n_pad = (n + 7) & ~(int64_t)7;
+  for (int64_t s = g0; s < n_pad; s += gstride) {
+    float part = 0.f;
+    bool keep = false;
+    if (s < n) {
+      float p[3] = {__ldg(xyz + 3 * s), __ldg(xyz + 3 * s + 1), __ldg(xyz + 3 * s + 2)}, xn[3];
+      keep = f.has_alpha_mask ? alpha_mask_keep(f, p) : true;
+      if (keep) {
+        normalize_pt(f, p, xn);
+        part = density_partial(f, xn, sub);
+      }
+    }
+    float feat = group_sum(part);
+    if (s < n && sub == 0) out[s] = keep ? activate(f, feat) : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------ backward
+// d sigma_feature arrives in ws.s_gsig.  Each lane scatters its own channel chunks with
+// red.global.add.v4.f32 (one 16-byte reduction per corner per chunk).
+__global__ void __launch_bounds__(256)
+density_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
+  const int sub = threadIdx.x & (GS - 1);
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  const FtrfFactorSet& d = f.den;
+  for (int64_t s = g0; s < n; s += gstride) {
+    const float g = ws.s_gsig[s];
+    if (g == 0.f) continue;
+    Ray ray = load_ray(f, c, ws.s_ray[s]);
+    float p[3], xn[3];
+    sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+    normalize_pt(f, p, xn);
+    if (f.model == FTRF_MODEL_VM) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int C = d.n_comp[k], W = d.plane_w[k];
+        Tap tx = make_tap(xn[mat0(k)], W);
+        Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
+        Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+        for (int ch = sub * 4; ch < C; ch += GS * 4) {
+          float4 pv = plane4(d.plane[k], W, C, tx, ty, ch);
+          float4 lv = line4(d.line[k], C, tl, ch);
+          float4 gm = make_float4(g, g, g, g);
+          if (d.mask[k]) {
+            float4 m = mask4(d.mask[k], d.mask_stride[k], ch);
+            gm = mul4(gm, mul4(m, m));
+          }
+          float4 gp = mul4(gm, lv);      // d/d plane sample
+          float4 gl = mul4(gm, pv);      // d/d line sample
+          float* gp0 = d.g_plane[k] + ((size_t)ty.i0 * W) * C + ch;
+          float* gp1 = d.g_plane[k] + ((size_t)ty.i1 * W) * C + ch;
+          float w;
+          if ((w = tx.w0 * ty.w0) != 0.f) red4(gp0 + (size_t)tx.i0 * C, scale4(w, gp));
+          if ((w = tx.w1 * ty.w0) != 0.f) red4(gp0 + (size_t)tx.i1 * C, scale4(w, gp));
+          if ((w = tx.w0 * ty.w1) != 0.f) red4(gp1 + (size_t)tx.i0 * C, scale4(w, gp));
+          if ((w = tx.w1 * ty.w1) != 0.f) red4(gp1 + (size_t)tx.i1 * C, scale4(w, gp));
+          if (tl.w0 != 0.f) red4(d.g_line[k] + (size_t)tl.i0 * C + ch, scale4(tl.w0, gl));
+          if (tl.w1 != 0.f) red4(d.g_line[k] + (size_t)tl.i1 * C + ch, scale4(tl.w1, gl));
+        }
+      }
+    } else {
+      const int C = d.n_comp[0];
+      Tap t[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) t[k] = make_tap(xn[vecm(k)], d.line_len[k]);
+      for (int ch = sub * 4; ch < C; ch += GS * 4) {
+        float4 l0 = line4(d.line[0], C, t[0], ch), l1 = line4(d.line[1], C, t[1], ch),
+               l2 = line4(d.line[2], C, t[2], ch);
+        float4 gm = make_float4(g, g, g, g);
+        if (d.mask[0]) gm = mul4(gm, mask4(d.mask[0], d.mask_stride[0], ch));
+        float4 gk[3] = {mul4(gm, mul4(l1, l2)), mul4(gm, mul4(l0, l2)), mul4(gm, mul4(l0, l1))};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          if (t[k].w0 != 0.f) red4(d.g_line[k] + (size_t)t[k].i0 * C + ch, scale4(t[k].w0, gk[k]));
+          if (t[k].w1 != 0.f) red4(d.g_line[k] + (size_t)t[k].i1 * C + ch, scale4(t[k].w1, gk[k]));
+        }
+      }
+    }
+  }
+}
+
+static int sample_grid(int64_t n_hint) {
+  int64_t blocks = (n_hint * GS + 255) / 256;
+  int64_t cap = (int64_t)FTRF_SMS * 8;
+  if (blocks < 1) blocks = 1;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+int launch_density(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  // the sample count lives on the device: persistent grid sized for the SM count, grid-stride inside
+  density_fwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
+  return check_launch("density_fwd");
+}
+
+int launch_density_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
+  return check_launch("density_bwd");
+}
+
+int launch_density_at(const FtrfField& f, const float* xyz, int64_t n, float* out, cudaStream_t st) {
+  if (n == 0) return FTRF_OK;
+  density_at_kernel<<<sample_grid(n), 256, 0, st>>>(f, xyz, n, out);
+  return check_launch("density_at");
+}
+
+}  // namespace ftrf

@@ -1,0 +1,209 @@
+// k_integrate.cu — stage 4: volume integration as a warp scan over each ray's packed samples.
+// Replaces raw2alpha (models/tensorBase.py:21-28), the dists construction (:346 / :340-342), the
+// shading threshold `weight > rayMarch_weight_thres` (:370), acc/depth (:377, :386-388),
+// num_valid_samples (:390) and, in composite, rgb accumulation + background + clamp (:375-384).
+//
+// Culled samples have sigma = 0 => alpha = 0 => their transmittance factor (1 - 0 + 1e-10) rounds
+// to exactly 1.0f, so scanning only the packed survivors is exact w.r.t. the dense cumprod up to
+// the association order of the fp32 products.
+// Algorithmic bytes: 12 B per packed sample forward (idx, sigma in; w out [+T when training]).
+#include "common.cuh"
+
+namespace ftrf {
+
+constexpr int INT_WARPS = 8;
+
+// dist_i * distance_scale exactly as forward builds it (:346, :340-342, :368)
+__device__ __forceinline__ float sample_dist(const FtrfField& f, const FtrfCall& c, const Ray& ray, int i, float z,
+                                             float dnorm) {
+  if (i >= c.n_samples - 1) return 0.f;
+  float d = __fsub_rn(sample_z(f, c, ray, i + 1), z);
+  if (c.ndc) d = __fmul_rn(d, dnorm);
+  return __fmul_rn(d, f.distance_scale);
+}
+
+__device__ __forceinline__ float ray_dnorm(const FtrfCall& c, const Ray& ray) {
+  return c.ndc ? sqrtf(ray.d[0] * ray.d[0] + ray.d[1] * ray.d[1] + ray.d[2] * ray.d[2]) : 1.f;
+}
+
+__global__ void __launch_bounds__(INT_WARPS * 32)
+integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
+  for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
+    const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
+    Ray ray = load_ray(f, c, r);
+    const float dnorm = ray_dnorm(c, ray);
+    float carry = 1.f, acc = 0.f, depth = 0.f;
+    for (int j0 = 0; j0 < cnt; j0 += 32) {
+      const int j = j0 + lane;
+      const bool live = j < cnt;
+      float alpha = 0.f, z = 0.f;
+      if (live) {
+        int i = ws.s_idx[off + j];
+        z = sample_z(f, c, ray, i);
+        float sd = ws.s_sigma[off + j] * sample_dist(f, c, ray, i, z, dnorm);
+        alpha = 1.f - expf(-sd);
+      }
+      float fac = (1.f - alpha) + 1e-10f;
+      // inclusive product scan over the 32 lanes
+      float incl = fac;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float up = __shfl_up_sync(FULL_MASK, incl, d);
+        if (lane >= d) incl *= up;
+      }
+      float excl = __shfl_up_sync(FULL_MASK, incl, 1);
+      float T = carry * (lane == 0 ? 1.f : excl);
+      carry *= __shfl_sync(FULL_MASK, incl, 31);
+      float w = alpha * T;
+      bool shade = live && (w > f.weight_thres);
+      uint32_t b = __ballot_sync(FULL_MASK, shade);
+      int base = 0;
+      if (lane == 0 && b) base = atomicAdd(ws.counters + 1, __popc(b));
+      base = __shfl_sync(FULL_MASK, base, 0);
+      int slot = -1;
+      if (shade) {
+        slot = base + __popc(b & ((1u << lane) - 1u));
+        if (slot < c.cap_app) ws.a_slot[slot] = off + j;
+        else { slot = -1; atomicOr(ws.counters + 2, 2); }
+      }
+      if (live) {
+        ws.s_w[off + j] = w;
+        ws.s_app[off + j] = slot;
+        if (c.save_for_backward) ws.s_T[off + j] = T;
+        acc += w;
+        depth = fmaf(w, z, depth);
+      }
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+      acc += __shfl_xor_sync(FULL_MASK, acc, d);
+      depth += __shfl_xor_sync(FULL_MASK, depth, d);
+    }
+    if (lane == 0) {
+      ws.acc[r] = acc;
+      float last = __ldg(c.rays + r * c.ray_cols + (c.ray_cols - 1));     // rays_chunk[..., -1], :388
+      c.depth_map[r] = depth + (1.f - acc) * last;
+    }
+  }
+}
+
+// rgb_map = sum_i w_i rgb_i (+ 1 - acc) -> clamp(0,1); one warp per ray over its packed samples.
+__global__ void __launch_bounds__(INT_WARPS * 32)
+composite_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
+  for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
+    const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
+    float rgb[3] = {0.f, 0.f, 0.f};
+    for (int j = lane; j < cnt; j += 32) {
+      int a = ws.s_app[off + j];
+      if (a >= 0) {
+        float w = ws.s_w[off + j];
+        const float* q = ws.a_rgb + (size_t)a * 3;
+        rgb[0] = fmaf(w, q[0], rgb[0]); rgb[1] = fmaf(w, q[1], rgb[1]); rgb[2] = fmaf(w, q[2], rgb[2]);
+      }
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1)
+#pragma unroll
+      for (int k = 0; k < 3; ++k) rgb[k] += __shfl_xor_sync(FULL_MASK, rgb[k], d);
+    if (lane < 3) {
+      float v = rgb[lane];
+      if (c.add_bg) v = v + (1.f - ws.acc[r]);
+      ws.rgb_pre[r * 3 + lane] = v;
+      c.rgb_map[r * 3 + lane] = fminf(fmaxf(v, 0.f), 1.f);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ backward
+// Inputs: g_rgb_map.  Outputs: a_grgb (dL/d rgb of every shaded sample) and s_gsig
+// (dL/d sigma_feature of every packed sample).
+//   g_w_i     = g_acc + [shaded] <g_map, rgb_i>,          g_acc = -sum_c g_map[c] if background added
+//   g_alpha_i = T_i g_w_i - (sum_{j>i} g_w_j w_j) / (1 - alpha_i + 1e-10)
+//   g_sigma_i = g_alpha_i * dist_i * (1 - alpha_i);  g_feat_i = g_sigma_i * act'(.)
+__global__ void __launch_bounds__(INT_WARPS * 32)
+integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
+  for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
+    const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
+    if (cnt == 0) continue;
+    Ray ray = load_ray(f, c, r);
+    const float dnorm = ray_dnorm(c, ray);
+    float gm[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      float pre = ws.rgb_pre[r * 3 + k];
+      gm[k] = (pre >= 0.f && pre <= 1.f) ? __ldg(c.g_rgb_map + r * 3 + k) : 0.f;   // clamp backward
+    }
+    const float g_acc = c.add_bg ? -(gm[0] + gm[1] + gm[2]) : 0.f;
+    float suffix = 0.f;                     // sum over later samples of g_w * w
+    const int last0 = ((cnt - 1) >> 5) << 5;
+    for (int j0 = last0; j0 >= 0; j0 -= 32) {
+      const int j = j0 + lane;
+      const bool live = j < cnt;
+      float gw = 0.f, w = 0.f, T = 0.f, alpha = 0.f, dist = 0.f, sigma = 0.f;
+      if (live) {
+        int i = ws.s_idx[off + j];
+        float z = sample_z(f, c, ray, i);
+        dist = sample_dist(f, c, ray, i, z, dnorm);
+        sigma = ws.s_sigma[off + j];
+        alpha = 1.f - expf(-sigma * dist);
+        T = ws.s_T[off + j];
+        w = ws.s_w[off + j];
+        gw = g_acc;
+        int a = ws.s_app[off + j];
+        if (a >= 0) {
+          const float* q = ws.a_rgb + (size_t)a * 3;
+          gw += gm[0] * q[0] + gm[1] * q[1] + gm[2] * q[2];
+          float* o = ws.a_grgb + (size_t)a * 3;
+          o[0] = w * gm[0]; o[1] = w * gm[1]; o[2] = w * gm[2];
+        }
+      }
+      // exclusive suffix sum of gw*w across lanes (higher lanes = later samples)
+      float v = gw * w, incl = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float dn = __shfl_down_sync(FULL_MASK, incl, d);
+        if (lane + d < 32) incl += dn;
+      }
+      float after = (incl - v) + suffix;
+      suffix += __shfl_sync(FULL_MASK, incl, 0);
+      if (live) {
+        float one_m = 1.f - alpha;
+        float g_alpha = T * gw - after / (one_m + 1e-10f);
+        float g_sigma = g_alpha * dist * one_m;
+        float dact = (f.act == FTRF_ACT_SOFTPLUS) ? (sigma > 20.f ? 1.f : 1.f - expf(-sigma))
+                                                  : (sigma > 0.f ? 1.f : 0.f);
+        ws.s_gsig[off + j] = g_sigma * dact;
+      }
+    }
+  }
+}
+
+static int ray_grid(int64_t n_rays) {
+  int64_t blocks = (n_rays + INT_WARPS - 1) / INT_WARPS;
+  int64_t cap = (int64_t)FTRF_SMS * 8;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+int launch_integrate(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (c.n_rays == 0) return FTRF_OK;
+  integrate_fwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
+  return check_launch("integrate_fwd");
+}
+int launch_composite(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (c.n_rays == 0) return FTRF_OK;
+  composite_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
+  return check_launch("composite");
+}
+int launch_integrate_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (c.n_rays == 0) return FTRF_OK;
+  integrate_bwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
+  return check_launch("integrate_bwd");
+}
+
+}  // namespace ftrf

@@ -1,0 +1,791 @@
+"""Drop-in modules for the reference's field API, backed by the sm_100a kernels.
+
+Mirrors (names, constructor arguments, attributes, state_dict keys, return values):
+  AlphaGridMask   models/tensorBase.py:30-48
+  TensorBase      models/tensorBase.py:51-395
+  TensorVMSplit   models/tensoRF.py:141-327
+  TensorCP        models/tensoRF.py:330-484
+  MLPRender_Fea / MLPRender_PE / MLPRender   models/mlp.py:27-155   (parameter containers)
+
+`forward()` (the hot path) runs entirely in libfewtensorf_b200.so through the C ABI of
+include/fewtensorf.h; there is no PyTorch or CPU fallback for it.  Factor parameters keep the
+reference's shapes — (1,C,H,W) planes, (1,C,L,1) lines — but live in channels-last memory so that
+the C channels of a texel are contiguous for the gather / scatter kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _abi
+from ._abi import FtrfCall, FtrfField, check, lib
+
+MAX_CANDIDATES = 1 << 26      # rays * samples processed per launch sequence (workspace bound)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _channels_last_param(t: torch.Tensor, device) -> nn.Parameter:
+    """(1,C,H,W) values -> Parameter of the same shape whose memory is [H][W][C]."""
+    buf = t.to(device).permute(0, 2, 3, 1).contiguous()
+    return nn.Parameter(buf.permute(0, 3, 1, 2))
+
+
+def _is_channels_last(p: torch.Tensor) -> bool:
+    _, c, h, w = p.shape
+    return p.stride() == (h * w * c, 1, w * c, c) or (p.numel() == 0)
+
+
+class AlphaGridMask(nn.Module):
+    """models/tensorBase.py:30-48.  Keeps the float volume the reference exposes and a bit-packed
+    copy (32 x-texels per word) that the march kernel reads."""
+
+    def __init__(self, device, aabb, alpha_volume):
+        super().__init__()
+        self.device = device
+        self.aabb = aabb.to(self.device)
+        self.aabbSize = self.aabb[1] - self.aabb[0]
+        self.invgridSize = 1.0 / self.aabbSize * 2
+        self.alpha_volume = alpha_volume.view(1, 1, *alpha_volume.shape[-3:])
+        self.gridSize = torch.LongTensor(
+            [alpha_volume.shape[-1], alpha_volume.shape[-2], alpha_volume.shape[-3]]).to(self.device)
+        self._bits = None
+        self._host = None
+
+    def packed(self):
+        """(bits tensor, dims [X,Y,Z], aabb0 list, invgrid list) — built once per mask."""
+        if self._bits is None:
+            vol = self.alpha_volume.detach().to(device=self.device, dtype=torch.float32).contiguous()
+            z, y, x = vol.shape[-3:]
+            words = lib.ftrf_alpha_mask_words(x, y, z)
+            bits = torch.empty(words, dtype=torch.int32, device=vol.device)
+            check(lib.ftrf_pack_alpha_mask(vol.data_ptr(), x, y, z, bits.data_ptr(), _stream()), "pack_alpha_mask")
+            self._bits = bits
+            a = self.aabb.detach().float().cpu()
+            inv = (1.0 / (a[1] - a[0]) * 2)          # same fp32 ops as :36-37
+            self._host = ([x, y, z], a[0].tolist(), inv.tolist())
+        return (self._bits,) + self._host
+
+    def sample_alpha(self, xyz_sampled):
+        c = self.normalize_coord(xyz_sampled).view(1, -1, 1, 1, 3)
+        return F.grid_sample(self.alpha_volume, c, align_corners=True).view(-1)
+
+    def normalize_coord(self, xyz_sampled):
+        return (xyz_sampled - self.aabb[0]) * self.invgridSize - 1
+
+
+class _ShadingMLP(nn.Module):
+    """Parameter container with the reference's layout: `.mlp` = Linear, ReLU, Linear, ReLU, Linear
+    (models/mlp.py:34-39) so that state_dict keys are renderModule.mlp.{0,2,4}.{weight,bias}."""
+    kind = ""
+
+    def __init__(self, in_mlpC: int, featureC: int):
+        super().__init__()
+        self.in_mlpC = in_mlpC
+        l1, l2, l3 = nn.Linear(in_mlpC, featureC), nn.Linear(featureC, featureC), nn.Linear(featureC, 3)
+        self.mlp = nn.Sequential(l1, nn.ReLU(inplace=True), l2, nn.ReLU(inplace=True), l3)
+        nn.init.constant_(self.mlp[-1].bias, 0)
+
+    def forward(self, pts, viewdirs, features, mask):
+        raise RuntimeError("the shading MLP runs fused inside TensorBase.forward (libfewtensorf_b200.so); "
+                           "it has no standalone PyTorch path")
+
+
+class MLPRender_Fea(_ShadingMLP):
+    kind = "MLP_Fea"
+
+    def __init__(self, inChanel, viewpe=6, feape=6, featureC=128):
+        super().__init__(2 * viewpe * 3 + 2 * feape * inChanel + 3 + inChanel, featureC)
+        self.viewpe, self.feape = viewpe, feape
+
+
+class MLPRender_PE(_ShadingMLP):
+    kind = "MLP_PE"
+
+    def __init__(self, inChanel, viewpe=6, pospe=6, featureC=128):
+        super().__init__((3 + 2 * viewpe * 3) + (2 * pospe * 3) + inChanel, featureC)
+        self.viewpe, self.pospe = viewpe, pospe
+
+
+class MLPRender(_ShadingMLP):
+    kind = "MLP"
+
+    def __init__(self, inChanel, viewpe=6, pospe=6, feape=6, featureC=128):
+        super().__init__((2 * pospe * 3) + (2 * viewpe * 3) + (2 * feape * inChanel) + inChanel + 3, featureC)
+        self.viewpe, self.pospe, self.feape = viewpe, pospe, feape
+
+
+def SHRender(xyz_sampled, viewdirs, features):
+    raise RuntimeError("SH shading runs fused inside TensorBase.forward (libfewtensorf_b200.so)")
+
+
+class _Workspace:
+    """Grow-only device byte buffer carved by the C side (FTRF_WS_* sections)."""
+
+    def __init__(self):
+        self.buf: Optional[torch.Tensor] = None
+        self.busy = False            # held by an autograd graph awaiting backward
+
+    def get(self, nbytes: int, device) -> torch.Tensor:
+        if self.buf is None or self.buf.numel() < nbytes or self.buf.device != torch.device(device):
+            self.buf = torch.empty(int(nbytes * 1.1) + 4096, dtype=torch.uint8, device=device)
+        return self.buf
+
+
+class _CallState:
+    """Everything backward needs from one forward call."""
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj")
+
+
+class TensorBase(nn.Module):
+    """models/tensorBase.py:51-395 with the per-ray path replaced by CUDA kernels."""
+
+    def __init__(self, args, aabb, gridSize, near_far=[2.0, 6.0], device='cuda', alphaMask=None,
+                 rayMarch_weight_thres=0.0001):
+        super().__init__()
+        self.aabb = aabb
+        self.device = device
+        self.near_far = near_far
+        self.alphaMask = alphaMask
+        self.rayMarch_weight_thres = rayMarch_weight_thres
+        self.matMode = [[0, 1], [0, 2], [1, 2]]
+        self.vecMode = [2, 1, 0]
+        self.comp_w = [1, 1, 1]
+
+        self.step_ratio = args['step_ratio']
+        self.fea2denseAct = args['fea2denseAct']
+        self.density_n_comp = args['density_n_comp']
+        self.app_n_comp = args['app_n_comp']
+        self.app_dim = args['app_dim']
+        self.density_shift = args['density_shift']
+        self.distance_scale = args['distance_scale']
+        self.alphaMask_thres = args['alphaMask_thres']
+        self.shadingMode = args['shadingMode']
+        self.pos_pe = args['pos_pe']
+        self.view_pe = args['view_pe']
+        self.fea_pe = args['fea_pe']
+        self.featureC = args['featureC']
+        self.pos_bit_length = [2 * args['pos_pe'] * 3]
+        self.view_bit_length = [2 * args['view_pe'] * 3]
+        self.fea_bit_length = [2 * args['fea_pe'] * self.app_dim]
+
+        if self.fea2denseAct not in ("softplus", "relu"):
+            raise ValueError(f"fea2denseAct {self.fea2denseAct!r} not supported")
+        self._ws_train = _Workspace()
+        self._ws_eval = _Workspace()
+        self._cap_hint = {}            # (n_rays, S, train) -> (cap_samples, cap_app)
+        self._gradbuf = None
+        self._counters_host = None
+        self._keepalive: List[torch.Tensor] = []
+        self.init_render_func(self.shadingMode, self.pos_pe, self.view_pe, self.fea_pe, self.featureC, device)
+        self.update_stepSize(gridSize)
+        self.init_svd_volume(gridSize[0], device)
+
+    # ------------------------------------------------------------------ construction
+    def init_render_func(self, shadingMode, pos_pe, view_pe, fea_pe, featureC, device):
+        if shadingMode == 'MLP_PE':
+            self.renderModule = MLPRender_PE(self.app_dim, view_pe, pos_pe, featureC).to(device)
+        elif shadingMode == 'MLP_Fea':
+            self.renderModule = MLPRender_Fea(self.app_dim, view_pe, fea_pe, featureC).to(device)
+        elif shadingMode == 'MLP':
+            self.renderModule = MLPRender(self.app_dim, view_pe, pos_pe, fea_pe, featureC).to(device)
+        elif shadingMode == 'SH':
+            # the reference has SHRender (models/mlp.py:15-19) but cannot select it (tensorBase.py:96-98)
+            self.renderModule = SHRender
+        else:
+            raise ValueError(f"Unrecognized shading module {shadingMode!r}")
+
+    def update_stepSize(self, gridSize):
+        """models/tensorBase.py:104-111.  Derived constants are evaluated in fp32 on the CPU so they
+        are the same numbers on every device (they decide which samples exist)."""
+        a = self.aabb.detach().float().cpu()
+        size = a[1] - a[0]
+        inv = 2.0 / size
+        g = torch.LongTensor([int(v) for v in gridSize])
+        units = size / (g - 1)
+        step = torch.mean(units) * self.step_ratio
+        diag = torch.sqrt(torch.sum(torch.square(size)))
+        self.aabbSize = size.to(self.device)
+        self.invaabbSize = inv.to(self.device)
+        self.gridSize = g.to(self.device)
+        self.units = units.to(self.device)
+        self.stepSize = step.to(self.device)
+        self.aabbDiag = diag.to(self.device)
+        self.nSamples = int((diag / step).item()) + 1
+        self._host = dict(aabb=a.reshape(-1).tolist(), inv=inv.tolist(), step=float(step),
+                          grid=[int(v) for v in gridSize])
+
+    def init_svd_volume(self, res, device):
+        pass
+
+    def normalize_coord(self, xyz_sampled):
+        return (xyz_sampled - self.aabb[0]) * self.invaabbSize - 1
+
+    def feature2density(self, density_features):
+        if self.fea2denseAct == "softplus":
+            return F.softplus(density_features + self.density_shift)
+        return F.relu(density_features)
+
+    # ------------------------------------------------------------------ checkpoint (tensorBase.py:136-175)
+    def get_kwargs(self):
+        return {
+            'aabb': self.aabb, 'gridSize': self.gridSize.tolist(), 'density_n_comp': self.density_n_comp,
+            'appearance_n_comp': self.app_n_comp, 'app_dim': self.app_dim, 'density_shift': self.density_shift,
+            'alphaMask_thres': self.alphaMask_thres, 'distance_scale': self.distance_scale,
+            'rayMarch_weight_thres': self.rayMarch_weight_thres, 'fea2denseAct': self.fea2denseAct,
+            'near_far': self.near_far, 'step_ratio': self.step_ratio, 'shadingMode': self.shadingMode,
+            'pos_pe': self.pos_pe, 'view_pe': self.view_pe, 'fea_pe': self.fea_pe, 'featureC': self.featureC,
+        }
+
+    def save(self, path):
+        ckpt = {'kwargs': self.get_kwargs(), 'state_dict': self.state_dict()}
+        if self.alphaMask is not None:
+            vol = self.alphaMask.alpha_volume.bool().cpu().numpy()
+            ckpt.update({'alphaMask.shape': vol.shape, 'alphaMask.mask': np.packbits(vol.reshape(-1)),
+                         'alphaMask.aabb': self.alphaMask.aabb.cpu()})
+        torch.save(ckpt, path)
+
+    def load(self, ckpt):
+        if 'alphaMask.aabb' in ckpt.keys():
+            length = np.prod(ckpt['alphaMask.shape'])
+            vol = torch.from_numpy(np.unpackbits(ckpt['alphaMask.mask'])[:length].reshape(ckpt['alphaMask.shape']))
+            self.alphaMask = AlphaGridMask(self.device, ckpt['alphaMask.aabb'].to(self.device),
+                                           vol.float().to(self.device))
+        self.load_state_dict(ckpt['state_dict'])
+
+    # ------------------------------------------------------------------ parameter plumbing
+    def _factor_params(self) -> List[nn.Parameter]:
+        raise NotImplementedError
+
+    def _mlp_params(self) -> List[nn.Parameter]:
+        if self.shadingMode == 'SH':
+            return []
+        m = self.renderModule.mlp
+        return [m[0].weight, m[0].bias, m[2].weight, m[2].bias, m[4].weight, m[4].bias]
+
+    def _all_params(self) -> List[nn.Parameter]:
+        return self._factor_params() + [self.basis_mat.weight] + self._mlp_params()
+
+    def _ensure_layout(self):
+        for p in self._factor_params():
+            if not _is_channels_last(p):
+                with torch.no_grad():
+                    p.data = p.data.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+        for p in [self.basis_mat.weight] + self._mlp_params():
+            if not p.is_contiguous():
+                with torch.no_grad():
+                    p.data = p.data.contiguous()
+
+    def grad_buffer(self, fresh: bool = False):
+        """Flat fp32 gradient buffer (the NCCL all-reduce operand) + one view per parameter, in
+        `_all_params()` order; factor views are channels-last like the parameters."""
+        params = self._all_params()
+        total = sum(p.numel() for p in params)
+        buf = self._gradbuf
+        if fresh or buf is None or buf.numel() != total or buf.device != params[0].device:
+            buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
+            if not fresh:
+                self._gradbuf = buf
+        views, off = [], 0
+        for p in params:
+            n = p.numel()
+            flat = buf[off:off + n]
+            if p.dim() == 4:
+                _, c, h, w = p.shape
+                views.append(flat.view(1, h, w, c).permute(0, 3, 1, 2))
+            else:
+                views.append(flat.view(p.shape))
+            off += n
+        return buf, views
+
+    # ------------------------------------------------------------------ C-ABI argument marshalling
+    def _fill_factor_set(self, fs, planes, lines, comps, mask, keep):
+        is_vm = planes is not None
+        g = self._host["grid"]
+        for k in range(3):
+            fs.n_comp[k] = int(comps[k] if is_vm else comps[0])
+            fs.line_len[k] = g[self.vecMode[k]]
+            fs.line[k] = lines[k].data_ptr()
+            if is_vm:
+                fs.plane_w[k] = g[self.matMode[k][0]]
+                fs.plane_h[k] = g[self.matMode[k][1]]
+                fs.plane[k] = planes[k].data_ptr()
+                if tuple(planes[k].shape) != (1, fs.n_comp[k], fs.plane_h[k], fs.plane_w[k]):
+                    raise RuntimeError(f"plane {k} has shape {tuple(planes[k].shape)}, gridSize says "
+                                       f"{(1, fs.n_comp[k], fs.plane_h[k], fs.plane_w[k])}")
+            if tuple(lines[k].shape) != (1, fs.n_comp[k], fs.line_len[k], 1):
+                raise RuntimeError(f"line {k} has shape {tuple(lines[k].shape)}")
+            fs.mask[k] = None
+            fs.mask_stride[k] = 0
+        if mask is not None:
+            # VM indexes mask[k] per plane (tensoRF.py:224,250,257); CP reads mask[0] (:384,:415)
+            for k in range(3 if is_vm else 1):
+                mk = mask[k]
+                mk = torch.as_tensor(mk).detach().to(device=lines[0].device, dtype=torch.float32).contiguous()
+                if mk.numel() == 1:
+                    fs.mask_stride[k] = 0
+                elif mk.numel() == fs.n_comp[k]:
+                    fs.mask_stride[k] = 1
+                else:
+                    raise RuntimeError(f"decomposition mask {k} has {mk.numel()} entries for {fs.n_comp[k]} components")
+                keep.append(mk)
+                fs.mask[k] = mk.data_ptr()
+
+    def _fill_field(self, mask, grad_views=None) -> FtrfField:
+        self._ensure_layout()
+        f = FtrfField()
+        keep: List[torch.Tensor] = []
+        h = self._host
+        f.model = _abi.MODEL_VM if self._is_vm else _abi.MODEL_CP
+        f.shading = _abi.SHADING_KINDS[self.shadingMode]
+        f.act = _abi.ACT_SOFTPLUS if self.fea2denseAct == "softplus" else _abi.ACT_RELU
+        f.app_dim, f.feature_c = int(self.app_dim), int(self.featureC)
+        f.pos_pe, f.view_pe, f.fea_pe = int(self.pos_pe), int(self.view_pe), int(self.fea_pe)
+        f.in_dim = 0 if self.shadingMode == 'SH' else int(self.renderModule.in_mlpC)
+        for i in range(6):
+            f.aabb[i] = h["aabb"][i]
+        for i in range(3):
+            f.inv_aabb[i] = h["inv"][i]
+        f.step_size = h["step"]
+        f.near_, f.far_ = float(self.near_far[0]), float(self.near_far[1])
+        f.distance_scale = float(self.distance_scale)
+        f.density_shift = float(self.density_shift)
+        f.weight_thres = float(self.rayMarch_weight_thres)
+        if self.alphaMask is not None:
+            bits, dims, a0, inv = self.alphaMask.packed()
+            f.has_alpha_mask = 1
+            for i in range(3):
+                f.am_dim[i], f.am_aabb0[i], f.am_inv[i] = dims[i], a0[i], inv[i]
+            f.am_bits = bits.data_ptr()
+        enc = {"pos": None, "view": None, "fea": None}
+        dmask = amask = None
+        if mask is not None:
+            enc, dmask, amask = mask['encoding'], mask['decomp']['den'], mask['decomp']['app']
+        dp = getattr(self, "density_plane", None) if self._is_vm else None
+        ap = getattr(self, "app_plane", None) if self._is_vm else None
+        self._fill_factor_set(f.den, dp, self.density_line, self.density_n_comp, dmask, keep)
+        self._fill_factor_set(f.app, ap, self.app_line, self.app_n_comp, amask, keep)
+        f.basis = self.basis_mat.weight.data_ptr()
+        mlp = self._mlp_params()
+        if mlp:
+            f.w1, f.b1, f.w2, f.b2, f.w3, f.b3 = [p.data_ptr() for p in mlp]
+            lens = {"pos": 2 * self.pos_pe * 3, "view": 2 * self.view_pe * 3, "fea": 2 * self.fea_pe * self.app_dim}
+            for i, key in enumerate(("pos", "view", "fea")):
+                m = enc.get(key)
+                if m is None:
+                    continue
+                m = torch.as_tensor(m).detach().to(device=mlp[0].device, dtype=torch.float32).contiguous()
+                if m.numel() not in (1, lens[key]):
+                    raise RuntimeError(f"encoding mask '{key}' has {m.numel()} entries, expected 1 or {lens[key]}")
+                keep.append(m)
+                f.enc_mask[i] = m.data_ptr()
+                f.enc_mask_len[i] = m.numel()
+        if grad_views is not None:
+            gv = list(grad_views)
+            nf = len(self._factor_params())
+            fg = gv[:nf]
+            if self._is_vm:
+                for k in range(3):
+                    f.den.g_plane[k], f.den.g_line[k] = fg[k].data_ptr(), fg[3 + k].data_ptr()
+                    f.app.g_plane[k], f.app.g_line[k] = fg[6 + k].data_ptr(), fg[9 + k].data_ptr()
+            else:
+                for k in range(3):
+                    f.den.g_line[k], f.app.g_line[k] = fg[k].data_ptr(), fg[3 + k].data_ptr()
+            f.g_basis = gv[nf].data_ptr()
+            if mlp:
+                f.g_w1, f.g_b1, f.g_w2, f.g_b2, f.g_w3, f.g_b3 = [v.data_ptr() for v in gv[nf + 1:nf + 7]]
+        f._keep = keep          # python-side keep-alive of mask tensors
+        return f
+
+    def _read_counters(self, ws: torch.Tensor):
+        if self._counters_host is None:
+            self._counters_host = torch.empty(8, dtype=torch.int32).pin_memory()
+        self._counters_host.copy_(ws[:32].view(torch.int32), non_blocking=True)
+        torch.cuda.current_stream().synchronize()        # the one host sync of a forward call
+        c = self._counters_host
+        return int(c[0]), int(c[1]), int(c[2])
+
+    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save) -> _CallState:
+        """March -> density -> integrate -> appearance -> shade -> composite, one C call, one sync."""
+        if not rays.is_cuda:
+            raise RuntimeError("fewtensorf_b200 needs CUDA tensors (no CPU path)")
+        N = rays.shape[0]
+        field = self._fill_field(mask)
+        call = FtrfCall()
+        call.n_rays, call.ray_cols, call.n_samples = N, rays.shape[1], S
+        call.is_train, call.ndc, call.add_bg, call.save_for_backward = int(is_train), int(ndc), int(add_bg), int(save)
+        call.rays = rays.data_ptr()
+        call.jitter = jitter.data_ptr() if jitter is not None else None
+        rgb = torch.empty(N, 3, dtype=torch.float32, device=rays.device)
+        depth = torch.empty(N, dtype=torch.float32, device=rays.device)
+        call.rgb_map, call.depth_map = rgb.data_ptr(), depth.data_ptr()
+        key = (N, S, bool(save))
+        cap_s, cap_a = self._cap_hint.get(key, (min(N * S, max(N * 64, 1 << 16)), max(N * 16, 1 << 14)))
+        wsobj = self._ws_train if save else self._ws_eval
+        if save and wsobj.busy:
+            wsobj = _Workspace()           # an earlier graph still owns the cached buffer
+        while True:
+            call.cap_samples, call.cap_app = cap_s, cap_a
+            nbytes = lib.ftrf_workspace_layout(C.byref(field), C.byref(call), None)
+            ws = wsobj.get(nbytes, rays.device)
+            check(lib.ftrf_forward(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream()), "forward")
+            need_s, need_a, flags = self._read_counters(ws)
+            if flags == 0:
+                break
+            cap_s = max(cap_s, int(need_s * 1.25) + 1024) if flags & 1 else cap_s
+            cap_a = max(cap_a, int(need_a * 1.25) + 1024) if (flags & 2 or flags & 1) else cap_a
+            cap_s = min(cap_s, N * S)
+            cap_a = min(cap_a, N * S)
+        self._cap_hint[key] = (max(cap_s, min(N * S, int(need_s * 1.1) + 1024)),
+                               max(cap_a, min(N * S, int(need_a * 1.1) + 1024)))
+        st = _CallState()
+        st.field, st.call, st.ws, st.ws_bytes, st.wsobj = field, call, ws, ws.numel(), wsobj
+        st.keep = (rays, jitter, rgb, depth)
+        st.n_samples, st.n_valid = need_s, need_a
+        self._last_call = st
+        return st
+
+    def workspace_section(self, st: _CallState, name: str, dtype, count: int) -> torch.Tensor:
+        """Typed view of one FTRF_WS_* section of a finished call (used by the stage parity tests)."""
+        offs = (C.c_int64 * _abi.WS_COUNT)()
+        lib.ftrf_workspace_layout(C.byref(st.field), C.byref(st.call), offs)
+        o = offs[_abi.WS[name]]
+        nbytes = count * torch.empty((), dtype=dtype).element_size()
+        return st.ws[o:o + nbytes].view(dtype)
+
+    def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views) -> None:
+        g_rgb = g_rgb.contiguous().float()
+        field = self._fill_field(None, grad_views)
+        # masks / alphaMask exactly as in the forward call
+        for name in ("mask", "mask_stride"):
+            for fs_new, fs_old in ((field.den, st.field.den), (field.app, st.field.app)):
+                for k in range(3):
+                    getattr(fs_new, name)[k] = getattr(fs_old, name)[k]
+        for i in range(3):
+            field.enc_mask[i], field.enc_mask_len[i] = st.field.enc_mask[i], st.field.enc_mask_len[i]
+        field._keep = st.field._keep
+        st.call.g_rgb_map = g_rgb.data_ptr()
+        check(lib.ftrf_backward(C.byref(field), C.byref(st.call), st.ws.data_ptr(), st.ws_bytes, _stream()), "backward")
+        st.keep = st.keep + (g_rgb,)
+
+    # ------------------------------------------------------------------ the hot path
+    def _draw_rng(self, n_rays, S, is_train, ndc_ray, white_bg, device):
+        """Host RNG draws in the reference's order and from the same (CPU) generator:
+        jitter (tensorBase.py:183 / :201) first, then the background coin (:380)."""
+        jitter = None
+        if ndc_ray:
+            near, far = self.near_far
+            z = torch.linspace(near, far, S).unsqueeze(0)
+            if is_train:
+                z = z + torch.rand_like(z) * ((far - near) / S)
+            jitter = z.reshape(-1)
+        elif is_train:
+            jitter = torch.rand(n_rays, 1).reshape(-1)
+        add_bg = bool(white_bg or (is_train and bool(torch.rand((1,)) < 0.5)))
+        if jitter is not None:
+            jitter = jitter.pin_memory().to(device, non_blocking=True)
+        return jitter, add_bg
+
+    def forward(self, rays_chunk, mask, white_bg=True, is_train=False, ndc_ray=False, N_samples=-1):
+        """models/tensorBase.py:321-395.  Returns (rgb_map [N,3], depth_map [N], num_valid_samples)."""
+        S = int(N_samples) if N_samples > 0 else int(self.nSamples)
+        rays = rays_chunk.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        N = rays.shape[0]
+        jitter, add_bg = self._draw_rng(N, S, is_train, ndc_ray, white_bg, rays.device)
+        params = self._all_params()
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        step = max(1, MAX_CANDIDATES // S)
+        outs = []
+        for lo in range(0, max(N, 1), step):
+            r = rays[lo:lo + step]
+            j = jitter[lo:lo + step] if (jitter is not None and not ndc_ray) else jitter
+            if need_grad:
+                outs.append(_RenderFn.apply(self, r, j, mask, S, is_train, ndc_ray, add_bg, *params))
+            else:
+                st = self._run_forward(r, j, mask, S, is_train, ndc_ray, add_bg, save=False)
+                outs.append((st.keep[2], st.keep[3], torch.tensor(st.n_valid, dtype=torch.int64)))
+        if len(outs) == 1:
+            return outs[0]
+        return (torch.cat([o[0] for o in outs]), torch.cat([o[1] for o in outs]), sum(o[2] for o in outs))
+
+    def train_step(self, rays, rgb_target, mask=None, white_bg=True, ndc_ray=False, N_samples=-1, grad_scale=1.0):
+        """Fused training step without the autograd engine: forward, MSE loss (train.py:338) and
+        backward into the flat gradient buffer.  Sets `.grad` of every parameter to its view of that
+        buffer and returns (loss 0-dim device tensor, num_valid_samples int)."""
+        S = int(N_samples) if N_samples > 0 else int(self.nSamples)
+        rays = rays.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        target = rgb_target.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        N = rays.shape[0]
+        if N * S > MAX_CANDIDATES:
+            raise RuntimeError("train_step: batch too large for one launch sequence; split the batch")
+        jitter, add_bg = self._draw_rng(N, S, True, ndc_ray, white_bg, rays.device)
+        buf, views = self.grad_buffer()
+        buf.zero_()
+        st = self._run_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
+        rgb = st.keep[2]
+        loss = torch.empty(1, dtype=torch.float32, device=rays.device)
+        g_rgb = torch.empty_like(rgb)
+        check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
+                                _stream()), "mse_loss")
+        if grad_scale != 1.0:
+            g_rgb.mul_(grad_scale)
+        self._run_backward(st, g_rgb, views)
+        for p, v in zip(self._all_params(), views):
+            p.grad = v
+        return loss[0], st.n_valid
+
+    # ------------------------------------------------------------------ helpers kept from the reference API
+    def sample_ray(self, rays_o, rays_d, is_train=True, N_samples=-1):
+        """models/tensorBase.py:189-208 (torch ops; used by filtering_rays, not by forward)."""
+        S = N_samples if N_samples > 0 else self.nSamples
+        near, far = self.near_far
+        d = torch.where(rays_d == 0, torch.full_like(rays_d, 1e-6), rays_d)
+        t_min = torch.minimum((self.aabb[1] - rays_o) / d, (self.aabb[0] - rays_o) / d).amax(-1).clamp(min=near, max=far)
+        rng = torch.arange(S)[None].float()
+        if is_train:
+            rng = rng.repeat(rays_d.shape[-2], 1)
+            rng += torch.rand_like(rng[:, [0]])
+        z = t_min[..., None] + self.stepSize * rng.to(rays_o.device)
+        pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., None]
+        inside = ~((self.aabb[0] > pts) | (pts > self.aabb[1])).any(dim=-1)
+        return pts, z, inside
+
+    @torch.no_grad()
+    def sigma_at(self, xyz: torch.Tensor, mask=None) -> torch.Tensor:
+        """sigma of compute_alpha (tensorBase.py:298-313) for world-space points, on the GPU kernels."""
+        pts = xyz.detach().reshape(-1, 3).to(device=self.device, dtype=torch.float32).contiguous()
+        den_mask = None if mask is None else {"encoding": {"pos": None, "view": None, "fea": None},
+                                              "decomp": {"den": mask, "app": None}}
+        field = self._fill_field(den_mask)
+        out = torch.empty(pts.shape[0], dtype=torch.float32, device=pts.device)
+        check(lib.ftrf_density_at(C.byref(field), pts.data_ptr(), pts.shape[0], out.data_ptr(), _stream()), "density_at")
+        return out.view(xyz.shape[:-1])
+
+    def compute_alpha(self, xyz_locs, mask, length=1):
+        sigma = self.sigma_at(xyz_locs, mask)
+        return 1 - torch.exp(-sigma * length)
+
+    @torch.no_grad()
+    def getDenseAlpha(self, gridSize=None, mask=None):
+        """models/tensorBase.py:215-230 — the whole lattice in one kernel launch per x-slab batch."""
+        gridSize = self.gridSize.tolist() if gridSize is None else list(gridSize)
+        lin = [torch.linspace(0, 1, int(g)) for g in gridSize]
+        samples = torch.stack(torch.meshgrid(*lin, indexing="ij"), -1).to(self.device)
+        dense_xyz = self.aabb[0] * (1 - samples) + self.aabb[1] * samples
+        alpha = self.compute_alpha(dense_xyz.view(-1, 3), mask, self.stepSize).view(dense_xyz.shape[:-1])
+        return alpha, dense_xyz
+
+    @torch.no_grad()
+    def updateAlphaMask(self, gridSize=(200, 200, 200), mask=None):
+        """models/tensorBase.py:233-256."""
+        gridSize = tuple(int(g) for g in gridSize)
+        alpha, dense_xyz = self.getDenseAlpha(gridSize, mask)
+        dense_xyz = dense_xyz.transpose(0, 2).contiguous()
+        alpha = alpha.clamp(0, 1).transpose(0, 2).contiguous()[None, None]
+        alpha = F.max_pool3d(alpha, kernel_size=3, padding=1, stride=1).view(gridSize[::-1])
+        alpha[alpha >= self.alphaMask_thres] = 1
+        alpha[alpha < self.alphaMask_thres] = 0
+        self.alphaMask = AlphaGridMask(self.device, self.aabb, alpha)
+        occ = dense_xyz[alpha > 0.5]
+        return torch.stack((occ.amin(0), occ.amax(0)))
+
+    @torch.no_grad()
+    def filtering_rays(self, all_rays, all_rgbs, N_samples=256, chunk=10240 * 5, bbox_only=False):
+        """models/tensorBase.py:259-288."""
+        n = int(torch.tensor(all_rays.shape[:-1]).prod())
+        flat = all_rays.reshape(n, all_rays.shape[-1])
+        keep = []
+        for lo in range(0, n, chunk):
+            rc = flat[lo:lo + chunk].to(self.device)
+            o, d = rc[..., :3], rc[..., 3:6]
+            if bbox_only:
+                v = torch.where(d == 0, torch.full_like(d, 1e-6), d)
+                ra, rb = (self.aabb[1] - o) / v, (self.aabb[0] - o) / v
+                ok = torch.maximum(ra, rb).amin(-1) > torch.minimum(ra, rb).amax(-1)
+            else:
+                pts, _, _ = self.sample_ray(o, d, N_samples=N_samples, is_train=False)
+                ok = (self.alphaMask.sample_alpha(pts).view(pts.shape[:-1]) > 0).any(-1)
+            keep.append(ok.cpu())
+        keep = torch.cat(keep).view(all_rgbs.shape[:-1])
+        return all_rays[keep], all_rgbs[keep]
+
+
+class _RenderFn(torch.autograd.Function):
+    """One autograd node for the whole per-ray path (replaces the ~60-op torch graph the reference
+    builds per call).  Gradients are produced by the backward kernels, not by autograd replay."""
+
+    @staticmethod
+    def forward(ctx, model, rays, jitter, mask, S, is_train, ndc, add_bg, *params):
+        st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True)
+        st.wsobj.busy = True
+        ctx.model, ctx.st = model, st
+        rgb, depth = st.keep[2], st.keep[3]
+        n_valid = torch.tensor(st.n_valid, dtype=torch.int64)
+        ctx.mark_non_differentiable(depth, n_valid)
+        return rgb, depth, n_valid
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, g_nv):
+        model, st = ctx.model, ctx.st
+        params = model._all_params()
+        buf = model._gradbuf
+        # never zero a buffer that still backs live .grad tensors (gradient accumulation)
+        aliased = buf is not None and any(
+            p.grad is not None and p.grad.untyped_storage().data_ptr() == buf.untyped_storage().data_ptr()
+            for p in params)
+        buf, views = model.grad_buffer(fresh=aliased)
+        if not aliased:
+            buf.zero_()
+        model._run_backward(st, g_rgb, views)
+        st.wsobj.busy = False
+        ctx.st = None
+        grads = tuple(v if p.requires_grad else None for p, v in zip(params, views))
+        return (None,) * 8 + grads
+
+
+class TensorVMSplit(TensorBase):
+    """models/tensoRF.py:141-327 — plane x line (VM) decomposition."""
+    _is_vm = True
+
+    def __init__(self, args, aabb, gridSize, near_far, device):
+        super().__init__(args, aabb, gridSize, near_far, device)
+
+    def init_svd_volume(self, res, device):
+        self.density_plane, self.density_line = self.init_one_svd(self.density_n_comp, self._host["grid"], 0.1, device)
+        self.app_plane, self.app_line = self.init_one_svd(self.app_n_comp, self._host["grid"], 0.1, device)
+        self.basis_mat = nn.Linear(sum(self.app_n_comp), self.app_dim, bias=False).to(device)
+
+    def init_one_svd(self, n_component, gridSize, scale, device):
+        """Same shapes, scale and CPU draw order as tensoRF.py:152-162; storage is channels-last."""
+        planes, lines = [], []
+        for i in range(3):
+            m0, m1 = self.matMode[i]
+            planes.append(_channels_last_param(scale * torch.randn((1, n_component[i], gridSize[m1], gridSize[m0])), device))
+            lines.append(_channels_last_param(scale * torch.randn((1, n_component[i], gridSize[self.vecMode[i]], 1)), device))
+        return nn.ParameterList(planes), nn.ParameterList(lines)
+
+    def _factor_params(self):
+        return list(self.density_plane) + list(self.density_line) + list(self.app_plane) + list(self.app_line)
+
+    def get_optparam_groups(self, lr_init_spatialxyz=0.02, lr_init_network=0.001):
+        """tensoRF.py:166-172."""
+        groups = [{'params': self.density_line, 'lr': lr_init_spatialxyz},
+                  {'params': self.density_plane, 'lr': lr_init_spatialxyz},
+                  {'params': self.app_line, 'lr': lr_init_spatialxyz},
+                  {'params': self.app_plane, 'lr': lr_init_spatialxyz},
+                  {'params': self.basis_mat.parameters(), 'lr': lr_init_network}]
+        if isinstance(self.renderModule, nn.Module):
+            groups += [{'params': self.renderModule.parameters(), 'lr': lr_init_network}]
+        return groups
+
+    @torch.no_grad()
+    def upsample_volume_grid(self, res_target):
+        """tensoRF.py:267-288 — bilinear (align_corners) resampling of every factor."""
+        res_target = [int(v) for v in res_target]
+        for planes, lines in ((self.app_plane, self.app_line), (self.density_plane, self.density_line)):
+            for i in range(3):
+                m0, m1 = self.matMode[i]
+                planes[i] = _channels_last_param(
+                    F.interpolate(planes[i].data, size=(res_target[m1], res_target[m0]), mode='bilinear', align_corners=True),
+                    planes[i].device)
+                lines[i] = _channels_last_param(
+                    F.interpolate(lines[i].data, size=(res_target[self.vecMode[i]], 1), mode='bilinear', align_corners=True),
+                    lines[i].device)
+        self.update_stepSize(res_target)
+
+    @torch.no_grad()
+    def shrink(self, new_aabb):
+        """tensoRF.py:290-327 — crop every factor to the occupied box."""
+        lo, hi = new_aabb
+        t_l = torch.round(torch.round((lo - self.aabb[0]) / self.units)).long()
+        b_r = torch.round((hi - self.aabb[0]) / self.units).long() + 1
+        b_r = torch.stack([b_r, self.gridSize]).amin(0)
+        for i in range(3):
+            v = self.vecMode[i]
+            m0, m1 = self.matMode[i]
+            for lines, planes in ((self.density_line, self.density_plane), (self.app_line, self.app_plane)):
+                lines[i] = _channels_last_param(lines[i].data[..., t_l[v]:b_r[v], :], lines[i].device)
+                planes[i] = _channels_last_param(planes[i].data[..., t_l[m1]:b_r[m1], t_l[m0]:b_r[m0]], planes[i].device)
+        new_aabb = self._corrected_aabb(new_aabb, t_l, b_r)
+        size = b_r - t_l
+        self.aabb = new_aabb
+        self.update_stepSize((int(size[0]), int(size[1]), int(size[2])))
+
+    def _corrected_aabb(self, new_aabb, t_l, b_r):
+        if torch.all(self.alphaMask.gridSize == self.gridSize):
+            return new_aabb
+        lo_r, hi_r = t_l / (self.gridSize - 1), (b_r - 1) / (self.gridSize - 1)
+        fixed = torch.zeros_like(new_aabb)
+        fixed[0] = (1 - lo_r) * self.aabb[0] + lo_r * self.aabb[1]
+        fixed[1] = (1 - hi_r) * self.aabb[0] + hi_r * self.aabb[1]
+        return fixed
+
+
+class TensorCP(TensorBase):
+    """models/tensoRF.py:330-484 — line x line x line (CP) decomposition.
+
+    The reference's own constructor forwards `device` into the near_far slot (tensoRF.py:331-332 vs
+    tensorBase.py:52) and cannot be called the way train.py:227-247 calls it; this one accepts both
+    the positional form and the keywords train.py uses."""
+    _is_vm = False
+
+    def __init__(self, args, aabb, gridSize, device='cuda', near_far=(2.0, 6.0), **kargs):
+        super().__init__(args, aabb, gridSize, list(near_far), device, **kargs)
+
+    def init_svd_volume(self, res, device):
+        self.density_line = self.init_one_svd(self.density_n_comp[0], self._host["grid"], 0.2, device)
+        self.app_line = self.init_one_svd(self.app_n_comp[0], self._host["grid"], 0.2, device)
+        self.basis_mat = nn.Linear(self.app_n_comp[0], self.app_dim, bias=False).to(device)
+
+    def init_one_svd(self, n_component, gridSize, scale, device):
+        """tensoRF.py:341-347."""
+        return nn.ParameterList([
+            _channels_last_param(scale * torch.randn((1, n_component, gridSize[self.vecMode[i]], 1)), device)
+            for i in range(3)])
+
+    def _factor_params(self):
+        return list(self.density_line) + list(self.app_line)
+
+    def get_optparam_groups(self, lr_init_spatialxyz=0.02, lr_init_network=0.001):
+        """tensoRF.py:350-356."""
+        groups = [{'params': self.density_line, 'lr': lr_init_spatialxyz},
+                  {'params': self.app_line, 'lr': lr_init_spatialxyz},
+                  {'params': self.basis_mat.parameters(), 'lr': lr_init_network}]
+        if isinstance(self.renderModule, nn.Module):
+            groups += [{'params': self.renderModule.parameters(), 'lr': lr_init_network}]
+        return groups
+
+    @torch.no_grad()
+    def upsample_volume_grid(self, res_target):
+        """tensoRF.py:418-435."""
+        res_target = [int(v) for v in res_target]
+        for lines in (self.density_line, self.app_line):
+            for i in range(3):
+                lines[i] = _channels_last_param(
+                    F.interpolate(lines[i].data, size=(res_target[self.vecMode[i]], 1), mode='bilinear', align_corners=True),
+                    lines[i].device)
+        self.update_stepSize(res_target)
+
+    @torch.no_grad()
+    def shrink(self, new_aabb):
+        """tensoRF.py:437-466."""
+        lo, hi = new_aabb
+        t_l = torch.round(torch.round((lo - self.aabb[0]) / self.units)).long()
+        b_r = torch.round((hi - self.aabb[0]) / self.units).long() + 1
+        b_r = torch.stack([b_r, self.gridSize]).amin(0)
+        for i in range(3):
+            v = self.vecMode[i]
+            for lines in (self.density_line, self.app_line):
+                lines[i] = _channels_last_param(lines[i].data[..., t_l[v]:b_r[v], :], lines[i].device)
+        new_aabb = TensorVMSplit._corrected_aabb(self, new_aabb, t_l, b_r)
+        size = b_r - t_l
+        self.aabb = new_aabb
+        self.update_stepSize((int(size[0]), int(size[1]), int(size[2])))

@@ -1,0 +1,171 @@
+/* fewtensorf.h — C ABI of the B200-native Few-TensoRF per-ray hot path.
+ *
+ * One shared library (fewtensorf_b200/libfewtensorf_b200.so), plain pointers and sizes only, no
+ * torch / ATen types.  Every pointer is a DEVICE pointer unless its comment says "host".
+ * All functions enqueue on the caller's stream and never synchronise, never throw, never exit();
+ * they return 0 on success or a negative FTRF_E_* code, with text from ftrf_last_error().
+ *
+ * What each entry point replaces in the reference (paths relative to the reference root;
+ * the reference has no FFI of its own, these are the torch call sites a maintainer re-points):
+ *   ftrf_forward            models/tensorBase.py:321-395  TensorBase.forward (whole call, no autograd)
+ *   ftrf_backward           train.py:374-376              autograd replay of that forward
+ *   ftrf_stage_march        models/tensorBase.py:178-208, :349-354, :41-48   sample_ray(+ndc) + alphaMask cull
+ *   ftrf_stage_density      models/tensoRF.py:207-227, :358-386; tensorBase.py:291-295, :361-365
+ *   ftrf_stage_integrate    models/tensorBase.py:21-28, :346, :368-370, :377, :386-390
+ *   ftrf_stage_appearance   models/tensoRF.py:230-263, :388-415  (+ basis_mat)
+ *   ftrf_stage_shade        models/mlp.py:8-19, :41-69, :88-107, :127-155; models/sh.py:87-112
+ *   ftrf_stage_composite    models/tensorBase.py:375-384
+ *   ftrf_mse_loss           train.py:338
+ *   ftrf_pack_alpha_mask    models/tensorBase.py:30-39   (AlphaGridMask volume -> bit field)
+ *   ftrf_density_at         models/tensorBase.py:298-318 compute_alpha's sigma (dense-lattice eval)
+ *
+ * Factor layout: CHANNEL-LAST.  A VM plane the reference holds as (1,C,H,W) is read as [H][W][C]
+ * (torch.channels_last memory of the same Parameter), a line (1,C,L,1) as [L][C].  C % 4 == 0.
+ */
+#ifndef FEWTENSORF_H
+#define FEWTENSORF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FTRF_ABI_VERSION 1
+
+enum { FTRF_MODEL_VM = 0, FTRF_MODEL_CP = 1 };
+enum { FTRF_SHADE_MLP_FEA = 0, FTRF_SHADE_MLP_PE = 1, FTRF_SHADE_MLP = 2, FTRF_SHADE_SH = 3 };
+enum { FTRF_ACT_SOFTPLUS = 0, FTRF_ACT_RELU = 1 };
+
+enum {
+  FTRF_OK = 0,
+  FTRF_E_ARG = -1,        /* bad argument / unsupported shape            */
+  FTRF_E_WORKSPACE = -2,  /* workspace buffer smaller than the layout    */
+  FTRF_E_CUDA = -3        /* a CUDA runtime call failed                  */
+};
+
+/* One decomposition (density or appearance): three planes (VM only) and three lines. */
+typedef struct FtrfFactorSet {
+  int32_t n_comp[3];        /* channels per plane/line k (CP: all equal)                    */
+  int32_t plane_w[3];       /* VM: gridSize[matMode[k][0]]                                   */
+  int32_t plane_h[3];       /* VM: gridSize[matMode[k][1]]                                   */
+  int32_t line_len[3];      /* gridSize[vecMode[k]]                                          */
+  const float* plane[3];    /* [H][W][C]   (NULL for CP)                                     */
+  const float* line[3];     /* [L][C]                                                        */
+  float* g_plane[3];        /* gradient accumulators, same layout (backward only, else NULL) */
+  float* g_line[3];
+  const float* mask[3];     /* FreeNeRF decomposition mask per k; NULL = none. CP reads [0]   */
+  int32_t mask_stride[3];   /* 0 = one scalar broadcast over channels, 1 = per-channel vector */
+} FtrfFactorSet;
+
+/* The field: hyper-parameters + borrowed parameter pointers.  Re-filled by the host every call
+ * (parameters are owned by the Python module and may be replaced between calls). */
+typedef struct FtrfField {
+  int32_t model;            /* FTRF_MODEL_*                                                  */
+  int32_t shading;          /* FTRF_SHADE_*                                                  */
+  int32_t act;              /* FTRF_ACT_*   (fea2denseAct)                                   */
+  int32_t app_dim;          /* data_dim_color (27)                                           */
+  int32_t feature_c;        /* MLP width (128)                                               */
+  int32_t pos_pe, view_pe, fea_pe;
+  int32_t in_dim;           /* MLP input width (mlp.py:31/:75/:113)                          */
+  float aabb[6];            /* min xyz, max xyz — fp32 values of the torch tensor            */
+  float inv_aabb[3];        /* 2/(max-min) as torch computed it (tensorBase.py:106)          */
+  float step_size;          /* tensorBase.py:109, the fp32 torch scalar                      */
+  float near_, far_;
+  float distance_scale, density_shift, weight_thres;
+  /* alphaMask (tensorBase.py:30-48); dims are X,Y,Z = volume.shape[-1],[-2],[-3] */
+  int32_t has_alpha_mask;
+  int32_t am_dim[3];
+  float am_aabb0[3];
+  float am_inv[3];          /* AlphaGridMask.invgridSize                                     */
+  const uint32_t* am_bits;  /* ftrf_pack_alpha_mask output                                   */
+  FtrfFactorSet den, app;
+  const float* basis;       /* basis_mat.weight [app_dim][sum n_comp]                        */
+  float* g_basis;
+  const float* w1; const float* b1;   /* renderModule.mlp.0  [feature_c][in_dim], [feature_c] */
+  const float* w2; const float* b2;   /* renderModule.mlp.2  [feature_c][feature_c]           */
+  const float* w3; const float* b3;   /* renderModule.mlp.4  [3][feature_c], [3]              */
+  float* g_w1; float* g_b1; float* g_w2; float* g_b2; float* g_w3; float* g_b3;
+  const float* enc_mask[3]; /* FreeNeRF encoding masks: pos, view, fea; NULL = none          */
+  int32_t enc_mask_len[3];  /* 1 = scalar broadcast, else 2*pe*channels                      */
+} FtrfField;
+
+/* One call on a ray chunk. */
+typedef struct FtrfCall {
+  int64_t n_rays;
+  int32_t ray_cols;         /* columns per ray row (>= 6); depth uses the LAST column (tensorBase.py:388) */
+  int32_t n_samples;        /* S                                                            */
+  int32_t is_train;         /* jitter present                                               */
+  int32_t ndc;              /* sample_ray_ndc path                                          */
+  int32_t add_bg;           /* white_bg or (is_train and coin), resolved by the host (:380) */
+  int32_t save_for_backward;/* keep activations in the workspace                            */
+  const float* rays;        /* [n_rays][ray_cols]                                           */
+  const float* jitter;      /* non-ndc train: [n_rays] U[0,1) (:201).  ndc: z table [S] (:181-183), always */
+  float* rgb_map;           /* out [n_rays][3]                                              */
+  float* depth_map;         /* out [n_rays]                                                 */
+  const float* g_rgb_map;   /* backward in: dL/d rgb_map [n_rays][3]                        */
+  int64_t cap_samples;      /* capacity of the packed valid-sample list                     */
+  int64_t cap_app;          /* capacity of the packed shaded-sample list                    */
+} FtrfCall;
+
+/* Workspace sections (offsets in bytes from the workspace base, filled by ftrf_workspace_layout). */
+enum {
+  FTRF_WS_COUNTERS = 0, /* int32[8]: [0] valid samples required, [1] shaded samples required,
+                                     [2] overflow flags (bit0 samples, bit1 shaded)          */
+  FTRF_WS_TMIN,         /* float[n_rays]                                                     */
+  FTRF_WS_RAY_OFF,      /* int32[n_rays]  first packed sample of the ray                     */
+  FTRF_WS_RAY_CNT,      /* int32[n_rays]                                                     */
+  FTRF_WS_ACC,          /* float[n_rays]  acc_map                                            */
+  FTRF_WS_RGB_PRE,      /* float[n_rays][3] rgb_map before clamp                             */
+  FTRF_WS_S_RAY,        /* int32[cap_samples] ray id                                         */
+  FTRF_WS_S_IDX,        /* int32[cap_samples] sample index i along the ray                   */
+  FTRF_WS_S_SIGMA,      /* float[cap_samples]                                                */
+  FTRF_WS_S_W,          /* float[cap_samples] weight                                         */
+  FTRF_WS_S_T,          /* float[cap_samples] transmittance before the sample                */
+  FTRF_WS_S_APP,        /* int32[cap_samples] shaded-list slot or -1                         */
+  FTRF_WS_S_GSIG,       /* float[cap_samples] dL/d sigma_feature (backward)                  */
+  FTRF_WS_A_SLOT,       /* int32[cap_app] packed-sample slot of the shaded sample            */
+  FTRF_WS_A_FEAT,       /* float[cap_app][app_dim]                                           */
+  FTRF_WS_A_RGB,        /* float[cap_app][3]                                                 */
+  FTRF_WS_A_H1,         /* float[cap_app][feature_c]  (save_for_backward)                    */
+  FTRF_WS_A_H2,         /* float[cap_app][feature_c]                                         */
+  FTRF_WS_A_GRGB,       /* float[cap_app][3]          backward                               */
+  FTRF_WS_A_GH1,        /* float[cap_app][feature_c]  backward                               */
+  FTRF_WS_A_GH2,        /* float[cap_app][feature_c]  backward                               */
+  FTRF_WS_A_GFEAT,      /* float[cap_app][app_dim]    backward                               */
+  FTRF_WS_COUNT
+};
+
+int ftrf_abi_version(void);
+const char* ftrf_last_error(void);          /* host string, thread-local */
+
+/* Returns total bytes; offsets_out (host, may be NULL) receives FTRF_WS_COUNT byte offsets. */
+size_t ftrf_workspace_layout(const FtrfField* field, const FtrfCall* call, int64_t* offsets_out);
+
+int ftrf_forward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
+int ftrf_backward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
+
+int ftrf_stage_march(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+int ftrf_stage_density(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+int ftrf_stage_integrate(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+int ftrf_stage_appearance(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+int ftrf_stage_shade(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+int ftrf_stage_composite(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
+
+/* loss_out[0] = mean((rgb-target)^2); g_rgb_out = d loss / d rgb (may be NULL). n = element count. */
+int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, float* loss_out, float* g_rgb_out,
+                  void* stream);
+
+/* volume: float (Z,Y,X) of {0,1}; bits: uint32[ftrf_alpha_mask_words(X,Y,Z)]. */
+size_t ftrf_alpha_mask_words(int32_t x, int32_t y, int32_t z);
+int ftrf_pack_alpha_mask(const float* volume, int32_t x, int32_t y, int32_t z, uint32_t* bits, void* stream);
+
+/* sigma_out[i] = feature2density(compute_densityfeature(normalize(xyz[i]))) for n world-space points,
+ * or 0 where the field's alphaMask rejects the point (tensorBase.py:298-313). */
+int ftrf_density_at(const FtrfField* field, const float* xyz, int64_t n, float* sigma_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEWTENSORF_H */

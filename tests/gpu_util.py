@@ -1,0 +1,63 @@
+"""Helpers for the `-m gpu` parity tests: build the product model from a golden fixture / oracle field."""
+import torch
+
+import fewtensorf_b200 as ft
+from oracle import field_oracle as O
+
+
+def args_from_cfg(cfg: O.FieldConfig):
+    return {'step_ratio': cfg.step_ratio, 'fea2denseAct': cfg.fea2dense, 'density_n_comp': list(cfg.density_n_comp),
+            'app_n_comp': list(cfg.app_n_comp), 'app_dim': cfg.app_dim, 'density_shift': cfg.density_shift,
+            'distance_scale': cfg.distance_scale, 'alphaMask_thres': cfg.alpha_mask_thres, 'shadingMode': cfg.shading,
+            'pos_pe': cfg.pos_pe, 'view_pe': cfg.view_pe, 'fea_pe': cfg.fea_pe, 'featureC': cfg.feature_c}
+
+
+def model_from_field(f: O.Field, device="cuda"):
+    """Product module holding exactly the oracle field's parameters / alphaMask."""
+    cfg = f.cfg
+    aabb = torch.tensor(cfg.aabb, dtype=torch.float32, device=device)
+    if cfg.model == "VM":
+        m = ft.TensorVMSplit(args_from_cfg(cfg), aabb, list(cfg.grid), list(cfg.near_far), device)
+    else:
+        m = ft.TensorCP(args_from_cfg(cfg), aabb, list(cfg.grid), device, near_far=list(cfg.near_far))
+    m.rayMarch_weight_thres = cfg.weight_thres
+    missing = m.load_state_dict({k: v for k, v in f.params.items()}, strict=True)
+    if f.alpha_mask is not None:
+        m.alphaMask = ft.AlphaGridMask(device, f.alpha_mask.aabb.to(device), f.alpha_mask.volume.to(device))
+    return m
+
+
+def pin_rng(model, jitter, coin, white_bg):
+    """Feed the model the exact RNG draws the reference / oracle consumed."""
+    def fixed(n_rays, S, is_train, ndc_ray, wb, device):
+        j = None
+        if ndc_ray:
+            near, far = model.near_far
+            z = torch.linspace(near, far, S).unsqueeze(0)
+            if is_train:
+                z = z + jitter * ((far - near) / S)
+            j = z.reshape(-1).to(device)
+        elif is_train:
+            j = jitter.reshape(-1).to(device)
+        return j, bool(wb or (is_train and coin))
+    model._draw_rng = fixed
+
+
+def dense_from_packed(model, st, n_rays, S):
+    """Scatter the packed per-sample sections of a finished call back to dense [N,S] tensors."""
+    V = st.n_samples
+    ray = model.workspace_section(st, "S_RAY", torch.int32, V).long().cpu()
+    idx = model.workspace_section(st, "S_IDX", torch.int32, V).long().cpu()
+    out = {"valid": torch.zeros(n_rays, S, dtype=torch.bool)}
+    out["valid"][ray, idx] = True
+    for name, key in (("S_SIGMA", "sigma"), ("S_W", "weight")):
+        d = torch.zeros(n_rays, S)
+        d[ray, idx] = model.workspace_section(st, name, torch.float32, V).cpu()
+        out[key] = d
+    app = model.workspace_section(st, "S_APP", torch.int32, V).cpu()
+    a = torch.zeros(n_rays, S, dtype=torch.bool)
+    a[ray, idx] = app >= 0
+    out["app"] = a
+    out["tmin"] = model.workspace_section(st, "TMIN", torch.float32, n_rays).cpu()
+    out["ray"], out["idx"] = ray, idx
+    return out
