@@ -105,8 +105,21 @@ def stage_capture(m, rays, mask, is_train, ndc, S, seed):
     return dict(z=z.contiguous(), valid=valid, sigma=sigma, weight=w, app=app, feat=feat)
 
 
-def run_case(name, kind, args, grid, n_rays, S, *, is_train, white_bg, ndc=False, mask=None,
-             mask_grid=None, sh=False, seed=7, near_far=(2.0, 6.0)):
+def run_case(name, kind, args, grid, n_rays, S, *, seed=7, **kw):
+    """Fixtures must not sit on the shading threshold: a sample whose weight is within fp32 noise of
+    rayMarch_weight_thres may be shaded by one implementation and not by another, which
+    moves rgb by ~1e-4 for reasons unrelated to kernel correctness.  Re-seed until the nearest weight
+    is at least 0.2 % away from the threshold."""
+    for attempt in range(50):
+        gap = _run_case(name, kind, args, grid, n_rays, S, seed=seed + 100 * attempt, **kw)
+        if gap > 2e-3:
+            return
+        print(f"  {name}: weight within {gap:.1e} of the threshold, re-seeding")
+    raise SystemExit(f"{name}: no seed without threshold straddlers")
+
+
+def _run_case(name, kind, args, grid, n_rays, S, *, is_train, white_bg, ndc=False, mask=None,
+              mask_grid=None, sh=False, seed=7, near_far=(2.0, 6.0)):
     m = build(kind, args, grid, seed, near_far)
     plant(m, kind, grid)
     if sh:   # SURVEY section 0.4: SH is wired by hand (mlp.py:15-19)
@@ -129,6 +142,10 @@ def run_case(name, kind, args, grid, n_rays, S, *, is_train, white_bg, ndc=False
     coin = bool(torch.rand((1,)) < 0.5) if (is_train and not white_bg) else False
 
     st = stage_capture(m, rays, mask, is_train, ndc, S, call_seed)
+    thres = m.rayMarch_weight_thres
+    gap = float(((st["weight"][st["valid"]] - thres).abs() / thres).min())
+    if gap <= 2e-3:
+        return gap
     torch.manual_seed(call_seed)
     for p in m.parameters():
         p.grad = None
@@ -169,7 +186,9 @@ def run_case(name, kind, args, grid, n_rays, S, *, is_train, white_bg, ndc=False
                 nSamples=int(m.nSamples))
     np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=np.array(repr(meta)),
                         **{k: (v.numpy() if torch.is_tensor(v) else v) for k, v in out.items()})
-    print(f"{name}: rgb mean {rgb.mean():.4f} n_valid {int(nv)} valid {int(st['valid'].sum())} loss {loss:.5f}")
+    print(f"{name}: seed {seed} rgb mean {rgb.mean():.4f} n_valid {int(nv)} valid {int(st['valid'].sum())} "
+          f"loss {loss:.5f} coin {coin} threshold gap {gap:.1e}")
+    return gap
 
 
 def main():
@@ -197,11 +216,11 @@ def main():
              is_train=True, white_bg=True, mask=sc_mask, seed=13)
     run_case("vm_sh_eval_mask", "VM", A("MLP_Fea", [8, 8, 8], [12, 12, 12], 27), (16, 16, 16), 64, -1,
              is_train=False, white_bg=True, sh=True, mask_grid=(16, 16, 16), seed=17)
-    run_case("cp_fea_train", "CP", A("MLP_Fea", [24], [48], 27), (18, 20, 16), 64, 56,
+    run_case("cp_fea_train", "CP", A("MLP_Fea", [24], [48], 27), (34, 36, 30), 64, 100,
              is_train=True, white_bg=True, mask_grid=(16, 16, 16), seed=19)
     cp_mask = {"encoding": {"pos": None, "view": None, "fea": torch.tensor(0.6)},
                "decomp": {"den": [fm(24)], "app": [fm(48)]}}
-    run_case("cp_fea_vecmask", "CP", A("MLP_Fea", [24], [48], 27), (16, 16, 16), 48, 40,
+    run_case("cp_fea_vecmask", "CP", A("MLP_Fea", [24], [48], 27), (32, 32, 32), 48, 90,
              is_train=True, white_bg=True, mask=cp_mask, seed=23)
     run_case("vm_fea_ndc_train", "VM", A("MLP_Fea", [8, 8, 8], [12, 12, 12], 27), (16, 16, 16), 48, 40,
              is_train=True, white_bg=False, ndc=True, seed=29, near_far=(0.0, 3.0))

@@ -55,7 +55,9 @@ def test_stage_values(case):
     flips = (d["app"] != ref_app)
     # only threshold straddlers may flip
     assert (g.t["st_weight"][flips] - 1e-4).abs().max().item() < 1e-7 if flips.any() else True
-    assert abs(int(nv) - int(g.t["n_valid"])) <= max(1, int(0.001 * int(g.t["n_valid"])))
+    n_flip = int(flips.sum())
+    assert n_flip <= max(4, int(0.001 * int(g.t["n_valid"]))), f"{n_flip} shading decisions differ"
+    assert abs(int(nv) - int(g.t["n_valid"])) <= n_flip
 
 
 @pytest.mark.parametrize("case", CASES)
@@ -71,7 +73,7 @@ def test_gradients_autograd(case):
     g, f, m, rgb, depth, nv = _run(case, grad=True)
     loss = torch.mean((rgb - g.target.cuda()) ** 2)
     loss.backward()
-    assert float(loss) == pytest.approx(float(g.t["loss"]), rel=1e-5)
+    assert float(loss.detach()) == pytest.approx(float(g.t["loss"]), rel=1e-5)
     got = {k: p.grad for k, p in m.named_parameters()}
     for k, ref in g.grads.items():
         assert got[k] is not None, k
@@ -88,6 +90,6 @@ def test_train_step_matches_autograd(case):
     pin_rng(m, g.jitter, g.coin, g.meta["white_bg"])
     loss, nv = m.train_step(g.rays.cuda(), g.target.cuda(), g.mask(), white_bg=g.meta["white_bg"],
                             N_samples=g.meta["S"])
-    assert float(loss) == pytest.approx(float(g.t["loss"]), rel=1e-5)
+    assert float(loss.detach()) == pytest.approx(float(g.t["loss"]), rel=1e-5)
     for k, p in m.named_parameters():
         assert rel_inf(p.grad.cpu(), g.grads[k]) < TOL, k
