@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""Benchmark of the Few-TensoRF per-ray hot path on B200 (BASELINE.json metric: training rays/sec, fwd+bwd).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" = one training pass of the hot path over one ray batch: march/cull -> density gather ->
+integrate -> appearance gather -> MLP_Fea shading -> composite, MSE loss (train.py:338), backward of all
+of it into a freshly zeroed gradient buffer (excluding optimiser and regularisers), plus
+the NCCL all-reduce of the flat gradient buffer when N > 1.  Workload: TensorVMSplit lego shape at
+N_voxel_final 300^3 (16/48 components, app_dim 27, MLP_Fea 150->128->128->3), S = 1039 samples per ray,
+alphaMask 256^3 built by the product's own updateAlphaMask, planted-box density, 4096
+synthetic rays per GPU.  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GRID = 300
+MASK_GRID = 256
+RAYS_PER_GPU = 4096
+N_SAMPLES = 1039          # int(norm([300]*3) / 0.5), utils.py:124-125 / train.py:208
+CPU_SAMPLE_RAYS = 2048    # bounded CPU sample (same workload, first rays of the batch)
+
+ARGS = {'step_ratio': 0.5, 'fea2denseAct': 'softplus', 'density_n_comp': [16, 16, 16], 'app_n_comp': [48, 48, 48],
+        'app_dim': 27, 'density_shift': -10.0, 'distance_scale': 25.0, 'alphaMask_thres': 0.001,
+        'shadingMode': 'MLP_Fea', 'pos_pe': 2, 'view_pe': 2, 'fea_pe': 2, 'featureC': 128}
+
+
+def synthetic_rays(n, seed):
+    """origins on a radius-4 sphere aimed at random points of the unit cube."""
+    g = torch.Generator().manual_seed(seed)
+    o = torch.randn(n, 3, generator=g)
+    o = 4.0 * o / o.norm(dim=-1, keepdim=True)
+    tgt = (torch.rand(n, 3, generator=g) - 0.5) * 2
+    d = tgt - o
+    d = d / d.norm(dim=-1, keepdim=True)
+    return torch.cat([o, d], -1), torch.rand(n, 3, generator=g)
+
+
+def build_model(device, grid=GRID, mask_grid=MASK_GRID):
+    import fewtensorf_b200 as ft
+    torch.manual_seed(20211202)                       # train.py:550
+    aabb = torch.tensor([[-1.5] * 3, [1.5] * 3], device=device)
+    m = ft.TensorVMSplit(ARGS, aabb, [grid] * 3, [2.0, 6.0], device)
+    with torch.no_grad():                             # planted box, SURVEY section 8(d)
+        ind = (torch.linspace(-1.5, 1.5, grid).abs() < 0.6).float().to(device)
+        m.density_plane[0][0, 0] = 11.0 * ind[:, None] * ind[None, :]
+        m.density_line[0][0, 0, :, 0] = ind
+    if mask_grid:
+        m.updateAlphaMask((mask_grid,) * 3)
+    return m
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": int(self.rows[0][1]) if self.rows and self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------ CPU leg
+def cpu_field(model=None):
+    """Oracle field (CPU restatement of the reference path) holding the benchmark workload.
+    With a product model: the very same parameters and alphaMask.  Without (--impl reference):
+    built on the host with the oracle's own initialiser, mask from the oracle's updateAlphaMask."""
+    from oracle import field_oracle as O
+    cfg = O.FieldConfig(model="VM", shading="MLP_Fea", grid=(GRID,) * 3)
+    if model is not None:
+        params = {k: v.detach().cpu().contiguous() for k, v in model.state_dict().items()}
+        f = O.Field(cfg, params)
+        am = model.alphaMask
+        if am is not None:
+            f.alpha_mask = O.AlphaMask(am.alpha_volume[0, 0].detach().cpu().float(), am.aabb.detach().cpu())
+        return f
+    params = O.init_params(cfg, seed=20211202)
+    O.plant_box(cfg, params)
+    f = O.Field(cfg, params)
+    O.build_alpha_mask(f, (MASK_GRID,) * 3)
+    return f
+
+
+def cpu_leg(field, rays, target, steps, warmup):
+    """rays/s of the oracle's forward + MSE + backward on a bounded sample, all host threads."""
+    from oracle import field_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    n = rays.shape[0]
+    times = []
+    for it in range(warmup + steps):
+        torch.manual_seed(1 + it)
+        jitter = torch.rand(n, 1)
+        t0 = time.perf_counter()
+        O.loss_and_grads(field, rays, target, is_train=True, white_bg=True, n_samples=N_SAMPLES, jitter=jitter)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    total = sum(times)
+    return n * len(times) / total, total / len(times)
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU implementation of the path (oracle port; the reference
+    itself is not on the GPU box) on the box's host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rays, target = synthetic_rays(RAYS_PER_GPU, seed=0)
+    rays, target = rays[:CPU_SAMPLE_RAYS], target[:CPU_SAMPLE_RAYS]
+    f = cpu_field(None)
+    rps, sec = cpu_leg(f, rays, target, args.steps, max(1, min(args.warmup, 2)))
+    cores = os.cpu_count() or 1
+    sample = f"first {CPU_SAMPLE_RAYS} of the 4096 rays per step, S={N_SAMPLES}, same factors shape / mask recipe"
+    print(json.dumps({
+        "impl": "reference", "metric": "training rays/sec (fwd+bwd)", "value": rps, "unit": "rays/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": rps, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rps, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(n_gpus):
+    return {"workload": f"TensorVMSplit lego shape, N_voxel {GRID}^3, n_lamb 16/48, MLP_Fea, alphaMask {MASK_GRID}^3, "
+                        f"planted-box density, {RAYS_PER_GPU} rays/GPU x S={N_SAMPLES}, fwd+MSE+bwd"
+                        + (" + NCCL all-reduce of the flat gradient buffer" if n_gpus > 1 else ""),
+            "rays_per_gpu": RAYS_PER_GPU, "n_samples": N_SAMPLES, "grid": GRID, "mask_grid": MASK_GRID,
+            "l2": "flushed between timed steps (512 MiB write)", "parallelism": f"ray-sharded x{n_gpus}"}
+
+
+# ------------------------------------------------------------------------------------------ GPU leg
+ALGO = {   # algorithmic work per unit (DESIGN.md / SURVEY section 8d): (unit, amount, bound)
+    "march": ("cand", 0.0, "hbm"),
+    "density_fwd": ("vd", 1152.0, "hbm"), "density_bwd": ("vd", 2304.0, "hbm"),
+    "integrate_fwd": ("vd", 12.0, "hbm"), "integrate_bwd": ("vd", 24.0, "hbm"), "composite": ("vd", 8.0, "hbm"),
+    "app_fwd": ("va", 3456.0, "hbm"), "app_bwd": ("va", 6912.0, "hbm"),
+    "shade_fwd": ("va", 71936.0, "tensor"), "shade_bwd_hidden": ("va", 2.0 * (128 * 128 + 3 * 128) * 1.0 + 2 * 3 * 128, "tensor"),
+    "shade_bwd_input": ("va", 2.0 * 150 * 128, "tensor"), "shade_wgrad2": ("va", 2.0 * 128 * 128, "tensor"),
+    "shade_wgrad1": ("va", 2.0 * 150 * 128, "tensor"),
+}
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            p = json.load(fh)
+        return {"hbm": float(p["hbm_gbs"]), "tensor": float(p["bf16_tflops"]), "src": "measured (MEASURED_PEAKS.json, burst)"}
+    except Exception:
+        return {"hbm": 6650.0, "tensor": 1590.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+def run_gpu(args):
+    import torch.distributed as dist
+    import fewtensorf_b200 as ft
+    from fewtensorf_b200._abi import PROF_STAGES, lib
+    import ctypes as C
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    model = build_model(dev)
+    rays_h, target_h = synthetic_rays(RAYS_PER_GPU, seed=rank)
+    rays, target = rays_h.to(dev), target_h.to(dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    torch.manual_seed(1 + rank)
+    inv_world = 1.0 / world
+
+    def step():
+        loss, nv = model.train_step(rays, target, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
+        if world > 1:
+            dist.all_reduce(model._gradbuf)
+        return loss, nv
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    def timed(k, profile):
+        lib.ftrf_profile_enable(1 if profile else 0)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+        stage = [0.0] * PROF_STAGES
+        buf = (C.c_float * PROF_STAGES)()
+        last = None
+        barrier()
+        for i in range(k):
+            flush.zero_()                       # evict L2 between timed steps (untimed)
+            ev[i][0].record()
+            last = step()
+            ev[i][1].record()
+            if profile:
+                torch.cuda.synchronize()
+                lib.ftrf_profile_read(buf)
+                for s in range(PROF_STAGES):
+                    stage[s] += max(buf[s], 0.0) / k
+        barrier()
+        lib.ftrf_profile_enable(0)
+        return sum(a.elapsed_time(b) for a, b in ev), stage, last
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    total_ms, _, last = timed(args.steps, False)
+    clocks = sampler.summary()
+    _, stage_ms, _ = timed(min(args.steps, 20), True)
+    t = torch.tensor([total_ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t)
+    st = model._last_call
+    vd, va = st.n_samples, st.n_valid
+
+    # ---- end to end through the drop-in API: host rays -> renderer -> torch loss -> autograd -> loss.item()
+    rays_p, target_p = rays_h.pin_memory(), target_h.pin_memory()
+    def e2e_step():
+        r = rays_p.to(dev, non_blocking=True)
+        tg = target_p.to(dev, non_blocking=True)
+        for p in model.parameters():
+            p.grad = None
+        rgb, _, depth, _, _, nvs = ft.OctreeRender_trilinear_fast(r, model, None, chunk=RAYS_PER_GPU, N_samples=N_SAMPLES,
+                                                                  white_bg=True, is_train=True, device=dev)
+        loss = torch.mean((rgb - tg) ** 2)
+        loss.backward()
+        if world > 1:
+            dist.all_reduce(model._gradbuf)
+        return loss.item()
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_rps = RAYS_PER_GPU * world * args.steps / float(e2e_s)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = load_peaks()
+    units = {"vd": vd, "va": va, "cand": RAYS_PER_GPU * N_SAMPLES}
+    names = [lib.ftrf_profile_stage_name(i).decode() for i in range(PROF_STAGES)]
+    stages = {}
+    for n_, ms in zip(names, stage_ms):
+        unit, amt, bound = ALGO[n_]
+        work = units[unit] * amt
+        ach = (work / (ms * 1e-3) / (1e9 if bound == "hbm" else 1e12)) if ms > 0 else 0.0
+        stages[n_] = {"ms": round(ms, 5), "bound": bound, "achieved": round(ach, 3),
+                      "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": round(ach / peaks[bound], 5)}
+    top = max(stages, key=lambda k: stages[k]["ms"])
+    roof = {"kernel": top, "bound": stages[top]["bound"], "achieved": stages[top]["achieved"], "peak": peaks[stages[top]["bound"]],
+            "unit": stages[top]["unit"], "frac": stages[top]["frac"], "traffic": None, "peak_source": peaks["src"],
+            "ms_per_launch": stages[top]["ms"]}
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        f = cpu_field(model)
+        rps, sec = cpu_leg(f, rays_h[:CPU_SAMPLE_RAYS], target_h[:CPU_SAMPLE_RAYS], 5, 1)
+        cpu = {"value": rps, "unit": "rays/s", "cores": os.cpu_count() or 1, "kind": "port",
+               "sample": f"first {CPU_SAMPLE_RAYS} of the 4096 rays, same factors and alphaMask, 5 steps after 1 warm-up"}
+    ms_step = total_ms / args.steps
+    out = {"metric": "training rays/sec (fwd+bwd)", "value": RAYS_PER_GPU * world / (ms_step * 1e-3), "unit": "rays/s",
+           "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": workload_config(world), "clocks": clocks,
+           "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32},
+           "gpu_launches": 14 * args.steps, "roofline": roof, "stages": stages,
+           "samples": {"valid_per_step": vd, "shaded_per_step": va, "loss": float(last[0])}}
+    if cpu:
+        out["cpu_baseline"] = cpu
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps > 10:
+            args.steps = 10            # bounded: each step is ~1-3 s of host work
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

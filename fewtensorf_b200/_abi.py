@@ -71,8 +71,10 @@ EXPORTS = [
     "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
-    "ftrf_pack_alpha_mask", "ftrf_density_at",
+    "ftrf_pack_alpha_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
+    "ftrf_profile_stage_name",
 ]
+PROF_STAGES = 13
 
 
 def _load():
@@ -102,6 +104,12 @@ def _load():
     lib.ftrf_pack_alpha_mask.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_density_at.restype = C.c_int
     lib.ftrf_density_at.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.ftrf_profile_enable.restype = C.c_int
+    lib.ftrf_profile_enable.argtypes = [C.c_int]
+    lib.ftrf_profile_read.restype = C.c_int
+    lib.ftrf_profile_read.argtypes = [C.POINTER(C.c_float)]
+    lib.ftrf_profile_stage_name.restype = C.c_char_p
+    lib.ftrf_profile_stage_name.argtypes = [C.c_int]
     if lib.ftrf_abi_version() != 1:
         raise ImportError("libfewtensorf_b200.so ABI version mismatch")
     return lib

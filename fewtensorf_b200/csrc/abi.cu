@@ -26,6 +26,21 @@ int check_launch(const char* what) {
   return FTRF_OK;
 }
 
+// ---- optional per-stage timing --------------------------------------------------------------
+static const char* kStageNames[FTRF_PROF_STAGES] = {
+    "march", "density_fwd", "integrate_fwd", "app_fwd", "shade_fwd", "composite",
+    "integrate_bwd", "shade_bwd_hidden", "shade_bwd_input", "shade_wgrad2", "shade_wgrad1", "app_bwd", "density_bwd"};
+static bool g_prof_on = false;
+static cudaEvent_t g_ev[FTRF_PROF_STAGES][2];
+static bool g_ev_made = false, g_ev_used[FTRF_PROF_STAGES];
+
+void prof_begin(int stage, cudaStream_t st) {
+  if (g_prof_on) cudaEventRecord(g_ev[stage][0], st);
+}
+void prof_end(int stage, cudaStream_t st) {
+  if (g_prof_on) { cudaEventRecord(g_ev[stage][1], st); g_ev_used[stage] = true; }
+}
+
 static inline size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
 
 size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws* ws) {
@@ -148,6 +163,33 @@ __global__ void mse_kernel(const float* __restrict__ rgb, const float* __restric
 
 using namespace ftrf;
 
+extern "C" int ftrf_profile_enable(int on) {
+  if (on && !g_ev_made) {
+    for (int i = 0; i < FTRF_PROF_STAGES; ++i)
+      for (int j = 0; j < 2; ++j)
+        if (cudaEventCreate(&g_ev[i][j]) != cudaSuccess) return check_launch("profile event");
+    g_ev_made = true;
+  }
+  for (int i = 0; i < FTRF_PROF_STAGES; ++i) g_ev_used[i] = false;
+  g_prof_on = on != 0;
+  return FTRF_OK;
+}
+extern "C" int ftrf_profile_read(float* ms_out) {
+  if (!ms_out) { set_error("profile_read: null"); return FTRF_E_ARG; }
+  for (int i = 0; i < FTRF_PROF_STAGES; ++i) {
+    ms_out[i] = -1.f;
+    if (g_ev_made && g_ev_used[i]) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, g_ev[i][0], g_ev[i][1]) == cudaSuccess) ms_out[i] = ms;
+      else cudaGetLastError();
+    }
+  }
+  return FTRF_OK;
+}
+extern "C" const char* ftrf_profile_stage_name(int stage) {
+  return (stage >= 0 && stage < FTRF_PROF_STAGES) ? kStageNames[stage] : "";
+}
+
 extern "C" int ftrf_abi_version(void) { return FTRF_ABI_VERSION; }
 extern "C" const char* ftrf_last_error(void) { return g_err; }
 
@@ -179,22 +221,36 @@ extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, si
   Ws ws;
   if (int e = check_args(f, c, wsb, ws_bytes, false, &ws)) return e;
   cudaStream_t st = (cudaStream_t)stream;
+  prof_begin(0, st);
   if (int e = march_with_reset(*f, *c, ws, st)) return e;
+  prof_end(0, st); prof_begin(1, st);
   if (int e = launch_density(*f, *c, ws, st)) return e;
+  prof_end(1, st); prof_begin(2, st);
   if (int e = launch_integrate(*f, *c, ws, st)) return e;
+  prof_end(2, st); prof_begin(3, st);
   if (int e = launch_appearance(*f, *c, ws, st)) return e;
+  prof_end(3, st); prof_begin(4, st);
   if (int e = launch_shade(*f, *c, ws, st)) return e;
-  return launch_composite(*f, *c, ws, st);
+  prof_end(4, st); prof_begin(5, st);
+  int e = launch_composite(*f, *c, ws, st);
+  prof_end(5, st);
+  return e;
 }
 
 extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
   Ws ws;
   if (int e = check_args(f, c, wsb, ws_bytes, true, &ws)) return e;
   cudaStream_t st = (cudaStream_t)stream;
+  prof_begin(6, st);
   if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
-  if (int e = launch_shade_bwd(*f, *c, ws, st)) return e;
+  prof_end(6, st);
+  if (int e = launch_shade_bwd(*f, *c, ws, st)) return e;     // stages 7-10 marked inside
+  prof_begin(11, st);
   if (int e = launch_appearance_bwd(*f, *c, ws, st)) return e;
-  return launch_density_bwd(*f, *c, ws, st);
+  prof_end(11, st); prof_begin(12, st);
+  int e = launch_density_bwd(*f, *c, ws, st);
+  prof_end(12, st);
+  return e;
 }
 
 extern "C" int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, float* loss_out, float* g_rgb_out,

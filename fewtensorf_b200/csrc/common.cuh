@@ -41,6 +41,8 @@ struct Ws {
 size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws* ws);
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+void prof_begin(int stage, cudaStream_t st);   // no-ops unless ftrf_profile_enable(1)
+void prof_end(int stage, cudaStream_t st);
 
 // launchers (one per stage; defined in the k_*.cu files)
 int launch_march(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);

@@ -287,14 +287,20 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   cudaFuncSetAttribute(shade_bwd_input_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_i);
   cudaFuncSetAttribute(shade_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_w1);
   cudaFuncSetAttribute(shade_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_w2);
+  prof_begin(7, st);
   shade_bwd_hidden_kernel<<<FTRF_SMS, 256, sm_h, st>>>(f, c, ws);
   if (int e = check_launch("shade_bwd_hidden")) return e;
+  prof_end(7, st); prof_begin(8, st);
   shade_bwd_input_kernel<<<FTRF_SMS, 256, sm_i, st>>>(f, c, ws, sp);
   if (int e = check_launch("shade_bwd_input")) return e;
+  prof_end(8, st); prof_begin(9, st);
   shade_wgrad_kernel<2><<<FTRF_SMS, 256, sm_w2, st>>>(f, c, ws, sp);
   if (int e = check_launch("shade_wgrad2")) return e;
+  prof_end(9, st); prof_begin(10, st);
   shade_wgrad_kernel<1><<<FTRF_SMS, 256, sm_w1, st>>>(f, c, ws, sp);
-  return check_launch("shade_wgrad1");
+  int e = check_launch("shade_wgrad1");
+  prof_end(10, st);
+  return e;
 }
 
 }  // namespace ftrf

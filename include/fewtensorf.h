@@ -165,6 +165,15 @@ int ftrf_pack_alpha_mask(const float* volume, int32_t x, int32_t y, int32_t z, u
  * or 0 where the field's alphaMask rejects the point (tensorBase.py:298-313). */
 int ftrf_density_at(const FtrfField* field, const float* xyz, int64_t n, float* sigma_out, void* stream);
 
+/* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
+ * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.
+ * ftrf_profile_read must be called after the stream has been synchronised; ms_out receives
+ * FTRF_PROF_STAGES durations in milliseconds (-1 for a stage that did not run since enabling). */
+#define FTRF_PROF_STAGES 13
+int ftrf_profile_enable(int on);
+int ftrf_profile_read(float* ms_out /* host */);
+const char* ftrf_profile_stage_name(int stage);
+
 #ifdef __cplusplus
 }
 #endif
