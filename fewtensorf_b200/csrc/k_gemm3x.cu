@@ -1,0 +1,207 @@
+// k_gemm3x.cu — the dense contraction of the shading MLP on the 5th-gen tensor cores.
+//   out[M][N] = epilogue( A[M][K] * B[N][K]^T )        fp32 in, fp32 out
+// computed as 3xTF32: A = Ah + Al, B = Bh + Bl (tf32 pairs), D = Ah*Bh + Ah*Bl + Al*Bh accumulated in
+// fp32 in TMEM by tcgen05.mma.kind::tf32 — ~2^-21 relative per product, i.e. fp32-grade, which is what
+// the 1e-4 parity budget on rgb / gradients needs (plain TF32 is ~1e-3).
+//
+// Persistent CTAs (one per SM).  B (the layer's weight matrix, <= 160 x 152) is split once per CTA
+// into hi/lo and stays resident in shared memory in the UMMA canonical K-major no-swizzle layout;
+// A streams through in 128-row x 32-column chunks: all threads LDG -> split -> STS (double buffered),
+// one elected thread issues the MMAs asynchronously, tcgen05.commit releases the chunk buffer through
+// an mbarrier, and after the last chunk the accumulator tile is read back with tcgen05.ld for the
+// fused epilogue (bias, ReLU, ReLU-mask of a saved activation).
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace ftrf {
+
+struct Gemm3xArgs {
+  const float* A; int lda; int ka;       // A[m][k], k < ka valid (ka % 4 == 0), others read as 0
+  const int32_t* count; int64_t cap;     // M = count ? min(*count, cap) : cap
+  const float* B; int64_t sn, sk;        // B element (n,k) at B[n*sn + k*sk]
+  int N, K;
+  const float* bias;                     // [N] or null
+  const float* mask; int ldm;            // out = mask[m][n] > 0 ? acc : 0   (ReLU backward) or null
+  int relu;                              // out = max(acc, 0)
+  float* out; int ldo;
+  int variant;                           // debug: bit0 swaps the LBO/SBO roles
+};
+
+constexpr int G_KC = 32;                 // K columns per streamed A chunk
+constexpr int G_TM = 128;                // rows per tile (UMMA M)
+constexpr int G_ABUF = G_TM * G_KC;      // floats per hi (or lo) chunk buffer
+
+__host__ __device__ inline int g_np(int N) { return (N + 15) & ~15; }
+__host__ __device__ inline int g_kp(int K) { return (K + 7) & ~7; }
+
+// canonical K-major no-swizzle position (in floats) of element (row, k) in a tile with `ku_total`
+// 16-byte units along K: units are ordered (row/8, ku, row%8).
+__device__ __forceinline__ int canon_off(int row, int ku, int ku_total) {
+  return (((row >> 3) * ku_total + ku) * 8 + (row & 7)) * 4;
+}
+
+__global__ void __launch_bounds__(256, 1)
+gemm3x_kernel(const Gemm3xArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const int Np = g_np(a.N), Kp = g_kp(a.K), KUB = Kp / 4;
+  float* Bhi = reinterpret_cast<float*>(smem_raw);
+  float* Blo = Bhi + (size_t)Np * Kp;
+  float* Abuf = Blo + (size_t)Np * Kp;                       // [2 buffers][hi, lo][G_ABUF]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Abuf + 4 * G_ABUF);
+  uint64_t* bar_free = bars;                                  // [2]
+  uint64_t* bar_acc = bars + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t M = a.count ? min((int64_t)*a.count, a.cap) : a.cap;
+  if ((int64_t)blockIdx.x * G_TM >= M) return;
+
+  if (tid == 0) {
+    tc::mbar_init(bar_free + 0, 1);
+    tc::mbar_init(bar_free + 1, 1);
+    tc::mbar_init(bar_acc, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  // resident B: split into hi / lo, canonical layout
+  for (int e = tid; e < Np * KUB; e += blockDim.x) {
+    int n = e % Np, ku = e / Np;
+    float hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int k = ku * 4 + j;
+      float v = (n < a.N && k < a.K) ? __ldg(a.B + (int64_t)n * a.sn + (int64_t)k * a.sk) : 0.f;
+      tc::split_tf32(v, hi[j], lo[j]);
+    }
+    int off = canon_off(n, ku, KUB);
+    *reinterpret_cast<float4*>(Bhi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<float4*>(Blo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  const bool swap = a.variant & 1;
+  const uint32_t a_lbo = 128, a_sbo = (G_KC / 4) * 128, b_lbo = 128, b_sbo = (uint32_t)KUB * 128;
+  const uint32_t idesc = tc::idesc_tf32(G_TM, Np);
+  const int nchunks = (Kp + G_KC - 1) / G_KC;
+  uint32_t it = 0, tcount = 0;
+
+  for (int64_t m0 = (int64_t)blockIdx.x * G_TM; m0 < M; m0 += (int64_t)gridDim.x * G_TM, ++tcount) {
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const int buf = it & 1;
+      float* Ahi = Abuf + buf * 2 * G_ABUF;
+      float* Alo = Ahi + G_ABUF;
+      // ---- stream one A chunk: LDG (8 rows x 64 B per warp item), split, STS
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int id = warp * 4 + j;
+        int r = (id >> 1) * 8 + (lane & 7), ku = (id & 1) * 4 + (lane >> 3);
+        int64_t row = m0 + r;
+        int col = c * G_KC + ku * 4;
+        v[j] = (row < M && col < a.ka) ? ld4(a.A + row * a.lda + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      if (it >= 2) tc::mbar_wait(bar_free + buf, ((it >> 1) - 1) & 1);   // MMAs that read this buffer are done
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int id = warp * 4 + j;
+        int r = (id >> 1) * 8 + (lane & 7), ku = (id & 1) * 4 + (lane >> 3);
+        float4 h, l;
+        tc::split_tf32(v[j].x, h.x, l.x); tc::split_tf32(v[j].y, h.y, l.y);
+        tc::split_tf32(v[j].z, h.z, l.z); tc::split_tf32(v[j].w, h.w, l.w);
+        int off = canon_off(r, ku, G_KC / 4);
+        *reinterpret_cast<float4*>(Ahi + off) = h;
+        *reinterpret_cast<float4*>(Alo + off) = l;
+      }
+      tc::fence_async_smem();
+      __syncthreads();
+      // ---- one thread issues this chunk's MMAs (async); commit frees the buffer
+      if (tid == 0) {
+        tc::fence_after_sync();
+        const int ksteps = min(G_KC, Kp - c * G_KC) / 8;
+        const uint32_t ah = tc::smem_u32(Ahi), al = tc::smem_u32(Alo);
+        const uint32_t bh = tc::smem_u32(Bhi) + (uint32_t)(c * (G_KC / 4)) * 128;
+        const uint32_t bl = tc::smem_u32(Blo) + (uint32_t)(c * (G_KC / 4)) * 128;
+        for (int s = 0; s < ksteps; ++s) {
+          uint32_t ko = s * 256;      // 8 tf32 = two 16-byte units along K
+          uint64_t dah = swap ? tc::smem_desc(ah + ko, a_sbo, a_lbo) : tc::smem_desc(ah + ko, a_lbo, a_sbo);
+          uint64_t dal = swap ? tc::smem_desc(al + ko, a_sbo, a_lbo) : tc::smem_desc(al + ko, a_lbo, a_sbo);
+          uint64_t dbh = swap ? tc::smem_desc(bh + ko, b_sbo, b_lbo) : tc::smem_desc(bh + ko, b_lbo, b_sbo);
+          uint64_t dbl = swap ? tc::smem_desc(bl + ko, b_sbo, b_lbo) : tc::smem_desc(bl + ko, b_lbo, b_sbo);
+          tc::mma_tf32_ss(tmem, dal, dbh, idesc, (c | s) != 0);
+          tc::mma_tf32_ss(tmem, dah, dbl, idesc, true);
+          tc::mma_tf32_ss(tmem, dah, dbh, idesc, true);
+        }
+        tc::mma_commit(bar_free + buf);
+        if (c == nchunks - 1) tc::mma_commit(bar_acc);
+      }
+    }
+    // ---- epilogue: TMEM -> registers -> global
+    tc::mbar_wait(bar_acc, tcount & 1);
+    tc::fence_after_sync();
+    {
+      const int q = warp & 3;
+      const int64_t row = m0 + q * 32 + lane;
+      for (int cc = warp >> 2; cc * 32 < Np; cc += 2) {
+        float acc[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), acc);
+        tc::tmem_wait_ld();
+        if (row < M) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            int col = cc * 32 + j;
+            if (col >= a.N) break;
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float x = acc[j + e];
+              if (a.bias && col + e < a.N) x += __ldg(a.bias + col + e);
+              if (a.relu) x = fmaxf(x, 0.f);
+              if (a.mask && col + e < a.N && !(__ldg(a.mask + row * a.ldm + col + e) > 0.f)) x = 0.f;
+              o[e] = x;
+            }
+            float* dst = a.out + row * a.ldo + col;
+            if (col + 3 < a.N && (a.ldo & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+            else
+              for (int e = 0; e < 4 && col + e < a.N; ++e) dst[e] = o[e];
+          }
+        }
+      }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+  }
+  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+}
+
+size_t gemm3x_smem(int N, int K) {
+  return (size_t)2 * g_np(N) * g_kp(K) * 4 + (size_t)4 * G_ABUF * 4 + 64;
+}
+
+int launch_gemm3x(const Gemm3xArgs& a, cudaStream_t st) {
+  if (a.N < 1 || a.N > 256 || a.K < 1 || (a.ka & 3) || (a.lda & 3) || a.cap < 0) { set_error("gemm3x: bad shape N=%d K=%d ka=%d lda=%d", a.N, a.K, a.ka, a.lda); return FTRF_E_ARG; }
+  size_t smem = gemm3x_smem(a.N, a.K);
+  if (smem > 227 * 1024) { set_error("gemm3x: N=%d K=%d needs %zu B of shared memory", a.N, a.K, smem); return FTRF_E_ARG; }
+  if (a.cap == 0) return FTRF_OK;
+  cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int64_t tiles = (a.cap + G_TM - 1) / G_TM;
+  int grid = (int)(tiles < FTRF_SMS ? tiles : FTRF_SMS);
+  gemm3x_kernel<<<grid, 256, smem, st>>>(a);
+  return check_launch("gemm3x");
+}
+
+}  // namespace ftrf
+
+// test / bring-up entry (declared in include/fewtensorf.h)
+extern "C" int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B, int64_t sn, int64_t sk, int N,
+                                int K, const float* bias, const float* mask, int ldm, int relu, float* out, int ldo,
+                                int variant, void* stream) {
+  ftrf::Gemm3xArgs a{};
+  a.A = A; a.lda = lda; a.ka = ka; a.count = nullptr; a.cap = M;
+  a.B = B; a.sn = sn; a.sk = sk; a.N = N; a.K = K;
+  a.bias = bias; a.mask = mask; a.ldm = ldm; a.relu = relu; a.out = out; a.ldo = ldo; a.variant = variant;
+  return ftrf::launch_gemm3x(a, (cudaStream_t)stream);
+}

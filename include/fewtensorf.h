@@ -165,6 +165,13 @@ int ftrf_pack_alpha_mask(const float* volume, int32_t x, int32_t y, int32_t z, u
  * or 0 where the field's alphaMask rejects the point (tensorBase.py:298-313). */
 int ftrf_density_at(const FtrfField* field, const float* xyz, int64_t n, float* sigma_out, void* stream);
 
+/* Bring-up / unit-test entry of the tensor-core contraction used by the shading MLP (tcgen05.mma
+ * kind::tf32, 3xTF32 split): out[M][N] = epi(A[M][K] * B^T), B element (n,k) at B[n*sn + k*sk].
+ * epi: + bias[n] (or NULL), ReLU if relu != 0, zero where mask[m*ldm+n] <= 0 (or NULL). */
+int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B, int64_t sn, int64_t sk, int N, int K,
+                     const float* bias, const float* mask, int ldm, int relu, float* out, int ldo, int variant,
+                     void* stream);
+
 /* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
  * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.
  * ftrf_profile_read must be called after the stream has been synchronised; ms_out receives
