@@ -17,7 +17,7 @@ ACT_SOFTPLUS, ACT_RELU = 0, 1
 SHADING_KINDS = {"MLP_Fea": SHADE_MLP_FEA, "MLP_PE": SHADE_MLP_PE, "MLP": SHADE_MLP, "SH": SHADE_SH}
 
 WS_NAMES = ["COUNTERS", "TMIN", "RAY_OFF", "RAY_CNT", "ACC", "RGB_PRE", "S_RAY", "S_IDX", "S_SIGMA", "S_W", "S_T",
-            "S_APP", "S_GSIG", "A_SLOT", "A_FEAT", "A_RGB", "A_H1", "A_H2", "A_GRGB", "A_GH1", "A_GH2", "A_GFEAT"]
+            "S_APP", "S_GSIG", "A_SLOT", "A_FEAT", "A_RGB", "A_H1", "A_H2", "A_GRGB", "A_GH1", "A_GH2", "A_GFEAT", "A_X", "A_GX"]
 WS_COUNT = len(WS_NAMES)
 WS = {n: i for i, n in enumerate(WS_NAMES)}
 
@@ -72,7 +72,7 @@ EXPORTS = [
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
-    "ftrf_profile_stage_name", "ftrf_test_gemm3x",
+    "ftrf_profile_stage_name", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
 
@@ -114,6 +114,11 @@ def _load():
     lib.ftrf_test_gemm3x.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int,
                                      C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
                                      C.c_void_p]
+    lib.ftrf_test_wgrad3x.restype = C.c_int
+    lib.ftrf_test_wgrad3x.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_int,
+                                      C.c_void_p, C.c_void_p]
+    lib.ftrf_set_shade_path.restype = C.c_int
+    lib.ftrf_set_shade_path.argtypes = [C.c_int]
     if lib.ftrf_abi_version() != 1:
         raise ImportError("libfewtensorf_b200.so ABI version mismatch")
     return lib

@@ -65,8 +65,11 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
   sz[FTRF_WS_A_SLOT] = A * 4;
   sz[FTRF_WS_A_FEAT] = A * D * 4;
   sz[FTRF_WS_A_RGB] = A * 12;
-  sz[FTRF_WS_A_H1] = (train && mlp) ? A * H * 4 : 0;
-  sz[FTRF_WS_A_H2] = (train && mlp) ? A * H * 4 : 0;
+  const size_t LDX = (size_t)((f.in_dim + 7) & ~7);
+  sz[FTRF_WS_A_H1] = mlp ? A * H * 4 : 0;
+  sz[FTRF_WS_A_H2] = mlp ? A * H * 4 : 0;
+  sz[FTRF_WS_A_X] = mlp ? A * LDX * 4 : 0;
+  sz[FTRF_WS_A_GX] = (train && mlp) ? A * LDX * 4 : 0;
   sz[FTRF_WS_A_GRGB] = train ? A * 12 : 0;
   sz[FTRF_WS_A_GH1] = (train && mlp) ? A * H * 4 : 0;
   sz[FTRF_WS_A_GH2] = (train && mlp) ? A * H * 4 : 0;
@@ -101,6 +104,9 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
     ws->a_gh1 = (float*)(b + offs[FTRF_WS_A_GH1]);
     ws->a_gh2 = (float*)(b + offs[FTRF_WS_A_GH2]);
     ws->a_gfeat = (float*)(b + offs[FTRF_WS_A_GFEAT]);
+    ws->a_x = (float*)(b + offs[FTRF_WS_A_X]);
+    ws->a_gx = (float*)(b + offs[FTRF_WS_A_GX]);
+    ws->ldx = (int)LDX;
   }
   return cur;
 }

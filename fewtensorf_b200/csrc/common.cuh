@@ -36,6 +36,9 @@ struct Ws {
   float* a_gh1;
   float* a_gh2;
   float* a_gfeat;
+  float* a_x;      // [cap_app][ldx]  MLP input rows (tensor-core path)
+  float* a_gx;     // [cap_app][ldx]  dL/dX
+  int ldx;
 };
 
 size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws* ws);

@@ -11,34 +11,17 @@
 // an mbarrier, and after the last chunk the accumulator tile is read back with tcgen05.ld for the
 // fused epilogue (bias, ReLU, ReLU-mask of a saved activation).
 #include "common.cuh"
+#include "gemm3x.cuh"
 #include "tc.cuh"
 
 namespace ftrf {
 
-struct Gemm3xArgs {
-  const float* A; int lda; int ka;       // A[m][k], k < ka valid (ka % 4 == 0), others read as 0
-  const int32_t* count; int64_t cap;     // M = count ? min(*count, cap) : cap
-  const float* B; int64_t sn, sk;        // B element (n,k) at B[n*sn + k*sk]
-  int N, K;
-  const float* bias;                     // [N] or null
-  const float* mask; int ldm;            // out = mask[m][n] > 0 ? acc : 0   (ReLU backward) or null
-  int relu;                              // out = max(acc, 0)
-  float* out; int ldo;
-  int variant;                           // debug: bit0 swaps the LBO/SBO roles
-};
 
 constexpr int G_KC = 32;                 // K columns per streamed A chunk
 constexpr int G_TM = 128;                // rows per tile (UMMA M)
 constexpr int G_ABUF = G_TM * G_KC;      // floats per hi (or lo) chunk buffer
 
-__host__ __device__ inline int g_np(int N) { return (N + 15) & ~15; }
-__host__ __device__ inline int g_kp(int K) { return (K + 7) & ~7; }
 
-// canonical K-major no-swizzle position (in floats) of element (row, k) in a tile with `ku_total`
-// 16-byte units along K: units are ordered (row/8, ku, row%8).
-__device__ __forceinline__ int canon_off(int row, int ku, int ku_total) {
-  return (((row >> 3) * ku_total + ku) * 8 + (row & 7)) * 4;
-}
 
 __global__ void __launch_bounds__(256, 1)
 gemm3x_kernel(const Gemm3xArgs a) {
@@ -73,7 +56,7 @@ gemm3x_kernel(const Gemm3xArgs a) {
       float v = (n < a.N && k < a.K) ? __ldg(a.B + (int64_t)n * a.sn + (int64_t)k * a.sk) : 0.f;
       tc::split_tf32(v, hi[j], lo[j]);
     }
-    int off = canon_off(n, ku, KUB);
+    int off = tc::canon_off(n, ku, KUB);
     *reinterpret_cast<float4*>(Bhi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
     *reinterpret_cast<float4*>(Blo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
   }
@@ -112,7 +95,7 @@ gemm3x_kernel(const Gemm3xArgs a) {
         float4 h, l;
         tc::split_tf32(v[j].x, h.x, l.x); tc::split_tf32(v[j].y, h.y, l.y);
         tc::split_tf32(v[j].z, h.z, l.z); tc::split_tf32(v[j].w, h.w, l.w);
-        int off = canon_off(r, ku, G_KC / 4);
+        int off = tc::canon_off(r, ku, G_KC / 4);
         *reinterpret_cast<float4*>(Ahi + off) = h;
         *reinterpret_cast<float4*>(Alo + off) = l;
       }

@@ -163,12 +163,13 @@ int shade_check(const FtrfField& f, const InSpec& sp) {
   return FTRF_OK;
 }
 
-int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.shading == FTRF_SHADE_SH) {
-    if (f.app_dim != 27) { set_error("SH shading needs app_dim 27"); return FTRF_E_ARG; }
-    shade_sh_fwd_kernel<<<FTRF_SMS * 4, 256, 0, st>>>(f, c, ws);
-    return check_launch("shade_sh_fwd");
-  }
+int launch_shade_sh(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (f.app_dim != 27) { set_error("SH shading needs app_dim 27"); return FTRF_E_ARG; }
+  shade_sh_fwd_kernel<<<FTRF_SMS * 4, 256, 0, st>>>(f, c, ws);
+  return check_launch("shade_sh_fwd");
+}
+
+int launch_shade_v1(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   size_t smem = shade_fwd_smem(sp);

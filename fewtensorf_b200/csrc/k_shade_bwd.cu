@@ -274,8 +274,7 @@ shade_wgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpe
 int shade_check(const FtrfField& f, const InSpec& sp);
 int launch_shade_sh_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 
-int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.shading == FTRF_SHADE_SH) return launch_shade_sh_bwd(f, c, ws, st);
+int launch_shade_bwd_v1(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   if (sp.kp > 192) { set_error("shade backward: input width %d > 192 unsupported", sp.in_dim); return FTRF_E_ARG; }

@@ -1,0 +1,233 @@
+// k_shade_tc.cu — stage 3 on the tensor cores: the shading MLP as tcgen05 3xTF32 contractions
+// (k_gemm3x.cu / k_wgrad3x.cu) plus the thin CUDA-core kernels around them:
+//   build_x      positional encoding + FreeNeRF encoding mask -> X[V_a][ldx]   (models/mlp.py:8-13, :41-64)
+//   layer3_fwd   rgb = sigmoid(h2 W3^T + b3)                                    (models/mlp.py:66-67)
+//   layer3_bwd   sigmoid' , g_h2 = relu'(h2) * (go W3), dW3, db3
+//   pe_bwd       g_feat from g_X (chain rule through sin/cos and the mask)
+// Forward:  build_x -> gemm(X,W1)+b1,ReLU -> gemm(h1,W2)+b2,ReLU -> layer3
+// Backward: layer3_bwd -> gemm(g_h2,W2^T)*relu'(h1) -> gemm(g_h1,W1^T) -> pe_bwd ; wgrad(g_h2,h1), wgrad(g_h1,X)
+#include "shade_common.cuh"
+#include "gemm3x.cuh"
+
+namespace ftrf {
+
+// ---------------------------------------------------------------------------------------- build_x
+__global__ void __launch_bounds__(256)
+build_x_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpec sp, int ldx) {
+  extern __shared__ __align__(16) float stage[];      // ST * (D + 6)
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int D = sp.D;
+  float* s_feat = stage;
+  float* s_view = stage + ST * D;
+  float* s_pos = s_view + ST * 3;
+  for (int64_t t0 = (int64_t)blockIdx.x * ST; t0 < n; t0 += (int64_t)gridDim.x * ST) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < ST * D; e += blockDim.x) {
+      int64_t s = t0 + e / D;
+      s_feat[e] = s < n ? ws.a_feat[s * D + (e % D)] : 0.f;
+    }
+    if (threadIdx.x < ST) {
+      int64_t s = t0 + threadIdx.x;
+      float v[3] = {0.f, 0.f, 0.f}, p[3] = {0.f, 0.f, 0.f};
+      if (s < n) shade_geometry(f, c, ws, s, v, p);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { s_view[threadIdx.x * 3 + k] = v[k]; s_pos[threadIdx.x * 3 + k] = p[k]; }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < ST * ldx; e += blockDim.x) {
+      int s = e / ldx, col = e - s * ldx;
+      if (t0 + s < n)
+        ws.a_x[(size_t)(t0 + s) * ldx + col] = in_col(f, sp, col, s_feat + s * D, s_view + s * 3, s_pos + s * 3);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------- layer 3
+// one warp per shaded sample: lane owns hidden units 4*lane .. 4*lane+3
+__global__ void __launch_bounds__(256)
+layer3_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int lane = threadIdx.x & 31;
+  float4 w[3];
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) w[ch] = ld4(f.w3 + ch * FC + lane * 4);
+  const float b0 = __ldg(f.b3), b1 = __ldg(f.b3 + 1), b2 = __ldg(f.b3 + 2);
+  const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t s = wid; s < n; s += nw) {
+    float4 h = *reinterpret_cast<const float4*>(ws.a_h2 + s * FC + lane * 4);
+    float a[3];
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) a[ch] = h.x * w[ch].x + h.y * w[ch].y + h.z * w[ch].z + h.w * w[ch].w;
+#pragma unroll
+    for (int d = 16; d; d >>= 1)
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) a[ch] += __shfl_xor_sync(FULL_MASK, a[ch], d);
+    if (lane < 3) {
+      float v = lane == 0 ? a[0] + b0 : (lane == 1 ? a[1] + b1 : a[2] + b2);
+      ws.a_rgb[s * 3 + lane] = 1.f / (1.f + expf(-v));
+    }
+  }
+}
+
+// g_h2, dW3, db3 (+ db2 = column sums of g_h2).  Per-lane partial sums over the warp's samples,
+// then a block reduction in shared memory and one atomic flush per CTA.
+__global__ void __launch_bounds__(256)
+layer3_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  __shared__ float red[8][16 * 32];       // [warp][12 dW3 + 4 db2 per lane]
+  __shared__ float red3[8][3];
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float4 w[3];
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) w[ch] = ld4(f.w3 + ch * FC + lane * 4);
+  float dw[3][4] = {}, db2[4] = {}, db3[3] = {};
+  const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t s = wid; s < n; s += nw) {
+    float go[3];
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      float r = ws.a_rgb[s * 3 + ch];
+      go[ch] = ws.a_grgb[s * 3 + ch] * r * (1.f - r);
+      db3[ch] += go[ch];
+    }
+    float4 h = *reinterpret_cast<const float4*>(ws.a_h2 + s * FC + lane * 4);
+    const float hh[4] = {h.x, h.y, h.z, h.w};
+    const float ww[3][4] = {{w[0].x, w[0].y, w[0].z, w[0].w}, {w[1].x, w[1].y, w[1].z, w[1].w}, {w[2].x, w[2].y, w[2].z, w[2].w}};
+    float g[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      g[j] = hh[j] > 0.f ? go[0] * ww[0][j] + go[1] * ww[1][j] + go[2] * ww[2][j] : 0.f;
+      db2[j] += g[j];
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) dw[ch][j] = fmaf(go[ch], hh[j], dw[ch][j]);
+    }
+    *reinterpret_cast<float4*>(ws.a_gh2 + s * FC + lane * 4) = make_float4(g[0], g[1], g[2], g[3]);
+  }
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[warp][(ch * 4 + j) * 32 + lane] = dw[ch][j];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) red[warp][(12 + j) * 32 + lane] = db2[j];
+  if (lane == 0) { red3[warp][0] = db3[0]; red3[warp][1] = db3[1]; red3[warp][2] = db3[2]; }   // same for all lanes
+  __syncthreads();
+  for (int e = threadIdx.x; e < 16 * 32; e += blockDim.x) {
+    float v = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v += red[q][e];
+    int item = e >> 5, ln = e & 31;          // item < 12: dW3[ch][4*ln + j]; else db2[4*ln + j]
+    if (v != 0.f) {
+      if (item < 12) atomicAdd(f.g_w3 + (item >> 2) * FC + ln * 4 + (item & 3), v);
+      else atomicAdd(f.g_b2 + ln * 4 + (item - 12), v);
+    }
+  }
+  if (threadIdx.x < 3) {
+    float v = 0.f;
+    for (int q = 0; q < 8; ++q) v += red3[q][threadIdx.x];
+    if (v != 0.f) atomicAdd(f.g_b3 + threadIdx.x, v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------- pe_bwd
+// g_feat[ch] = gX[ch] + sum over PE(fea) blocks of 2^f * (cos(a) m_s gX[sin col] - sin(a) m_c gX[cos col])
+__global__ void __launch_bounds__(256)
+pe_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpec sp) {
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int D = sp.D, ldx = ws.ldx;
+  const int64_t total = n * D;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t s = e / D;
+    int ch = (int)(e - s * D);
+    const float* gx = ws.a_gx + s * ldx;
+    float g = gx[ch];
+    for (int b = 0; b < sp.nblk; ++b) {
+      const PeBlock& pb = sp.b[b];
+      if (pb.src != SRC_FEA) continue;
+      float v = ws.a_feat[e];
+      int half = pb.F * pb.C;
+      for (int fq = 0; fq < pb.F; ++fq) {
+        float sc = (float)(1 << fq), sn, cs;
+        sincosf(v * sc, &sn, &cs);
+        int q = ch * pb.F + fq;
+        float ms = enc_mask_at(f, SRC_FEA, q), mc = enc_mask_at(f, SRC_FEA, half + q);
+        g += sc * (cs * ms * gx[pb.col0 + q] - sn * mc * gx[pb.col0 + half + q]);
+      }
+    }
+    ws.a_gfeat[e] = g;
+  }
+}
+
+// ---------------------------------------------------------------------------------------- drivers
+int shade_check(const FtrfField& f, const InSpec& sp);
+int launch_shade_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_shade_bwd_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_shade_sh(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_shade_sh_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+
+static int g_shade_path = 1;     // 1 = tensor cores (tcgen05 3xTF32), 0 = fp32 CUDA cores (v1)
+
+static Gemm3xArgs gemm_args(const Ws& ws, const FtrfCall& c) {
+  Gemm3xArgs g{};
+  g.count = ws.counters + 1;
+  g.cap = c.cap_app;
+  return g;
+}
+
+int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (f.shading == FTRF_SHADE_SH) return launch_shade_sh(f, c, ws, st);
+  if (!g_shade_path) return launch_shade_v1(f, c, ws, st);
+  InSpec sp = make_spec(f);
+  if (int e = shade_check(f, sp)) return e;
+  if (c.cap_app == 0) return FTRF_OK;
+  size_t smem = (size_t)ST * (sp.D + 6) * sizeof(float);
+  build_x_kernel<<<FTRF_SMS * 4, 256, smem, st>>>(f, c, ws, sp, ws.ldx);
+  if (int e = check_launch("build_x")) return e;
+  Gemm3xArgs g = gemm_args(ws, c);
+  g.A = ws.a_x; g.lda = ws.ldx; g.ka = ws.ldx; g.B = f.w1; g.sn = sp.in_dim; g.sk = 1; g.N = FC; g.K = sp.in_dim;
+  g.bias = f.b1; g.relu = 1; g.out = ws.a_h1; g.ldo = FC;
+  if (int e = launch_gemm3x(g, st)) return e;
+  g.A = ws.a_h1; g.lda = FC; g.ka = FC; g.B = f.w2; g.sn = FC; g.sk = 1; g.N = FC; g.K = FC;
+  g.bias = f.b2; g.out = ws.a_h2;
+  if (int e = launch_gemm3x(g, st)) return e;
+  layer3_fwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
+  return check_launch("layer3_fwd");
+}
+
+int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (f.shading == FTRF_SHADE_SH) return launch_shade_sh_bwd(f, c, ws, st);
+  if (!g_shade_path) return launch_shade_bwd_v1(f, c, ws, st);
+  InSpec sp = make_spec(f);
+  if (int e = shade_check(f, sp)) return e;
+  if (c.cap_app == 0) return FTRF_OK;
+  prof_begin(7, st);
+  layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
+  if (int e = check_launch("layer3_bwd")) return e;
+  Gemm3xArgs g = gemm_args(ws, c);        // g_h1 = relu'(h1) * (g_h2 W2):  B(n=i,k=o) = W2[o][i]
+  g.A = ws.a_gh2; g.lda = FC; g.ka = FC; g.B = f.w2; g.sn = 1; g.sk = FC; g.N = FC; g.K = FC;
+  g.mask = ws.a_h1; g.ldm = FC; g.out = ws.a_gh1; g.ldo = FC;
+  if (int e = launch_gemm3x(g, st)) return e;
+  prof_end(7, st); prof_begin(8, st);
+  g = gemm_args(ws, c);                   // g_X = g_h1 W1:  B(n=j,k=o) = W1[o][j]
+  g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;
+  g.out = ws.a_gx; g.ldo = ws.ldx;
+  if (int e = launch_gemm3x(g, st)) return e;
+  pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
+  if (int e = check_launch("pe_bwd")) return e;
+  prof_end(8, st); prof_begin(9, st);
+  Wgrad3xArgs w{};
+  w.count = ws.counters + 1; w.cap = c.cap_app;
+  w.G = ws.a_gh2; w.ldg = FC; w.A = ws.a_h1; w.lda = FC; w.K = FC; w.dW = f.g_w2; w.ldw = FC; w.dbias = nullptr;  // db2 done in layer3_bwd
+  if (int e = launch_wgrad3x(w, st)) return e;
+  prof_end(9, st); prof_begin(10, st);
+  w.G = ws.a_gh1; w.A = ws.a_x; w.lda = ws.ldx; w.K = sp.in_dim; w.dW = f.g_w1; w.ldw = sp.in_dim; w.dbias = f.g_b1;
+  int e = launch_wgrad3x(w, st);
+  prof_end(10, st);
+  return e;
+}
+
+}  // namespace ftrf
+
+extern "C" int ftrf_set_shade_path(int tensor_cores) {
+  ftrf::g_shade_path = tensor_cores ? 1 : 0;
+  return FTRF_OK;
+}

@@ -104,5 +104,11 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   lo = __uint_as_float(l);
 }
 
+// canonical K-major no-swizzle position (in floats) of element (row, 4*ku) in a tile with `ku_total`
+// 16-byte units along K: units are ordered (row/8, ku, row%8) => LBO = 128 B, SBO = ku_total * 128 B.
+__device__ __forceinline__ int canon_off(int row, int ku, int ku_total) {
+  return (((row >> 3) * ku_total + ku) * 8 + (row & 7)) * 4;
+}
+
 }  // namespace tc
 }  // namespace ftrf

@@ -134,6 +134,8 @@ enum {
   FTRF_WS_A_GH1,        /* float[cap_app][feature_c]  backward                               */
   FTRF_WS_A_GH2,        /* float[cap_app][feature_c]  backward                               */
   FTRF_WS_A_GFEAT,      /* float[cap_app][app_dim]    backward                               */
+  FTRF_WS_A_X,          /* float[cap_app][ldx]  MLP input rows, ldx = in_dim rounded up to 8     */
+  FTRF_WS_A_GX,         /* float[cap_app][ldx]  backward                                         */
   FTRF_WS_COUNT
 };
 
@@ -171,6 +173,13 @@ int ftrf_density_at(const FtrfField* field, const float* xyz, int64_t n, float* 
 int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B, int64_t sn, int64_t sk, int N, int K,
                      const float* bias, const float* mask, int ldm, int relu, float* out, int ldo, int variant,
                      void* stream);
+
+/* dW[o][k] += sum_s G[s][o] A[s][k] (o < 128, k < K), dbias[o] += sum_s G[s][o] (or NULL) — the
+ * tensor-core weight-gradient contraction, exposed for unit tests. */
+int ftrf_test_wgrad3x(const float* G, int ldg, const float* A, int lda, int K, int64_t M, float* dW, int ldw,
+                      float* dbias, void* stream);
+/* 1 (default): shading MLP on tcgen05 tensor cores (3xTF32); 0: fp32 CUDA-core kernels (both CUDA). */
+int ftrf_set_shade_path(int tensor_cores);
 
 /* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
  * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.

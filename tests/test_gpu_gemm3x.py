@@ -60,3 +60,23 @@ def test_gemm3x_epilogues_and_strided_b():
     out = run_gemm(A, W, mask=mask, transposed_b=True)
     ref = torch.where(mask > 0, (A.double() @ W.double()), torch.zeros((), dtype=torch.float64, device="cuda"))
     assert float((out.double() - ref).abs().max()) < 2e-5
+
+
+@pytest.mark.parametrize("M,K,with_bias", [(32, 128, False), (1000, 150, True), (5000, 128, True), (100000, 150, True)])
+def test_wgrad3x_matches_fp64(M, K, with_bias):
+    from fewtensorf_b200._abi import check, lib
+    g = torch.Generator(device="cuda").manual_seed(M + K)
+    lda = (K + 7) // 8 * 8
+    G = torch.randn(M, 128, device="cuda", generator=g) * (torch.rand(M, 128, device="cuda", generator=g) > 0.5)
+    A = torch.randn(M, lda, device="cuda", generator=g)
+    dW = torch.zeros(128, K, device="cuda")
+    db = torch.zeros(128, device="cuda") if with_bias else None
+    check(lib.ftrf_test_wgrad3x(G.data_ptr(), 128, A.data_ptr(), lda, K, M, dW.data_ptr(), K,
+                                None if db is None else db.data_ptr(), torch.cuda.current_stream().cuda_stream), "wgrad3x")
+    torch.cuda.synchronize()
+    ref = G.double().T @ A[:, :K].double()
+    scale = (G.double().abs().T @ A[:, :K].double().abs()).clamp_min(1e-30)
+    assert float(((dW.double() - ref).abs() / scale).max()) < 4e-6
+    if with_bias:
+        refb = G.double().sum(0)
+        assert float((db.double() - refb).abs().max() / G.double().abs().sum(0).max()) < 4e-6

@@ -81,6 +81,23 @@ def test_gradients_autograd(case):
         assert rel_inf(got[k].cpu(), ref) < TOL, f"{k}: {rel_inf(got[k].cpu(), ref):.3e}"
 
 
+@pytest.mark.parametrize("case", [c for c in CASES if "sh" not in c])
+def test_cuda_core_shading_path(case):
+    """The fp32 CUDA-core MLP kernels (ftrf_set_shade_path(0)) must meet the same bars as the
+    tcgen05 path that the other tests exercise by default."""
+    from fewtensorf_b200._abi import lib
+    lib.ftrf_set_shade_path(0)
+    try:
+        g, f, m, rgb, depth, nv = _run(case, grad=True)
+        loss = torch.mean((rgb - g.target.cuda()) ** 2)
+        loss.backward()
+        assert rel_inf(rgb.detach().cpu(), g.t["rgb_map"]) < TOL
+        for k, p in m.named_parameters():
+            assert rel_inf(p.grad.cpu(), g.grads[k]) < TOL, k
+    finally:
+        lib.ftrf_set_shade_path(1)
+
+
 @pytest.mark.parametrize("case", [c for c in CASES if "train" in c and "ndc" not in c][:2])
 def test_train_step_matches_autograd(case):
     """The fused train_step (no autograd engine) must give the same loss and gradients."""
