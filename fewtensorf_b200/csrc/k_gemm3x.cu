@@ -32,8 +32,9 @@ gemm3x_kernel(const Gemm3xArgs a) {
   float* Abuf = Blo + (size_t)Np * Kp;                       // [2 buffers][hi, lo][G_ABUF]
   uint64_t* bars = reinterpret_cast<uint64_t*>(Abuf + 4 * G_ABUF);
   uint64_t* bar_free = bars;                                  // [2]
-  uint64_t* bar_acc = bars + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+  uint64_t* bar_acc = bars + 2;                               // [2] accumulator stages
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+  float* s_bias = reinterpret_cast<float*>(bars + 6);        // [Np]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t M = a.count ? min((int64_t)*a.count, a.cap) : a.cap;
@@ -42,13 +43,18 @@ gemm3x_kernel(const Gemm3xArgs a) {
   if (tid == 0) {
     tc::mbar_init(bar_free + 0, 1);
     tc::mbar_init(bar_free + 1, 1);
-    tc::mbar_init(bar_acc, 1);
+    tc::mbar_init(bar_acc + 0, 1);
+    tc::mbar_init(bar_acc + 1, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
-  // resident B: split into hi / lo, canonical layout
-  for (int e = tid; e < Np * KUB; e += blockDim.x) {
-    int n = e % Np, ku = e / Np;
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
+  for (int e = tid; e < Np; e += blockDim.x) s_bias[e] = (a.bias && e < a.N) ? __ldg(a.bias + e) : 0.f;
+  // resident B: split into hi / lo, canonical layout.  Lanes run along the contiguous global axis.
+  const bool k_contig = a.sk == 1;
+  const int dbg = a.variant;     // bring-up switches: 2 no MMA, 4 no epilogue, 8 no A loads, 16 no B fill
+#pragma unroll 4
+  for (int e = tid; e < ((dbg & 16) ? 0 : Np * KUB); e += blockDim.x) {
+    int n = k_contig ? e / KUB : e % Np, ku = k_contig ? e % KUB : e / Np;
     float hi[4], lo[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -66,102 +72,133 @@ gemm3x_kernel(const Gemm3xArgs a) {
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  const bool swap = a.variant & 1;
   const uint32_t a_lbo = 128, a_sbo = (G_KC / 4) * 128, b_lbo = 128, b_sbo = (uint32_t)KUB * 128;
   const uint32_t idesc = tc::idesc_tf32(G_TM, Np);
   const int nchunks = (Kp + G_KC - 1) / G_KC;
-  uint32_t it = 0, tcount = 0;
+  const int64_t ntiles = (M + G_TM - 1) / G_TM;
+  const int my_tiles = (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int total = my_tiles * nchunks;
 
-  for (int64_t m0 = (int64_t)blockIdx.x * G_TM; m0 < M; m0 += (int64_t)gridDim.x * G_TM, ++tcount) {
-    for (int c = 0; c < nchunks; ++c, ++it) {
-      const int buf = it & 1;
-      float* Ahi = Abuf + buf * 2 * G_ABUF;
-      float* Alo = Ahi + G_ABUF;
-      // ---- stream one A chunk: LDG (8 rows x 64 B per warp item), split, STS
-      float4 v[4];
+  // this thread's 4 (row, k-unit) slots of a chunk: 8 rows x 64 B per warp item
+  int slot_r[4], slot_ku[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        int id = warp * 4 + j;
-        int r = (id >> 1) * 8 + (lane & 7), ku = (id & 1) * 4 + (lane >> 3);
-        int64_t row = m0 + r;
-        int col = c * G_KC + ku * 4;
-        v[j] = (row < M && col < a.ka) ? ld4(a.A + row * a.lda + col) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      if (it >= 2) tc::mbar_wait(bar_free + buf, ((it >> 1) - 1) & 1);   // MMAs that read this buffer are done
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        int id = warp * 4 + j;
-        int r = (id >> 1) * 8 + (lane & 7), ku = (id & 1) * 4 + (lane >> 3);
-        float4 h, l;
-        tc::split_tf32(v[j].x, h.x, l.x); tc::split_tf32(v[j].y, h.y, l.y);
-        tc::split_tf32(v[j].z, h.z, l.z); tc::split_tf32(v[j].w, h.w, l.w);
-        int off = tc::canon_off(r, ku, G_KC / 4);
-        *reinterpret_cast<float4*>(Ahi + off) = h;
-        *reinterpret_cast<float4*>(Alo + off) = l;
-      }
-      tc::fence_async_smem();
-      __syncthreads();
-      // ---- one thread issues this chunk's MMAs (async); commit frees the buffer
-      if (tid == 0) {
-        tc::fence_after_sync();
-        const int ksteps = min(G_KC, Kp - c * G_KC) / 8;
-        const uint32_t ah = tc::smem_u32(Ahi), al = tc::smem_u32(Alo);
-        const uint32_t bh = tc::smem_u32(Bhi) + (uint32_t)(c * (G_KC / 4)) * 128;
-        const uint32_t bl = tc::smem_u32(Blo) + (uint32_t)(c * (G_KC / 4)) * 128;
-        for (int s = 0; s < ksteps; ++s) {
-          uint32_t ko = s * 256;      // 8 tf32 = two 16-byte units along K
-          uint64_t dah = swap ? tc::smem_desc(ah + ko, a_sbo, a_lbo) : tc::smem_desc(ah + ko, a_lbo, a_sbo);
-          uint64_t dal = swap ? tc::smem_desc(al + ko, a_sbo, a_lbo) : tc::smem_desc(al + ko, a_lbo, a_sbo);
-          uint64_t dbh = swap ? tc::smem_desc(bh + ko, b_sbo, b_lbo) : tc::smem_desc(bh + ko, b_lbo, b_sbo);
-          uint64_t dbl = swap ? tc::smem_desc(bl + ko, b_sbo, b_lbo) : tc::smem_desc(bl + ko, b_lbo, b_sbo);
-          tc::mma_tf32_ss(tmem, dal, dbh, idesc, (c | s) != 0);
-          tc::mma_tf32_ss(tmem, dah, dbl, idesc, true);
-          tc::mma_tf32_ss(tmem, dah, dbh, idesc, true);
-        }
-        tc::mma_commit(bar_free + buf);
-        if (c == nchunks - 1) tc::mma_commit(bar_acc);
-      }
-    }
-    // ---- epilogue: TMEM -> registers -> global
-    tc::mbar_wait(bar_acc, tcount & 1);
-    tc::fence_after_sync();
-    {
-      const int q = warp & 3;
-      const int64_t row = m0 + q * 32 + lane;
-      for (int cc = warp >> 2; cc * 32 < Np; cc += 2) {
-        float acc[32];
-        tc::tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), acc);
-        tc::tmem_wait_ld();
-        if (row < M) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            int col = cc * 32 + j;
-            if (col >= a.N) break;
-            float o[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              float x = acc[j + e];
-              if (a.bias && col + e < a.N) x += __ldg(a.bias + col + e);
-              if (a.relu) x = fmaxf(x, 0.f);
-              if (a.mask && col + e < a.N && !(__ldg(a.mask + row * a.ldm + col + e) > 0.f)) x = 0.f;
-              o[e] = x;
-            }
-            float* dst = a.out + row * a.ldo + col;
-            if (col + 3 < a.N && (a.ldo & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-            else
-              for (int e = 0; e < 4 && col + e < a.N; ++e) dst[e] = o[e];
-          }
-        }
-      }
-    }
-    tc::fence_before_sync();
-    __syncthreads();
+  for (int j = 0; j < 4; ++j) {
+    int id = warp * 4 + j;
+    slot_r[j] = (id >> 1) * 8 + (lane & 7);
+    slot_ku[j] = (id & 1) * 4 + (lane >> 3);
   }
-  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+  auto load_chunk = [&](int step, float4 v[4]) {
+    int t = step / nchunks, c = step - t * nchunks;
+    int64_t m0 = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * G_TM;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int64_t row = m0 + slot_r[j];
+      int col = c * G_KC + slot_ku[j] * 4;
+      v[j] = (row < M && col < a.ka && !(dbg & 8)) ? ld4(a.A + row * a.lda + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  // TMEM -> registers -> global for one finished tile (accumulator stage `stg`)
+  auto epilogue = [&](int t) {
+    const int stg = t & 1;
+    tc::mbar_wait(bar_acc + stg, (t >> 1) & 1);
+    tc::fence_after_sync();
+    const int64_t m0 = ((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * G_TM;
+    const int q = warp & 3;
+    const int64_t row = m0 + q * 32 + lane;
+    for (int cc = warp >> 2; cc * 32 < ((dbg & 4) ? 0 : Np); cc += 2) {
+      float acc[32];
+      tc::tmem_ld32(tmem + (uint32_t)(stg * 256) + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), acc);
+      tc::tmem_wait_ld();
+      if (row < M) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          int col = cc * 32 + j;
+          if (col >= a.N) break;
+          float o[4], mk[4] = {1.f, 1.f, 1.f, 1.f};
+          if (a.mask) {
+            if (col + 3 < a.N && (a.ldm & 3) == 0) {
+              float4 m4 = ld4(a.mask + row * a.ldm + col);
+              mk[0] = m4.x; mk[1] = m4.y; mk[2] = m4.z; mk[3] = m4.w;
+            } else
+              for (int e = 0; e < 4 && col + e < a.N; ++e) mk[e] = __ldg(a.mask + row * a.ldm + col + e);
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x = acc[j + e];
+            x += s_bias[col + e];
+            if (a.relu) x = fmaxf(x, 0.f);
+            if (!(mk[e] > 0.f)) x = 0.f;
+            o[e] = x;
+          }
+          float* dst = a.out + row * a.ldo + col;
+          if (col + 3 < a.N && (a.ldo & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+          else
+            for (int e = 0; e < 4 && col + e < a.N; ++e) dst[e] = o[e];
+        }
+      }
+    }
+    tc::fence_before_sync();     // ordered before the next __syncthreads / MMA that reuses this stage
+  };
+
+  // One pipeline step = one A chunk.  Three register sets rotate (the loop is unrolled by 3 so the
+  // sets are static registers): the LDGs of step s+3 are issued as soon as step s has been written
+  // to shared memory, i.e. global latency is covered by ~3 steps of MMA time.
+  auto body = [&](int step, float4 (&v)[4]) {
+    if (step >= total) return;
+    const int t = step / nchunks, c = step - t * nchunks;
+    const int buf = step & 1;
+    float* Ahi = Abuf + buf * 2 * G_ABUF;
+    float* Alo = Ahi + G_ABUF;
+    if (step >= 2) tc::mbar_wait(bar_free + buf, ((step >> 1) - 1) & 1);   // MMAs that read this buffer are done
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float4 h, l;
+      tc::split_tf32(v[j].x, h.x, l.x); tc::split_tf32(v[j].y, h.y, l.y);
+      tc::split_tf32(v[j].z, h.z, l.z); tc::split_tf32(v[j].w, h.w, l.w);
+      int off = tc::canon_off(slot_r[j], slot_ku[j], G_KC / 4);
+      *reinterpret_cast<float4*>(Ahi + off) = h;
+      *reinterpret_cast<float4*>(Alo + off) = l;
+    }
+    if (step + 3 < total) load_chunk(step + 3, v);
+    tc::fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {              // one thread issues this chunk's MMAs (async); commit frees the buffer
+      tc::fence_after_sync();
+      const uint32_t acc_t = tmem + (uint32_t)((t & 1) * 256);
+      const int ksteps = min(G_KC, Kp - c * G_KC) / 8;
+      const uint32_t ah = tc::smem_u32(Ahi), al = tc::smem_u32(Alo);
+      const uint32_t bh = tc::smem_u32(Bhi) + (uint32_t)(c * (G_KC / 4)) * 128;
+      const uint32_t bl = tc::smem_u32(Blo) + (uint32_t)(c * (G_KC / 4)) * 128;
+      for (int s = 0; s < ((dbg & 2) ? 0 : ksteps); ++s) {
+        uint32_t ko = s * 256;      // 8 tf32 = two 16-byte units along K
+        uint64_t dah = tc::smem_desc(ah + ko, a_lbo, a_sbo), dal = tc::smem_desc(al + ko, a_lbo, a_sbo);
+        uint64_t dbh = tc::smem_desc(bh + ko, b_lbo, b_sbo), dbl = tc::smem_desc(bl + ko, b_lbo, b_sbo);
+        tc::mma_tf32_ss(acc_t, dal, dbh, idesc, (c | s) != 0);
+        tc::mma_tf32_ss(acc_t, dah, dbl, idesc, true);
+        tc::mma_tf32_ss(acc_t, dah, dbh, idesc, true);
+      }
+      tc::mma_commit(bar_free + buf);
+      if (c == nchunks - 1) tc::mma_commit(bar_acc + (t & 1));
+    }
+    // the previous tile's epilogue runs while this tile's first MMAs execute
+    if (c == 0 && t > 0) epilogue(t - 1);
+  };
+  float4 r0[4], r1[4], r2[4];
+  load_chunk(0, r0);
+  if (1 < total) load_chunk(1, r1);
+  if (2 < total) load_chunk(2, r2);
+  for (int step = 0; step < total; step += 3) {
+    body(step, r0);
+    body(step + 1, r1);
+    body(step + 2, r2);
+  }
+  epilogue(my_tiles - 1);
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
 size_t gemm3x_smem(int N, int K) {
-  return (size_t)2 * g_np(N) * g_kp(K) * 4 + (size_t)4 * G_ABUF * 4 + 64;
+  return (size_t)2 * g_np(N) * g_kp(K) * 4 + (size_t)4 * G_ABUF * 4 + 64 + (size_t)g_np(N) * 4;
 }
 
 int launch_gemm3x(const Gemm3xArgs& a, cudaStream_t st) {

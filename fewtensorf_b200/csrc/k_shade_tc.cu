@@ -12,32 +12,66 @@
 namespace ftrf {
 
 // ---------------------------------------------------------------------------------------- build_x
+// Per-column recipe, built once per CTA: where the value comes from and what is applied to it.
+struct XCol {
+  int src;       // offset into the staged [feat(D) | view(3) | pos(3)] row, or -1 for a padding column
+  int mode;      // 0 copy, 1 sin, 2 cos
+  float scale;   // 2^f
+  float mask;    // FreeNeRF encoding-mask value of this column (1 if none)
+};
+
 __global__ void __launch_bounds__(256)
 build_x_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpec sp, int ldx) {
-  extern __shared__ __align__(16) float stage[];      // ST * (D + 6)
+  extern __shared__ __align__(16) float stage[];      // ST * (D + 6) floats, then XCol[ldx]
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
-  const int D = sp.D;
-  float* s_feat = stage;
-  float* s_view = stage + ST * D;
-  float* s_pos = s_view + ST * 3;
+  const int D = sp.D, RW = D + 6;
+  XCol* cols = reinterpret_cast<XCol*>(stage + ST * RW);
+  for (int col = threadIdx.x; col < ldx; col += blockDim.x) {
+    XCol x{-1, 0, 1.f, 1.f};
+    if (col < D) x.src = col;
+    else if (col < D + 3) x.src = col;                  // view follows feat in the staged row
+    else
+      for (int b = 0; b < sp.nblk; ++b) {
+        const PeBlock& pb = sp.b[b];
+        int e = col - pb.col0, half = pb.F * pb.C;
+        if (e >= 0 && e < 2 * half) {
+          int q = e >= half ? e - half : e;
+          int ch = q / pb.F, fq = q - ch * pb.F;
+          x.src = (pb.src == SRC_FEA ? 0 : (pb.src == SRC_VIEW ? D : D + 3)) + ch;
+          x.mode = e >= half ? 2 : 1;
+          x.scale = (float)(1 << fq);
+          x.mask = enc_mask_at(f, pb.src, e);
+        }
+      }
+    cols[col] = x;
+  }
   for (int64_t t0 = (int64_t)blockIdx.x * ST; t0 < n; t0 += (int64_t)gridDim.x * ST) {
     __syncthreads();
     for (int e = threadIdx.x; e < ST * D; e += blockDim.x) {
-      int64_t s = t0 + e / D;
-      s_feat[e] = s < n ? ws.a_feat[s * D + (e % D)] : 0.f;
+      int s = e / D, ch = e - s * D;
+      stage[s * RW + ch] = t0 + s < n ? ws.a_feat[(t0 + s) * D + ch] : 0.f;
     }
     if (threadIdx.x < ST) {
       int64_t s = t0 + threadIdx.x;
       float v[3] = {0.f, 0.f, 0.f}, p[3] = {0.f, 0.f, 0.f};
       if (s < n) shade_geometry(f, c, ws, s, v, p);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) { s_view[threadIdx.x * 3 + k] = v[k]; s_pos[threadIdx.x * 3 + k] = p[k]; }
+      for (int k = 0; k < 3; ++k) { stage[threadIdx.x * RW + D + k] = v[k]; stage[threadIdx.x * RW + D + 3 + k] = p[k]; }
     }
     __syncthreads();
-    for (int e = threadIdx.x; e < ST * ldx; e += blockDim.x) {
+    const int rows = (int)min((int64_t)ST, n - t0);
+    for (int e = threadIdx.x; e < rows * ldx; e += blockDim.x) {
       int s = e / ldx, col = e - s * ldx;
-      if (t0 + s < n)
-        ws.a_x[(size_t)(t0 + s) * ldx + col] = in_col(f, sp, col, s_feat + s * D, s_view + s * 3, s_pos + s * 3);
+      XCol x = cols[col];
+      float v = 0.f;
+      if (x.src >= 0) {
+        v = stage[s * RW + x.src];
+        if (x.mode) {
+          float arg = v * x.scale;
+          v = (x.mode == 1 ? sinf(arg) : cosf(arg)) * x.mask;
+        }
+      }
+      ws.a_x[(size_t)t0 * ldx + e] = v;
     }
   }
 }
@@ -179,7 +213,7 @@ int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
-  size_t smem = (size_t)ST * (sp.D + 6) * sizeof(float);
+  size_t smem = (size_t)ST * (sp.D + 6) * sizeof(float) + (size_t)ws.ldx * 16;
   build_x_kernel<<<FTRF_SMS * 4, 256, smem, st>>>(f, c, ws, sp, ws.ldx);
   if (int e = check_launch("build_x")) return e;
   Gemm3xArgs g = gemm_args(ws, c);

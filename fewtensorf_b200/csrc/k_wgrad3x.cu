@@ -44,47 +44,67 @@ wgrad3x_kernel(const Wgrad3xArgs a) {
   const uint32_t idesc = tc::idesc_tf32(128, Np);
   const uint32_t lbo = 128, sbo = (W_KC / 4) * 128;
 
-  uint32_t it = 0;
-  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++it) {
+  constexpr int GU = 128 * (W_KC / 4) / 256;     // G units per thread (4)
+  constexpr int AU = 6;                          // A units per thread (Np <= 192)
+  const int a_units = Np * (W_KC / 4);
+  auto load_chunk = [&](int64_t ch, float gv[GU][4], float av[AU][4]) {
+    const int64_t s0 = ch * W_KC;
+#pragma unroll
+    for (int u = 0; u < GU; ++u) {
+      int e = tid + u * 256, o = e & 127, ku = e >> 7;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        int64_t s = s0 + ku * 4 + i;
+        gv[u][i] = s < M ? a.G[s * a.ldg + o] : 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < AU; ++u) {
+      int e = tid + u * 256;
+      if (e < a_units) {
+        int n = e % Np, ku = e / Np;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          int64_t s = s0 + ku * 4 + i;
+          av[u][i] = (s < M) ? (n < a.K ? a.A[s * a.lda + n] : (n == a.K && a.dbias ? 1.f : 0.f)) : 0.f;
+        }
+      }
+    }
+  };
+  // Two register sets alternate (loop unrolled by 2, so they are static registers): the loads of the
+  // chunk two iterations ahead are issued right after the current one is written to shared memory.
+  auto body = [&](int64_t ch, uint32_t it, float (&gv)[GU][4], float (&av)[AU][4]) {
+    if (ch >= nchunks) return;
     const int buf = it & 1;
     float* Ghi = base + buf * bufsz;
     float* Glo = Ghi + gsz;
     float* Ahi = Glo + gsz;
     float* Alo = Ahi + asz;
-    const int64_t s0 = ch * W_KC;
     if (it >= 2) tc::mbar_wait(bar_free + buf, ((it >> 1) - 1) & 1);
-    // G^T: rows o, K = samples
-    for (int e = tid; e < 128 * (W_KC / 4); e += 256) {
-      int o = e & 127, ku = e >> 7;
-      float4 h, l;
-      float v[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        int64_t s = s0 + ku * 4 + i;
-        v[i] = s < M ? a.G[s * a.ldg + o] : 0.f;
-      }
-      tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y);
-      tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+    for (int u = 0; u < GU; ++u) {               // G^T: rows o, K = samples
+      int e = tid + u * 256, o = e & 127, ku = e >> 7;
+      float4 h, l;
+      tc::split_tf32(gv[u][0], h.x, l.x); tc::split_tf32(gv[u][1], h.y, l.y);
+      tc::split_tf32(gv[u][2], h.z, l.z); tc::split_tf32(gv[u][3], h.w, l.w);
       int off = tc::canon_off(o, ku, W_KC / 4);
       *reinterpret_cast<float4*>(Ghi + off) = h;
       *reinterpret_cast<float4*>(Glo + off) = l;
     }
-    // A^T: rows k (+ the virtual ones column), K = samples
-    for (int e = tid; e < Np * (W_KC / 4); e += 256) {
-      int n = e % Np, ku = e / Np;
-      float4 h, l;
-      float v[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        int64_t s = s0 + ku * 4 + i;
-        v[i] = (s < M) ? (n < a.K ? a.A[s * a.lda + n] : (n == a.K && a.dbias ? 1.f : 0.f)) : 0.f;
+    for (int u = 0; u < AU; ++u) {               // A^T: rows k (+ the virtual ones column), K = samples
+      int e = tid + u * 256;
+      if (e < a_units) {
+        int n = e % Np, ku = e / Np;
+        float4 h, l;
+        tc::split_tf32(av[u][0], h.x, l.x); tc::split_tf32(av[u][1], h.y, l.y);
+        tc::split_tf32(av[u][2], h.z, l.z); tc::split_tf32(av[u][3], h.w, l.w);
+        int off = tc::canon_off(n, ku, W_KC / 4);
+        *reinterpret_cast<float4*>(Ahi + off) = h;
+        *reinterpret_cast<float4*>(Alo + off) = l;
       }
-      tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y);
-      tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
-      int off = tc::canon_off(n, ku, W_KC / 4);
-      *reinterpret_cast<float4*>(Ahi + off) = h;
-      *reinterpret_cast<float4*>(Alo + off) = l;
     }
+    if (ch + 2 * (int64_t)gridDim.x < nchunks) load_chunk(ch + 2 * (int64_t)gridDim.x, gv, av);
     tc::fence_async_smem();
     __syncthreads();
     if (tid == 0) {
@@ -101,6 +121,14 @@ wgrad3x_kernel(const Wgrad3xArgs a) {
       }
       tc::mma_commit(bar_free + buf);
     }
+  };
+  float g0[GU][4], a0[AU][4], g1[GU][4], a1[AU][4];
+  load_chunk(blockIdx.x, g0, a0);
+  if ((int64_t)blockIdx.x + gridDim.x < nchunks) load_chunk((int64_t)blockIdx.x + gridDim.x, g1, a1);
+  uint32_t it = 0;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += 2 * (int64_t)gridDim.x, it += 2) {
+    body(ch, it, g0, a0);
+    body(ch + gridDim.x, it + 1, g1, a1);
   }
   if (tid == 0) tc::mma_commit(bar_acc);
   tc::mbar_wait(bar_acc, 0);
@@ -127,7 +155,7 @@ wgrad3x_kernel(const Wgrad3xArgs a) {
 
 int launch_wgrad3x(const Wgrad3xArgs& a, cudaStream_t st) {
   int Np = g_np(a.K + (a.dbias ? 1 : 0));
-  if (a.K < 1 || Np > 256 || a.cap < 0) { set_error("wgrad3x: bad shape K=%d", a.K); return FTRF_E_ARG; }
+  if (a.K < 1 || Np > 192 || a.cap < 0) { set_error("wgrad3x: bad shape K=%d", a.K); return FTRF_E_ARG; }
   size_t smem = (size_t)2 * (2 * 128 * W_KC + 2 * Np * W_KC) * 4 + 64;
   if (smem > 227 * 1024) { set_error("wgrad3x: K=%d needs %zu B of shared memory", a.K, smem); return FTRF_E_ARG; }
   if (a.cap == 0) return FTRF_OK;
