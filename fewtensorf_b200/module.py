@@ -142,7 +142,7 @@ class _Workspace:
 
 class _CallState:
     """Everything backward needs from one forward call."""
-    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj")
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask")
 
 
 class TensorBase(nn.Module):
@@ -286,14 +286,15 @@ class TensorBase(nn.Module):
 
     def grad_buffer(self, fresh: bool = False):
         """Flat fp32 gradient buffer (the NCCL all-reduce operand) + one view per parameter, in
-        `_all_params()` order; factor views are channels-last like the parameters."""
+        `_all_params()` order; factor views are channels-last like the parameters.  The persistent
+        buffer and its views are cached until the parameter set changes (upsample / shrink)."""
         params = self._all_params()
+        key = tuple((id(p), tuple(p.shape)) for p in params)
+        cache = getattr(self, "_grad_cache", None)
+        if not fresh and cache is not None and cache[0] == key and cache[1].device == params[0].device:
+            return cache[1], cache[2]
         total = sum(p.numel() for p in params)
-        buf = self._gradbuf
-        if fresh or buf is None or buf.numel() != total or buf.device != params[0].device:
-            buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
-            if not fresh:
-                self._gradbuf = buf
+        buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
         views, off = [], 0
         for p in params:
             n = p.numel()
@@ -304,6 +305,10 @@ class TensorBase(nn.Module):
             else:
                 views.append(flat.view(p.shape))
             off += n
+        if not fresh:
+            self._gradbuf = buf
+            self._grad_cache = (key, buf, views)
+            self._field_cache = {}
         return buf, views
 
     # ------------------------------------------------------------------ C-ABI argument marshalling
@@ -340,6 +345,21 @@ class TensorBase(nn.Module):
                 fs.mask[k] = mk.data_ptr()
 
     def _fill_field(self, mask, grad_views=None) -> FtrfField:
+        """FtrfField for this call.  Without FreeNeRF masks the struct only depends on the parameter
+        pointers, the alphaMask and the derived constants, so it is cached on exactly those."""
+        if mask is None:
+            key = (tuple(p.data_ptr() for p in self._all_params()), id(self.alphaMask), id(self._host),
+                   self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr())
+            cache = self.__dict__.setdefault("_field_cache", {})
+            f = cache.get(key)
+            if f is None:
+                if len(cache) > 8:
+                    cache.clear()
+                f = cache[key] = self._build_field(None, grad_views)
+            return f
+        return self._build_field(mask, grad_views)
+
+    def _build_field(self, mask, grad_views=None) -> FtrfField:
         self._ensure_layout()
         f = FtrfField()
         keep: List[torch.Tensor] = []
@@ -413,8 +433,8 @@ class TensorBase(nn.Module):
         c = self._counters_host
         return int(c[0]), int(c[1]), int(c[2])
 
-    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save) -> _CallState:
-        """March -> density -> integrate -> appearance -> shade -> composite, one C call, one sync."""
+    def _launch_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, caps=None) -> _CallState:
+        """Enqueue march -> density -> integrate -> appearance -> shade -> composite (one C call, no sync)."""
         if not rays.is_cuda:
             raise RuntimeError("fewtensorf_b200 needs CUDA tensors (no CPU path)")
         N = rays.shape[0]
@@ -428,30 +448,53 @@ class TensorBase(nn.Module):
         depth = torch.empty(N, dtype=torch.float32, device=rays.device)
         call.rgb_map, call.depth_map = rgb.data_ptr(), depth.data_ptr()
         key = (N, S, bool(save))
-        cap_s, cap_a = self._cap_hint.get(key, (min(N * S, max(N * 64, 1 << 16)), max(N * 16, 1 << 14)))
+        if caps is None:
+            caps = self._cap_hint.get(key, (min(N * S, max(N * 64, 1 << 16)), max(N * 16, 1 << 14)))
+        call.cap_samples, call.cap_app = caps
         wsobj = self._ws_train if save else self._ws_eval
         if save and wsobj.busy:
             wsobj = _Workspace()           # an earlier graph still owns the cached buffer
-        while True:
-            call.cap_samples, call.cap_app = cap_s, cap_a
+        lkey = (key, caps, field.shading, field.in_dim, field.app_dim)
+        nbytes = self._layout_cache.get(lkey) if hasattr(self, "_layout_cache") else None
+        if nbytes is None:
             nbytes = lib.ftrf_workspace_layout(C.byref(field), C.byref(call), None)
-            ws = wsobj.get(nbytes, rays.device)
-            check(lib.ftrf_forward(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream()), "forward")
-            need_s, need_a, flags = self._read_counters(ws)
-            if flags == 0:
-                break
-            cap_s = max(cap_s, int(need_s * 1.25) + 1024) if flags & 1 else cap_s
-            cap_a = max(cap_a, int(need_a * 1.25) + 1024) if (flags & 2 or flags & 1) else cap_a
-            cap_s = min(cap_s, N * S)
-            cap_a = min(cap_a, N * S)
-        self._cap_hint[key] = (max(cap_s, min(N * S, int(need_s * 1.1) + 1024)),
-                               max(cap_a, min(N * S, int(need_a * 1.1) + 1024)))
+            self.__dict__.setdefault("_layout_cache", {})[lkey] = nbytes
+        ws = wsobj.get(nbytes, rays.device)
+        check(lib.ftrf_forward(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream()), "forward")
         st = _CallState()
         st.field, st.call, st.ws, st.ws_bytes, st.wsobj = field, call, ws, ws.numel(), wsobj
         st.keep = (rays, jitter, rgb, depth)
-        st.n_samples, st.n_valid = need_s, need_a
-        self._last_call = st
+        st.mask = mask
+        st.n_samples = st.n_valid = -1
         return st
+
+    def _finish_forward(self, st: _CallState) -> bool:
+        """The one host sync of a call: read the counters; returns False (and grows the capacity hints)
+        if a packed list overflowed and the call has to be repeated."""
+        need_s, need_a, flags = self._read_counters(st.ws)
+        N, S = st.call.n_rays, st.call.n_samples
+        key = (N, S, bool(st.call.save_for_backward))
+        cap_s, cap_a = st.call.cap_samples, st.call.cap_app
+        st.n_samples, st.n_valid = need_s, need_a
+        if flags:
+            if flags & 1:
+                cap_s = max(cap_s, int(need_s * 1.25) + 1024)
+                cap_a = max(cap_a, 2 * cap_a)      # the shaded count of a truncated sample list is a lower bound
+            if flags & 2:
+                cap_a = max(cap_a, int(need_a * 1.25) + 1024)
+            self._cap_hint[key] = (min(cap_s, N * S), min(cap_a, N * S))
+            return False
+        self._cap_hint[key] = (max(cap_s, min(N * S, int(need_s * 1.1) + 1024)),
+                               max(cap_a, min(N * S, int(need_a * 1.1) + 1024)))
+        self._last_call = st
+        return True
+
+    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save) -> _CallState:
+        """Forward with overflow handling: launch, sync once, repeat with larger lists if needed."""
+        while True:
+            st = self._launch_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save)
+            if self._finish_forward(st):
+                return st
 
     def workspace_section(self, st: _CallState, name: str, dtype, count: int) -> torch.Tensor:
         """Typed view of one FTRF_WS_* section of a finished call (used by the stage parity tests)."""
@@ -462,19 +505,12 @@ class TensorBase(nn.Module):
         return st.ws[o:o + nbytes].view(dtype)
 
     def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views) -> None:
-        g_rgb = g_rgb.contiguous().float()
-        field = self._fill_field(None, grad_views)
-        # masks / alphaMask exactly as in the forward call
-        for name in ("mask", "mask_stride"):
-            for fs_new, fs_old in ((field.den, st.field.den), (field.app, st.field.app)):
-                for k in range(3):
-                    getattr(fs_new, name)[k] = getattr(fs_old, name)[k]
-        for i in range(3):
-            field.enc_mask[i], field.enc_mask_len[i] = st.field.enc_mask[i], st.field.enc_mask_len[i]
-        field._keep = st.field._keep
+        if g_rgb.dtype != torch.float32 or not g_rgb.is_contiguous():
+            g_rgb = g_rgb.contiguous().float()
+        field = self._fill_field(st.mask, grad_views)
         st.call.g_rgb_map = g_rgb.data_ptr()
         check(lib.ftrf_backward(C.byref(field), C.byref(st.call), st.ws.data_ptr(), st.ws_bytes, _stream()), "backward")
-        st.keep = st.keep + (g_rgb,)
+        st.keep = st.keep + (g_rgb, field)
 
     # ------------------------------------------------------------------ the hot path
     def _draw_rng(self, n_rays, S, is_train, ndc_ray, white_bg, device):
@@ -491,7 +527,14 @@ class TensorBase(nn.Module):
             jitter = torch.rand(n_rays, 1).reshape(-1)
         add_bg = bool(white_bg or (is_train and bool(torch.rand((1,)) < 0.5)))
         if jitter is not None:
-            jitter = jitter.pin_memory().to(device, non_blocking=True)
+            # staged through a persistent pinned buffer; every call ends with a stream sync before the
+            # next draw can overwrite it
+            n = jitter.numel()
+            pin = getattr(self, "_jitter_pin", None)
+            if pin is None or pin.numel() < n:
+                pin = self._jitter_pin = torch.empty(max(n, 1 << 16), dtype=torch.float32).pin_memory()
+            pin[:n].copy_(jitter)
+            jitter = pin[:n].to(device, non_blocking=True)
         return jitter, add_bg
 
     def forward(self, rays_chunk, mask, white_bg=True, is_train=False, ndc_ray=False, N_samples=-1):
@@ -528,18 +571,24 @@ class TensorBase(nn.Module):
             raise RuntimeError("train_step: batch too large for one launch sequence; split the batch")
         jitter, add_bg = self._draw_rng(N, S, True, ndc_ray, white_bg, rays.device)
         buf, views = self.grad_buffer()
-        buf.zero_()
-        st = self._run_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
-        rgb = st.keep[2]
         loss = torch.empty(1, dtype=torch.float32, device=rays.device)
-        g_rgb = torch.empty_like(rgb)
-        check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
-                                _stream()), "mse_loss")
-        if grad_scale != 1.0:
-            g_rgb.mul_(grad_scale)
-        self._run_backward(st, g_rgb, views)
+        g_rgb = torch.empty(N, 3, dtype=torch.float32, device=rays.device)
+        while True:
+            # everything is enqueued back to back (the kernels read the sample counts from device memory);
+            # the single host sync comes at the end and only decides whether a list overflowed
+            buf.zero_()
+            st = self._launch_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
+            rgb = st.keep[2]
+            check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
+                                    _stream()), "mse_loss")
+            if grad_scale != 1.0:
+                g_rgb.mul_(grad_scale)
+            self._run_backward(st, g_rgb, views)
+            if self._finish_forward(st):
+                break
         for p, v in zip(self._all_params(), views):
-            p.grad = v
+            if p.grad is not v:
+                p.grad = v
         return loss[0], st.n_valid
 
     # ------------------------------------------------------------------ helpers kept from the reference API
@@ -647,7 +696,8 @@ class _RenderFn(torch.autograd.Function):
         model._run_backward(st, g_rgb, views)
         st.wsobj.busy = False
         ctx.st = None
-        grads = tuple(v if p.requires_grad else None for p, v in zip(params, views))
+        # fresh aliases of the cached views: autograd can adopt them as .grad without a copy
+        grads = tuple((v.detach() if p.requires_grad else None) for p, v in zip(params, views))
         return (None,) * 8 + grads
 
 
