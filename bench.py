@@ -46,11 +46,11 @@ def synthetic_rays(n, seed):
     return torch.cat([o, d], -1), torch.rand(n, 3, generator=g)
 
 
-def build_model(device, grid=GRID, mask_grid=MASK_GRID):
+def build_model(device, grid=GRID, mask_grid=MASK_GRID, shading="MLP_Fea"):
     import fewtensorf_b200 as ft
     torch.manual_seed(20211202)                       # train.py:550
     aabb = torch.tensor([[-1.5] * 3, [1.5] * 3], device=device)
-    m = ft.TensorVMSplit(ARGS, aabb, [grid] * 3, [2.0, 6.0], device)
+    m = ft.TensorVMSplit(dict(ARGS, shadingMode=shading), aabb, [grid] * 3, [2.0, 6.0], device)
     with torch.no_grad():                             # planted box, SURVEY section 8(d)
         ind = (torch.linspace(-1.5, 1.5, grid).abs() < 0.6).float().to(device)
         m.density_plane[0][0, 0] = 11.0 * ind[:, None] * ind[None, :]
@@ -58,6 +58,68 @@ def build_model(device, grid=GRID, mask_grid=MASK_GRID):
     if mask_grid:
         m.updateAlphaMask((mask_grid,) * 3)
     return m
+
+
+def camera_rays(device, h=800, w=800, elev_deg=30.0, azim_deg=45.0, radius=4.0311):
+    """One 800x800 NeRF-synthetic test view: focal from camera_angle_x = 0.6911112
+    (dataLoader/blender.py:53), directions per get_ray_directions (+0.5 px, ray_utils.py:34-40) normalised
+    (blender.py:59), rotated by an OpenCV-convention c2w looking at the origin (ray_utils.py:79-85)."""
+    import math
+    focal = 0.5 * 800 / math.tan(0.5 * 0.6911112) * (w / 800)
+    el, az = math.radians(elev_deg), math.radians(azim_deg)
+    o = torch.tensor([math.cos(el) * math.cos(az), math.cos(el) * math.sin(az), math.sin(el)]) * radius
+    fwd = -o / o.norm()
+    right = torch.linalg.cross(fwd, torch.tensor([0.0, 0.0, 1.0]))
+    right = right / right.norm()
+    down = torch.linalg.cross(fwd, right)
+    c2w = torch.stack([right, down, fwd], 1).to(device)           # columns: x right, y down, z forward
+    j, i = torch.meshgrid(torch.arange(h, device=device, dtype=torch.float32) + 0.5,
+                          torch.arange(w, device=device, dtype=torch.float32) + 0.5, indexing="ij")
+    d = torch.stack([(i - w / 2) / focal, (j - h / 2) / focal, torch.ones_like(i)], -1)
+    d = d / d.norm(dim=-1, keepdim=True)
+    rays_d = (d @ c2w.T).reshape(-1, 3)
+    rays_o = o.to(device).expand_as(rays_d)
+    return torch.cat([rays_o, rays_d], -1).contiguous()
+
+
+def render_leg(dev, frames=5):
+    """Second half of BASELINE.json's metric: 800x800 test-view render, ms/frame, rays resident in HBM,
+    through OctreeRender_trilinear_fast(is_train=False, N_samples=-1) on this GPU's rows of the image
+    (row-interleaved across ranks).  Config 1 of BASELINE.json (SH shading) is the
+    headline; the MLP_Fea model of the training bench is rendered too."""
+    import torch.distributed as dist
+    import fewtensorf_b200 as ft
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    rays = camera_rays(dev)
+    rows = torch.arange(rank, 800, world, device=dev)
+    mine = rays.view(800, 800, 6)[rows].reshape(-1, 6).contiguous()
+    out = {}
+    for shading in ("SH", "MLP_Fea"):
+        model = build_model(dev, shading=shading)
+        def frame():
+            with torch.no_grad():
+                return ft.OctreeRender_trilinear_fast(mine, model, None, chunk=1 << 20, N_samples=-1, white_bg=True,
+                                                      is_train=False, device=dev)
+        for _ in range(2):
+            res = frame()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(frames):
+            res = frame()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / frames], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        st = model._last_call
+        out[shading] = {"ms_per_frame": float(t), "shaded_samples": float(res[5]),
+                        "mean_rgb": float(res[0].mean()), "rays_this_gpu": int(mine.shape[0])}
+        del model
+    return out
 
 
 class ClockSampler(threading.Thread):
@@ -296,6 +358,8 @@ def run_gpu(args):
         dist.all_reduce(e2e_f, op=dist.ReduceOp.MAX)
     e2e_fused_rps = RAYS_PER_GPU * world * args.steps / float(e2e_f)
 
+    render = None if args.no_render else render_leg(dev)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -330,6 +394,10 @@ def run_gpu(args):
                    "train_step_api_value": e2e_fused_rps},
            "gpu_launches": 14 * args.steps, "roofline": roof, "stages": stages,
            "samples": {"valid_per_step": vd, "shaded_per_step": va, "loss": float(last[0])}}
+    if render:
+        out["render"] = {"metric": "800x800 render ms/frame (N_samples=-1, rays in HBM, rows interleaved over GPUs)",
+                         "unit": "ms", "higher_is_better": False,
+                         "sh": render["SH"], "mlp_fea": render["MLP_Fea"]}
     if cpu:
         out["cpu_baseline"] = cpu
     print(json.dumps(out))
@@ -344,6 +412,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-render", action="store_true", help="skip the 800x800 render leg")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps > 10:

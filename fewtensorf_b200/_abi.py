@@ -17,7 +17,7 @@ ACT_SOFTPLUS, ACT_RELU = 0, 1
 SHADING_KINDS = {"MLP_Fea": SHADE_MLP_FEA, "MLP_PE": SHADE_MLP_PE, "MLP": SHADE_MLP, "SH": SHADE_SH}
 
 WS_NAMES = ["COUNTERS", "TMIN", "RAY_OFF", "RAY_CNT", "ACC", "RGB_PRE", "S_RAY", "S_IDX", "S_SIGMA", "S_W", "S_T",
-            "S_APP", "S_GSIG", "A_SLOT", "A_FEAT", "A_RGB", "A_H1", "A_H2", "A_GRGB", "A_GH1", "A_GH2", "A_GFEAT", "A_X", "A_GX"]
+            "S_APP", "S_GSIG", "A_SLOT", "A_FEAT", "A_RGB", "A_H1", "A_H2", "A_GRGB", "A_GH1", "A_GH2", "A_GFEAT", "A_X", "A_GX", "WIMG"]
 WS_COUNT = len(WS_NAMES)
 WS = {n: i for i, n in enumerate(WS_NAMES)}
 
@@ -48,7 +48,7 @@ class FtrfField(C.Structure):
         ("near_", C.c_float), ("far_", C.c_float),
         ("distance_scale", C.c_float), ("density_shift", C.c_float), ("weight_thres", C.c_float),
         ("has_alpha_mask", C.c_int32), ("am_dim", C.c_int32 * 3), ("am_aabb0", C.c_float * 3),
-        ("am_inv", C.c_float * 3), ("am_bits", C.c_void_p),
+        ("am_inv", C.c_float * 3), ("am_bits", C.c_void_p), ("am_coarse", C.c_void_p),
         ("den", FtrfFactorSet), ("app", FtrfFactorSet),
         ("basis", _f32p), ("g_basis", _f32p),
         ("w1", _f32p), ("b1", _f32p), ("w2", _f32p), ("b2", _f32p), ("w3", _f32p), ("b3", _f32p),
@@ -71,7 +71,7 @@ EXPORTS = [
     "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
-    "ftrf_pack_alpha_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
+    "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
     "ftrf_profile_stage_name", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
@@ -102,6 +102,10 @@ def _load():
     lib.ftrf_alpha_mask_words.argtypes = [C.c_int32, C.c_int32, C.c_int32]
     lib.ftrf_pack_alpha_mask.restype = C.c_int
     lib.ftrf_pack_alpha_mask.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.ftrf_alpha_mask_coarse_words.restype = C.c_size_t
+    lib.ftrf_alpha_mask_coarse_words.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    lib.ftrf_build_coarse_mask.restype = C.c_int
+    lib.ftrf_build_coarse_mask.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_density_at.restype = C.c_int
     lib.ftrf_density_at.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.ftrf_profile_enable.restype = C.c_int

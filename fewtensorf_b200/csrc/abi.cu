@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "common.cuh"
+#include "fused.cuh"
 
 namespace ftrf {
 
@@ -65,7 +66,7 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
   sz[FTRF_WS_A_SLOT] = A * 4;
   sz[FTRF_WS_A_FEAT] = A * D * 4;
   sz[FTRF_WS_A_RGB] = A * 12;
-  const size_t LDX = (size_t)((f.in_dim + 7) & ~7);
+  const size_t LDX = (size_t)((f.in_dim + 1 + 7) & ~7);
   sz[FTRF_WS_A_H1] = mlp ? A * H * 4 : 0;
   sz[FTRF_WS_A_H2] = mlp ? A * H * 4 : 0;
   sz[FTRF_WS_A_X] = mlp ? A * LDX * 4 : 0;
@@ -74,6 +75,7 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
   sz[FTRF_WS_A_GH1] = (train && mlp) ? A * H * 4 : 0;
   sz[FTRF_WS_A_GH2] = (train && mlp) ? A * H * 4 : 0;
   sz[FTRF_WS_A_GFEAT] = train ? A * D * 4 : 0;
+  sz[FTRF_WS_WIMG] = mlp ? fused_wimg_bytes() : 0;
   size_t cur = 0, offs[FTRF_WS_COUNT];
   for (int i = 0; i < FTRF_WS_COUNT; ++i) {
     offs[i] = cur;
@@ -106,6 +108,7 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
     ws->a_gfeat = (float*)(b + offs[FTRF_WS_A_GFEAT]);
     ws->a_x = (float*)(b + offs[FTRF_WS_A_X]);
     ws->a_gx = (float*)(b + offs[FTRF_WS_A_GX]);
+    ws->wimg = mlp ? (float*)(b + offs[FTRF_WS_WIMG]) : nullptr;
     ws->ldx = (int)LDX;
   }
   return cur;

@@ -38,6 +38,7 @@ struct Ws {
   float* a_gfeat;
   float* a_x;      // [cap_app][ldx]  MLP input rows (tensor-core path)
   float* a_gx;     // [cap_app][ldx]  dL/dX
+  float* wimg;     // weight images of the fused MLP kernels (fused.cuh)
   int ldx;
 };
 
@@ -149,6 +150,13 @@ __device__ __forceinline__ bool alpha_mask_keep(const FtrfField& f, const float 
     if (!(fl >= -2.f && fl <= 1e9f)) return false;
     i0[k] = (int)fl;
     up[k] = __fsub_rn(fx[k], fl) > 0.f;
+  }
+  if (f.am_coarse && i0[0] >= 0 && i0[1] >= 0 && i0[2] >= 0 && i0[0] < f.am_dim[0] && i0[1] < f.am_dim[1] && i0[2] < f.am_dim[2]) {
+    // both interpolation corners along every axis lie in [8c, 8c+8]: covered by the coarse bit of block c
+    const int CX = (f.am_dim[0] + 7) >> 3, CY = (f.am_dim[1] + 7) >> 3, cxw = (CX + 31) >> 5;
+    const int cx = i0[0] >> 3, cy = i0[1] >> 3, cz = i0[2] >> 3;
+    uint32_t w = __ldg(f.am_coarse + ((size_t)cz * CY + cy) * cxw + (cx >> 5));
+    if (!((w >> (cx & 31)) & 1u)) return false;
   }
 #pragma unroll
   for (int dz = 0; dz < 2; ++dz) {

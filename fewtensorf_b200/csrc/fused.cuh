@@ -1,0 +1,88 @@
+// fused.cuh — shared definitions of the fused shading-MLP kernels (k_shade_fused.cu) and the kernels
+// that consume what they save for backward.
+//
+// INTERNAL COLUMN ORDER of the MLP input.  The first layer is linear, so the columns of X (and of W1)
+// may be permuted freely.  The fused kernels use an order in which sin(a) and cos(a) of the same
+// argument are neighbours, so one sincosf() yields two columns and every 16-byte unit of the operand
+// tile is complete when it is written:
+//     [ feat(0..D) | view(0..3) | (pad to even) | block0 pairs | block1 pairs | ... | zero pad to 8 ]
+// pair q = ch*F + f of a PE block holds (sin, cos) of src[ch] * 2^f  (models/mlp.py:8-13 flattens
+// channel-major / frequency-minor, [sin | cos]).  `orig[]` maps an internal column to the reference's
+// column (mlp.py:41-64 / :88-101 / :127-149 concat order), -1 for padding.
+#pragma once
+#include "shade_common.cuh"
+
+namespace ftrf {
+
+constexpr int FZ_MAX_K = 192;        // widest internal MLP input supported by the fused path
+constexpr int FZ_MAX_SRC = 40;       // D + 6 staged source values per sample
+
+enum { PK_ZERO = 0, PK_COPY2 = 1, PK_COPY1 = 2, PK_TRIG = 3 };
+
+struct PairRec {          // two neighbouring internal columns
+  uint8_t kind;           // PK_*
+  uint8_t sa, sb;         // source slots ([feat | view | pos] staged row); TRIG uses sa only
+  uint8_t fexp;           // TRIG: argument scale 2^fexp
+  uint8_t msrc;           // TRIG: encoding-mask table (SRC_*)
+  uint8_t pad_;
+  int16_t ma, mb;         // TRIG: index of the sin / cos column inside that mask vector
+};
+
+struct FusedSpec {
+  int kp;                 // internal width, multiple of 8
+  int n1;                 // 32-column chunks of layer 1
+  int nsrc;               // D + 6
+  int D;
+  int need_pos;
+  int blk_icol0[3];       // internal column of pair 0 of each PE block (InSpec block order)
+  int16_t orig[FZ_MAX_K];
+  PairRec pair[FZ_MAX_K / 2];
+};
+
+// Returns false when the fused path does not cover this configuration (caller falls back).
+inline bool make_fused_spec(const FtrfField& f, const InSpec& sp, FusedSpec& fs) {
+  fs = FusedSpec{};
+  const int D = sp.D;
+  if (D + 6 > FZ_MAX_SRC || f.feature_c != FC) return false;
+  int col = 0;
+  auto push = [&](PairRec r, int o0, int o1) {
+    if (col + 2 > FZ_MAX_K) { col += 2; return; }
+    fs.pair[col / 2] = r;
+    fs.orig[col] = (int16_t)o0;
+    fs.orig[col + 1] = (int16_t)o1;
+    col += 2;
+  };
+  const int ncopy = D + 3;
+  for (int i = 0; i + 1 < ncopy; i += 2) push(PairRec{PK_COPY2, (uint8_t)i, (uint8_t)(i + 1), 0, 0, 0, 0, 0}, i, i + 1);
+  if (ncopy & 1) push(PairRec{PK_COPY1, (uint8_t)(ncopy - 1), 0, 0, 0, 0, 0, 0}, ncopy - 1, -1);
+  for (int b = 0; b < sp.nblk; ++b) {
+    const PeBlock& pb = sp.b[b];
+    const int half = pb.F * pb.C;
+    const int s0 = pb.src == SRC_FEA ? 0 : (pb.src == SRC_VIEW ? D : D + 3);
+    fs.blk_icol0[b] = col;
+    for (int ch = 0; ch < pb.C; ++ch)
+      for (int fq = 0; fq < pb.F; ++fq) {
+        int q = ch * pb.F + fq;
+        push(PairRec{PK_TRIG, (uint8_t)(s0 + ch), 0, (uint8_t)fq, (uint8_t)pb.src, 0, (int16_t)q, (int16_t)(half + q)},
+             pb.col0 + q, pb.col0 + half + q);
+      }
+  }
+  if (col > FZ_MAX_K) return false;
+  while (col & 7) push(PairRec{PK_ZERO, 0, 0, 0, 0, 0, 0, 0}, -1, -1);
+  fs.kp = col;
+  fs.n1 = (col + 31) / 32;
+  fs.nsrc = D + 6;
+  fs.D = D;
+  fs.need_pos = sp.need_pos;
+  return true;
+}
+
+// Weight images in the workspace (FTRF_WS_WIMG), all pre-split into tf32 hi / lo and laid out as
+// UMMA K-major no-swizzle [128 rows x 32 k] chunks (hi 16 KB then lo 16 KB), ready for bulk copies:
+//   forward : n1 chunks of W1 (rows = hidden unit, k = internal input column), then 4 chunks of W2.
+constexpr size_t FZ_CHUNK_BYTES = 2u * 128u * 32u * 4u;     // 32 KB
+inline size_t fused_wimg_bytes() { return (size_t)(FZ_MAX_K / 32 + 4) * FZ_CHUNK_BYTES + (size_t)FC * FZ_MAX_K * 4; }
+
+int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
+
+}  // namespace ftrf

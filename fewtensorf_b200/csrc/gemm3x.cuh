@@ -24,6 +24,8 @@ struct Wgrad3xArgs {
   const int32_t* count; int64_t cap;
   float* dW; int ldw;                    // [128][ldw]
   float* dbias;                          // [128] or null
+  int use_perm;                          // dW column of input column k is perm[k] (-1: dropped)
+  int16_t perm[192];
 };
 
 __host__ __device__ inline int g_np(int N) { return (N + 15) & ~15; }

@@ -63,6 +63,9 @@ __device__ __forceinline__ float activate(const FtrfField& f, float feat) {
 
 __global__ void __launch_bounds__(256)
 density_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  // a sample list that overflowed has unwritten holes (rays that did not fit): the host repeats the
+  // call with a larger list, nothing may be read from this one
+  if (ws.counters[2] & 1) return;
   const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
   const int sub = threadIdx.x & (GS - 1);
   const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
@@ -111,6 +114,7 @@ density_at_kernel(const FtrfField f, const float* __restrict__ xyz, int64_t n, f
 // red.global.add.v4.f32 (one 16-byte reduction per corner per chunk).
 __global__ void __launch_bounds__(256)
 density_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  if (ws.counters[2] & 1) return;
   const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
   const int sub = threadIdx.x & (GS - 1);
   const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;

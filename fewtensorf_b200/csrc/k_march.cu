@@ -98,7 +98,48 @@ __global__ void pack_mask_kernel(const float* __restrict__ vol, int X, int Y, in
   }
 }
 
+// Coarse occupancy: one bit per 8x8x8 block of texels, set iff any texel of the block OR of its +1
+// neighbours in x / y / z is set.  A sample whose lower interpolation corner lies in a block with a
+// clear bit cannot touch a set texel, so the march kernel rejects it with one L1-resident load
+// instead of eight dependent ones; samples in blocks with a set bit take the exact test.
+__global__ void coarse_mask_kernel(const uint32_t* __restrict__ bits, int X, int Y, int Z, uint32_t* __restrict__ coarse) {
+  const int xw = (X + 31) >> 5;
+  const int CX = (X + 7) >> 3, CY = (Y + 7) >> 3, CZ = (Z + 7) >> 3, cxw = (CX + 31) >> 5;
+  const int64_t words = (int64_t)cxw * CY * CZ;
+  const int lane = threadIdx.x & 31;
+  const int64_t gw = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, wstride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = gw; w < words; w += wstride) {
+    const int cw = (int)(w % cxw), cy = (int)((w / cxw) % CY), cz = (int)(w / ((int64_t)cxw * CY));
+    const int cx = cw * 32 + lane;
+    bool on = false;
+    if (cx < CX) {
+      const int x0 = cx * 8, x1 = min(x0 + 8, X - 1);
+      for (int z = cz * 8; z <= min(cz * 8 + 8, Z - 1) && !on; ++z)
+        for (int y = cy * 8; y <= min(cy * 8 + 8, Y - 1) && !on; ++y) {
+          const uint32_t* row = bits + ((size_t)z * Y + y) * xw;
+          for (int x = x0; x <= x1; ++x)
+            if ((row[x >> 5] >> (x & 31)) & 1u) { on = true; break; }
+        }
+    }
+    uint32_t b = __ballot_sync(FULL_MASK, on);
+    if (lane == 0) coarse[w] = b;
+  }
+}
+
 }  // namespace ftrf
+
+extern "C" size_t ftrf_alpha_mask_coarse_words(int32_t x, int32_t y, int32_t z) {
+  return (size_t)(((x + 7) / 8 + 31) / 32) * (size_t)((y + 7) / 8) * (size_t)((z + 7) / 8);
+}
+
+extern "C" int ftrf_build_coarse_mask(const uint32_t* bits, int32_t x, int32_t y, int32_t z, uint32_t* coarse, void* stream) {
+  if (!bits || !coarse || x <= 0 || y <= 0 || z <= 0) { ftrf::set_error("build_coarse_mask: bad argument"); return FTRF_E_ARG; }
+  int64_t words = (int64_t)ftrf_alpha_mask_coarse_words(x, y, z);
+  int64_t blocks = (words * 32 + 255) / 256;
+  int grid = (int)(blocks < FTRF_SMS * 16 ? blocks : FTRF_SMS * 16);
+  ftrf::coarse_mask_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(bits, x, y, z, coarse);
+  return ftrf::check_launch("build_coarse_mask");
+}
 
 extern "C" size_t ftrf_alpha_mask_words(int32_t x, int32_t y, int32_t z) {
   return (size_t)((x + 31) / 32) * (size_t)y * (size_t)z;

@@ -1,0 +1,337 @@
+// k_shade_fused.cu — stage 3 forward as ONE persistent, warp-specialised tcgen05 kernel:
+//   positional encoding (+ FreeNeRF encoding masks) -> Linear+ReLU -> Linear+ReLU -> Linear -> sigmoid
+// (models/mlp.py:8-13, :41-69, :88-107, :127-155) for a pair of 128-sample tiles at a time, without
+// sending X / h1 / h2 through HBM (they are written out only when saved for backward).
+//
+//   warps 0-7  (256 threads, one per sample row; warps 0-3 = sub-tile a, 4-7 = sub-tile b):
+//              build the encoded input rows chunk by chunk (32 columns) straight into the UMMA
+//              operand ring (tf32 hi / lo split in registers), later turn the layer-1 accumulator
+//              (tcgen05.ld) into the layer-2 operand chunks (bias + ReLU + split), and finish with
+//              the layer-2 epilogue: bias + ReLU, the 128->3 layer on CUDA cores, sigmoid.
+//   warp 8     one elected lane issues tcgen05.mma.kind::tf32 (3xTF32: Al*Bh + Ah*Bl + Ah*Bh, fp32
+//              accumulate in TMEM, fp32-grade accuracy) for every (activation chunk, weight chunk).
+//   warp 9     one elected lane streams the pre-split weight chunks (32 KB each, prepared once per
+//              call by prep_weights_kernel) from L2 into a shared-memory ring with cp.async.bulk
+//              (TMA), completion on mbarriers.  Each weight chunk serves both sub-tiles.
+// Roles meet only through mbarriers: a_full / a_empty (operand ring), w_full / w_empty (weight
+// ring), acc1_full / acc2_full (tcgen05.commit).  TMEM: acc1[a,b] columns 0-255, acc2[a,b] 256-511.
+#include "fused.cuh"
+#include "tc.cuh"
+
+namespace ftrf {
+
+constexpr int FZ_A_STAGES = 2;
+constexpr int FZ_W_STAGES = 2;
+constexpr int FZ_CHUNK_FLOATS = 128 * 32;              // one hi (or lo) [128 x 32] chunk
+constexpr int FZ_THREADS = 320;
+constexpr int FZ_PAIR_ROWS = 256;
+
+// ------------------------------------------------------------------------------------------ prep
+// Weight images (see fused.cuh).  One launch per forward call: the weights change every step.
+__global__ void __launch_bounds__(256)
+prep_weights_kernel(const FtrfField f, const FusedSpec fs, float* __restrict__ img, float* __restrict__ w1p, int in_dim) {
+  const int nchunks = fs.n1 + 4;
+  const int total = nchunks * 128 * 8;                  // (chunk, row n, 16-byte unit ku)
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int ku = e & 7, n = (e >> 3) & 127, ch = e >> 10;
+    float hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v;
+      if (ch < fs.n1) {
+        int k = ch * 32 + ku * 4 + j;
+        int o = k < fs.kp ? fs.orig[k] : -1;
+        v = o >= 0 ? __ldg(f.w1 + (size_t)n * in_dim + o) : 0.f;
+      } else {
+        v = __ldg(f.w2 + (size_t)n * FC + (ch - fs.n1) * 32 + ku * 4 + j);
+      }
+      tc::split_tf32(v, hi[j], lo[j]);
+    }
+    float* base = img + (size_t)ch * (2 * FZ_CHUNK_FLOATS);
+    const int off = tc::canon_off(n, ku, 8);
+    *reinterpret_cast<float4*>(base + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<float4*>(base + FZ_CHUNK_FLOATS + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  if (w1p) {     // plain fp32 W1 in internal column order, [128][kp] (backward: g_X = g_h1 W1)
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < FC * fs.kp; e += gridDim.x * blockDim.x) {
+      int n = e / fs.kp, k = e - n * fs.kp, o = fs.orig[k];
+      w1p[e] = o >= 0 ? __ldg(f.w1 + (size_t)n * in_dim + o) : 0.f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ PTX bits
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(tc::smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(tc::smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void split4(const float v[4], float4& h, float4& l) {
+  tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y);
+  tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+}
+
+struct SPair { int meta; float scale, ma, mb; };     // meta = kind | sa << 8 | sb << 16
+
+// ------------------------------------------------------------------------------------------ kernel
+__global__ void __launch_bounds__(FZ_THREADS, 1)
+shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [A_STAGES][2 subs][hi, lo][4096]
+  float* w_ring = a_ring + (size_t)FZ_A_STAGES * 4 * FZ_CHUNK_FLOATS;               // [W_STAGES][hi, lo][4096]
+  float* s_b1 = w_ring + (size_t)FZ_W_STAGES * 2 * FZ_CHUNK_FLOATS;                 // [128]
+  float* s_b2 = s_b1 + FC;                                                          // [128]
+  float* s_w3 = s_b2 + FC;                                                          // [3][128]
+  SPair* s_pair = reinterpret_cast<SPair*>(s_w3 + 3 * FC);                          // [kp/2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_pair + FZ_MAX_K / 2);
+  uint64_t* a_full = bars;                       // [A_STAGES]  8 warp arrivals
+  uint64_t* a_empty = a_full + FZ_A_STAGES;      // [A_STAGES]  tcgen05.commit
+  uint64_t* w_full = a_empty + FZ_A_STAGES;      // [W_STAGES]  expect_tx + bulk copy
+  uint64_t* w_empty = w_full + FZ_W_STAGES;      // [W_STAGES]  tcgen05.commit
+  uint64_t* acc_full = w_empty + FZ_W_STAGES;    // [2]         layer 1, layer 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int64_t npairs = (n + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
+  if ((int64_t)blockIdx.x >= npairs) return;
+  const int my_pairs = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int n1 = fs.n1, nck = n1 + 4;
+
+  if (tid == 0) {
+    for (int i = 0; i < FZ_A_STAGES; ++i) { tc::mbar_init(a_full + i, 8); tc::mbar_init(a_empty + i, 1); }
+    for (int i = 0; i < FZ_W_STAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
+    tc::mbar_init(acc_full + 0, 1);
+    tc::mbar_init(acc_full + 1, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
+  for (int e = tid; e < FC; e += FZ_THREADS) { s_b1[e] = __ldg(f.b1 + e); s_b2[e] = __ldg(f.b2 + e); }
+  for (int e = tid; e < 3 * FC; e += FZ_THREADS) s_w3[e] = __ldg(f.w3 + e);
+  for (int e = tid; e < fs.kp / 2; e += FZ_THREADS) {
+    const PairRec r = fs.pair[e];
+    SPair p;
+    p.meta = (int)r.kind | ((int)r.sa << 8) | ((int)r.sb << 16);
+    p.scale = (float)(1 << r.fexp);
+    p.ma = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.ma) : 1.f;
+    p.mb = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.mb) : 1.f;
+    s_pair[e] = p;
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 8) {
+    // =============================================================== compute warps (one row per thread)
+    const int sub = warp >> 2, q = warp & 3, r_in = q * 32 + lane;
+    const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
+    const uint32_t t_acc1 = tmem + t_lane + (uint32_t)(sub * 128);
+    const uint32_t t_acc2 = tmem + t_lane + (uint32_t)(256 + sub * 128);
+    const float b3[3] = {__ldg(f.b3), __ldg(f.b3 + 1), __ldg(f.b3 + 2)};
+    const bool save = c.save_for_backward != 0;
+    const int D = fs.D;
+    uint32_t ac = 0;                                   // operand-ring chunk counter
+    for (int it = 0; it < my_pairs; ++it) {
+      const int64_t pair_id = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+      const int64_t row = pair_id * FZ_PAIR_ROWS + sub * 128 + r_in;
+      const bool live = row < n;
+      // ---- stage this row's sources: [feat(D) | view(3) | pos(3)]
+      float src[FZ_MAX_SRC];
+      if (live) {
+        const float* fp = ws.a_feat + row * D;
+        for (int k = 0; k < D; ++k) src[k] = fp[k];
+        float v[3], p[3];
+        shade_geometry(f, c, ws, row, v, p);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { src[D + k] = v[k]; src[D + 3 + k] = p[k]; }
+      } else {
+        for (int k = 0; k < D + 6; ++k) src[k] = 0.f;
+      }
+      // ---- layer-1 operand chunks
+      for (int ch = 0; ch < n1; ++ch, ++ac) {
+        const int stg = ac % FZ_A_STAGES;
+        tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
+        float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
+        float* Alo = Ahi + FZ_CHUNK_FLOATS;
+        const int units = min(8, (fs.kp - ch * 32) / 4);
+        for (int u = 0; u < units; ++u) {
+          float v[4];
+#pragma unroll
+          for (int p2 = 0; p2 < 2; ++p2) {
+            const SPair pr = s_pair[(ch * 32 + u * 4) / 2 + p2];
+            const int kind = pr.meta & 0xff, sa = (pr.meta >> 8) & 0xff, sb = (pr.meta >> 16) & 0xff;
+            float x0 = 0.f, x1 = 0.f;
+            if (kind == PK_TRIG) {
+              float sn, cs;
+              sincosf(src[sa] * pr.scale, &sn, &cs);
+              x0 = sn * pr.ma;
+              x1 = cs * pr.mb;
+            } else if (kind == PK_COPY2) {
+              x0 = src[sa];
+              x1 = src[sb];
+            } else if (kind == PK_COPY1) {
+              x0 = src[sa];
+            }
+            v[2 * p2] = x0;
+            v[2 * p2 + 1] = x1;
+          }
+          float4 h, l;
+          split4(v, h, l);
+          const int off = tc::canon_off(r_in, u, 8);
+          *reinterpret_cast<float4*>(Ahi + off) = h;
+          *reinterpret_cast<float4*>(Alo + off) = l;
+          if (save && live) *reinterpret_cast<float4*>(ws.a_x + row * ws.ldx + ch * 32 + u * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        tc::fence_async_smem();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(a_full + stg);
+      }
+      // ---- layer-1 accumulator -> layer-2 operand chunks (bias + ReLU + split)
+      tc::mbar_wait(acc_full + 0, it & 1);
+      tc::fence_after_sync();
+      for (int j = 0; j < 4; ++j, ++ac) {
+        const int stg = ac % FZ_A_STAGES;
+        float acc[32];
+        tc::tmem_ld32(t_acc1 + (uint32_t)(j * 32), acc);
+        tc::tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b1[j * 32 + i], 0.f);
+        if (save && live) {
+          float4* dst = reinterpret_cast<float4*>(ws.a_h1 + row * FC + j * 32);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) dst[u] = make_float4(acc[4 * u], acc[4 * u + 1], acc[4 * u + 2], acc[4 * u + 3]);
+        }
+        tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
+        float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
+        float* Alo = Ahi + FZ_CHUNK_FLOATS;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          float4 h, l;
+          split4(acc + 4 * u, h, l);
+          const int off = tc::canon_off(r_in, u, 8);
+          *reinterpret_cast<float4*>(Ahi + off) = h;
+          *reinterpret_cast<float4*>(Alo + off) = l;
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(a_full + stg);
+      }
+      // ---- layer-2 epilogue: bias + ReLU, layer 3 (128 -> 3) on CUDA cores, sigmoid
+      tc::mbar_wait(acc_full + 1, it & 1);
+      tc::fence_after_sync();
+      float o3[3] = {b3[0], b3[1], b3[2]};
+      for (int j = 0; j < 4; ++j) {
+        float acc[32];
+        tc::tmem_ld32(t_acc2 + (uint32_t)(j * 32), acc);
+        tc::tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b2[j * 32 + i], 0.f);
+        if (save && live) {
+          float4* dst = reinterpret_cast<float4*>(ws.a_h2 + row * FC + j * 32);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) dst[u] = make_float4(acc[4 * u], acc[4 * u + 1], acc[4 * u + 2], acc[4 * u + 3]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float4* wr = reinterpret_cast<const float4*>(s_w3 + k * FC + j * 32);
+          float s = 0.f;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            float4 w4 = wr[u];
+            s = fmaf(acc[4 * u], w4.x, s); s = fmaf(acc[4 * u + 1], w4.y, s);
+            s = fmaf(acc[4 * u + 2], w4.z, s); s = fmaf(acc[4 * u + 3], w4.w, s);
+          }
+          o3[k] += s;
+        }
+      }
+      tc::fence_before_sync();     // accumulator reads are ordered before the a_full arrivals of the next pair
+      if (live) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) ws.a_rgb[row * 3 + k] = 1.f / (1.f + expf(-o3[k]));
+      }
+    }
+  } else if (warp == 8) {
+    // =============================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_tf32(128, 128);
+      uint32_t ac = 0, wc = 0;
+      for (int it = 0; it < my_pairs; ++it) {
+        for (int ch = 0; ch < nck; ++ch, ++ac, ++wc) {
+          const int as = ac % FZ_A_STAGES, wsg = wc % FZ_W_STAGES;
+          const bool l1 = ch < n1;
+          const int ksteps = l1 ? min(32, fs.kp - ch * 32) / 8 : 4;
+          tc::mbar_wait(w_full + wsg, (wc / FZ_W_STAGES) & 1);
+          tc::mbar_wait(a_full + as, (ac / FZ_A_STAGES) & 1);
+          tc::fence_after_sync();
+          const uint32_t bh = tc::smem_u32(w_ring + (size_t)wsg * 2 * FZ_CHUNK_FLOATS), bl = bh + FZ_CHUNK_FLOATS * 4;
+          const bool first = l1 ? ch == 0 : ch == n1;
+#pragma unroll
+          for (int sub = 0; sub < 2; ++sub) {
+            const uint32_t ah = tc::smem_u32(a_ring + ((size_t)as * 2 + sub) * (2 * FZ_CHUNK_FLOATS)), al = ah + FZ_CHUNK_FLOATS * 4;
+            const uint32_t d = tmem + (uint32_t)((l1 ? 0 : 256) + sub * 128);
+            for (int s = 0; s < ksteps; ++s) {
+              const uint32_t ko = s * 256;       // 8 tf32 = two 16-byte units along K
+              const uint64_t dah = tc::smem_desc(ah + ko, 128, 1024), dal = tc::smem_desc(al + ko, 128, 1024);
+              const uint64_t dbh = tc::smem_desc(bh + ko, 128, 1024), dbl = tc::smem_desc(bl + ko, 128, 1024);
+              tc::mma_tf32_ss(d, dal, dbh, idesc, !(first && s == 0));
+              tc::mma_tf32_ss(d, dah, dbl, idesc, true);
+              tc::mma_tf32_ss(d, dah, dbh, idesc, true);
+            }
+          }
+          tc::mma_commit(a_empty + as);
+          tc::mma_commit(w_empty + wsg);
+          if (ch == n1 - 1) tc::mma_commit(acc_full + 0);
+          if (ch == nck - 1) tc::mma_commit(acc_full + 1);
+        }
+      }
+    }
+  } else {
+    // =============================================================== weight-chunk streamer (TMA)
+    if (lane == 0) {
+      uint32_t wc = 0;
+      for (int it = 0; it < my_pairs; ++it)
+        for (int ch = 0; ch < nck; ++ch, ++wc) {
+          const int wsg = wc % FZ_W_STAGES;
+          tc::mbar_wait(w_empty + wsg, ((wc / FZ_W_STAGES) & 1) ^ 1);
+          mbar_expect_tx(w_full + wsg, (uint32_t)FZ_CHUNK_BYTES);
+          bulk_g2s(w_ring + (size_t)wsg * 2 * FZ_CHUNK_FLOATS, wimg + (size_t)ch * 2 * FZ_CHUNK_FLOATS, (uint32_t)FZ_CHUNK_BYTES,
+                   w_full + wsg);
+        }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 8) tc::tmem_dealloc(tmem, 512);
+}
+
+static size_t fused_fwd_smem() {
+  return (size_t)FZ_A_STAGES * 4 * FZ_CHUNK_FLOATS * 4 + (size_t)FZ_W_STAGES * 2 * FZ_CHUNK_FLOATS * 4 +
+         (size_t)(2 * FC + 3 * FC) * 4 + (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 16 * 8 + 16;
+}
+
+// Forward of the MLP shading modes.  *handled = false when this configuration is not covered.
+int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, bool* handled) {
+  *handled = false;
+  InSpec sp = make_spec(f);
+  FusedSpec fs;
+  if (!make_fused_spec(f, sp, fs) || fs.kp > ws.ldx || !ws.wimg) return FTRF_OK;
+  *handled = true;
+  if (c.cap_app == 0) return FTRF_OK;
+  float* img = ws.wimg;
+  float* w1p = c.save_for_backward ? img + (size_t)(FZ_MAX_K / 32 + 4) * 2 * FZ_CHUNK_FLOATS : nullptr;
+  prep_weights_kernel<<<32, 256, 0, st>>>(f, fs, img, w1p, sp.in_dim);
+  if (int e = check_launch("prep_weights")) return e;
+  const size_t smem = fused_fwd_smem();
+  cudaFuncSetAttribute(shade_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int64_t pairs = (c.cap_app + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
+  int grid = (int)(pairs < FTRF_SMS ? pairs : FTRF_SMS);
+  shade_fused_fwd_kernel<<<grid, FZ_THREADS, smem, st>>>(f, c, ws, fs, img);
+  return check_launch("shade_fused_fwd");
+}
+
+}  // namespace ftrf

@@ -8,6 +8,7 @@
 // Backward: layer3_bwd -> gemm(g_h2,W2^T)*relu'(h1) -> gemm(g_h1,W1^T) -> pe_bwd ; wgrad(g_h2,h1), wgrad(g_h1,X)
 #include "shade_common.cuh"
 #include "gemm3x.cuh"
+#include "fused.cuh"
 
 namespace ftrf {
 
@@ -191,6 +192,35 @@ pe_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpec sp)
   }
 }
 
+// same chain rule for X rows in the fused kernels' internal column order (fused.cuh)
+__global__ void __launch_bounds__(256)
+pe_bwd_internal_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpec sp, int icol0, int icol1, int icol2) {
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int D = sp.D, ldx = ws.ldx;
+  const int icol[3] = {icol0, icol1, icol2};
+  const int64_t total = n * D;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t s = e / D;
+    int ch = (int)(e - s * D);
+    const float* gx = ws.a_gx + s * ldx;
+    float g = gx[ch];
+    for (int b = 0; b < sp.nblk; ++b) {
+      const PeBlock& pb = sp.b[b];
+      if (pb.src != SRC_FEA) continue;
+      float v = ws.a_feat[e];
+      int half = pb.F * pb.C;
+      for (int fq = 0; fq < pb.F; ++fq) {
+        float sc = (float)(1 << fq), sn, cs;
+        sincosf(v * sc, &sn, &cs);
+        int q = ch * pb.F + fq;
+        float ms = enc_mask_at(f, SRC_FEA, q), mc = enc_mask_at(f, SRC_FEA, half + q);
+        g += sc * (cs * ms * gx[icol[b] + 2 * q] - sn * mc * gx[icol[b] + 2 * q + 1]);
+      }
+    }
+    ws.a_gfeat[e] = g;
+  }
+}
+
 // ---------------------------------------------------------------------------------------- drivers
 int shade_check(const FtrfField& f, const InSpec& sp);
 int launch_shade_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
@@ -198,7 +228,7 @@ int launch_shade_bwd_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream
 int launch_shade_sh(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_sh_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 
-static int g_shade_path = 1;     // 1 = tensor cores (tcgen05 3xTF32), 0 = fp32 CUDA cores (v1)
+static int g_shade_path = 2;     // 2 = fused tcgen05 kernels, 1 = tcgen05 GEMM per layer, 0 = fp32 CUDA cores (v1)
 
 static Gemm3xArgs gemm_args(const Ws& ws, const FtrfCall& c) {
   Gemm3xArgs g{};
@@ -213,6 +243,11 @@ int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
+  if (g_shade_path == 2) {
+    bool handled = false;
+    if (int e = launch_shade_fused(f, c, ws, st, &handled)) return e;
+    if (handled) return FTRF_OK;
+  }
   size_t smem = (size_t)ST * (sp.D + 6) * sizeof(float) + (size_t)ws.ldx * 16;
   build_x_kernel<<<FTRF_SMS * 4, 256, smem, st>>>(f, c, ws, sp, ws.ldx);
   if (int e = check_launch("build_x")) return e;
@@ -233,6 +268,9 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
+  FusedSpec fs;
+  const bool internal = g_shade_path == 2 && make_fused_spec(f, sp, fs) && fs.kp <= ws.ldx && ws.wimg;   // X saved by the fused forward
+  const float* w1p = ws.wimg ? ws.wimg + (size_t)(FZ_MAX_K / 32 + 4) * 2 * 128 * 32 : nullptr;
   prof_begin(7, st);
   layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
   if (int e = check_launch("layer3_bwd")) return e;
@@ -243,9 +281,11 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   prof_end(7, st); prof_begin(8, st);
   g = gemm_args(ws, c);                   // g_X = g_h1 W1:  B(n=j,k=o) = W1[o][j]
   g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;
+  if (internal) { g.B = w1p; g.sk = fs.kp; g.N = fs.kp; }
   g.out = ws.a_gx; g.ldo = ws.ldx;
   if (int e = launch_gemm3x(g, st)) return e;
-  pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
+  if (internal) pe_bwd_internal_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp, fs.blk_icol0[0], fs.blk_icol0[1], fs.blk_icol0[2]);
+  else pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
   if (int e = check_launch("pe_bwd")) return e;
   prof_end(8, st); prof_begin(9, st);
   Wgrad3xArgs w{};
@@ -254,6 +294,10 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   if (int e = launch_wgrad3x(w, st)) return e;
   prof_end(9, st); prof_begin(10, st);
   w.G = ws.a_gh1; w.A = ws.a_x; w.lda = ws.ldx; w.K = sp.in_dim; w.dW = f.g_w1; w.ldw = sp.in_dim; w.dbias = f.g_b1;
+  if (internal) {
+    w.K = fs.kp; w.use_perm = 1;
+    for (int k = 0; k < fs.kp; ++k) w.perm[k] = fs.orig[k];
+  }
   int e = launch_wgrad3x(w, st);
   prof_end(10, st);
   return e;
@@ -262,6 +306,6 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
 }  // namespace ftrf
 
 extern "C" int ftrf_set_shade_path(int tensor_cores) {
-  ftrf::g_shade_path = tensor_cores ? 1 : 0;
+  ftrf::g_shade_path = tensor_cores < 0 ? 0 : (tensor_cores > 2 ? 2 : tensor_cores);
   return FTRF_OK;
 }

@@ -143,7 +143,10 @@ wgrad3x_kernel(const Wgrad3xArgs a) {
       for (int j = 0; j < 32; ++j) {
         int col = cc * 32 + j;
         float v = acc[j];
-        if (col < a.K) { if (v != 0.f) atomicAdd(a.dW + (size_t)o * a.ldw + col, v); }
+        if (col < a.K) {
+          int dst = a.use_perm ? a.perm[col] : col;
+          if (v != 0.f && dst >= 0) atomicAdd(a.dW + (size_t)o * a.ldw + dst, v);
+        }
         else if (col == a.K && a.dbias) { if (v != 0.f) atomicAdd(a.dbias + o, v); }
       }
     }

@@ -69,6 +69,9 @@ class AlphaGridMask(nn.Module):
             bits = torch.empty(words, dtype=torch.int32, device=vol.device)
             check(lib.ftrf_pack_alpha_mask(vol.data_ptr(), x, y, z, bits.data_ptr(), _stream()), "pack_alpha_mask")
             self._bits = bits
+            coarse = torch.empty(lib.ftrf_alpha_mask_coarse_words(x, y, z), dtype=torch.int32, device=vol.device)
+            check(lib.ftrf_build_coarse_mask(bits.data_ptr(), x, y, z, coarse.data_ptr(), _stream()), "build_coarse_mask")
+            self._coarse = coarse
             a = self.aabb.detach().float().cpu()
             inv = (1.0 / (a[1] - a[0]) * 2)          # same fp32 ops as :36-37
             self._host = ([x, y, z], a[0].tolist(), inv.tolist())
@@ -159,6 +162,7 @@ class TensorBase(nn.Module):
         self.matMode = [[0, 1], [0, 2], [1, 2]]
         self.vecMode = [2, 1, 0]
         self.comp_w = [1, 1, 1]
+        self.use_coarse_mask = True     # 8^3-block occupancy in front of the alphaMask test (same decisions)
 
         self.step_ratio = args['step_ratio']
         self.fea2denseAct = args['fea2denseAct']
@@ -385,6 +389,7 @@ class TensorBase(nn.Module):
             for i in range(3):
                 f.am_dim[i], f.am_aabb0[i], f.am_inv[i] = dims[i], a0[i], inv[i]
             f.am_bits = bits.data_ptr()
+            f.am_coarse = self.alphaMask._coarse.data_ptr() if self.use_coarse_mask else None
         enc = {"pos": None, "view": None, "fea": None}
         dmask = amask = None
         if mask is not None:

@@ -17,6 +17,7 @@
  *   ftrf_stage_composite    models/tensorBase.py:375-384
  *   ftrf_mse_loss           train.py:338
  *   ftrf_pack_alpha_mask    models/tensorBase.py:30-39   (AlphaGridMask volume -> bit field)
+ *   ftrf_build_coarse_mask  (none: empty-space acceleration of the alphaMask cull, same decisions)
  *   ftrf_density_at         models/tensorBase.py:298-318 compute_alpha's sigma (dense-lattice eval)
  *
  * Factor layout: CHANNEL-LAST.  A VM plane the reference holds as (1,C,H,W) is read as [H][W][C]
@@ -80,6 +81,7 @@ typedef struct FtrfField {
   float am_aabb0[3];
   float am_inv[3];          /* AlphaGridMask.invgridSize                                     */
   const uint32_t* am_bits;  /* ftrf_pack_alpha_mask output                                   */
+  const uint32_t* am_coarse;/* ftrf_build_coarse_mask output (8^3-block occupancy) or NULL   */
   FtrfFactorSet den, app;
   const float* basis;       /* basis_mat.weight [app_dim][sum n_comp]                        */
   float* g_basis;
@@ -134,8 +136,9 @@ enum {
   FTRF_WS_A_GH1,        /* float[cap_app][feature_c]  backward                               */
   FTRF_WS_A_GH2,        /* float[cap_app][feature_c]  backward                               */
   FTRF_WS_A_GFEAT,      /* float[cap_app][app_dim]    backward                               */
-  FTRF_WS_A_X,          /* float[cap_app][ldx]  MLP input rows, ldx = in_dim rounded up to 8     */
+  FTRF_WS_A_X,          /* float[cap_app][ldx]  MLP input rows, ldx = in_dim + 1 rounded up to 8  */
   FTRF_WS_A_GX,         /* float[cap_app][ldx]  backward                                         */
+  FTRF_WS_WIMG,         /* pre-split tf32 hi/lo weight images streamed by the fused MLP kernels      */
   FTRF_WS_COUNT
 };
 
@@ -162,6 +165,11 @@ int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, float* loss_
 /* volume: float (Z,Y,X) of {0,1}; bits: uint32[ftrf_alpha_mask_words(X,Y,Z)]. */
 size_t ftrf_alpha_mask_words(int32_t x, int32_t y, int32_t z);
 int ftrf_pack_alpha_mask(const float* volume, int32_t x, int32_t y, int32_t z, uint32_t* bits, void* stream);
+/* Optional acceleration structure of the march kernel (no reference counterpart): one bit per 8x8x8
+ * texel block (dilated by one texel), coarse: uint32[ftrf_alpha_mask_coarse_words(X,Y,Z)].  It never
+ * changes a keep / cull decision, it only answers the empty-space ones early. */
+size_t ftrf_alpha_mask_coarse_words(int32_t x, int32_t y, int32_t z);
+int ftrf_build_coarse_mask(const uint32_t* bits, int32_t x, int32_t y, int32_t z, uint32_t* coarse, void* stream);
 
 /* sigma_out[i] = feature2density(compute_densityfeature(normalize(xyz[i]))) for n world-space points,
  * or 0 where the field's alphaMask rejects the point (tensorBase.py:298-313). */
@@ -178,8 +186,9 @@ int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B,
  * tensor-core weight-gradient contraction, exposed for unit tests. */
 int ftrf_test_wgrad3x(const float* G, int ldg, const float* A, int lda, int K, int64_t M, float* dW, int ldw,
                       float* dbias, void* stream);
-/* 1 (default): shading MLP on tcgen05 tensor cores (3xTF32); 0: fp32 CUDA-core kernels (both CUDA). */
-int ftrf_set_shade_path(int tensor_cores);
+/* Shading-MLP back end (all CUDA): 2 (default) fused persistent tcgen05 kernels (3xTF32), 1 one tcgen05
+ * GEMM launch per layer, 0 fp32 CUDA-core kernels. */
+int ftrf_set_shade_path(int path);
 
 /* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
  * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.

@@ -81,12 +81,13 @@ def test_gradients_autograd(case):
         assert rel_inf(got[k].cpu(), ref) < TOL, f"{k}: {rel_inf(got[k].cpu(), ref):.3e}"
 
 
+@pytest.mark.parametrize("path", [0, 1])
 @pytest.mark.parametrize("case", [c for c in CASES if "sh" not in c])
-def test_cuda_core_shading_path(case):
-    """The fp32 CUDA-core MLP kernels (ftrf_set_shade_path(0)) must meet the same bars as the
-    tcgen05 path that the other tests exercise by default."""
+def test_other_shading_paths(case, path):
+    """The fp32 CUDA-core MLP kernels (ftrf_set_shade_path(0)) and the one-GEMM-per-layer tcgen05
+    path (1) must meet the same bars as the fused tcgen05 path (2) the other tests exercise by default."""
     from fewtensorf_b200._abi import lib
-    lib.ftrf_set_shade_path(0)
+    lib.ftrf_set_shade_path(path)
     try:
         g, f, m, rgb, depth, nv = _run(case, grad=True)
         loss = torch.mean((rgb - g.target.cuda()) ** 2)
@@ -95,7 +96,7 @@ def test_cuda_core_shading_path(case):
         for k, p in m.named_parameters():
             assert rel_inf(p.grad.cpu(), g.grads[k]) < TOL, k
     finally:
-        lib.ftrf_set_shade_path(1)
+        lib.ftrf_set_shade_path(2)
 
 
 @pytest.mark.parametrize("case", [c for c in CASES if "train" in c and "ndc" not in c][:2])
