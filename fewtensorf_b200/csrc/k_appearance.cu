@@ -13,6 +13,7 @@ namespace ftrf {
 
 constexpr int AGS = 4;          // lanes per sample
 constexpr int ATILE = 64;       // samples per CTA tile
+constexpr int LDP = ATILE + 4;  // row stride of the transposed product tile
 
 __host__ __device__ inline int app_np(const FtrfField& f) {
   return f.model == FTRF_MODEL_VM ? f.app.n_comp[0] + f.app.n_comp[1] + f.app.n_comp[2] : f.app.n_comp[0];
@@ -62,37 +63,104 @@ __device__ __forceinline__ void app_products(const FtrfField& f, const float xn[
   }
 }
 
-// smem: Wb [D][NPs] | P [ATILE][NPs] | G [ATILE][Dp] (backward only)
+// products of this lane's channel chunks -> column `sl` of the TRANSPOSED tile PT[k][LDP]
+__device__ __forceinline__ void app_products_t(const FtrfField& f, const float xn[3], int sub, float* PT, int sl) {
+  const FtrfFactorSet& a = f.app;
+  auto put = [&](int k, float4 v) {
+    float* p = PT + (size_t)k * LDP + sl;
+    p[0] = v.x; p[LDP] = v.y; p[2 * LDP] = v.z; p[3 * LDP] = v.w;
+  };
+  if (f.model == FTRF_MODEL_VM) {
+    int base = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int C = a.n_comp[k];
+      Tap tx = make_tap(xn[mat0(k)], a.plane_w[k]);
+      Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
+      Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+      for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+        float4 p = plane4(a.plane[k], a.plane_w[k], C, tx, ty, ch);
+        float4 l = line4(a.line[k], C, tl, ch);
+        if (a.mask[k]) {                                   // tensoRF.py:250, :257
+          float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+          p = mul4(p, m);
+          l = mul4(l, m);
+        }
+        put(base + ch, mul4(p, l));
+      }
+      base += C;
+    }
+  } else {
+    const int C = a.n_comp[0];
+    Tap t0 = make_tap(xn[vecm(0)], a.line_len[0]);
+    Tap t1 = make_tap(xn[vecm(1)], a.line_len[1]);
+    Tap t2 = make_tap(xn[vecm(2)], a.line_len[2]);
+    for (int ch = sub * 4; ch < C; ch += AGS * 4) {
+      float4 v = mul4(mul4(line4(a.line[0], C, t0, ch), line4(a.line[1], C, t1, ch)), line4(a.line[2], C, t2, ch));
+      if (a.mask[0]) v = mul4(v, mask4(a.mask[0], a.mask_stride[0], ch));   // tensoRF.py:415
+      put(ch, v);
+    }
+  }
+}
+
+// Forward.  smem: WT [NP][32] (basis_mat transposed, outputs padded to 32) | PT [NP][LDP] (products,
+// transposed).  Phase 1: 4 lanes per sample gather the plane x line products.  Phase 2: the
+// [64 x NP] x [NP x app_dim] projection as a register-tiled mini GEMM — warp w owns outputs 4w..4w+3,
+// a thread owns 4 samples and half of K (the two halves meet in one shuffle), so every pair of
+// 16-byte shared-memory loads feeds 16 FMAs.
 __global__ void __launch_bounds__(256)
 app_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   extern __shared__ __align__(16) float smem[];
-  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim;
-  float* Wb = smem;
-  float* P = Wb + (size_t)D * NPs;
+  const int NP = app_np(f), D = f.app_dim;
+  float* WT = smem;                          // [NP][32]
+  float* PT = WT + (size_t)NP * 32;          // [NP][LDP]
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
-  for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
+  for (int e = threadIdx.x; e < NP * 32; e += blockDim.x) {
+    int k = e >> 5, o = e & 31;
+    WT[e] = o < D ? __ldg(f.basis + (size_t)o * NP + k) : 0.f;
+  }
   const int sl = threadIdx.x / AGS, sub = threadIdx.x % AGS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int khalf = lane & 1, sq = lane >> 1;            // phase 2: K half, sample quad
+  const int kh = (NP / 2 + 3) & ~3;                      // first half of K (multiple of 4)
   for (int64_t t0 = (int64_t)blockIdx.x * ATILE; t0 < n; t0 += (int64_t)gridDim.x * ATILE) {
     const int64_t s = t0 + sl;
-    __syncthreads();                     // Wb visible / previous tile's P consumed
+    __syncthreads();                     // WT visible / previous tile's PT consumed
     if (s < n) {
       float xn[3];
       app_point(f, c, ws, s, xn);
-      app_products(f, xn, sub, P + (size_t)sl * NPs);
+      app_products_t(f, xn, sub, PT, sl);
+    } else {
+      for (int k = sub; k < NP; k += AGS) PT[(size_t)k * LDP + sl] = 0.f;
     }
     __syncthreads();
-    if (s < n) {
-      const float* prow = P + (size_t)sl * NPs;
-      for (int o = sub; o < D; o += AGS) {
-        const float* wrow = Wb + (size_t)o * NPs;
-        float acc = 0.f;
-        for (int k = 0; k < NP; k += 4) {
-          float4 pv = *reinterpret_cast<const float4*>(prow + k);
-          float4 wv = *reinterpret_cast<const float4*>(wrow + k);
-          acc = fmaf(pv.x, wv.x, acc); acc = fmaf(pv.y, wv.y, acc);
-          acc = fmaf(pv.z, wv.z, acc); acc = fmaf(pv.w, wv.w, acc);
-        }
-        ws.a_feat[s * D + o] = acc;
+    if (warp * 4 < D) {
+      float acc[4][4] = {};
+      const int k0 = khalf ? kh : 0, k1 = khalf ? NP : kh;
+      const float* pp = PT + sq * 4;
+      const float* wp = WT + warp * 4;
+#pragma unroll 4
+      for (int k = k0; k < k1; ++k) {
+        float4 pv = *reinterpret_cast<const float4*>(pp + (size_t)k * LDP);
+        float4 wv = *reinterpret_cast<const float4*>(wp + (size_t)k * 32);
+        const float ps[4] = {pv.x, pv.y, pv.z, pv.w}, wo[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(ps[i], wo[j], acc[i][j]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] += __shfl_xor_sync(FULL_MASK, acc[i][j], 1);
+      // lane khalf = 0 writes samples 0,1 of the quad, khalf = 1 samples 2,3
+#pragma unroll
+      for (int ii = 0; ii < 2; ++ii) {
+        const int64_t so = t0 + sq * 4 + khalf * 2 + ii;
+        if (so < n)
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (warp * 4 + j < D) ws.a_feat[so * D + warp * 4 + j] = khalf ? acc[2 + ii][j] : acc[ii][j];
       }
     }
   }
@@ -108,6 +176,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   float* Wb = smem;
   float* P = Wb + (size_t)D * NPs;
   float* G = P + (size_t)ATILE * NPs;
+  float* GT = G + (size_t)ATILE * Dp;          // [Dp][LDP]  g_feat transposed (samples contiguous)
   const FtrfFactorSet& a = f.app;
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
   for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
@@ -126,10 +195,14 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     if (s < n) {
       app_point(f, c, ws, s, xn);
       app_products(f, xn, sub, P + (size_t)sl * NPs);
-      for (int o = sub; o < Dp; o += AGS) G[sl * Dp + o] = o < D ? ws.a_gfeat[s * D + o] : 0.f;
+      for (int o = sub; o < Dp; o += AGS) {
+        float g = o < D ? ws.a_gfeat[s * D + o] : 0.f;
+        G[sl * Dp + o] = g;
+        GT[o * LDP + sl] = g;
+      }
     } else {
       for (int k = sub * 4; k < NP; k += AGS * 4) *reinterpret_cast<float4*>(P + (size_t)sl * NPs + k) = make_float4(0, 0, 0, 0);
-      for (int o = sub; o < Dp; o += AGS) G[sl * Dp + o] = 0.f;
+      for (int o = sub; o < Dp; o += AGS) { G[sl * Dp + o] = 0.f; GT[o * LDP + sl] = 0.f; }
     }
     __syncthreads();
     // (a) basis gradient: 4x4 register tiles over (output group, component group)
@@ -149,9 +222,29 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
         }
       }
     }
-    // (b) gradient w.r.t. the products, then scatter into plane / line gradients
+    // (b) gradient w.r.t. the products, GQ[64 x NP] = G[64 x D] Wb[D x NP], as a register-tiled mini
+    // GEMM (4 samples x 4 components per thread) written over the product tile
+    __syncthreads();                       // every dW tile has consumed P
+    for (int id = threadIdx.x; id < n_kg * (ATILE / 4); id += blockDim.x) {
+      const int kg = id % n_kg, sq = id / n_kg;
+      float acc[4][4] = {};
+      for (int o = 0; o < D; ++o) {
+        float4 wv = *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + kg * 4);
+        float4 gv = *reinterpret_cast<const float4*>(GT + o * LDP + sq * 4);
+        const float ww[4] = {wv.x, wv.y, wv.z, wv.w}, gs[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(gs[i], ww[j], acc[i][j]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(P + (size_t)(sq * 4 + i) * NPs + kg * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+    __syncthreads();
+    // scatter into plane / line gradients
     if (s < n) {
-      const float* grow = G + sl * Dp;
+      const float* gqrow = P + (size_t)sl * NPs;
       if (f.model == FTRF_MODEL_VM) {
         int base = 0;
 #pragma unroll
@@ -161,8 +254,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
           Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
           Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
           for (int ch = sub * 4; ch < C; ch += AGS * 4) {
-            float4 gq = make_float4(0, 0, 0, 0);
-            for (int o = 0; o < D; ++o) gq = fma4(grow[o], *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + base + ch), gq);
+            float4 gq = *reinterpret_cast<const float4*>(gqrow + base + ch);
             if (a.mask[k]) {
               float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
               gq = mul4(gq, mul4(m, m));
@@ -188,8 +280,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) t[k] = make_tap(xn[vecm(k)], a.line_len[k]);
         for (int ch = sub * 4; ch < C; ch += AGS * 4) {
-          float4 gq = make_float4(0, 0, 0, 0);
-          for (int o = 0; o < D; ++o) gq = fma4(grow[o], *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + ch), gq);
+          float4 gq = *reinterpret_cast<const float4*>(gqrow + ch);
           if (a.mask[0]) gq = mul4(gq, mask4(a.mask[0], a.mask_stride[0], ch));
           float4 l0 = line4(a.line[0], C, t[0], ch), l1 = line4(a.line[1], C, t[1], ch), l2 = line4(a.line[2], C, t[2], ch);
           float4 gk[3] = {mul4(gq, mul4(l1, l2)), mul4(gq, mul4(l0, l2)), mul4(gq, mul4(l0, l1))};
@@ -230,8 +321,8 @@ static int app_check(const FtrfField& f, size_t smem) {
 }
 
 int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  int NPs = app_np(f) + 4;
-  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs) * sizeof(float);
+  if (f.app_dim > 32) { set_error("appearance: app_dim %d > 32 unsupported", f.app_dim); return FTRF_E_ARG; }
+  size_t smem = ((size_t)app_np(f) * 32 + (size_t)app_np(f) * LDP) * sizeof(float);
   if (int e = app_check(f, smem)) return e;
   cudaFuncSetAttribute(app_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   app_fwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);
@@ -240,7 +331,7 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
 
 int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   int NPs = app_np(f) + 4, Dp = (f.app_dim + 3) & ~3;
-  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp) * sizeof(float);
+  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp + (size_t)Dp * LDP) * sizeof(float);
   if (int e = app_check(f, smem)) return e;
   cudaFuncSetAttribute(app_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);

@@ -74,11 +74,62 @@ __device__ __forceinline__ void split4(const float v[4], float4& h, float4& l) {
   tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
 }
 
+// one full 32-byte sector per store instruction (sm_100: 256-bit global stores)
+__device__ __forceinline__ void st_global_v8(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+               "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
+
 struct SPair { int meta; float scale, ma, mb; };     // meta = kind | sa << 8 | sb << 16
 
+// Compile-time copy of make_fused_spec()'s column recipe for the shipped configurations: with every
+// loop of the input build unrolled, the per-row source values stay in registers (the generic path
+// indexes them dynamically, i.e. through local memory, which the 200 KB of operand rings leave
+// almost no L1 for).
+struct PairInfo { int kind, sa, sb, fexp; };
+template <int MODE, int D_, int FPOS, int FVIEW, int FFEA>
+struct StaticSpec {
+  static constexpr bool is_static = true;
+  static constexpr int D = D_;
+  static constexpr int ncopy = D_ + 3, ncp = (ncopy + 1) / 2;
+  static constexpr int nb = MODE == FTRF_SHADE_MLP ? 3 : 2;
+  __host__ __device__ static constexpr int blk_src(int b) {
+    return MODE == FTRF_SHADE_MLP_FEA ? (b == 0 ? SRC_FEA : SRC_VIEW)
+         : MODE == FTRF_SHADE_MLP_PE ? (b == 0 ? SRC_POS : SRC_VIEW)
+         : (b == 0 ? SRC_POS : (b == 1 ? SRC_VIEW : SRC_FEA));
+  }
+  __host__ __device__ static constexpr int blk_f(int b) { return blk_src(b) == SRC_FEA ? FFEA : (blk_src(b) == SRC_VIEW ? FVIEW : FPOS); }
+  __host__ __device__ static constexpr int blk_c(int b) { return blk_src(b) == SRC_FEA ? D_ : 3; }
+  __host__ __device__ static constexpr int blk_s0(int b) { return blk_src(b) == SRC_FEA ? 0 : (blk_src(b) == SRC_VIEW ? D_ : D_ + 3); }
+  __host__ __device__ static constexpr int npairs() {
+    int n = ncp;
+    for (int b = 0; b < nb; ++b) n += blk_f(b) * blk_c(b);
+    return (n + 3) & ~3;
+  }
+  static constexpr int kp = npairs() * 2;
+  static constexpr int n1 = (kp + 31) / 32;
+  __host__ __device__ static constexpr PairInfo pair(int P) {
+    if (P < ncp) return (2 * P + 1 < ncopy) ? PairInfo{PK_COPY2, 2 * P, 2 * P + 1, 0} : PairInfo{PK_COPY1, 2 * P, 0, 0};
+    int q = P - ncp;
+    for (int b = 0; b < nb; ++b) {
+      const int n = blk_f(b) * blk_c(b);
+      if (q < n) return PairInfo{PK_TRIG, blk_s0(b) + q / blk_f(b), 0, q % blk_f(b)};
+      q -= n;
+    }
+    return PairInfo{PK_ZERO, 0, 0, 0};
+  }
+};
+struct DynamicSpec { static constexpr bool is_static = false; };
+
+// optional phase timeline of CTA 0 (debug aid, scripts/fused_timeline.py): dbg[role*512 + n]
+static long long* g_fused_dbg = nullptr;
+#define FZ_T(role, n) do { if (dbg && blockIdx.x == 0 && (n) < 512) dbg[(role) * 512 + (n)] = clock64(); } while (0)
+
+
 // ------------------------------------------------------------------------------------------ kernel
+template <class SS>
 __global__ void __launch_bounds__(FZ_THREADS, 1)
-shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg) {
+shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [A_STAGES][2 subs][hi, lo][4096]
   float* w_ring = a_ring + (size_t)FZ_A_STAGES * 4 * FZ_CHUNK_FLOATS;               // [W_STAGES][hi, lo][4096]
@@ -134,29 +185,86 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
     const float b3[3] = {__ldg(f.b3), __ldg(f.b3 + 1), __ldg(f.b3 + 2)};
     const bool save = c.save_for_backward != 0;
     const int D = fs.D;
+    const bool tl = warp == 0 && lane == 0;
     uint32_t ac = 0;                                   // operand-ring chunk counter
-    for (int it = 0; it < my_pairs; ++it) {
-      const int64_t pair_id = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
-      const int64_t row = pair_id * FZ_PAIR_ROWS + sub * 128 + r_in;
+    auto pair_row = [&](int it) { return ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * FZ_PAIR_ROWS + sub * 128 + r_in; };
+    // sources of one row: [feat(D) | view(3) | pos(3)]
+    auto load_src = [&](int64_t row, float* dst) {
       const bool live = row < n;
-      // ---- stage this row's sources: [feat(D) | view(3) | pos(3)]
-      float src[FZ_MAX_SRC];
-      if (live) {
-        const float* fp = ws.a_feat + row * D;
-        for (int k = 0; k < D; ++k) src[k] = fp[k];
-        float v[3], p[3];
-        shade_geometry(f, c, ws, row, v, p);
+      if constexpr (SS::is_static) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) { src[D + k] = v[k]; src[D + 3 + k] = p[k]; }
+        for (int k = 0; k < SS::D + 6; ++k) dst[k] = 0.f;
+        if (live) {
+          const float* fp = ws.a_feat + row * SS::D;
+#pragma unroll
+          for (int k = 0; k < SS::D; ++k) dst[k] = fp[k];
+          float v[3], p[3];
+          shade_geometry(f, c, ws, row, v, p);
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { dst[SS::D + k] = v[k]; dst[SS::D + 3 + k] = p[k]; }
+        }
       } else {
-        for (int k = 0; k < D + 6; ++k) src[k] = 0.f;
+        if (live) {
+          const float* fp = ws.a_feat + row * D;
+          for (int k = 0; k < D; ++k) dst[k] = fp[k];
+          float v[3], p[3];
+          shade_geometry(f, c, ws, row, v, p);
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { dst[D + k] = v[k]; dst[D + 3 + k] = p[k]; }
+        } else {
+          for (int k = 0; k < D + 6; ++k) dst[k] = 0.f;
+        }
       }
-      // ---- layer-1 operand chunks
-      for (int ch = 0; ch < n1; ++ch, ++ac) {
-        const int stg = ac % FZ_A_STAGES;
-        tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
-        float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
-        float* Alo = Ahi + FZ_CHUNK_FLOATS;
+    };
+    float src[FZ_MAX_SRC];                             // sources of the pair whose input rows are being built
+    float da_s = 0.f, da_c = 1.f;                      // running (sin, cos) of the current source at the current octave
+
+    // one 32-column chunk of the encoded input rows -> operand ring (+ X saved for backward)
+    auto x_chunk = [&](int ch, int64_t row) {
+      const bool live = row < n;
+      const int stg = ac % FZ_A_STAGES;
+      tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
+      float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
+      float* Alo = Ahi + FZ_CHUNK_FLOATS;
+      auto emit = [&](int u, const float v[4]) {
+        float4 h, l;
+        split4(v, h, l);
+        const int off = tc::canon_off(r_in, u, 8);
+        *reinterpret_cast<float4*>(Ahi + off) = h;
+        *reinterpret_cast<float4*>(Alo + off) = l;
+        if (save && live) *reinterpret_cast<float4*>(ws.a_x + row * ws.ldx + ch * 32 + u * 4) = make_float4(v[0], v[1], v[2], v[3]);
+      };
+      if constexpr (SS::is_static) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (ch * 32 + u * 4 < SS::kp) {
+            float v[4];
+#pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {
+              const int P = (ch * 32 + u * 4) / 2 + p2;
+              const PairInfo pi = SS::pair(P);
+              float x0 = 0.f, x1 = 0.f;
+              if (pi.kind == PK_TRIG) {
+                const SPair pr = s_pair[P];
+                // octave 0: sincosf; octave f: double-angle step from octave f-1 (the pairs of one
+                // channel are consecutive, frequency-minor) — 2 ulp-grade, far inside the 1e-4 budget
+                if (pi.fexp == 0) sincosf(src[pi.sa], &da_s, &da_c);
+                else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
+                x0 = da_s * pr.ma;
+                x1 = da_c * pr.mb;
+              } else if (pi.kind == PK_COPY2) {
+                x0 = src[pi.sa];
+                x1 = src[pi.sb];
+              } else if (pi.kind == PK_COPY1) {
+                x0 = src[pi.sa];
+              }
+              v[2 * p2] = x0;
+              v[2 * p2 + 1] = x1;
+            }
+            emit(u, v);
+          }
+        }
+      } else {
         const int units = min(8, (fs.kp - ch * 32) / 4);
         for (int u = 0; u < units; ++u) {
           float v[4];
@@ -166,10 +274,10 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
             const int kind = pr.meta & 0xff, sa = (pr.meta >> 8) & 0xff, sb = (pr.meta >> 16) & 0xff;
             float x0 = 0.f, x1 = 0.f;
             if (kind == PK_TRIG) {
-              float sn, cs;
-              sincosf(src[sa] * pr.scale, &sn, &cs);
-              x0 = sn * pr.ma;
-              x1 = cs * pr.mb;
+              if (pr.scale == 1.f) sincosf(src[sa], &da_s, &da_c);
+              else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
+              x0 = da_s * pr.ma;
+              x1 = da_c * pr.mb;
             } else if (kind == PK_COPY2) {
               x0 = src[sa];
               x1 = src[sb];
@@ -179,20 +287,42 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
             v[2 * p2] = x0;
             v[2 * p2 + 1] = x1;
           }
-          float4 h, l;
-          split4(v, h, l);
-          const int off = tc::canon_off(r_in, u, 8);
-          *reinterpret_cast<float4*>(Ahi + off) = h;
-          *reinterpret_cast<float4*>(Alo + off) = l;
-          if (save && live) *reinterpret_cast<float4*>(ws.a_x + row * ws.ldx + ch * 32 + u * 4) = make_float4(v[0], v[1], v[2], v[3]);
+          emit(u, v);
         }
-        tc::fence_async_smem();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(a_full + stg);
       }
+      tc::fence_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(a_full + stg);
+      ++ac;
+    };
+    // Schedule per pair `it` (the operand ring keeps production order = MMA consumption order):
+    //   tail chunks of X(it) | wait acc1 | h1 chunks (layer-2 operand) | HEAD chunks of X(it+1) | wait acc2 | epilogue(it)
+    // so the tensor pipe already works on the next pair's first layer while this pair's epilogue runs.
+    constexpr int HEAD = FZ_A_STAGES;
+    load_src(pair_row(0), src);
+    if constexpr (SS::is_static) {
+#pragma unroll
+      for (int ch = 0; ch < (HEAD < SS::n1 ? HEAD : SS::n1); ++ch) x_chunk(ch, pair_row(0));
+    } else {
+      for (int ch = 0; ch < min(HEAD, n1); ++ch) x_chunk(ch, pair_row(0));
+    }
+    for (int it = 0; it < my_pairs; ++it) {
+      const int64_t row = pair_row(it), row_next = pair_row(it + 1);
+      const bool live = row < n, more = it + 1 < my_pairs;
+      if (tl) FZ_T(0, it * 8 + 0);
+      if constexpr (SS::is_static) {
+#pragma unroll
+        for (int ch = HEAD; ch < SS::n1; ++ch) x_chunk(ch, row);
+      } else {
+        for (int ch = HEAD; ch < n1; ++ch) x_chunk(ch, row);
+      }
+      if (tl) FZ_T(0, it * 8 + 1);
+      if (more) load_src(row_next, src);               // in flight during the layer-1 epilogue below
+      if (tl) FZ_T(0, it * 8 + 2);
       // ---- layer-1 accumulator -> layer-2 operand chunks (bias + ReLU + split)
       tc::mbar_wait(acc_full + 0, it & 1);
       tc::fence_after_sync();
+      if (tl) FZ_T(0, it * 8 + 3);
       for (int j = 0; j < 4; ++j, ++ac) {
         const int stg = ac % FZ_A_STAGES;
         float acc[32];
@@ -201,9 +331,8 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
 #pragma unroll
         for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b1[j * 32 + i], 0.f);
         if (save && live) {
-          float4* dst = reinterpret_cast<float4*>(ws.a_h1 + row * FC + j * 32);
 #pragma unroll
-          for (int u = 0; u < 8; ++u) dst[u] = make_float4(acc[4 * u], acc[4 * u + 1], acc[4 * u + 2], acc[4 * u + 3]);
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h1 + row * FC + j * 32 + u * 8, acc + 8 * u);
         }
         tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
         float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
@@ -221,9 +350,20 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(a_full + stg);
       }
+      if (tl) FZ_T(0, it * 8 + 4);
+      // ---- head chunks of the next pair's input rows (acc1 is free: every warp has read it)
+      if (more) {
+        if constexpr (SS::is_static) {
+#pragma unroll
+          for (int ch = 0; ch < (HEAD < SS::n1 ? HEAD : SS::n1); ++ch) x_chunk(ch, row_next);
+        } else {
+          for (int ch = 0; ch < min(HEAD, n1); ++ch) x_chunk(ch, row_next);
+        }
+      }
       // ---- layer-2 epilogue: bias + ReLU, layer 3 (128 -> 3) on CUDA cores, sigmoid
       tc::mbar_wait(acc_full + 1, it & 1);
       tc::fence_after_sync();
+      if (tl) FZ_T(0, it * 8 + 5);
       float o3[3] = {b3[0], b3[1], b3[2]};
       for (int j = 0; j < 4; ++j) {
         float acc[32];
@@ -232,24 +372,24 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
 #pragma unroll
         for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b2[j * 32 + i], 0.f);
         if (save && live) {
-          float4* dst = reinterpret_cast<float4*>(ws.a_h2 + row * FC + j * 32);
 #pragma unroll
-          for (int u = 0; u < 8; ++u) dst[u] = make_float4(acc[4 * u], acc[4 * u + 1], acc[4 * u + 2], acc[4 * u + 3]);
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h2 + row * FC + j * 32 + u * 8, acc + 8 * u);
         }
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
           const float4* wr = reinterpret_cast<const float4*>(s_w3 + k * FC + j * 32);
-          float s = 0.f;
+          float sacc = 0.f;
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
             float4 w4 = wr[u];
-            s = fmaf(acc[4 * u], w4.x, s); s = fmaf(acc[4 * u + 1], w4.y, s);
-            s = fmaf(acc[4 * u + 2], w4.z, s); s = fmaf(acc[4 * u + 3], w4.w, s);
+            sacc = fmaf(acc[4 * u], w4.x, sacc); sacc = fmaf(acc[4 * u + 1], w4.y, sacc);
+            sacc = fmaf(acc[4 * u + 2], w4.z, sacc); sacc = fmaf(acc[4 * u + 3], w4.w, sacc);
           }
-          o3[k] += s;
+          o3[k] += sacc;
         }
       }
-      tc::fence_before_sync();     // accumulator reads are ordered before the a_full arrivals of the next pair
+      if (tl) FZ_T(0, it * 8 + 6);
+      tc::fence_before_sync();     // accumulator reads are ordered before the a_full arrivals that follow
       if (live) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) ws.a_rgb[row * 3 + k] = 1.f / (1.f + expf(-o3[k]));
@@ -259,28 +399,36 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
     // =============================================================== MMA issuer
     if (lane == 0) {
       const uint32_t idesc = tc::idesc_tf32(128, 128);
+      const uint32_t a_lo0 = tc::desc_lo(tc::smem_u32(a_ring), 128), w_lo0 = tc::desc_lo(tc::smem_u32(w_ring), 128);
+      const uint32_t d_hi = tc::desc_hi(1024);
       uint32_t ac = 0, wc = 0;
       for (int it = 0; it < my_pairs; ++it) {
         for (int ch = 0; ch < nck; ++ch, ++ac, ++wc) {
           const int as = ac % FZ_A_STAGES, wsg = wc % FZ_W_STAGES;
           const bool l1 = ch < n1;
           const int ksteps = l1 ? min(32, fs.kp - ch * 32) / 8 : 4;
+          FZ_T(1, wc * 3 + 0);
           tc::mbar_wait(w_full + wsg, (wc / FZ_W_STAGES) & 1);
+          FZ_T(1, wc * 3 + 1);
           tc::mbar_wait(a_full + as, (ac / FZ_A_STAGES) & 1);
+          FZ_T(1, wc * 3 + 2);
           tc::fence_after_sync();
-          const uint32_t bh = tc::smem_u32(w_ring + (size_t)wsg * 2 * FZ_CHUNK_FLOATS), bl = bh + FZ_CHUNK_FLOATS * 4;
-          const bool first = l1 ? ch == 0 : ch == n1;
+          // descriptor low words: address >> 4 (+ LBO field); a k-step advances by 256 B = 16 units
+          const uint32_t w_lo = w_lo0 + (uint32_t)wsg * (2 * FZ_CHUNK_FLOATS * 4 / 16);
+          const uint32_t a_lo = a_lo0 + (uint32_t)as * (4 * FZ_CHUNK_FLOATS * 4 / 16);
+          const uint32_t d0 = tmem + (uint32_t)(l1 ? 0 : 256);
+          const uint32_t fresh = (l1 ? ch == 0 : ch == n1) ? 0u : 1u;
+          constexpr uint32_t LO = FZ_CHUNK_FLOATS * 4 / 16;      // hi -> lo half of a chunk, in 16-byte units
 #pragma unroll
           for (int sub = 0; sub < 2; ++sub) {
-            const uint32_t ah = tc::smem_u32(a_ring + ((size_t)as * 2 + sub) * (2 * FZ_CHUNK_FLOATS)), al = ah + FZ_CHUNK_FLOATS * 4;
-            const uint32_t d = tmem + (uint32_t)((l1 ? 0 : 256) + sub * 128);
-            for (int s = 0; s < ksteps; ++s) {
-              const uint32_t ko = s * 256;       // 8 tf32 = two 16-byte units along K
-              const uint64_t dah = tc::smem_desc(ah + ko, 128, 1024), dal = tc::smem_desc(al + ko, 128, 1024);
-              const uint64_t dbh = tc::smem_desc(bh + ko, 128, 1024), dbl = tc::smem_desc(bl + ko, 128, 1024);
-              tc::mma_tf32_ss(d, dal, dbh, idesc, !(first && s == 0));
-              tc::mma_tf32_ss(d, dah, dbl, idesc, true);
-              tc::mma_tf32_ss(d, dah, dbh, idesc, true);
+            const uint32_t ah = a_lo + (uint32_t)sub * (2 * LO), d = d0 + (uint32_t)(sub * 128);
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+              if (s < ksteps) {
+                tc::mma_tf32_ss_lo(d, ah + LO + s * 16, w_lo + s * 16, d_hi, idesc, s == 0 ? fresh : 1u);
+                tc::mma_tf32_ss_lo(d, ah + s * 16, w_lo + LO + s * 16, d_hi, idesc, 1u);
+                tc::mma_tf32_ss_lo(d, ah + s * 16, w_lo + s * 16, d_hi, idesc, 1u);
+              }
             }
           }
           tc::mma_commit(a_empty + as);
@@ -298,6 +446,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         for (int ch = 0; ch < nck; ++ch, ++wc) {
           const int wsg = wc % FZ_W_STAGES;
           tc::mbar_wait(w_empty + wsg, ((wc / FZ_W_STAGES) & 1) ^ 1);
+          FZ_T(2, wc);
           mbar_expect_tx(w_full + wsg, (uint32_t)FZ_CHUNK_BYTES);
           bulk_g2s(w_ring + (size_t)wsg * 2 * FZ_CHUNK_FLOATS, wimg + (size_t)ch * 2 * FZ_CHUNK_FLOATS, (uint32_t)FZ_CHUNK_BYTES,
                    w_full + wsg);
@@ -327,11 +476,27 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   prep_weights_kernel<<<32, 256, 0, st>>>(f, fs, img, w1p, sp.in_dim);
   if (int e = check_launch("prep_weights")) return e;
   const size_t smem = fused_fwd_smem();
-  cudaFuncSetAttribute(shade_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int64_t pairs = (c.cap_app + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
   int grid = (int)(pairs < FTRF_SMS ? pairs : FTRF_SMS);
-  shade_fused_fwd_kernel<<<grid, FZ_THREADS, smem, st>>>(f, c, ws, fs, img);
+  auto go = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, FZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_fused_dbg);
+  };
+  // shipped configurations (app_dim 27, pe 2/2/2 — configs/*.txt, config.yaml) get the unrolled build
+  using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
+  using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
+  using SMlp = StaticSpec<FTRF_SHADE_MLP, 27, 2, 2, 2>;
+  const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
+  if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) go(shade_fused_fwd_kernel<SFea>);
+  else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) go(shade_fused_fwd_kernel<SPe>);
+  else if (f.shading == FTRF_SHADE_MLP && pe2 && f.pos_pe == 2 && f.fea_pe == 2 && fs.kp == SMlp::kp) go(shade_fused_fwd_kernel<SMlp>);
+  else go(shade_fused_fwd_kernel<DynamicSpec>);
   return check_launch("shade_fused_fwd");
 }
 
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_fused_timeline(void* device_buffer_3x512_i64) {
+  ftrf::g_fused_dbg = (long long*)device_buffer_3x512_i64;
+  return FTRF_OK;
+}
