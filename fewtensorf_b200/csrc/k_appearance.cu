@@ -325,7 +325,7 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
   size_t smem = ((size_t)app_np(f) * 32 + (size_t)app_np(f) * LDP) * sizeof(float);
   if (int e = app_check(f, smem)) return e;
   cudaFuncSetAttribute(app_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  app_fwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);
+  app_fwd_kernel<<<FTRF_SMS * 3, 256, smem, st>>>(f, c, ws);
   return check_launch("app_fwd");
 }
 
