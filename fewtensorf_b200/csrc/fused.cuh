@@ -81,8 +81,23 @@ inline bool make_fused_spec(const FtrfField& f, const InSpec& sp, FusedSpec& fs)
 // UMMA K-major no-swizzle [128 rows x 32 k] chunks (hi 16 KB then lo 16 KB), ready for bulk copies:
 //   forward : n1 chunks of W1 (rows = hidden unit, k = internal input column), then 4 chunks of W2.
 constexpr size_t FZ_CHUNK_BYTES = 2u * 128u * 32u * 4u;     // 32 KB
-inline size_t fused_wimg_bytes() { return (size_t)(FZ_MAX_K / 32 + 4) * FZ_CHUNK_BYTES + (size_t)FC * FZ_MAX_K * 4; }
+inline size_t fused_w1p_offset_floats() { return (size_t)(FZ_MAX_K / 32 + 4) * (FZ_CHUNK_BYTES / 4); }
+inline size_t fused_scratch_offset_floats() { return fused_w1p_offset_floats() + (size_t)FC * FZ_MAX_K; }
+inline size_t fused_wimg_bytes() { return (fused_scratch_offset_floats() + (size_t)128 * 48 * 4) * 4; }
 
 int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
+
+// argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)
+struct WgradFusedArgs {
+  const float* g2; const float* h1; const float* g1;   // [M][128] row-major
+  const float* x; int ldx; int kp;                     // [M][ldx], kp <= 152 data columns (multiple of 4)
+  const int32_t* count; int64_t cap;
+  float* dw2;                                          // [128][128]  +=
+  float* dw1i;                                         // [128][ngt*4] zeroed scratch, internal column order; col kp = db1
+  int ngt;                                             // X operand groups (N of the dW1 product = 4 ngt)
+  int dw2_vec;                                         // dw2 is 16-byte aligned
+  int variant;                                         // bring-up switches
+};
+int launch_wgrad_fused(const WgradFusedArgs&, const FusedSpec&, float* g_w1, int ldw, float* g_b1, cudaStream_t);
 
 }  // namespace ftrf

@@ -70,7 +70,57 @@ __global__ void __launch_bounds__(128, 1) mma_probe_kernel(int iters, long long*
   if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 512);
 }
 
+// Layout probe: A region filled with (16-byte unit index) or (element index within the unit); B is a
+// K-major identity, so D[m][k] (k < 8) returns whichever shared-memory float the tensor core used as A(m,k).
+__global__ void __launch_bounds__(128, 1) layout_probe_kernel(int a_mn, uint32_t lbo, uint32_t sbo, int within, float* out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  float* A = reinterpret_cast<float*>(smem_raw);            // 64 KB region
+  float* B = A + 16384;                                     // K-major identity [128 x 8]: units (n/8)*2*8... LBO 128, SBO 256
+  for (int i = threadIdx.x; i < 16384; i += blockDim.x) A[i] = within ? (float)(i & 3) : (float)(i >> 2);
+  for (int i = threadIdx.x; i < 4096; i += blockDim.x) B[i] = 0.f;
+  __syncthreads();
+  if (threadIdx.x < 8) {      // B[n][k] = 1 for n == k < 8 : K-major no-swizzle, rows 0-7 in core matrix 0 (k 0-3) and LBO later (k 4-7)
+    int n = threadIdx.x, k = n;
+    B[(k >> 2) * 32 + n * 4 + (k & 3)] = 1.f;               // unit (k/4) at LBO = 128 B = 32 floats; row n at 16 B
+  }
+  if (threadIdx.x == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  if (threadIdx.x < 32) tc::tmem_alloc(&slot, 512);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = slot;
+  if (threadIdx.x == 0) {
+    uint32_t idesc = tc::idesc_tf32(128, 128) | (a_mn ? (1u << 15) : 0u);
+    uint64_t da = tc::smem_desc(tc::smem_u32(A), lbo, sbo);
+    uint64_t db = tc::smem_desc(tc::smem_u32(B), 128, 256);
+    tc::mma_tf32_ss(tmem, da, db, idesc, false);
+    tc::mma_commit(&bar);
+    tc::mbar_wait(&bar, 0);
+  }
+  __syncthreads();
+  tc::fence_after_sync();
+  {
+    float acc[32];
+    const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    tc::tmem_ld32(tmem + (((uint32_t)(q * 32)) << 16), acc);
+    tc::tmem_wait_ld();
+    for (int k = 0; k < 8; ++k) out[(q * 32 + lane) * 8 + k] = acc[k];
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 512);
+}
+
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_layout_probe(int a_mn, unsigned lbo, unsigned sbo, int within, float* out_device, void* stream) {
+  cudaFuncSetAttribute(ftrf::layout_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304);
+  ftrf::layout_probe_kernel<<<1, 128, 98304, (cudaStream_t)stream>>>(a_mn, lbo, sbo, within, out_device);
+  return ftrf::check_launch("layout_probe");
+}
 
 extern "C" int ftrf_debug_mma_probe(int mode, int iters, int ctas, long long* out_device, void* stream) {
   auto go = [&](auto kern) {

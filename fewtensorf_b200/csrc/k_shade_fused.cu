@@ -472,7 +472,7 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   *handled = true;
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg;
-  float* w1p = c.save_for_backward ? img + (size_t)(FZ_MAX_K / 32 + 4) * 2 * FZ_CHUNK_FLOATS : nullptr;
+  float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
   prep_weights_kernel<<<32, 256, 0, st>>>(f, fs, img, w1p, sp.in_dim);
   if (int e = check_launch("prep_weights")) return e;
   const size_t smem = fused_fwd_smem();

@@ -80,3 +80,35 @@ def test_wgrad3x_matches_fp64(M, K, with_bias):
     if with_bias:
         refb = G.double().sum(0)
         assert float((db.double() - refb).abs().max() / G.double().abs().sum(0).max()) < 4e-6
+
+
+@pytest.mark.parametrize("M,kp", [(16, 152), (17, 152), (1000, 152), (5000, 56), (100000, 152), (4097, 168)])
+def test_wgrad_fused_matches_fp64(M, kp):
+    """Both MLP weight gradients + the bias gradient from one kernel (MN-major UMMA operands)."""
+    from fewtensorf_b200._abi import check, lib
+    lib.ftrf_test_wgrad_fused.restype = C.c_int
+    lib.ftrf_test_wgrad_fused.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64,
+                                          C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    g = torch.Generator(device="cuda").manual_seed(M + kp)
+    rnd = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    G2 = rnd(M, 128) * (torch.rand(M, 128, device="cuda", generator=g) > 0.5)
+    G1 = rnd(M, 128) * (torch.rand(M, 128, device="cuda", generator=g) > 0.5)
+    H1 = torch.relu(rnd(M, 128))
+    X = rnd(M, kp)
+    K = kp - 2                                  # the last two data columns are padding: dropped by the un-permute
+    dW2 = torch.zeros(128, 128, device="cuda")
+    dW1 = torch.zeros(128, K, device="cuda")
+    db1 = torch.zeros(128, device="cuda")
+    scratch = torch.empty(128 * 48 * 4, device="cuda")
+    check(lib.ftrf_test_wgrad_fused(G2.data_ptr(), H1.data_ptr(), G1.data_ptr(), X.data_ptr(), kp, kp, M, dW2.data_ptr(),
+                                    dW1.data_ptr(), K, db1.data_ptr(), scratch.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream), "wgrad_fused")
+    torch.cuda.synchronize()
+
+    def err(out, A, B):
+        ref = A.double().T @ B.double()
+        scale = (A.double().abs().T @ B.double().abs()).clamp_min(1e-30)
+        return float(((out.double() - ref).abs() / scale).max())
+    assert err(dW2, G2, H1) < 4e-6
+    assert err(dW1, G1, X[:, :K]) < 4e-6
+    assert float((db1.double() - G1.double().sum(0)).abs().max() / G1.double().abs().sum(0).max()) < 4e-6
