@@ -83,9 +83,11 @@ inline bool make_fused_spec(const FtrfField& f, const InSpec& sp, FusedSpec& fs)
 constexpr size_t FZ_CHUNK_BYTES = 2u * 128u * 32u * 4u;     // 32 KB
 inline size_t fused_w1p_offset_floats() { return (size_t)(FZ_MAX_K / 32 + 4) * (FZ_CHUNK_BYTES / 4); }
 inline size_t fused_scratch_offset_floats() { return fused_w1p_offset_floats() + (size_t)FC * FZ_MAX_K; }
-inline size_t fused_wimg_bytes() { return (fused_scratch_offset_floats() + (size_t)128 * 48 * 4) * 4; }
+inline size_t fused_bwd_offset_floats() { return fused_scratch_offset_floats() + (size_t)128 * 48 * 4; }
+inline size_t fused_wimg_bytes() { return (fused_bwd_offset_floats() + (size_t)4 * 8192 + (size_t)4 * 2 * 160 * 32) * 4; }
 
 int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
+int launch_shade_dgrad_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 
 // argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)
 struct WgradFusedArgs {

@@ -123,6 +123,7 @@ struct DynamicSpec { static constexpr bool is_static = false; };
 
 // optional phase timeline of CTA 0 (debug aid, scripts/fused_timeline.py): dbg[role*512 + n]
 static long long* g_fused_dbg = nullptr;
+static long long* g_dgrad_dbg = nullptr;
 #define FZ_T(role, n) do { if (dbg && blockIdx.x == 0 && (n) < 512) dbg[(role) * 512 + (n)] = clock64(); } while (0)
 
 
@@ -458,6 +459,348 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
   if (warp == 8) tc::tmem_dealloc(tmem, 512);
 }
 
+// ================================================================================================
+// Backward input-gradient chain as ONE persistent kernel:
+//   g_h1 = relu'(h1) * (g_h2 W2)  ->  g_X = g_h1 W1  ->  g_feat (chain rule through the encoding)
+// per 128-sample tile.  g_h2 arrives from layer3_bwd_kernel; g_h1 is written out for the weight-gradient
+// kernel; g_X never leaves the SM.
+// Roles: two groups of 8 compute warps work on alternate tiles (one group's loads / epilogue overlap
+// the other group's products), thread = (sample row, half of the columns); warp 16 issues the MMAs tile
+// by tile; warp 17 streams the weights by TMA: per tile 8 sub-chunks (K = 16) of W2^T [128 x 16] then 8
+// of W1^T [160 x 16] (internal column order).  Each group owns a 2-stage operand ring, so a group never
+// runs more than one barrier phase ahead of the MMA warp.  TMEM: acc1 columns 0-127 (shared: a tile's
+// acc1 is drained before its second product ends), acc2 of group g at 128 + 160 g.
+constexpr int BZ_GROUPS = 2, BZ_A_STAGES = 2, BZ_W_STAGES = 4;
+constexpr int BZ_W1_ROWS = 160;                                  // kp (152) padded to a multiple of 16
+constexpr int BZ_SUB_K = 16;                                     // k extent of a streamed weight sub-chunk
+constexpr int BZ_W2_SUB_FLOATS = 2 * 128 * BZ_SUB_K;             // hi + lo
+constexpr int BZ_W1_SUB_FLOATS = 2 * BZ_W1_ROWS * BZ_SUB_K;
+constexpr int BZ_WSTAGE_FLOATS = BZ_W1_SUB_FLOATS;
+constexpr int BZ_THREADS = (BZ_GROUPS * 8 + 2) * 32;
+
+__global__ void __launch_bounds__(256)
+prep_weights_bwd_kernel(const FtrfField f, const FusedSpec fs, float* __restrict__ img, int in_dim) {
+  // sub-chunks 0-7: B[n = i][k = o] = W2[o][i], o in [16 sc, 16 sc + 16);  8-15: B[n = kint][k = o] = W1[o][orig(kint)]
+  const int per2 = 128 * 4, per1 = BZ_W1_ROWS * 4;
+  const int total = 8 * per2 + 8 * per1;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const bool second = e >= 8 * per2;
+    const int ee = second ? e - 8 * per2 : e, per = second ? per1 : per2;
+    const int sc = ee / per, r = ee - sc * per, ku = r & 3, nrow = r >> 2;
+    float hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int o = sc * BZ_SUB_K + ku * 4 + j;
+      float v;
+      if (!second) v = __ldg(f.w2 + (size_t)o * FC + nrow);
+      else {
+        const int oc = nrow < fs.kp ? fs.orig[nrow] : -1;
+        v = oc >= 0 ? __ldg(f.w1 + (size_t)o * in_dim + oc) : 0.f;
+      }
+      tc::split_tf32(v, hi[j], lo[j]);
+    }
+    float* base = img + (second ? (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)sc * BZ_W1_SUB_FLOATS : (size_t)sc * BZ_W2_SUB_FLOATS);
+    const int half = (second ? BZ_W1_SUB_FLOATS : BZ_W2_SUB_FLOATS) / 2;
+    const int off = tc::canon_off(nrow, ku, 4);
+    *reinterpret_cast<float4*>(base + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<float4*>(base + half + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
+
+__device__ __forceinline__ void ld_global_v8(const float* p, float* v) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
+
+// which 32-column chunks of g_X hold a column that column-half H turns into g_feat (channels split 14 / rest)
+constexpr int BZ_SPLIT = 14;
+template <class SS>
+__host__ __device__ constexpr bool bz_owned(int sa, int H) { return sa < SS::D && (sa < BZ_SPLIT ? 0 : 1) == H; }
+template <class SS>
+__host__ __device__ constexpr uint32_t bz_chunk_mask(int H) {
+  uint32_t m = 0;
+  for (int P = 0; 2 * P < SS::kp; ++P) {
+    const PairInfo pi = SS::pair(P);
+    bool use = false;
+    if (pi.kind == PK_COPY2) use = bz_owned<SS>(pi.sa, H) || bz_owned<SS>(pi.sb, H);
+    else if (pi.kind == PK_COPY1 || pi.kind == PK_TRIG) use = bz_owned<SS>(pi.sa, H);
+    if (use) m |= 1u << (P / 16);
+  }
+  return m;
+}
+
+template <class SS, int H>
+__device__ __forceinline__ void bz_epilogue(uint32_t t_acc2, const SPair* s_pair, const float* __restrict__ feat_row,
+                                            float* __restrict__ gfeat_row, bool live) {
+  constexpr int C0 = H == 0 ? 0 : BZ_SPLIT, C1 = H == 0 ? (SS::D < BZ_SPLIT ? SS::D : BZ_SPLIT) : SS::D;
+  constexpr int NC = C1 - C0 > 0 ? C1 - C0 : 1;
+  constexpr uint32_t CM = bz_chunk_mask<SS>(H);
+  float gf[NC], ft[NC];
+#pragma unroll
+  for (int k = 0; k < NC; ++k) { gf[k] = 0.f; ft[k] = (live && C0 + k < C1) ? __ldg(feat_row + C0 + k) : 0.f; }
+  float da_s = 0.f, da_c = 1.f;
+#pragma unroll
+  for (int cb = 0; cb < SS::n1; ++cb) {
+    if (!((CM >> cb) & 1u)) continue;
+    float gx[32];
+    tc::tmem_ld32(t_acc2 + (uint32_t)(cb * 32), gx);
+    tc::tmem_wait_ld();
+#pragma unroll
+    for (int pp = 0; pp < 16; ++pp) {
+      const int P = cb * 16 + pp;
+      if (2 * P >= SS::kp) continue;
+      const PairInfo pi = SS::pair(P);
+      if (pi.kind == PK_COPY2 || pi.kind == PK_COPY1) {
+        if (bz_owned<SS>(pi.sa, H)) gf[pi.sa - C0] += gx[2 * pp];
+        if (pi.kind == PK_COPY2 && bz_owned<SS>(pi.sb, H)) gf[pi.sb - C0] += gx[2 * pp + 1];
+      } else if (pi.kind == PK_TRIG && bz_owned<SS>(pi.sa, H)) {
+        const SPair pr = s_pair[P];
+        if (pi.fexp == 0) sincosf(ft[pi.sa - C0], &da_s, &da_c);
+        else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
+        // d/dfeat of (sin(a) ms, cos(a) mc), a = feat 2^f
+        gf[pi.sa - C0] += (float)(1 << pi.fexp) * (da_c * pr.ma * gx[2 * pp] - da_s * pr.mb * gx[2 * pp + 1]);
+      }
+    }
+  }
+  tc::fence_before_sync();
+  if (live) {
+#pragma unroll
+    for (int k = 0; k < NC; ++k)
+      if (C0 + k < C1) gfeat_row[C0 + k] = gf[k];
+  }
+}
+
+template <class SS>
+__global__ void __launch_bounds__(BZ_THREADS, 1)
+shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg) {
+  static_assert(SS::is_static && SS::kp <= BZ_W1_ROWS, "dgrad kernel is built for the static specs only");
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [group][A_STAGES][hi, lo][4096]
+  float* w_ring = a_ring + (size_t)BZ_GROUPS * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS;   // [W_STAGES][BZ_WSTAGE_FLOATS]
+  SPair* s_pair = reinterpret_cast<SPair*>(w_ring + (size_t)BZ_W_STAGES * BZ_WSTAGE_FLOATS);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_pair + FZ_MAX_K / 2);
+  uint64_t* a_full = bars;                                   // [group][A_STAGES]  4 warp arrivals (the column half that owns the chunk)
+  uint64_t* a_empty = a_full + BZ_GROUPS * BZ_A_STAGES;
+  uint64_t* w_full = a_empty + BZ_GROUPS * BZ_A_STAGES;      // [W_STAGES]
+  uint64_t* w_empty = w_full + BZ_W_STAGES;
+  uint64_t* acc_full = w_empty + BZ_W_STAGES;                // [group][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + BZ_GROUPS * 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int64_t ntiles = (n + 127) / 128;
+  if ((int64_t)blockIdx.x >= ntiles) return;
+  const int my_tiles = (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+
+  if (tid == 0) {
+    for (int i = 0; i < BZ_GROUPS * BZ_A_STAGES; ++i) { tc::mbar_init(a_full + i, 4); tc::mbar_init(a_empty + i, 1); }
+    for (int i = 0; i < BZ_W_STAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
+    for (int i = 0; i < BZ_GROUPS * 2; ++i) tc::mbar_init(acc_full + i, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 16) tc::tmem_alloc(tmem_slot, 512);
+  for (int e = tid; e < fs.kp / 2; e += BZ_THREADS) {
+    const PairRec r = fs.pair[e];
+    SPair p;
+    p.meta = (int)r.kind | ((int)r.sa << 8) | ((int)r.sb << 16);
+    p.scale = (float)(1 << r.fexp);
+    p.ma = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.ma) : 1.f;
+    p.mb = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.mb) : 1.f;
+    s_pair[e] = p;
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 16) {
+    // =============================================================== compute warps
+    const int g = warp >> 3, half = (warp >> 2) & 1, q = warp & 3, r_in = q * 32 + lane;
+    const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
+    float* my_ring = a_ring + (size_t)g * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS;
+    uint64_t* my_full = a_full + g * BZ_A_STAGES;
+    uint64_t* my_empty = a_empty + g * BZ_A_STAGES;
+    auto put_chunk = [&](uint32_t ac, const float* vals) {          // 32 values of this row -> operand ring stage
+      const int stg = ac % BZ_A_STAGES;
+      tc::mbar_wait(my_empty + stg, ((ac / BZ_A_STAGES) & 1) ^ 1);
+      float* Ahi = my_ring + (size_t)stg * 2 * FZ_CHUNK_FLOATS;
+      float* Alo = Ahi + FZ_CHUNK_FLOATS;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        float4 h, l;
+        split4(vals + 4 * u, h, l);
+        const int off = tc::canon_off(r_in, u, 8);
+        *reinterpret_cast<float4*>(Ahi + off) = h;
+        *reinterpret_cast<float4*>(Alo + off) = l;
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(my_full + stg);
+    };
+    const bool tl = lane == 0 && q == 0 && half == 0;
+    for (int li = 0; g + 2 * li < my_tiles; ++li) {
+      const int it = g + 2 * li;
+      const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * 128 + r_in;
+      const bool live = row < n;
+      const uint32_t ac0 = (uint32_t)li * 8;
+      if (tl) FZ_T(g, li * 8 + 0);
+      // ---- g_h2 chunks (half, half + 2) -> operand ring (A of g_h2 W2); all loads in flight at once
+      {
+        float v[64];
+        if (live) {
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_gh2 + row * FC + (jj * 2 + half) * 32 + u * 8, v + jj * 32 + 8 * u);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) v[i] = 0.f;
+        }
+        put_chunk(ac0 + half, v);
+        put_chunk(ac0 + 2 + half, v + 32);
+      }
+      if (tl) FZ_T(g, li * 8 + 1);
+      // ---- relu'(h1) of my two chunks as bit masks, fetched while the first product runs
+      uint32_t hm[2] = {0u, 0u};
+      if (live) {
+        float h1[64];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+          for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_h1 + row * FC + (jj * 2 + half) * 32 + u * 8, h1 + jj * 32 + 8 * u);
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) hm[jj] |= (h1[jj * 32 + i] > 0.f ? 1u : 0u) << i;
+      }
+      // ---- g_h1 = relu'(h1) * acc1: saved for the weight-gradient kernel and fed to the second product
+      tc::mbar_wait(acc_full + g * 2 + 0, li & 1);
+      tc::fence_after_sync();
+      if (tl) FZ_T(g, li * 8 + 2);
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj) {
+        const int j = jj * 2 + half;
+        float acc[32];
+        tc::tmem_ld32(tmem + t_lane + (uint32_t)(j * 32), acc);
+        tc::tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = ((hm[jj] >> i) & 1u) ? acc[i] : 0.f;
+        if (live) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_gh1 + row * FC + j * 32 + u * 8, acc + 8 * u);
+        }
+        put_chunk(ac0 + 4 + j, acc);
+      }
+      if (tl) FZ_T(g, li * 8 + 3);
+      // ---- g_X (acc2) -> g_feat: copy column + chain rule through sin / cos, channels split between the halves
+      tc::mbar_wait(acc_full + g * 2 + 1, li & 1);
+      tc::fence_after_sync();
+      if (tl) FZ_T(g, li * 8 + 4);
+      const uint32_t t_acc2 = tmem + t_lane + (uint32_t)(128 + BZ_W1_ROWS * g);
+      if (half == 0) bz_epilogue<SS, 0>(t_acc2, s_pair, ws.a_feat + row * SS::D, ws.a_gfeat + row * SS::D, live);
+      else bz_epilogue<SS, 1>(t_acc2, s_pair, ws.a_feat + row * SS::D, ws.a_gfeat + row * SS::D, live);
+      if (tl) FZ_T(g, li * 8 + 5);
+    }
+  } else if (warp == 16) {
+    // =============================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc2 = tc::idesc_tf32(128, 128), idesc1 = tc::idesc_tf32(128, BZ_W1_ROWS);
+      const uint32_t a_lo0 = tc::desc_lo(tc::smem_u32(a_ring), 128), w_lo0 = tc::desc_lo(tc::smem_u32(w_ring), 128);
+      const uint32_t a_hi = tc::desc_hi(1024), w_hi = tc::desc_hi(512);
+      constexpr uint32_t ALO = FZ_CHUNK_FLOATS * 4 / 16;
+      uint32_t wc = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int g = it & 1, li = it >> 1;
+        for (int ch = 0; ch < 8; ++ch) {
+          const uint32_t ac = (uint32_t)li * 8 + ch;
+          const int as = ac % BZ_A_STAGES;
+          const bool first = ch < 4;
+          const uint32_t ah = a_lo0 + (uint32_t)(g * BZ_A_STAGES + as) * (2 * ALO);
+          const uint32_t wlo = (uint32_t)((first ? BZ_W2_SUB_FLOATS : BZ_W1_SUB_FLOATS) / 2 * 4 / 16);
+          const uint32_t d = tmem + (first ? 0u : (uint32_t)(128 + BZ_W1_ROWS * g)), idesc = first ? idesc2 : idesc1;
+          FZ_T(2, (it * 8 + ch) * 2 + 0);
+          tc::mbar_wait(a_full + g * BZ_A_STAGES + as, (ac / BZ_A_STAGES) & 1);
+          FZ_T(2, (it * 8 + ch) * 2 + 1);
+#pragma unroll
+          for (int sub = 0; sub < 2; ++sub, ++wc) {
+            const int wsg = wc % BZ_W_STAGES;
+            tc::mbar_wait(w_full + wsg, (wc / BZ_W_STAGES) & 1);
+            tc::fence_after_sync();
+            const uint32_t wh = w_lo0 + (uint32_t)wsg * (BZ_WSTAGE_FLOATS * 4 / 16);
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+              const uint32_t ao = (uint32_t)(sub * 2 + s) * 16, wo = (uint32_t)s * 16;
+              const uint32_t fresh = ((ch & 3) == 0 && sub == 0 && s == 0) ? 0u : 1u;
+              tc::mma_tf32_ss_lo2(d, ah + ALO + ao, a_hi, wh + wo, w_hi, idesc, fresh);
+              tc::mma_tf32_ss_lo2(d, ah + ao, a_hi, wh + wlo + wo, w_hi, idesc, 1u);
+              tc::mma_tf32_ss_lo2(d, ah + ao, a_hi, wh + wo, w_hi, idesc, 1u);
+            }
+            tc::mma_commit(w_empty + wsg);
+          }
+          tc::mma_commit(a_empty + g * BZ_A_STAGES + as);
+          if (ch == 3) tc::mma_commit(acc_full + g * 2 + 0);
+          if (ch == 7) tc::mma_commit(acc_full + g * 2 + 1);
+        }
+      }
+    }
+  } else {
+    // =============================================================== weight sub-chunk streamer (TMA)
+    if (lane == 0) {
+      uint32_t wc = 0;
+      for (int it = 0; it < my_tiles; ++it)
+        for (int sc = 0; sc < 16; ++sc, ++wc) {
+          const int wsg = wc % BZ_W_STAGES;
+          const bool first = sc < 8;
+          const uint32_t bytes = (uint32_t)(first ? BZ_W2_SUB_FLOATS : BZ_W1_SUB_FLOATS) * 4;
+          const float* src = first ? wimg + (size_t)sc * BZ_W2_SUB_FLOATS
+                                   : wimg + (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)(sc - 8) * BZ_W1_SUB_FLOATS;
+          tc::mbar_wait(w_empty + wsg, ((wc / BZ_W_STAGES) & 1) ^ 1);
+          mbar_expect_tx(w_full + wsg, bytes);
+          bulk_g2s(w_ring + (size_t)wsg * BZ_WSTAGE_FLOATS, src, bytes, w_full + wsg);
+        }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 16) tc::tmem_dealloc(tmem, 512);
+}
+
+size_t fused_bwd_wimg_floats() { return (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)8 * BZ_W1_SUB_FLOATS; }
+
+// g_h2 (from layer3_bwd) -> g_h1 (saved) and g_feat.  *handled = false: configuration not covered.
+int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, bool* handled) {
+  *handled = false;
+  InSpec sp = make_spec(f);
+  FusedSpec fs;
+  if (!make_fused_spec(f, sp, fs) || fs.kp > ws.ldx || !ws.wimg) return FTRF_OK;
+  using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
+  using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
+  using SMlp = StaticSpec<FTRF_SHADE_MLP, 27, 2, 2, 2>;
+  const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
+  int which = -1;
+  if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) which = 0;
+  else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) which = 1;
+  if (which < 0) return FTRF_OK;                 // (MLP: kp = 168 > 160 rows of the W1^T chunk; generic path)
+  (void)sizeof(SMlp);
+  *handled = true;
+  if (c.cap_app == 0) return FTRF_OK;
+  float* img = ws.wimg + fused_bwd_offset_floats();
+  prep_weights_bwd_kernel<<<32, 256, 0, st>>>(f, fs, img, sp.in_dim);
+  if (int e = check_launch("prep_weights_bwd")) return e;
+  const size_t smem = ((size_t)BZ_GROUPS * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS + (size_t)BZ_W_STAGES * BZ_WSTAGE_FLOATS) * 4 +
+                      (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 24 * 8 + 16;
+  int64_t tiles = (c.cap_app + 127) / 128;
+  int grid = (int)(tiles < FTRF_SMS ? tiles : FTRF_SMS);
+  auto go = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, BZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_dgrad_dbg);
+  };
+  if (which == 0) go(shade_fused_dgrad_kernel<SFea>);
+  else go(shade_fused_dgrad_kernel<SPe>);
+  return check_launch("shade_fused_dgrad");
+}
+
 static size_t fused_fwd_smem() {
   return (size_t)FZ_A_STAGES * 4 * FZ_CHUNK_FLOATS * 4 + (size_t)FZ_W_STAGES * 2 * FZ_CHUNK_FLOATS * 4 +
          (size_t)(2 * FC + 3 * FC) * 4 + (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 16 * 8 + 16;
@@ -495,6 +838,11 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
 }
 
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_dgrad_timeline(void* device_buffer_3x512_i64) {
+  ftrf::g_dgrad_dbg = (long long*)device_buffer_3x512_i64;
+  return FTRF_OK;
+}
 
 extern "C" int ftrf_debug_fused_timeline(void* device_buffer_3x512_i64) {
   ftrf::g_fused_dbg = (long long*)device_buffer_3x512_i64;

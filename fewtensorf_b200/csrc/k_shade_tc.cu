@@ -274,19 +274,28 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   prof_begin(7, st);
   layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
   if (int e = check_launch("layer3_bwd")) return e;
-  Gemm3xArgs g = gemm_args(ws, c);        // g_h1 = relu'(h1) * (g_h2 W2):  B(n=i,k=o) = W2[o][i]
-  g.A = ws.a_gh2; g.lda = FC; g.ka = FC; g.B = f.w2; g.sn = 1; g.sk = FC; g.N = FC; g.K = FC;
-  g.mask = ws.a_h1; g.ldm = FC; g.out = ws.a_gh1; g.ldo = FC;
-  if (int e = launch_gemm3x(g, st)) return e;
+  bool fused_dgrad = false;
+  if (internal) {
+    if (int e = launch_shade_dgrad_fused(f, c, ws, st, &fused_dgrad)) return e;
+  }
+  Gemm3xArgs g = gemm_args(ws, c);
+  if (!fused_dgrad) {
+    // g_h1 = relu'(h1) * (g_h2 W2):  B(n=i,k=o) = W2[o][i]
+    g.A = ws.a_gh2; g.lda = FC; g.ka = FC; g.B = f.w2; g.sn = 1; g.sk = FC; g.N = FC; g.K = FC;
+    g.mask = ws.a_h1; g.ldm = FC; g.out = ws.a_gh1; g.ldo = FC;
+    if (int e = launch_gemm3x(g, st)) return e;
+  }
   prof_end(7, st); prof_begin(8, st);
-  g = gemm_args(ws, c);                   // g_X = g_h1 W1:  B(n=j,k=o) = W1[o][j]
-  g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;
-  if (internal) { g.B = w1p; g.sk = fs.kp; g.N = fs.kp; }
-  g.out = ws.a_gx; g.ldo = ws.ldx;
-  if (int e = launch_gemm3x(g, st)) return e;
-  if (internal) pe_bwd_internal_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp, fs.blk_icol0[0], fs.blk_icol0[1], fs.blk_icol0[2]);
-  else pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
-  if (int e = check_launch("pe_bwd")) return e;
+  if (!fused_dgrad) {
+    g = gemm_args(ws, c);                   // g_X = g_h1 W1:  B(n=j,k=o) = W1[o][j]
+    g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;
+    if (internal) { g.B = w1p; g.sk = fs.kp; g.N = fs.kp; }
+    g.out = ws.a_gx; g.ldo = ws.ldx;
+    if (int e = launch_gemm3x(g, st)) return e;
+    if (internal) pe_bwd_internal_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp, fs.blk_icol0[0], fs.blk_icol0[1], fs.blk_icol0[2]);
+    else pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
+    if (int e = check_launch("pe_bwd")) return e;
+  }
   prof_end(8, st); prof_begin(9, st);
   if (internal) {          // both weight gradients in one kernel (k_wgrad_fused.cu)
     WgradFusedArgs wa{};

@@ -24,8 +24,25 @@ constexpr int WG_KS = 16;                 // samples per chunk (2 k-steps of 8)
 constexpr int WG_STAGES = 3;
 constexpr int WG_NGX_MAX = 48;            // 16-byte column groups of the X operand: data + ones column, padded to a multiple of 4
 constexpr int WG_G_FLOATS = WG_KS * 128;  // one hi (or lo) tile of a 128-wide operand
-constexpr int WG_THREADS = 288;
+constexpr int WG_PROD_WARPS = 16;
+constexpr int WG_PROD = WG_PROD_WARPS * 32;
+constexpr int WG_THREADS = WG_PROD + 32;
 
+
+// Predicated read-only 4-byte load that stays where it is written: `volatile` keeps it ordered with the
+// mbarrier waits / arrivals around it, so the prefetch of a later chunk really is issued before the
+// current chunk is processed (plain loads get sunk towards their use under register pressure).
+__device__ __forceinline__ float ldg_early(const float* p, bool ok) {
+  float v;
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %2, 0;\n\t"
+      "mov.f32 %0, 0f00000000;\n\t"
+      "@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"((int)ok));
+  return v;
+}
 
 __device__ __forceinline__ void red4g(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -51,11 +68,11 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   const int my_chunks = (int)((nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x);
 
   if (tid == 0) {
-    for (int i = 0; i < WG_STAGES; ++i) { tc::mbar_init(full + i, 8); tc::mbar_init(empty + i, 1); }
+    for (int i = 0; i < WG_STAGES; ++i) { tc::mbar_init(full + i, WG_PROD_WARPS); tc::mbar_init(empty + i, 1); }
     tc::mbar_init(done, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
+  if (warp == WG_PROD_WARPS) tc::tmem_alloc(tmem_slot, 512);
   // constant part of every X stage: the ones column (bias gradient) and the zero padding columns
   for (int e = tid; e < WG_STAGES * 2 * (WG_NGX * 4 - a.kp) * 4; e += WG_THREADS) {
     int ku = e & 3, r = e >> 2;
@@ -71,33 +88,31 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;            // dW2: columns 0-127, dW1: columns 128-...
 
-  if (warp < 8) {
+  if (warp < WG_PROD_WARPS) {
     // ============================================================ producers
-    // unit (col, ku) = samples 4ku..4ku+3 of one column; lanes run over col (coalesced 4-byte loads)
-    float v[2][36];
+    // unit (col, ku) = samples 4ku..4ku+3 of one column; lanes run over col (coalesced 4-byte loads).
+    // Three register sets rotate, so the loads of chunk j+3 are in flight while chunks j..j+2 are written.
+    float v[3][20];
     const int xu = a.kp * 4;                              // X units per chunk
-    auto load = [&](int j, float (&r)[36]) {
+    const int gcol = tid & 127, gku = tid >> 7;           // this thread's unit of every 128-wide tile
+    auto load = [&](int j, float (&r)[20]) {
       const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS;
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {                       // 128-wide arrays: unit id = tid + 256 q
-        const int id = tid + 256 * q, col = id & 127, ku = id >> 7;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int64_t s = s0 + ku * 4 + i;
-          const bool ok = s < M;
-          r[q * 12 + i] = ok ? __ldg(a.g2 + s * 128 + col) : 0.f;
-          r[q * 12 + 4 + i] = ok ? __ldg(a.h1 + s * 128 + col) : 0.f;
-          r[q * 12 + 8 + i] = ok ? __ldg(a.g1 + s * 128 + col) : 0.f;
-        }
+      for (int i = 0; i < 4; ++i) {
+        const int64_t s = s0 + gku * 4 + i;
+        const bool ok = s < M;
+        r[i] = ldg_early(a.g2 + s * 128 + gcol, ok);
+        r[4 + i] = ldg_early(a.h1 + s * 128 + gcol, ok);
+        r[8 + i] = ldg_early(a.g1 + s * 128 + gcol, ok);
       }
 #pragma unroll
-      for (int q = 0; q < 3; ++q) {                       // X: kp columns x 4 units
-        const int id = tid + 256 * q;
+      for (int q = 0; q < 2; ++q) {                       // X: kp columns x 4 units
+        const int id = tid + WG_PROD * q;
         const int ku = id / a.kp, col = id - ku * a.kp;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int64_t s = s0 + ku * 4 + i;
-          r[24 + q * 4 + i] = (id < xu && s < M) ? __ldg(a.x + s * a.ldx + col) : 0.f;
+          r[12 + q * 4 + i] = ldg_early(a.x + s * a.ldx + col, id < xu && s < M);
         }
       }
     };
@@ -108,22 +123,19 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
       *reinterpret_cast<float4*>(hi + off) = h;
       *reinterpret_cast<float4*>(lo + off) = l;
     };
-    auto store = [&](int j, float (&r)[36]) {
+    auto store = [&](int j, float (&r)[20]) {
       const int stg = j % WG_STAGES;
       tc::mbar_wait(empty + stg, ((j / WG_STAGES) & 1) ^ 1);
       float* S = ring + (size_t)stg * WG_STAGE_FLOATS;
+      const int off = tc::canon_off(gcol, gku, 4);
+      put(S, S + WG_G_FLOATS, off, r);
+      put(S + 2 * WG_G_FLOATS, S + 3 * WG_G_FLOATS, off, r + 4);
+      put(S + 4 * WG_G_FLOATS, S + 5 * WG_G_FLOATS, off, r + 8);
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
-        const int id = tid + 256 * q, off = tc::canon_off(id & 127, id >> 7, 4);
-        put(S, S + WG_G_FLOATS, off, r + q * 12);
-        put(S + 2 * WG_G_FLOATS, S + 3 * WG_G_FLOATS, off, r + q * 12 + 4);
-        put(S + 4 * WG_G_FLOATS, S + 5 * WG_G_FLOATS, off, r + q * 12 + 8);
-      }
-#pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        const int id = tid + 256 * q;
+        const int id = tid + WG_PROD * q;
         const int ku = id / a.kp, col = id - ku * a.kp;
-        if (id < xu) put(S + 6 * WG_G_FLOATS, S + 6 * WG_G_FLOATS + WG_X_FLOATS, tc::canon_off(col, ku, 4), r + 24 + q * 4);
+        if (id < xu) put(S + 6 * WG_G_FLOATS, S + 6 * WG_G_FLOATS + WG_X_FLOATS, tc::canon_off(col, ku, 4), r + 12 + q * 4);
       }
       tc::fence_async_smem();
       __syncwarp();
@@ -131,12 +143,17 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     };
     load(0, v[0]);
     if (1 < my_chunks) load(1, v[1]);
-    for (int j = 0; j < my_chunks; j += 2) {
+    if (2 < my_chunks) load(2, v[2]);
+    for (int j = 0; j < my_chunks; j += 3) {
       store(j, v[0]);
-      if (j + 2 < my_chunks) load(j + 2, v[0]);
+      if (j + 3 < my_chunks) load(j + 3, v[0]);
       if (j + 1 < my_chunks) {
         store(j + 1, v[1]);
-        if (j + 3 < my_chunks) load(j + 3, v[1]);
+        if (j + 4 < my_chunks) load(j + 4, v[1]);
+      }
+      if (j + 2 < my_chunks) {
+        store(j + 2, v[2]);
+        if (j + 5 < my_chunks) load(j + 5, v[2]);
       }
     }
   } else if (lane == 0) {
@@ -169,13 +186,13 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     tc::mma_commit(done);
   }
   // ============================================================ epilogue: TMEM -> red.global.add.v4
-  if (warp < 8) {
+  if (warp < WG_PROD_WARPS) {
     tc::mbar_wait(done, 0);
     tc::fence_after_sync();
     const int q = warp & 3, o = q * 32 + lane;
     const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
     const int ncb = 4 + (WG_NGX * 4 + 31) / 32;
-    for (int cb = warp >> 2; cb < ncb; cb += 2) {         // 4 column blocks of dW2, then those of dW1
+    for (int cb = warp >> 2; cb < ncb; cb += WG_PROD_WARPS / 4) {         // 4 column blocks of dW2, then those of dW1
       float acc[32];
       tc::tmem_ld32(tmem + t_lane + (uint32_t)(cb * 32), acc);
       tc::tmem_wait_ld();
@@ -193,7 +210,7 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 8) tc::tmem_dealloc(tmem, 512);
+  if (warp == WG_PROD_WARPS) tc::tmem_dealloc(tmem, 512);
 }
 
 // dW1 (internal column order, column kp = bias gradient) -> parameter gradients

@@ -77,8 +77,22 @@ def _mlp_grads_fp64(model, st, internal):
     h2_ref = torch.relu(h1_ref @ W2.t() + m[2].bias.double())
     rgb_ref = torch.sigmoid(h2_ref @ W3.t() + m[4].bias.double())
     gx_ref = g_h1 @ W1i
-    chain = {"h1": (h1, h1_ref), "h2": (h2, h2_ref), "rgb": (rgb, rgb_ref),
-             "g_x": (sec("A_GX", ldx)[:, :gx_ref.shape[1]], gx_ref)}
+    chain = {"h1": (h1, h1_ref), "h2": (h2, h2_ref), "rgb": (rgb, rgb_ref), "g_h1": (sec("A_GH1", 128), g_h1)}
+    if internal is None:
+        chain["g_x"] = (sec("A_GX", ldx)[:, :gx_ref.shape[1]], gx_ref)
+    else:
+        # the fused dgrad kernel keeps g_X on chip: check what it hands on, g_feat, through the chain rule of
+        # [feat | view | PE(feat) | PE(view)] (models/mlp.py:41-64; the bench field has no frequency masks)
+        D, F = 27, 2
+        feat = sec("A_FEAT", D)
+        g_feat = gx_ref[:, :D].clone()
+        c0 = D + 3 + ((D + 3) & 1)
+        for ch in range(D):
+            for fq in range(F):
+                k = c0 + 2 * (ch * F + fq)
+                a = feat[:, ch] * 2.0 ** fq
+                g_feat[:, ch] += 2.0 ** fq * (torch.cos(a) * gx_ref[:, k] - torch.sin(a) * gx_ref[:, k + 1])
+        chain["g_feat"] = (sec("A_GFEAT", D), g_feat)
     return out, chain
 
 
