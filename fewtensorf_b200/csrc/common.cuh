@@ -236,8 +236,31 @@ __device__ __forceinline__ float4 line4(const float* ln, int C, const Tap& t, in
 
 // vectorised reduction into global memory (sm_90+: red.global.add.v4.f32)
 __device__ __forceinline__ void red4(float* p, float4 v) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
+  // no "memory" clobber: the gradient buffers are never read back inside a kernel, and the clobber would
+  // pin the gathers of the next sample behind the reductions of this one
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
+}
+
+// run merging of the gather backward kernels: gradient of the plane / line cell a lane is walking through,
+// reduced into global memory when the cell changes
+struct PlaneRun { int kx, ky; float4 a00, a10, a01, a11; };   // k = i0 | i1 << 16 of the taps
+struct LineRun { int kl; float4 a0, a1; };
+
+__device__ __forceinline__ float4 z4() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ void flush_plane(const PlaneRun& r, float* gp, int W, int C, int ch) {
+  if (r.kx < 0) return;
+  const int x0 = r.kx & 0xffff, x1 = r.kx >> 16, y0 = r.ky & 0xffff, y1 = r.ky >> 16;
+  float* r0 = gp + ((size_t)y0 * W) * C + ch;
+  float* r1 = gp + ((size_t)y1 * W) * C + ch;
+  red4(r0 + (size_t)x0 * C, r.a00);
+  red4(r0 + (size_t)x1 * C, r.a10);
+  red4(r1 + (size_t)x0 * C, r.a01);
+  red4(r1 + (size_t)x1 * C, r.a11);
+}
+__device__ __forceinline__ void flush_line(const LineRun& r, float* gl, int C, int ch) {
+  if (r.kl < 0) return;
+  red4(gl + (size_t)(r.kl & 0xffff) * C + ch, r.a0);
+  red4(gl + (size_t)(r.kl >> 16) * C + ch, r.a1);
 }
 
 __device__ __forceinline__ float softplus_f(float x) {          // F.softplus, beta 1, threshold 20

@@ -168,15 +168,17 @@ app_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 
 // Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
 constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thread
+int g_app_bwd_runs = -1;        // samples per run-merging segment of the VM scatter; 0 = one reduction set per sample, -1 = auto
 
-__global__ void __launch_bounds__(256)
-app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+__global__ void __launch_bounds__(256, 2)
+app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun) {
   extern __shared__ __align__(16) float smem[];
   const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, Dp = (D + 3) & ~3;
   float* Wb = smem;
   float* P = Wb + (size_t)D * NPs;
   float* G = P + (size_t)ATILE * NPs;
   float* GT = G + (size_t)ATILE * Dp;          // [Dp][LDP]  g_feat transposed (samples contiguous)
+  float* XN = GT + (size_t)Dp * LDP;           // [ATILE][3]  normalised sample positions
   const FtrfFactorSet& a = f.app;
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
   for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
@@ -192,8 +194,10 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     const int64_t s = t0 + sl;
     __syncthreads();
     float xn[3] = {0.f, 0.f, 0.f};
-    if (s < n) {
+    if (sl >= ATILE) {
+    } else if (s < n) {
       app_point(f, c, ws, s, xn);
+      if (sub < 3) XN[sl * 3 + sub] = sub == 0 ? xn[0] : (sub == 1 ? xn[1] : xn[2]);
       app_products(f, xn, sub, P + (size_t)sl * NPs);
       for (int o = sub; o < Dp; o += AGS) {
         float g = o < D ? ws.a_gfeat[s * D + o] : 0.f;
@@ -201,6 +205,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
         GT[o * LDP + sl] = g;
       }
     } else {
+      if (sub < 3) XN[sl * 3 + sub] = 0.f;
       for (int k = sub * 4; k < NP; k += AGS * 4) *reinterpret_cast<float4*>(P + (size_t)sl * NPs + k) = make_float4(0, 0, 0, 0);
       for (int o = sub; o < Dp; o += AGS) { G[sl * Dp + o] = 0.f; GT[o * LDP + sl] = 0.f; }
     }
@@ -208,7 +213,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     // (a) basis gradient: 4x4 register tiles over (output group, component group)
 #pragma unroll
     for (int t = 0; t < BW_TT; ++t) {
-      int tt = threadIdx.x + t * 256;
+      int tt = threadIdx.x + t * blockDim.x;
       if (tt < n_tt) {
         int og = tt / n_kg, kg = tt % n_kg;
         for (int r = 0; r < ATILE; ++r) {
@@ -243,7 +248,52 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     }
     __syncthreads();
     // scatter into plane / line gradients
-    if (s < n) {
+    if (arun > 0 && f.model == FTRF_MODEL_VM) {
+      // run merging (see k_density.cu): a thread owns one 4-channel chunk of one factor and walks `arun`
+      // consecutive samples of the tile, reducing into global memory only when the cell changes
+      const int nq = NP / 4, nsegs = (ATILE + arun - 1) / arun;
+      const int tile_n = (int)min((int64_t)ATILE, n - t0);
+      for (int item = threadIdx.x; item < nsegs * nq; item += blockDim.x) {
+        const int seg = item / nq, q = item - seg * nq;
+        int k = 0, base = 0;
+        while (k < 2 && 4 * q >= base + a.n_comp[k]) { base += a.n_comp[k]; ++k; }
+        const int ch = 4 * q - base, C = a.n_comp[k], W = a.plane_w[k], H = a.plane_h[k], L = a.line_len[k];
+        const int m0 = mat0(k), m1 = mat1(k), mv = vecm(k);
+        float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (a.mask[k]) { const float4 m = mask4(a.mask[k], a.mask_stride[k], ch); m2 = mul4(m, m); }
+        PlaneRun pr; LineRun lr;
+        pr.kx = -1; pr.ky = -1; lr.kl = -1;
+        const int i1 = min(tile_n, (seg + 1) * arun);
+        for (int i = seg * arun; i < i1; ++i) {
+          const Tap tx = make_tap(XN[i * 3 + m0], W);
+          const Tap ty = make_tap(XN[i * 3 + m1], H);
+          const Tap tl = make_tap(XN[i * 3 + mv], L);
+          const float4 gq = mul4(*reinterpret_cast<const float4*>(P + (size_t)i * NPs + 4 * q), m2);
+          const float4 pv = plane4(a.plane[k], W, C, tx, ty, ch);
+          const float4 lv = line4(a.line[k], C, tl, ch);
+          const float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
+          const int kx = tx.i0 | (tx.i1 << 16), ky = ty.i0 | (ty.i1 << 16), kl = tl.i0 | (tl.i1 << 16);
+          if (kx != pr.kx || ky != pr.ky) {
+            flush_plane(pr, a.g_plane[k], W, C, ch);
+            pr.kx = kx; pr.ky = ky;
+            pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+          }
+          pr.a00 = fma4(tx.w0 * ty.w0, gp, pr.a00);
+          pr.a10 = fma4(tx.w1 * ty.w0, gp, pr.a10);
+          pr.a01 = fma4(tx.w0 * ty.w1, gp, pr.a01);
+          pr.a11 = fma4(tx.w1 * ty.w1, gp, pr.a11);
+          if (kl != lr.kl) {
+            flush_line(lr, a.g_line[k], C, ch);
+            lr.kl = kl;
+            lr.a0 = z4(); lr.a1 = z4();
+          }
+          lr.a0 = fma4(tl.w0, gl, lr.a0);
+          lr.a1 = fma4(tl.w1, gl, lr.a1);
+        }
+        flush_plane(pr, a.g_plane[k], W, C, ch);
+        flush_line(lr, a.g_line[k], C, ch);
+      }
+    } else if (sl < ATILE && s < n) {
       const float* gqrow = P + (size_t)sl * NPs;
       if (f.model == FTRF_MODEL_VM) {
         int base = 0;
@@ -296,7 +346,7 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   // flush the basis gradient tiles
 #pragma unroll
   for (int t = 0; t < BW_TT; ++t) {
-    int tt = threadIdx.x + t * 256;
+    int tt = threadIdx.x + t * blockDim.x;
     if (tt < n_tt) {
       int og = tt / n_kg, kg = tt % n_kg;
 #pragma unroll
@@ -331,11 +381,23 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
 
 int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   int NPs = app_np(f) + 4, Dp = (f.app_dim + 3) & ~3;
-  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp + (size_t)Dp * LDP) * sizeof(float);
+  size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp + (size_t)Dp * LDP + (size_t)ATILE * 3) * sizeof(float);
   if (int e = app_check(f, smem)) return e;
   cudaFuncSetAttribute(app_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws);
+  // run-merging scatter: (ATILE / run) * NP / 4 work items per tile; auto = the shortest run whose items fit
+  // one pass of the CTA (48x3 components: run 10, 252 items)
+  int arun = f.model == FTRF_MODEL_VM ? g_app_bwd_runs : 0;
+  if (arun < 0) {
+    arun = 4;
+    while (arun < ATILE && ((ATILE + arun - 1) / arun) * (app_np(f) / 4) > 256) ++arun;
+  }
+  app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws, arun);
   return check_launch("app_bwd");
 }
 
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_set_app_runs(int runs) {
+  ftrf::g_app_bwd_runs = runs;
+  return 0;
+}

@@ -14,6 +14,7 @@
 namespace ftrf {
 
 constexpr int GS = 4;   // lanes per sample
+int g_density_bwd_runs = 12;  // longest segment a lane group of the run-merging backward walks; 0 = one reduction set per sample (ftrf_debug_set_runs)
 
 __device__ __forceinline__ float group_sum(float v) {
   v += __shfl_xor_sync(FULL_MASK, v, 1);
@@ -176,6 +177,83 @@ density_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   }
 }
 
+// VM backward with run merging.  A lane group walks up to 12 consecutive entries of the packed list (the
+// samples of one ray are consecutive and half a texel apart), keeps the gradient of the plane cell
+// and of the line cell it is in in registers, and issues the reductions only when the cell changes:
+// ~2x fewer red.global operations than one set per sample (the kernel is bound by their issue rate).
+
+__global__ void __launch_bounds__(256, 2)
+density_bwd_vm_runs_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int DRUN_MAX) {
+  if (ws.counters[2] & 1) return;
+  const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
+  const int sub = threadIdx.x & (GS - 1);
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  // every lane group gets the same number of equally long segments (the grid is one resident wave)
+  const int64_t per = (n + gstride - 1) / gstride;
+  const int64_t rounds = max((int64_t)1, (per + DRUN_MAX - 1) / DRUN_MAX);
+  const int64_t DRUN = max((int64_t)1, (per + rounds - 1) / rounds);
+  const int64_t nseg = (n + DRUN - 1) / DRUN;
+  const FtrfFactorSet& d = f.den;
+  const int cmax = max(d.n_comp[0], max(d.n_comp[1], d.n_comp[2]));
+  for (int64_t seg = g0; seg < nseg; seg += gstride) {
+    const int64_t s0 = seg * DRUN, s1 = min(n, s0 + DRUN);
+    for (int ch = sub * 4; ch < cmax; ch += GS * 4) {
+      PlaneRun pr[3];
+      LineRun lr[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { pr[k].kx = -1; pr[k].ky = -1; lr[k].kl = -1; }
+      for (int64_t s = s0; s < s1; ++s) {
+        const float g = ws.s_gsig[s];
+        if (g == 0.f) continue;
+        Ray ray = load_ray(f, c, ws.s_ray[s]);
+        float p[3], xn[3];
+        sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+        normalize_pt(f, p, xn);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int C = d.n_comp[k], W = d.plane_w[k];
+          if (ch >= C) continue;
+          const Tap tx = make_tap(xn[mat0(k)], W);
+          const Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
+          const Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+          const float4 pv = plane4(d.plane[k], W, C, tx, ty, ch);
+          const float4 lv = line4(d.line[k], C, tl, ch);
+          float4 gm = make_float4(g, g, g, g);
+          if (d.mask[k]) {
+            const float4 m = mask4(d.mask[k], d.mask_stride[k], ch);
+            gm = mul4(gm, mul4(m, m));
+          }
+          const float4 gp = mul4(gm, lv);      // d/d plane sample
+          const float4 gl = mul4(gm, pv);      // d/d line sample
+          const int kx = tx.i0 | (tx.i1 << 16), ky = ty.i0 | (ty.i1 << 16), kl = tl.i0 | (tl.i1 << 16);
+          if (kx != pr[k].kx || ky != pr[k].ky) {
+            flush_plane(pr[k], d.g_plane[k], W, C, ch);
+            pr[k].kx = kx; pr[k].ky = ky;
+            pr[k].a00 = z4(); pr[k].a10 = z4(); pr[k].a01 = z4(); pr[k].a11 = z4();
+          }
+          pr[k].a00 = fma4(tx.w0 * ty.w0, gp, pr[k].a00);
+          pr[k].a10 = fma4(tx.w1 * ty.w0, gp, pr[k].a10);
+          pr[k].a01 = fma4(tx.w0 * ty.w1, gp, pr[k].a01);
+          pr[k].a11 = fma4(tx.w1 * ty.w1, gp, pr[k].a11);
+          if (kl != lr[k].kl) {
+            flush_line(lr[k], d.g_line[k], C, ch);
+            lr[k].kl = kl;
+            lr[k].a0 = z4(); lr[k].a1 = z4();
+          }
+          lr[k].a0 = fma4(tl.w0, gl, lr[k].a0);
+          lr[k].a1 = fma4(tl.w1, gl, lr[k].a1);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        flush_plane(pr[k], d.g_plane[k], d.plane_w[k], d.n_comp[k], ch);
+        flush_line(lr[k], d.g_line[k], d.n_comp[k], ch);
+      }
+    }
+  }
+}
+
 static int sample_grid(int64_t n_hint) {
   int64_t blocks = (n_hint * GS + 255) / 256;
   int64_t cap = (int64_t)FTRF_SMS * 8;
@@ -190,7 +268,8 @@ int launch_density(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStre
 }
 
 int launch_density_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
+  if (f.model == FTRF_MODEL_VM && g_density_bwd_runs) density_bwd_vm_runs_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws, g_density_bwd_runs);
+  else density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
   return check_launch("density_bwd");
 }
 
@@ -201,3 +280,8 @@ int launch_density_at(const FtrfField& f, const float* xyz, int64_t n, float* ou
 }
 
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_set_runs(int density_runs) {
+  ftrf::g_density_bwd_runs = density_runs;
+  return 0;
+}
