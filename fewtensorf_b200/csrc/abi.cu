@@ -122,6 +122,15 @@ static int check_factor_set(const FtrfFactorSet& s, int model, const char* name,
     if (model == FTRF_MODEL_CP && s.n_comp[k] != s.n_comp[0]) { set_error("%s: CP needs equal n_comp", name); return FTRF_E_ARG; }
     if (need_grad && (!s.g_line[k] || (model == FTRF_MODEL_VM && !s.g_plane[k]))) { set_error("%s: gradient pointer %d missing", name, k); return FTRF_E_ARG; }
   }
+  if (model == FTRF_MODEL_VM) {
+    // one resolution per axis (tensoRF.py:186-198): plane k is [size(mat1 k)][size(mat0 k)], line k is size(vecm k)
+    const int size[3] = {s.plane_w[0], s.plane_h[0], s.line_len[0]};
+    for (int k = 0; k < 3; ++k)
+      if (s.plane_w[k] != size[mat0(k)] || s.plane_h[k] != size[mat1(k)] || s.line_len[k] != size[vecm(k)]) {
+        set_error("%s: plane / line %d does not match the per-axis resolutions %d x %d x %d", name, k, size[0], size[1], size[2]);
+        return FTRF_E_ARG;
+      }
+  }
   return FTRF_OK;
 }
 

@@ -199,6 +199,18 @@ __device__ __forceinline__ Tap make_tap(float c, int size) {
   return t;
 }
 
+// The three planes and three lines of a VM factor set sample each axis at ONE resolution (plane k is
+// gridSize[mat1(k)] x gridSize[mat0(k)], line k is gridSize[vecm(k)]; tensoRF.py:186-198; checked by
+// the ABI), so a sample has three distinct taps, not nine.
+struct Taps3 { Tap a[3]; };
+__device__ __forceinline__ Taps3 make_taps3(const FtrfFactorSet& s, const float xn[3]) {
+  Taps3 t;
+  t.a[0] = make_tap(xn[0], s.plane_w[0]);
+  t.a[1] = make_tap(xn[1], s.plane_h[0]);
+  t.a[2] = make_tap(xn[2], s.line_len[0]);
+  return t;
+}
+
 __device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 __device__ __forceinline__ float4 fma4(float w, float4 v, float4 a) {

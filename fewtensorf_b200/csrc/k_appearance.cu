@@ -32,12 +32,11 @@ __device__ __forceinline__ void app_products(const FtrfField& f, const float xn[
   const FtrfFactorSet& a = f.app;
   if (f.model == FTRF_MODEL_VM) {
     int base = 0;
+    const Taps3 T3 = make_taps3(a, xn);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const int C = a.n_comp[k];
-      Tap tx = make_tap(xn[mat0(k)], a.plane_w[k]);
-      Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
-      Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+      const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
       for (int ch = sub * 4; ch < C; ch += AGS * 4) {
         float4 p = plane4(a.plane[k], a.plane_w[k], C, tx, ty, ch);
         float4 l = line4(a.line[k], C, tl, ch);
@@ -72,12 +71,11 @@ __device__ __forceinline__ void app_products_t(const FtrfField& f, const float x
   };
   if (f.model == FTRF_MODEL_VM) {
     int base = 0;
+    const Taps3 T3 = make_taps3(a, xn);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const int C = a.n_comp[k];
-      Tap tx = make_tap(xn[mat0(k)], a.plane_w[k]);
-      Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
-      Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+      const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
       for (int ch = sub * 4; ch < C; ch += AGS * 4) {
         float4 p = plane4(a.plane[k], a.plane_w[k], C, tx, ty, ch);
         float4 l = line4(a.line[k], C, tl, ch);
@@ -297,12 +295,11 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun)
       const float* gqrow = P + (size_t)sl * NPs;
       if (f.model == FTRF_MODEL_VM) {
         int base = 0;
+        const Taps3 T3 = make_taps3(a, xn);
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
           const int C = a.n_comp[k], W = a.plane_w[k];
-          Tap tx = make_tap(xn[mat0(k)], W);
-          Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
-          Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
+          const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
           for (int ch = sub * 4; ch < C; ch += AGS * 4) {
             float4 gq = *reinterpret_cast<const float4*>(gqrow + base + ch);
             if (a.mask[k]) {

@@ -27,12 +27,11 @@ __device__ __forceinline__ float density_partial(const FtrfField& f, const float
   const FtrfFactorSet& d = f.den;
   float acc = 0.f;
   if (f.model == FTRF_MODEL_VM) {
+    const Taps3 T3 = make_taps3(d, xn);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const int C = d.n_comp[k];
-      Tap tx = make_tap(xn[mat0(k)], d.plane_w[k]);
-      Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
-      Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+      const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
       for (int c = sub * 4; c < C; c += GS * 4) {
         float4 p = plane4(d.plane[k], d.plane_w[k], C, tx, ty, c);
         float4 l = line4(d.line[k], C, tl, c);
@@ -129,12 +128,11 @@ density_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
     normalize_pt(f, p, xn);
     if (f.model == FTRF_MODEL_VM) {
+      const Taps3 T3 = make_taps3(d, xn);
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const int C = d.n_comp[k], W = d.plane_w[k];
-        Tap tx = make_tap(xn[mat0(k)], W);
-        Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
-        Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+        const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
         for (int ch = sub * 4; ch < C; ch += GS * 4) {
           float4 pv = plane4(d.plane[k], W, C, tx, ty, ch);
           float4 lv = line4(d.line[k], C, tl, ch);
@@ -210,13 +208,12 @@ density_bwd_vm_runs_kernel(const FtrfField f, const FtrfCall c, const Ws ws, con
         float p[3], xn[3];
         sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
         normalize_pt(f, p, xn);
+        const Taps3 T3 = make_taps3(d, xn);
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
           const int C = d.n_comp[k], W = d.plane_w[k];
           if (ch >= C) continue;
-          const Tap tx = make_tap(xn[mat0(k)], W);
-          const Tap ty = make_tap(xn[mat1(k)], d.plane_h[k]);
-          const Tap tl = make_tap(xn[vecm(k)], d.line_len[k]);
+          const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
           const float4 pv = plane4(d.plane[k], W, C, tx, ty, ch);
           const float4 lv = line4(d.line[k], C, tl, ch);
           float4 gm = make_float4(g, g, g, g);

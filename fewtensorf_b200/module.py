@@ -26,7 +26,7 @@ import torch.nn.functional as F
 from . import _abi
 from ._abi import FtrfCall, FtrfField, check, lib
 
-MAX_CANDIDATES = 1 << 26      # rays * samples processed per launch sequence (workspace bound)
+MAX_CANDIDATES = 1 << 30      # rays * samples per launch sequence (int32 sample cursors); an 800x800 frame is one sequence
 
 
 def _stream() -> int:

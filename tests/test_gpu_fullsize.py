@@ -159,3 +159,28 @@ def test_eval_render_matches_training_forward_without_jitter(workload):
     assert int(nv_e) == int(nv_t)
     assert torch.equal(depth_e, depth_t)
     assert _rel(rgb_t.detach(), rgb_e) < 1e-6
+
+
+def test_coarse_occupancy_keeps_sample_lists_bit_exact(workload):
+    """The march kernel's coarse-block shortcut (approximate texel coordinate + dilated 8^3 occupancy) must
+    not change a single keep decision: packed (ray, index) lists with and without it are the same set."""
+    import bench
+    model, rays, target = workload
+    cam = bench.camera_rays(rays.device)[::7][:60000].contiguous()      # image-wide subset of a test view
+    keys = []
+    for use in (True, False):
+        model.use_coarse_mask = use
+        try:
+            with torch.no_grad():
+                model(cam, None, white_bg=True, is_train=False, N_samples=-1)
+        finally:
+            model.use_coarse_mask = True
+        st = model._last_call
+        n = st.n_samples
+        ray = model.workspace_section(st, "S_RAY", torch.int32, n).long()
+        idx = model.workspace_section(st, "S_IDX", torch.int32, n).long()
+        cnt = model.workspace_section(st, "RAY_CNT", torch.int32, cam.shape[0]).clone()
+        keys.append((torch.sort(ray * 4096 + idx).values.clone(), cnt, n))
+    assert keys[0][2] == keys[1][2] and keys[0][2] > 100000
+    assert torch.equal(keys[0][1], keys[1][1])
+    assert torch.equal(keys[0][0], keys[1][0])
