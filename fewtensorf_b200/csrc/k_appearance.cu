@@ -8,6 +8,7 @@
 // held in shared memory.  Algorithmic bytes per shaded sample (VM 48x3): 3*48*(4+2)*4 = 3456 B
 // forward, 6912 B backward (re-read + gradient reduction).
 #include "common.cuh"
+#include "tc.cuh"
 
 namespace ftrf {
 
@@ -71,11 +72,12 @@ __device__ __forceinline__ void app_products_t(const FtrfField& f, const float x
   };
   if (f.model == FTRF_MODEL_VM) {
     int base = 0;
-    const Taps3 T3 = make_taps3(a, xn);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const int C = a.n_comp[k];
-      const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
+      Tap tx = make_tap(xn[mat0(k)], a.plane_w[k]);
+      Tap ty = make_tap(xn[mat1(k)], a.plane_h[k]);
+      Tap tl = make_tap(xn[vecm(k)], a.line_len[k]);
       for (int ch = sub * 4; ch < C; ch += AGS * 4) {
         float4 p = plane4(a.plane[k], a.plane_w[k], C, tx, ty, ch);
         float4 l = line4(a.line[k], C, tl, ch);
@@ -162,6 +164,177 @@ app_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
       }
     }
   }
+}
+
+// Forward on the tensor cores (VM, every n_comp a multiple of 8 and <= 64, app_dim <= 32).
+// A CTA owns tiles of 128 shaded samples.  Per tile: 128 threads compute the three taps of their sample
+// once into shared memory; then, per factor pair k, all 256 threads gather plane x line products —
+// consecutive lanes take consecutive 16-byte channel chunks of one texel, so a warp reads whole 192-byte
+// texels — split them into tf32 hi / lo and store them as a UMMA K-major operand tile [128 x C_k]; one
+// thread issues the 3xTF32 products against the pre-split basis matrix image [32 x C_k]
+// (tcgen05.mma M=128 N=32 K=8, accumulating over the three pairs in 32 TMEM columns); the epilogue reads
+// the accumulator rows back and stores app_dim features per sample.  Two CTAs per SM overlap one CTA's
+// gathers with the other's products.
+constexpr int TCT = 128;
+constexpr int TC_LBO_F = 36;      // operand tile: 144 B between K-adjacent core matrices (128 B + 16 B skew: the 12 lanes that
+                                  // write the chunks of one sample row then hit different banks)
+int g_app_fwd_tc = 1;           // bring-up switch (ftrf_debug_set_app_tc)
+
+__global__ void __launch_bounds__(256, 2)
+app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM) {
+  extern __shared__ __align__(1024) uint8_t app_raw[];
+  const FtrfFactorSet& a = f.app;
+  const int NP = a.n_comp[0] + a.n_comp[1] + a.n_comp[2], D = f.app_dim;
+  float* Bimg = reinterpret_cast<float*>(app_raw);             // per pair k: hi [32 x C_k] then lo [32 x C_k]
+  float* Phi = Bimg + (size_t)2 * 32 * NP;                      // [128 x CM]
+  float* Plo = Phi + (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F;
+  float4* TAP = reinterpret_cast<float4*>(Plo + (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F);   // [128][3] (i0, i1, w0, w1) per axis
+  uint64_t* bar = reinterpret_cast<uint64_t*>(TAP + TCT * 3);
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar + 1);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  if ((int64_t)blockIdx.x * TCT >= n) return;
+
+  {   // basis matrix image (outputs padded to 32 rows of zeros)
+    int base = 0, kb = 0;
+    for (int k = 0; k < 3; ++k) {
+      const int Ck = a.n_comp[k], nq = Ck >> 2;
+      for (int e = tid; e < 32 * nq; e += 256) {
+        const int o = e / nq, ku = e - o * nq;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f), h, l;
+        if (o < D) w = ld4(f.basis + (size_t)o * NP + kb + ku * 4);
+        const float v[4] = {w.x, w.y, w.z, w.w};
+        tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y); tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+        const int off = tc::canon_off(o, ku, nq);
+        *reinterpret_cast<float4*>(Bimg + base + off) = h;
+        *reinterpret_cast<float4*>(Bimg + base + 32 * Ck + off) = l;
+      }
+      base += 2 * 32 * Ck;
+      kb += Ck;
+    }
+  }
+  if (tid == 0) { tc::mbar_init(bar, 1); tc::fence_barrier_init(); }
+  if (warp == 0) tc::tmem_alloc(tslot, 32);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tslot;
+  const uint32_t idesc = tc::idesc_tf32(128, 32);
+  uint32_t ph = 0;
+
+  for (int64_t t0 = (int64_t)blockIdx.x * TCT; t0 < n; t0 += (int64_t)gridDim.x * TCT) {
+    if (tid < TCT) {
+      const int64_t s = t0 + tid;
+      float4 tp[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) tp[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // index 0, weight 0
+      if (s < n) {
+        float xn[3];
+        app_point(f, c, ws, s, xn);
+        const Taps3 T = make_taps3(a, xn);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
+      }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) TAP[tid * 3 + j] = tp[j];
+    }
+    __syncthreads();
+    int bbase = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int Ck = a.n_comp[k], nq = Ck >> 2, W = a.plane_w[k];
+      if (k > 0) {                      // the previous pair's products have consumed the operand tile
+        tc::mbar_wait(bar, ph);
+        ph ^= 1;
+        tc::fence_after_sync();
+      }
+      // two items per iteration, all twelve gathers issued before the first use
+      for (int item = tid; item < TCT * nq; item += 512) {
+        float4 pv[2], lv[2];
+        int off[2];
+        bool on[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int it2 = item + u * 256;
+          on[u] = it2 < TCT * nq;
+          const int sl = on[u] ? it2 / nq : 0, cq = on[u] ? it2 - sl * nq : 0, ch = cq * 4;
+          const float4 ax = TAP[sl * 3 + mat0(k)], ay = TAP[sl * 3 + mat1(k)], al = TAP[sl * 3 + vecm(k)];
+          const Tap tx = {__float_as_int(ax.x), __float_as_int(ax.y), ax.z, ax.w};
+          const Tap ty = {__float_as_int(ay.x), __float_as_int(ay.y), ay.z, ay.w};
+          const Tap tl = {__float_as_int(al.x), __float_as_int(al.y), al.z, al.w};
+          pv[u] = plane4(a.plane[k], W, Ck, tx, ty, ch);
+          lv[u] = line4(a.line[k], Ck, tl, ch);
+          if (a.mask[k]) {                                   // (plane m)(line m), tensoRF.py:250, :257
+            const float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+            pv[u] = mul4(pv[u], m);
+            lv[u] = mul4(lv[u], m);
+          }
+          off[u] = ((sl >> 3) * nq + cq) * TC_LBO_F + (sl & 7) * 4;
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (!on[u]) continue;
+          const float4 v4 = mul4(pv[u], lv[u]);
+          float4 h, l;
+          const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+          tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y); tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+          *reinterpret_cast<float4*>(Phi + off[u]) = h;
+          *reinterpret_cast<float4*>(Plo + off[u]) = l;
+        }
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      __syncthreads();
+      if (tid == 0) {
+        tc::fence_after_sync();
+        const uint32_t hi_w = tc::desc_hi((uint32_t)nq * 128u), hi_a = tc::desc_hi((uint32_t)nq * TC_LBO_F * 4u);
+        const uint32_t ah = tc::desc_lo(tc::smem_u32(Phi), TC_LBO_F * 4), al_ = tc::desc_lo(tc::smem_u32(Plo), TC_LBO_F * 4);
+        const uint32_t bh = tc::desc_lo(tc::smem_u32(Bimg + bbase), 128), bl = tc::desc_lo(tc::smem_u32(Bimg + bbase + 32 * Ck), 128);
+        for (int ks = 0; ks < (Ck >> 3); ++ks) {
+          const uint32_t o = (uint32_t)ks * 16u;          // two core-matrix columns per k-step
+          const uint32_t oa = (uint32_t)ks * (2u * TC_LBO_F * 4u / 16u);
+          tc::mma_tf32_ss_lo2(tmem, al_ + oa, hi_a, bh + o, hi_w, idesc, (k == 0 && ks == 0) ? 0u : 1u);
+          tc::mma_tf32_ss_lo2(tmem, ah + oa, hi_a, bl + o, hi_w, idesc, 1u);
+          tc::mma_tf32_ss_lo2(tmem, ah + oa, hi_a, bh + o, hi_w, idesc, 1u);
+        }
+        tc::mma_commit(bar);
+      }
+      bbase += 2 * 32 * Ck;
+    }
+    tc::mbar_wait(bar, ph);
+    ph ^= 1;
+    tc::fence_after_sync();
+    // accumulator rows -> shared (the operand tile is free: its last products have completed) -> one
+    // contiguous block of app_dim * 128 floats in global memory, written with full 16-byte lanes
+    float* stage = Phi;
+    if (warp < 4) {
+      float acc[32];
+      tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16), acc);
+      tc::tmem_wait_ld();
+#pragma unroll
+      for (int o = 0; o < 32; ++o)
+        if (o < D) stage[tid * D + o] = acc[o];
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    {
+      const int rows = (int)min((int64_t)TCT, n - t0);
+      const int total = rows * D;                       // floats; the block starts 16-byte aligned (t0 % 128 == 0)
+      float* dst = ws.a_feat + t0 * D;
+      if ((((size_t)dst) & 15) == 0) {
+        for (int e = tid * 4; e < total; e += 256 * 4) {
+          if (e + 4 <= total) *reinterpret_cast<float4*>(dst + e) = *reinterpret_cast<const float4*>(stage + e);
+          else for (int j = e; j < total; ++j) dst[j] = stage[j];
+        }
+      } else {
+        for (int e = tid; e < total; e += 256) dst[e] = stage[e];
+      }
+    }
+    tc::fence_before_sync();
+    __syncthreads();                    // accumulator read, TAP / operand tile free for the next tile
+  }
+  if (warp == 0) tc::tmem_dealloc(tmem, 32);
 }
 
 // Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
@@ -369,6 +542,14 @@ static int app_check(const FtrfField& f, size_t smem) {
 
 int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (f.app_dim > 32) { set_error("appearance: app_dim %d > 32 unsupported", f.app_dim); return FTRF_E_ARG; }
+  const FtrfFactorSet& a = f.app;
+  const int cm = f.model == FTRF_MODEL_VM ? (a.n_comp[0] > a.n_comp[1] ? (a.n_comp[0] > a.n_comp[2] ? a.n_comp[0] : a.n_comp[2]) : (a.n_comp[1] > a.n_comp[2] ? a.n_comp[1] : a.n_comp[2])) : 0;
+  if (g_app_fwd_tc && f.model == FTRF_MODEL_VM && a.n_comp[0] % 8 == 0 && a.n_comp[1] % 8 == 0 && a.n_comp[2] % 8 == 0 && cm <= 64) {
+    const size_t sm = ((size_t)2 * 32 * app_np(f) + (size_t)2 * (TCT / 8) * (cm / 4) * TC_LBO_F) * sizeof(float) + (size_t)TCT * 3 * sizeof(float4) + 32;
+    cudaFuncSetAttribute(app_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    app_fwd_tc_kernel<<<FTRF_SMS * 2, 256, sm, st>>>(f, c, ws, cm);
+    return check_launch("app_fwd_tc");
+  }
   size_t smem = ((size_t)app_np(f) * 32 + (size_t)app_np(f) * LDP) * sizeof(float);
   if (int e = app_check(f, smem)) return e;
   cudaFuncSetAttribute(app_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -393,6 +574,11 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
 }
 
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_set_app_tc(int on) {
+  ftrf::g_app_fwd_tc = on;
+  return 0;
+}
 
 extern "C" int ftrf_debug_set_app_runs(int runs) {
   ftrf::g_app_bwd_runs = runs;

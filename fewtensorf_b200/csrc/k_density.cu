@@ -72,15 +72,25 @@ density_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
   // all lanes of a warp run the same trip count so the group shuffles stay converged
   const int64_t n_pad = (n + 7) & ~(int64_t)7;
+  // the list entry and the ray of the NEXT iteration are fetched while this one gathers: without that a
+  // sample is three dependent global round trips (entry -> ray -> texels) with nothing else in flight
+  Ray ray_n = {};
+  int idx_n = 0;
+  if (g0 < n) { ray_n = load_ray(f, c, ws.s_ray[g0]); idx_n = ws.s_idx[g0]; }
   for (int64_t s = g0; s < n_pad; s += gstride) {
+    const Ray ray = ray_n;
+    const int idx = idx_n;
+    const int64_t s2 = s + gstride;
+    int r2 = 0;
+    if (s2 < n) { r2 = ws.s_ray[s2]; idx_n = ws.s_idx[s2]; }
     float part = 0.f;
     if (s < n) {
-      Ray ray = load_ray(f, c, ws.s_ray[s]);
       float p[3], xn[3];
-      sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+      sample_pt(ray, sample_z(f, c, ray, idx), p);
       normalize_pt(f, p, xn);
       part = density_partial(f, xn, sub);
     }
+    if (s2 < n) ray_n = load_ray(f, c, r2);
     float feat = group_sum(part);
     if (s < n && sub == 0) ws.s_sigma[s] = activate(f, feat);
   }
