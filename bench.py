@@ -224,15 +224,26 @@ def workload_config(n_gpus):
 
 
 # ------------------------------------------------------------------------------------------ GPU leg
-ALGO = {   # algorithmic work per unit (DESIGN.md / SURVEY section 8d): (unit, amount, bound)
-    "march": ("cand", 0.0, "hbm"),
-    "density_fwd": ("vd", 1152.0, "hbm"), "density_bwd": ("vd", 2304.0, "hbm"),
-    "integrate_fwd": ("vd", 12.0, "hbm"), "integrate_bwd": ("vd", 24.0, "hbm"), "composite": ("vd", 8.0, "hbm"),
-    "app_fwd": ("va", 3456.0, "hbm"), "app_bwd": ("va", 6912.0, "hbm"),
-    "shade_fwd": ("va", 71936.0, "tensor"), "shade_bwd_hidden": ("va", 2.0 * (128 * 128 + 3 * 128) * 1.0 + 2 * 3 * 128, "tensor"),
-    "shade_bwd_input": ("va", 2.0 * 150 * 128, "tensor"), "shade_wgrad2": ("va", 2.0 * 128 * 128, "tensor"),
-    "shade_wgrad1": ("va", 2.0 * 150 * 128, "tensor"),
+# Algorithmic HBM bytes per unit and stage (DESIGN.md section 5 derives each figure): what the stage must
+# read and write once if every reuse hit on chip.  vd = samples that survive the alphaMask cull, va = shaded
+# samples (weight > threshold), ray = rays of the step.  Every stage is memory-side bound on B200: even the
+# MLP stages need < 45 flop per algorithmic byte, far under the tensor/HBM ratio (1658 TF/s : 6.5 TB/s = 254).
+ALGO = {
+    "march": (("vd", 8.0), ("ray", 36.0)),                 # packed (ray, index) out; ray in, tmin/offset/count out
+    "density_fwd": (("vd", 1152.0 + 8 + 4),),              # 3 x 16 comps x (4 plane + 2 line taps) x 4 B; list in, sigma out
+    "integrate_fwd": (("vd", 12.0), ("va", 4.0)),
+    "app_fwd": (("va", 3456.0 + 12 + 108),),               # 3 x 48 comps x 6 taps x 4 B; slot + list in, 27 features out
+    "shade_fwd": (("va", 108.0 + 608 + 512 + 512 + 12),),  # features in; X, h1, h2 (saved for backward) and rgb out
+    "composite": (("vd", 8.0), ("va", 12.0), ("ray", 16.0)),
+    "integrate_bwd": (("vd", 24.0), ("va", 24.0)),
+    "shade_bwd_out": (("va", 512.0 + 512 + 24),),          # h2 in, g_h2 out, rgb / g_rgb in
+    "shade_bwd_dgrad": (("va", 512.0 + 512 + 512 + 108 + 108),),   # g_h2, h1 in; g_h1 out; features in, g_feat out
+    "shade_wgrad": (("va", 512.0 * 3 + 608),),             # g_h2, h1, g_h1, X in (weight gradients stay on chip)
+    "shade_wgrad1_unfused": (("va", 0.0),),
+    "app_bwd": (("va", 2 * 3456.0 + 108 + 12),),           # taps re-read + gradient reduced into the same texels
+    "density_bwd": (("vd", 2 * 1152.0 + 12),),
 }
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "dram_traffic.json")   # per-launch dram bytes from `ncu --set full` (scripts/ncu_summary.py traffic)
 
 
 def load_peaks():
@@ -302,7 +313,9 @@ def run_gpu(args):
 
     sampler = ClockSampler(local)
     sampler.start()
+    launches0 = lib.ftrf_launch_count()
     total_ms, _, last = timed(args.steps, False)
+    launches = int(lib.ftrf_launch_count() - launches0)
     clocks = sampler.summary()
     _, stage_ms, _ = timed(min(args.steps, 20), True)
     t = torch.tensor([total_ms], device=dev)
@@ -365,19 +378,24 @@ def run_gpu(args):
             dist.destroy_process_group()
         return
     peaks = load_peaks()
-    units = {"vd": vd, "va": va, "cand": RAYS_PER_GPU * N_SAMPLES}
+    units = {"vd": vd, "va": va, "ray": RAYS_PER_GPU}
     names = [lib.ftrf_profile_stage_name(i).decode() for i in range(PROF_STAGES)]
+    try:
+        with open(TRAFFIC_FILE) as fh:
+            traffic = json.load(fh)
+    except Exception:
+        traffic = {}
     stages = {}
     for n_, ms in zip(names, stage_ms):
-        unit, amt, bound = ALGO[n_]
-        work = units[unit] * amt
-        ach = (work / (ms * 1e-3) / (1e9 if bound == "hbm" else 1e12)) if ms > 0 else 0.0
-        stages[n_] = {"ms": round(ms, 5), "bound": bound, "achieved": round(ach, 3),
-                      "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": round(ach / peaks[bound], 5)}
+        work = sum(units[u] * amt for u, amt in ALGO[n_])
+        ach = (work / (ms * 1e-3) / 1e9) if ms > 0 else 0.0
+        stages[n_] = {"ms": round(ms, 5), "bound": "hbm", "algorithmic_bytes": int(work), "achieved": round(ach, 3),
+                      "unit": "GB/s", "frac": round(ach / peaks["hbm"], 5)}
     top = max(stages, key=lambda k: stages[k]["ms"])
-    roof = {"kernel": top, "bound": stages[top]["bound"], "achieved": stages[top]["achieved"], "peak": peaks[stages[top]["bound"]],
-            "unit": stages[top]["unit"], "frac": stages[top]["frac"], "traffic": None, "peak_source": peaks["src"],
-            "ms_per_launch": stages[top]["ms"]}
+    roof = {"kernel": top, "bound": "hbm", "achieved": stages[top]["achieved"], "peak": peaks["hbm"],
+            "unit": "GB/s", "frac": stages[top]["frac"], "traffic": traffic.get(top, {}).get("dram_bytes_per_launch"),
+            "traffic_source": traffic.get(top, {}).get("source"), "peak_source": peaks["src"],
+            "ms_per_launch": stages[top]["ms"], "algorithmic_bytes_per_launch": stages[top]["algorithmic_bytes"]}
     cpu = None
     if world == 1 and not args.no_cpu:
         f = cpu_field(model)
@@ -392,7 +410,7 @@ def run_gpu(args):
            "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32,
                    "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing)",
                    "train_step_api_value": e2e_fused_rps},
-           "gpu_launches": 14 * args.steps, "roofline": roof, "stages": stages,
+           "gpu_launches": launches, "roofline": roof, "stages": stages,
            "samples": {"valid_per_step": vd, "shaded_per_step": va, "loss": float(last[0])}}
     if render:
         out["render"] = {"metric": "800x800 render ms/frame (N_samples=-1, rays in HBM, rows interleaved over GPUs)",

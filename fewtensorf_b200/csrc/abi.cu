@@ -18,7 +18,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static unsigned long long g_launches = 0;   // kernels this library has launched (every launch is followed by check_launch)
+
 int check_launch(const char* what) {
+  ++g_launches;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
@@ -30,7 +33,7 @@ int check_launch(const char* what) {
 // ---- optional per-stage timing --------------------------------------------------------------
 static const char* kStageNames[FTRF_PROF_STAGES] = {
     "march", "density_fwd", "integrate_fwd", "app_fwd", "shade_fwd", "composite",
-    "integrate_bwd", "shade_bwd_hidden", "shade_bwd_input", "shade_wgrad2", "shade_wgrad1", "app_bwd", "density_bwd"};
+    "integrate_bwd", "shade_bwd_out", "shade_bwd_dgrad", "shade_wgrad", "shade_wgrad1_unfused", "app_bwd", "density_bwd"};
 static bool g_prof_on = false;
 static cudaEvent_t g_ev[FTRF_PROF_STAGES][2];
 static bool g_ev_made = false, g_ev_used[FTRF_PROF_STAGES];
@@ -208,6 +211,7 @@ extern "C" const char* ftrf_profile_stage_name(int stage) {
   return (stage >= 0 && stage < FTRF_PROF_STAGES) ? kStageNames[stage] : "";
 }
 
+extern "C" unsigned long long ftrf_launch_count(void) { return ftrf::g_launches; }
 extern "C" int ftrf_abi_version(void) { return FTRF_ABI_VERSION; }
 extern "C" const char* ftrf_last_error(void) { return g_err; }
 

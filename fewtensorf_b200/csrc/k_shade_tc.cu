@@ -274,6 +274,7 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   prof_begin(7, st);
   layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
   if (int e = check_launch("layer3_bwd")) return e;
+  prof_end(7, st); prof_begin(8, st);      // stage 7: output layer; stage 8: dgrad chain down to g_feat
   bool fused_dgrad = false;
   if (internal) {
     if (int e = launch_shade_dgrad_fused(f, c, ws, st, &fused_dgrad)) return e;
@@ -285,7 +286,6 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     g.mask = ws.a_h1; g.ldm = FC; g.out = ws.a_gh1; g.ldo = FC;
     if (int e = launch_gemm3x(g, st)) return e;
   }
-  prof_end(7, st); prof_begin(8, st);
   if (!fused_dgrad) {
     g = gemm_args(ws, c);                   // g_X = g_h1 W1:  B(n=j,k=o) = W1[o][j]
     g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;

@@ -198,6 +198,8 @@ int ftrf_set_shade_path(int path);
 int ftrf_profile_enable(int on);
 int ftrf_profile_read(float* ms_out /* host */);
 const char* ftrf_profile_stage_name(int stage);
+/* Number of CUDA kernels this library has launched since it was loaded (bench.py's gpu_launches). */
+unsigned long long ftrf_launch_count(void);
 
 #ifdef __cplusplus
 }
