@@ -68,7 +68,7 @@ class FtrfCall(C.Structure):
 
 # every symbol include/fewtensorf.h declares
 EXPORTS = [
-    "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward",
+    "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward", "ftrf_backward_part",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
@@ -91,6 +91,8 @@ def _load():
     lib.ftrf_workspace_layout.restype = C.c_size_t
     lib.ftrf_workspace_layout.argtypes = [C.POINTER(FtrfField), C.POINTER(FtrfCall), C.POINTER(C.c_int64)]
     stage_args = [C.POINTER(FtrfField), C.POINTER(FtrfCall), C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.ftrf_backward_part.restype = C.c_int
+    lib.ftrf_backward_part.argtypes = stage_args + [C.c_int]
     for name in ("ftrf_forward", "ftrf_backward", "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate",
                  "ftrf_stage_appearance", "ftrf_stage_shade", "ftrf_stage_composite"):
         fn = getattr(lib, name)

@@ -259,20 +259,33 @@ extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, si
   return e;
 }
 
-extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+// part 1: everything but the density backward (after it every gradient except the density factors' is
+// final); part 2: the density backward; part 0: both.
+extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream, int part) {
   Ws ws;
+  if (part < 0 || part > 2) { set_error("backward: part %d", part); return FTRF_E_ARG; }
   if (int e = check_args(f, c, wsb, ws_bytes, true, &ws)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  prof_begin(6, st);
-  if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
-  prof_end(6, st);
-  if (int e = launch_shade_bwd(*f, *c, ws, st)) return e;     // stages 7-10 marked inside
-  prof_begin(11, st);
-  if (int e = launch_appearance_bwd(*f, *c, ws, st)) return e;
-  prof_end(11, st); prof_begin(12, st);
-  int e = launch_density_bwd(*f, *c, ws, st);
-  prof_end(12, st);
-  return e;
+  if (part != 2) {
+    prof_begin(6, st);
+    if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
+    prof_end(6, st);
+    if (int e = launch_shade_bwd(*f, *c, ws, st, 0)) return e;     // stages 7-10 marked inside
+    prof_begin(11, st);
+    if (int e = launch_appearance_bwd(*f, *c, ws, st)) return e;
+    prof_end(11, st);
+  }
+  if (part != 1) {
+    prof_begin(12, st);
+    int e = launch_density_bwd(*f, *c, ws, st);
+    prof_end(12, st);
+    return e;
+  }
+  return FTRF_OK;
+}
+
+extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+  return ftrf_backward_part(f, c, wsb, ws_bytes, stream, 0);
 }
 
 extern "C" int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, float* loss_out, float* g_rgb_out,

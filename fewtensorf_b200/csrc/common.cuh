@@ -56,7 +56,7 @@ int launch_appearance(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t
 int launch_shade(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_composite(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_integrate_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
-int launch_shade_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_shade_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int part = 0);
 int launch_appearance_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_at(const FtrfField&, const float* xyz, int64_t n, float* out, cudaStream_t);

@@ -262,15 +262,29 @@ int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream
   return check_launch("layer3_fwd");
 }
 
-int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.shading == FTRF_SHADE_SH) return launch_shade_sh_bwd(f, c, ws, st);
-  if (!g_shade_path) return launch_shade_bwd_v1(f, c, ws, st);
+// part 0: everything.  part 1: down to g_feat (what the appearance backward waits for).  part 2: the MLP
+// weight gradients, which nothing downstream reads.  Only the fused path splits; the other back ends do
+// all their work in part 1.
+int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, int part) {
+  if (f.shading == FTRF_SHADE_SH) return part == 2 ? FTRF_OK : launch_shade_sh_bwd(f, c, ws, st);
+  if (!g_shade_path) return part == 2 ? FTRF_OK : launch_shade_bwd_v1(f, c, ws, st);
   InSpec sp = make_spec(f);
   if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
   FusedSpec fs;
   const bool internal = g_shade_path == 2 && make_fused_spec(f, sp, fs) && fs.kp <= ws.ldx && ws.wimg;   // X saved by the fused forward
   const float* w1p = ws.wimg ? ws.wimg + fused_w1p_offset_floats() : nullptr;
+  if (part == 2) {
+    if (!internal) return FTRF_OK;
+    prof_begin(9, st);
+    WgradFusedArgs wa{};
+    wa.g2 = ws.a_gh2; wa.h1 = ws.a_h1; wa.g1 = ws.a_gh1; wa.x = ws.a_x; wa.ldx = ws.ldx; wa.kp = fs.kp;
+    wa.count = ws.counters + 1; wa.cap = c.cap_app; wa.dw2 = f.g_w2;
+    wa.dw1i = ws.wimg + fused_scratch_offset_floats();
+    int e = launch_wgrad_fused(wa, fs, f.g_w1, sp.in_dim, f.g_b1, st);
+    prof_end(9, st);
+    return e;
+  }
   prof_begin(7, st);
   layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
   if (int e = check_launch("layer3_bwd")) return e;
@@ -296,16 +310,9 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     else pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
     if (int e = check_launch("pe_bwd")) return e;
   }
-  prof_end(8, st); prof_begin(9, st);
-  if (internal) {          // both weight gradients in one kernel (k_wgrad_fused.cu)
-    WgradFusedArgs wa{};
-    wa.g2 = ws.a_gh2; wa.h1 = ws.a_h1; wa.g1 = ws.a_gh1; wa.x = ws.a_x; wa.ldx = ws.ldx; wa.kp = fs.kp;
-    wa.count = ws.counters + 1; wa.cap = c.cap_app; wa.dw2 = f.g_w2;
-    wa.dw1i = ws.wimg + fused_scratch_offset_floats();
-    int e = launch_wgrad_fused(wa, fs, f.g_w1, sp.in_dim, f.g_b1, st);
-    prof_end(9, st);
-    return e;
-  }
+  prof_end(8, st);
+  if (internal) return part == 1 ? FTRF_OK : launch_shade_bwd(f, c, ws, st, 2);   // both weight gradients in one kernel (k_wgrad_fused.cu)
+  prof_begin(9, st);
   Wgrad3xArgs w{};
   w.count = ws.counters + 1; w.cap = c.cap_app;
   w.G = ws.a_gh2; w.ldg = FC; w.A = ws.a_h1; w.lda = FC; w.K = FC; w.dW = f.g_w2; w.ldw = FC; w.dbias = nullptr;  // db2 done in layer3_bwd

@@ -19,6 +19,7 @@ def init_from_env(backend: str | None = None) -> tuple[int, int]:
         backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
         kw = {}
         if backend == "nccl":
+            os.environ.setdefault("NCCL_MIN_CTAS", "64")      # more CTAs for the one large all-reduce of a step
             local = int(os.environ.get("LOCAL_RANK", "0"))
             torch.cuda.set_device(local)
             kw["device_id"] = torch.device("cuda", local)

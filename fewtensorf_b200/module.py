@@ -26,6 +26,7 @@ import torch.nn.functional as F
 from . import _abi
 from ._abi import FtrfCall, FtrfField, check, lib
 
+GRAD_TAIL = 4
 MAX_CANDIDATES = 1 << 30      # rays * samples per launch sequence (int32 sample cursors); an 800x800 frame is one sequence
 
 
@@ -145,7 +146,7 @@ class _Workspace:
 
 class _CallState:
     """Everything backward needs from one forward call."""
-    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask")
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield")
 
 
 class TensorBase(nn.Module):
@@ -298,7 +299,9 @@ class TensorBase(nn.Module):
         if not fresh and cache is not None and cache[0] == key and cache[1].device == params[0].device:
             return cache[1], cache[2]
         total = sum(p.numel() for p in params)
-        buf = torch.zeros(total, dtype=torch.float32, device=params[0].device)
+        # + GRAD_TAIL floats after the last parameter: slot 0 carries this rank's list-overflow flag through
+        # the all-reduce of an overlapped multi-GPU step (train_step(allreduce=True))
+        buf = torch.zeros(total + GRAD_TAIL, dtype=torch.float32, device=params[0].device)
         views, off = [], 0
         for p in params:
             n = p.numel()
@@ -509,13 +512,16 @@ class TensorBase(nn.Module):
         nbytes = count * torch.empty((), dtype=dtype).element_size()
         return st.ws[o:o + nbytes].view(dtype)
 
-    def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views) -> None:
-        if g_rgb.dtype != torch.float32 or not g_rgb.is_contiguous():
-            g_rgb = g_rgb.contiguous().float()
-        field = self._fill_field(st.mask, grad_views)
-        st.call.g_rgb_map = g_rgb.data_ptr()
-        check(lib.ftrf_backward(C.byref(field), C.byref(st.call), st.ws.data_ptr(), st.ws_bytes, _stream()), "backward")
-        st.keep = st.keep + (g_rgb, field)
+    def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views, part: int = 0) -> None:
+        """part 0: the whole backward; 1 / 2: its two halves (ftrf_backward_part), 2 reuses 1's arguments."""
+        if part != 2:
+            if g_rgb.dtype != torch.float32 or not g_rgb.is_contiguous():
+                g_rgb = g_rgb.contiguous().float()
+            st.bfield = self._fill_field(st.mask, grad_views)
+            st.call.g_rgb_map = g_rgb.data_ptr()
+            st.keep = st.keep + (g_rgb, st.bfield)
+        check(lib.ftrf_backward_part(C.byref(st.bfield), C.byref(st.call), st.ws.data_ptr(), st.ws_bytes, _stream(), part),
+              "backward")
 
     # ------------------------------------------------------------------ the hot path
     def _draw_rng(self, n_rays, S, is_train, ndc_ray, white_bg, device):
@@ -564,10 +570,19 @@ class TensorBase(nn.Module):
             return outs[0]
         return (torch.cat([o[0] for o in outs]), torch.cat([o[1] for o in outs]), sum(o[2] for o in outs))
 
-    def train_step(self, rays, rgb_target, mask=None, white_bg=True, ndc_ray=False, N_samples=-1, grad_scale=1.0):
+    def train_step(self, rays, rgb_target, mask=None, white_bg=True, ndc_ray=False, N_samples=-1, grad_scale=1.0,
+                   allreduce=False, group=None):
         """Fused training step without the autograd engine: forward, MSE loss (train.py:338) and
         backward into the flat gradient buffer.  Sets `.grad` of every parameter to its view of that
-        buffer and returns (loss 0-dim device tensor, num_valid_samples int)."""
+        buffer and returns (loss 0-dim device tensor, num_valid_samples int).
+
+        allreduce=True (one process per GPU, torch.distributed initialised): the gradients are summed over
+        `group` inside the step, overlapped with the backward — the appearance planes / lines / basis
+        and the MLP (3/4 of the bytes) are final before the density backward and travel while it runs; the
+        density gradients follow.  Pass grad_scale = n_local / n_global
+        (dist.grad_scale).  A rank whose packed lists overflowed raises a flag that rides in the buffer's
+        tail slot, so every rank repeats the step together."""
+        import torch.distributed as dist
         S = int(N_samples) if N_samples > 0 else int(self.nSamples)
         rays = rays.detach().to(device=self.device, dtype=torch.float32).contiguous()
         target = rgb_target.detach().to(device=self.device, dtype=torch.float32).contiguous()
@@ -578,6 +593,8 @@ class TensorBase(nn.Module):
         buf, views = self.grad_buffer()
         loss = torch.empty(1, dtype=torch.float32, device=rays.device)
         g_rgb = torch.empty(N, 3, dtype=torch.float32, device=rays.device)
+        reduce_on = bool(allreduce) and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        lo, hi = self._early_grad_span() if reduce_on else (0, 0)
         while True:
             # everything is enqueued back to back (the kernels read the sample counts from device memory);
             # the single host sync comes at the end and only decides whether a list overflowed
@@ -588,13 +605,48 @@ class TensorBase(nn.Module):
                                     _stream()), "mse_loss")
             if grad_scale != 1.0:
                 g_rgb.mul_(grad_scale)
-            self._run_backward(st, g_rgb, views)
-            if self._finish_forward(st):
+            if not reduce_on:
+                self._run_backward(st, g_rgb, views)
+                if self._finish_forward(st):
+                    break
+                continue
+            # this rank's overflow flag (final after the forward) rides in the tail slot
+            counters = self.workspace_section(st, "COUNTERS", torch.int32, 8)
+            buf[-GRAD_TAIL:-GRAD_TAIL + 1].copy_(counters[2:3].ne(0))
+            self._run_backward(st, g_rgb, views, part=1)
+            works = [dist.all_reduce(buf[lo:], group=group, async_op=True)]
+            self._run_backward(st, g_rgb, views, part=2)
+            works.append(dist.all_reduce(buf[:lo], group=group, async_op=True))
+            for w in works:
+                w.wait()                      # stream-level: the current stream waits for the collectives
+            flag = self._tail_flag(buf)       # async copy; _finish_forward's sync completes it
+            ok = self._finish_forward(st)
+            if float(flag[0]) == 0.0 and ok:
                 break
         for p, v in zip(self._all_params(), views):
             if p.grad is not v:
                 p.grad = v
         return loss[0], st.n_valid
+
+    def _tail_flag(self, buf):
+        pin = getattr(self, "_tail_pin", None)
+        if pin is None:
+            pin = self._tail_pin = torch.zeros(1, dtype=torch.float32).pin_memory()
+        pin.copy_(buf[-GRAD_TAIL:-GRAD_TAIL + 1], non_blocking=True)
+        return pin
+
+    def _early_grad_span(self):
+        """[lo, hi) of the flat gradient buffer holding the appearance planes / lines and basis_mat (contiguous
+        in `_all_params()` order); everything from lo on is final after backward part 1."""
+        params = self._all_params()
+        first = {id(p) for p in list(getattr(self, "app_plane", [])) + list(self.app_line) + [self.basis_mat.weight]}
+        off, lo, hi = 0, None, 0
+        for p in params:
+            if id(p) in first:
+                lo = off if lo is None else lo
+                hi = off + p.numel()
+            off += p.numel()
+        return (lo or 0), hi
 
     # ------------------------------------------------------------------ helpers kept from the reference API
     def sample_ray(self, rays_o, rays_d, is_train=True, N_samples=-1):

@@ -150,6 +150,11 @@ size_t ftrf_workspace_layout(const FtrfField* field, const FtrfCall* call, int64
 
 int ftrf_forward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
 int ftrf_backward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
+/* The same work in two halves, for callers that overlap a gradient all-reduce with it (dist.py):
+ * part 1 = everything but the density backward (all gradients except the density factors' are final after
+ * it), part 2 = the density backward, part 0 = both (ftrf_backward). */
+int ftrf_backward_part(const FtrfField* field, const FtrfCall* call, void* workspace, size_t workspace_bytes,
+                       void* stream, int part);
 
 int ftrf_stage_march(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
 int ftrf_stage_density(const FtrfField*, const FtrfCall*, void* ws, size_t ws_bytes, void* stream);
