@@ -339,6 +339,7 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
 
 // Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
 constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thread
+int g_app_bwd_onegather = 1;    // VM: single-gather kernel (app_bwd_vm_kernel); 0 = two-gather kernel below
 int g_app_bwd_runs = -1;        // samples per run-merging segment of the VM scatter; 0 = one reduction set per sample, -1 = auto
 
 __global__ void __launch_bounds__(256, 2)
@@ -533,6 +534,170 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun)
   }
 }
 
+// VM backward, one gather per sample.  Order per 64-sample tile: g_feat rows and the three taps of every
+// sample go to shared memory; GQ = G Wb (gradient w.r.t. the plane x line products) is formed first; then
+// ONE pass over the factor texels both rebuilds the products (for dWb += G^T P afterwards) and turns GQ
+// into plane / line gradients with run merging.  Work items of that pass are (segment of `arun` samples,
+// 16-byte channel chunk), consecutive lanes on consecutive chunks of the same texel.
+__global__ void __launch_bounds__(256, 2)
+app_bwd_vm_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun) {
+  extern __shared__ __align__(16) float smem[];
+  const FtrfFactorSet& a = f.app;
+  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, Dp = (D + 3) & ~3;
+  float* Wb = smem;
+  float* P = Wb + (size_t)D * NPs;
+  float* Q = P + (size_t)ATILE * NPs;
+  float* G = Q + (size_t)ATILE * NPs;
+  float* GT = G + (size_t)ATILE * Dp;          // [Dp][LDP]  g_feat transposed (samples contiguous)
+  float4* TAP = reinterpret_cast<float4*>(GT + (size_t)Dp * LDP);   // [ATILE][3]
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  for (int e = threadIdx.x; e < D * NP; e += blockDim.x) Wb[(e / NP) * NPs + (e % NP)] = __ldg(f.basis + e);
+  const int sl = threadIdx.x / AGS, sub = threadIdx.x % AGS;
+  const int n_og = Dp / 4, n_kg = NP / 4, n_tt = n_og * n_kg;
+  const int nsegs = (ATILE + arun - 1) / arun;
+  float dW[BW_TT][16];
+#pragma unroll
+  for (int t = 0; t < BW_TT; ++t)
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dW[t][i] = 0.f;
+
+  for (int64_t t0 = (int64_t)blockIdx.x * ATILE; t0 < n; t0 += (int64_t)gridDim.x * ATILE) {
+    const int64_t s = t0 + sl;
+    const int tile_n = (int)min((int64_t)ATILE, n - t0);
+    __syncthreads();                               // previous tile's dWb pass has consumed P and G
+    if (s < n) {
+      for (int o = sub; o < Dp; o += AGS) {
+        const float g = o < D ? ws.a_gfeat[s * D + o] : 0.f;
+        G[sl * Dp + o] = g;
+        GT[o * LDP + sl] = g;
+      }
+    } else {
+      for (int o = sub; o < Dp; o += AGS) { G[sl * Dp + o] = 0.f; GT[o * LDP + sl] = 0.f; }
+      for (int k = sub * 4; k < NP; k += AGS * 4) *reinterpret_cast<float4*>(P + (size_t)sl * NPs + k) = make_float4(0, 0, 0, 0);
+    }
+    if (threadIdx.x < ATILE) {
+      const int64_t st = t0 + threadIdx.x;
+      float4 tp[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) tp[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (st < n) {
+        float xn[3];
+        app_point(f, c, ws, st, xn);
+        const Taps3 T = make_taps3(a, xn);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
+      }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) TAP[threadIdx.x * 3 + j] = tp[j];
+    }
+    __syncthreads();
+    // GQ[64 x NP] = G[64 x D] Wb[D x NP]: register-tiled mini GEMM (4 samples x 4 components per thread)
+    for (int id = threadIdx.x; id < n_kg * (ATILE / 4); id += blockDim.x) {
+      const int kg = id % n_kg, sq = id / n_kg;
+      float acc[4][4] = {};
+      for (int o = 0; o < D; ++o) {
+        const float4 wv = *reinterpret_cast<const float4*>(Wb + (size_t)o * NPs + kg * 4);
+        const float4 gv = *reinterpret_cast<const float4*>(GT + o * LDP + sq * 4);
+        const float ww[4] = {wv.x, wv.y, wv.z, wv.w}, gs[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(gs[i], ww[j], acc[i][j]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(Q + (size_t)(sq * 4 + i) * NPs + kg * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+    __syncthreads();
+    // gather once: products for dWb, plane / line gradients with run merging
+    for (int item = threadIdx.x; item < nsegs * n_kg; item += blockDim.x) {
+      const int seg = item / n_kg, q = item - seg * n_kg;
+      int k = 0, base = 0;
+      while (k < 2 && 4 * q >= base + a.n_comp[k]) { base += a.n_comp[k]; ++k; }
+      const int ch = 4 * q - base, C = a.n_comp[k], W = a.plane_w[k];
+      const int m0 = mat0(k), m1 = mat1(k), mv = vecm(k);
+      float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (a.mask[k]) { const float4 m = mask4(a.mask[k], a.mask_stride[k], ch); m2 = mul4(m, m); }
+      const float* pl = a.plane[k] + ch;
+      const float* ln = a.line[k] + ch;
+      PlaneRun pr; LineRun lr;
+      pr.kx = -1; pr.ky = -1; lr.kl = -1;
+      const int i1 = min(tile_n, (seg + 1) * arun);
+      for (int i = seg * arun; i < i1; ++i) {
+        const float4 ax = TAP[i * 3 + m0], ay = TAP[i * 3 + m1], al = TAP[i * 3 + mv];
+        const int x0 = __float_as_int(ax.x), x1 = __float_as_int(ax.y), y0 = __float_as_int(ay.x), y1 = __float_as_int(ay.y);
+        const int l0 = __float_as_int(al.x), l1 = __float_as_int(al.y);
+        const float* r0 = pl + ((size_t)y0 * W) * C;
+        const float* r1 = pl + ((size_t)y1 * W) * C;
+        const float4 c00 = ld4(r0 + (size_t)x0 * C), c10 = ld4(r0 + (size_t)x1 * C);
+        const float4 c01 = ld4(r1 + (size_t)x0 * C), c11 = ld4(r1 + (size_t)x1 * C);
+        const float4 e0 = ld4(ln + (size_t)l0 * C), e1 = ld4(ln + (size_t)l1 * C);
+        const float w00 = ax.z * ay.z, w10 = ax.w * ay.z, w01 = ax.z * ay.w, w11 = ax.w * ay.w;
+        float4 pv = z4(), lv = z4();
+        pv = fma4(w00, c00, pv); pv = fma4(w10, c10, pv); pv = fma4(w01, c01, pv); pv = fma4(w11, c11, pv);
+        lv = fma4(al.z, e0, lv); lv = fma4(al.w, e1, lv);
+        *reinterpret_cast<float4*>(P + (size_t)i * NPs + 4 * q) = mul4(mul4(pv, lv), m2);
+        const float4 gq = mul4(*reinterpret_cast<const float4*>(Q + (size_t)i * NPs + 4 * q), m2);
+        const float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
+        const int kx = x0 | (x1 << 16), ky = y0 | (y1 << 16), kl = l0 | (l1 << 16);
+        if (kx != pr.kx || ky != pr.ky) {
+          flush_plane(pr, a.g_plane[k], W, C, ch);
+          pr.kx = kx; pr.ky = ky;
+          pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+        }
+        pr.a00 = fma4(w00, gp, pr.a00);
+        pr.a10 = fma4(w10, gp, pr.a10);
+        pr.a01 = fma4(w01, gp, pr.a01);
+        pr.a11 = fma4(w11, gp, pr.a11);
+        if (kl != lr.kl) {
+          flush_line(lr, a.g_line[k], C, ch);
+          lr.kl = kl;
+          lr.a0 = z4(); lr.a1 = z4();
+        }
+        lr.a0 = fma4(al.z, gl, lr.a0);
+        lr.a1 = fma4(al.w, gl, lr.a1);
+      }
+      flush_plane(pr, a.g_plane[k], W, C, ch);
+      flush_line(lr, a.g_line[k], C, ch);
+    }
+    __syncthreads();
+    // basis gradient: 4x4 register tiles over (output group, component group)
+#pragma unroll
+    for (int t = 0; t < BW_TT; ++t) {
+      const int tt = threadIdx.x + t * blockDim.x;
+      if (tt < n_tt) {
+        const int og = tt / n_kg, kg = tt % n_kg;
+        for (int r = 0; r < ATILE; ++r) {
+          const float4 gv = *reinterpret_cast<const float4*>(G + r * Dp + og * 4);
+          const float4 pv = *reinterpret_cast<const float4*>(P + (size_t)r * NPs + kg * 4);
+          const float gg[4] = {gv.x, gv.y, gv.z, gv.w}, pp[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dW[t][i * 4 + j] = fmaf(gg[i], pp[j], dW[t][i * 4 + j]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < BW_TT; ++t) {
+    const int tt = threadIdx.x + t * blockDim.x;
+    if (tt < n_tt) {
+      const int og = tt / n_kg, kg = tt % n_kg;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int o = og * 4 + i;
+        if (o < D)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float v = dW[t][i * 4 + j];
+            if (v != 0.f) atomicAdd(f.g_basis + (size_t)o * NP + kg * 4 + j, v);
+          }
+      }
+    }
+  }
+}
+
 static int app_check(const FtrfField& f, size_t smem) {
   int NP = app_np(f), Dp = (f.app_dim + 3) & ~3;
   if (NP % 4 || (Dp / 4) * (NP / 4) > BW_TT * 256) { set_error("appearance: unsupported component count %d", NP); return FTRF_E_ARG; }
@@ -569,6 +734,12 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
     arun = 4;
     while (arun < ATILE && ((ATILE + arun - 1) / arun) * (app_np(f) / 4) > 256) ++arun;
   }
+  if (arun > 0 && g_app_bwd_onegather) {
+    const size_t sm2 = smem + ((size_t)ATILE * NPs + (size_t)ATILE * 3 * 4) * sizeof(float);
+    cudaFuncSetAttribute(app_bwd_vm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    app_bwd_vm_kernel<<<FTRF_SMS * 2, 256, sm2, st>>>(f, c, ws, arun);
+    return check_launch("app_bwd_vm");
+  }
   app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws, arun);
   return check_launch("app_bwd");
 }
@@ -581,6 +752,8 @@ extern "C" int ftrf_debug_set_app_tc(int on) {
 }
 
 extern "C" int ftrf_debug_set_app_runs(int runs) {
+  if (runs == -2) { ftrf::g_app_bwd_onegather = 0; runs = -1; }
+  else ftrf::g_app_bwd_onegather = 1;
   ftrf::g_app_bwd_runs = runs;
   return 0;
 }
