@@ -74,6 +74,17 @@ __device__ __forceinline__ void split4(const float v[4], float4& h, float4& l) {
   tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
 }
 
+// sin / cos with an explicit two-constant Cody-Waite reduction to [-pi, pi] followed by the SFU
+// approximations (abs error ~2^-21 there): ~12 instructions instead of sincosf()'s ~50, which made the
+// input build and the encoding chain rule the longest phases of the fused kernels.  Absolute error stays
+// ~1e-6 for |x| up to ~1e4 (the PE arguments are app features times 2^f).
+__device__ __forceinline__ void fast_sincos(float x, float* s, float* c) {
+  const float k = rintf(x * 0.15915494309189535f);
+  float r = fmaf(-k, 6.2831854820251465f, x);          // 2 pi, high part (fp32)
+  r = fmaf(-k, -1.7484556000744883e-7f, r);            // 2 pi, low part
+  __sincosf(r, s, c);
+}
+
 // one full 32-byte sector per store instruction (sm_100: 256-bit global stores)
 __device__ __forceinline__ void st_global_v8(float* p, const float* v) {
   asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
@@ -249,7 +260,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
                 const SPair pr = s_pair[P];
                 // octave 0: sincosf; octave f: double-angle step from octave f-1 (the pairs of one
                 // channel are consecutive, frequency-minor) — 2 ulp-grade, far inside the 1e-4 budget
-                if (pi.fexp == 0) sincosf(src[pi.sa], &da_s, &da_c);
+                if (pi.fexp == 0) fast_sincos(src[pi.sa], &da_s, &da_c);
                 else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
                 x0 = da_s * pr.ma;
                 x1 = da_c * pr.mb;
@@ -275,7 +286,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
             const int kind = pr.meta & 0xff, sa = (pr.meta >> 8) & 0xff, sb = (pr.meta >> 16) & 0xff;
             float x0 = 0.f, x1 = 0.f;
             if (kind == PK_TRIG) {
-              if (pr.scale == 1.f) sincosf(src[sa], &da_s, &da_c);
+              if (pr.scale == 1.f) fast_sincos(src[sa], &da_s, &da_c);
               else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
               x0 = da_s * pr.ma;
               x1 = da_c * pr.mb;
@@ -555,7 +566,7 @@ __device__ __forceinline__ void bz_epilogue(uint32_t t_acc2, const SPair* s_pair
         if (pi.kind == PK_COPY2 && bz_owned<SS>(pi.sb, H)) gf[pi.sb - C0] += gx[2 * pp + 1];
       } else if (pi.kind == PK_TRIG && bz_owned<SS>(pi.sa, H)) {
         const SPair pr = s_pair[P];
-        if (pi.fexp == 0) sincosf(ft[pi.sa - C0], &da_s, &da_c);
+        if (pi.fexp == 0) fast_sincos(ft[pi.sa - C0], &da_s, &da_c);
         else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
         // d/dfeat of (sin(a) ms, cos(a) mc), a = feat 2^f
         gf[pi.sa - C0] += (float)(1 << pi.fexp) * (da_c * pr.ma * gx[2 * pp] - da_s * pr.mb * gx[2 * pp + 1]);

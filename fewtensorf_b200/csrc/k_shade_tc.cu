@@ -117,26 +117,43 @@ layer3_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   for (int ch = 0; ch < 3; ++ch) w[ch] = ld4(f.w3 + ch * FC + lane * 4);
   float dw[3][4] = {}, db2[4] = {}, db3[3] = {};
   const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t s = wid; s < n; s += nw) {
-    float go[3];
+  // four rows per iteration: their loads are all issued before the first use (one 512-byte row in flight
+  // per warp left the kernel latency-bound at 2 TB/s)
+  constexpr int U = 4;
+  for (int64_t s0 = wid; s0 < n; s0 += nw * U) {
+    float4 h[U];
+    float r[U][3], gr[U][3];
 #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-      float r = ws.a_rgb[s * 3 + ch];
-      go[ch] = ws.a_grgb[s * 3 + ch] * r * (1.f - r);
-      db3[ch] += go[ch];
+    for (int u = 0; u < U; ++u) {
+      const int64_t s = s0 + (int64_t)u * nw;
+      if (s < n) {
+        h[u] = *reinterpret_cast<const float4*>(ws.a_h2 + s * FC + lane * 4);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) { r[u][ch] = ws.a_rgb[s * 3 + ch]; gr[u][ch] = ws.a_grgb[s * 3 + ch]; }
+      }
     }
-    float4 h = *reinterpret_cast<const float4*>(ws.a_h2 + s * FC + lane * 4);
-    const float hh[4] = {h.x, h.y, h.z, h.w};
-    const float ww[3][4] = {{w[0].x, w[0].y, w[0].z, w[0].w}, {w[1].x, w[1].y, w[1].z, w[1].w}, {w[2].x, w[2].y, w[2].z, w[2].w}};
-    float g[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      g[j] = hh[j] > 0.f ? go[0] * ww[0][j] + go[1] * ww[1][j] + go[2] * ww[2][j] : 0.f;
-      db2[j] += g[j];
+    for (int u = 0; u < U; ++u) {
+      const int64_t s = s0 + (int64_t)u * nw;
+      if (s >= n) continue;
+      float go[3];
 #pragma unroll
-      for (int ch = 0; ch < 3; ++ch) dw[ch][j] = fmaf(go[ch], hh[j], dw[ch][j]);
+      for (int ch = 0; ch < 3; ++ch) {
+        go[ch] = gr[u][ch] * r[u][ch] * (1.f - r[u][ch]);
+        db3[ch] += go[ch];
+      }
+      const float hh[4] = {h[u].x, h[u].y, h[u].z, h[u].w};
+      const float ww[3][4] = {{w[0].x, w[0].y, w[0].z, w[0].w}, {w[1].x, w[1].y, w[1].z, w[1].w}, {w[2].x, w[2].y, w[2].z, w[2].w}};
+      float g[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        g[j] = hh[j] > 0.f ? go[0] * ww[0][j] + go[1] * ww[1][j] + go[2] * ww[2][j] : 0.f;
+        db2[j] += g[j];
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) dw[ch][j] = fmaf(go[ch], hh[j], dw[ch][j]);
+      }
+      *reinterpret_cast<float4*>(ws.a_gh2 + s * FC + lane * 4) = make_float4(g[0], g[1], g[2], g[3]);
     }
-    *reinterpret_cast<float4*>(ws.a_gh2 + s * FC + lane * 4) = make_float4(g[0], g[1], g[2], g[3]);
   }
 #pragma unroll
   for (int ch = 0; ch < 3; ++ch)
