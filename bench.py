@@ -218,7 +218,7 @@ def run_reference(args):
 def workload_config(n_gpus):
     return {"workload": f"TensorVMSplit lego shape, N_voxel {GRID}^3, n_lamb 16/48, MLP_Fea, alphaMask {MASK_GRID}^3, "
                         f"planted-box density, {RAYS_PER_GPU} rays/GPU x S={N_SAMPLES}, fwd+MSE+bwd"
-                        + (" + NCCL all-reduce of the flat gradient buffer" if n_gpus > 1 else ""),
+                        + (" + all-reduce of the flat gradient buffer" if n_gpus > 1 else ""),
             "rays_per_gpu": RAYS_PER_GPU, "n_samples": N_SAMPLES, "grid": GRID, "mask_grid": MASK_GRID,
             "l2": "flushed between timed steps (512 MiB write)", "parallelism": f"ray-sharded x{n_gpus}"}
 
@@ -275,6 +275,18 @@ def run_gpu(args):
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     torch.manual_seed(1 + rank)
     inv_world = 1.0 / world
+    # N > 1: the gradient buffer goes into symmetric memory and is all-reduced through the NVSwitch multicast
+    # address by the library's own kernel (dist.SymmetricGradients); NCCL is the fallback where NVLS is absent
+    sg = None
+    if world > 1:
+        from fewtensorf_b200.dist import SymmetricGradients
+        sg = SymmetricGradients.create(model)
+
+    def reduce_grads():
+        if sg is not None:
+            sg.all_reduce()
+        else:
+            dist.all_reduce(model._gradbuf)
 
     def step():
         # N > 1: one all-reduce(sum) of the flat gradient buffer after the step.  (train_step(allreduce=True)
@@ -282,7 +294,7 @@ def run_gpu(args):
         # backward kernels fill every SM and the NCCL CTAs queue behind them, so it is not used here.)
         loss, nv = model.train_step(rays, target, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
         if world > 1:
-            dist.all_reduce(model._gradbuf)
+            reduce_grads()
         return loss, nv
 
     def barrier():
@@ -341,7 +353,7 @@ def run_gpu(args):
         loss = torch.mean((rgb - tg) ** 2)
         loss.backward()
         if world > 1:
-            dist.all_reduce(model._gradbuf)
+            reduce_grads()
         return loss.item()
     for _ in range(3):
         e2e_step()
@@ -361,7 +373,7 @@ def run_gpu(args):
         tg = target_p.to(dev, non_blocking=True)
         loss, nv = model.train_step(r, tg, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
         if world > 1:
-            dist.all_reduce(model._gradbuf)
+            reduce_grads()
         return loss.item()
     for _ in range(3):
         e2e_fused()
@@ -410,7 +422,7 @@ def run_gpu(args):
     out = {"metric": "training rays/sec (fwd+bwd)", "value": RAYS_PER_GPU * world / (ms_step * 1e-3), "unit": "rays/s",
            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": workload_config(world), "clocks": clocks,
+           "config": dict(workload_config(world), **({"allreduce": (f"{sg.kind} (autotuned, ms: {sg.timings_ms})" if sg is not None else "nccl")} if world > 1 else {})), "clocks": clocks,
            "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32,
                    "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing)",
                    "train_step_api_value": e2e_fused_rps},

@@ -72,7 +72,7 @@ EXPORTS = [
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
-    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
+    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
 
@@ -116,6 +116,10 @@ def _load():
     lib.ftrf_profile_read.argtypes = [C.POINTER(C.c_float)]
     lib.ftrf_profile_stage_name.restype = C.c_char_p
     lib.ftrf_profile_stage_name.argtypes = [C.c_int]
+    lib.ftrf_multimem_allreduce.restype = C.c_int
+    lib.ftrf_multimem_allreduce.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+    lib.ftrf_p2p_allreduce.restype = C.c_int
+    lib.ftrf_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_size_t, C.c_int, C.c_int, C.c_void_p]
     lib.ftrf_launch_count.restype = C.c_ulonglong
     lib.ftrf_launch_count.argtypes = []
     lib.ftrf_test_gemm3x.restype = C.c_int

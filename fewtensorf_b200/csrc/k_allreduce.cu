@@ -1,0 +1,109 @@
+// k_allreduce.cu — all-reduce(sum) of the flat gradient buffer over NVSwitch multicast (NVLS), the one
+// collective of a multi-GPU training step.  The buffer lives in symmetric memory (same
+// offset on every GPU, one multicast address that maps all copies).  Rank r owns the r-th slice:
+// `multimem.ld_reduce` pulls the element-wise fp32 sum of all ranks' copies out of the switch and
+// `multimem.st` writes the result back to every copy, so each GPU moves ~N bytes in and ~N bytes out
+// regardless of the number of ranks.  The caller brackets the launch with two cross-GPU barriers (all
+// gradients written before; all slices written after) — fewtensorf_b200/dist.py uses the symmetric-memory
+// signal pads for them.
+#include "common.cuh"
+
+namespace ftrf {
+
+__global__ void __launch_bounds__(512)
+multimem_allreduce_kernel(float* __restrict__ mc, size_t lo4, size_t hi4) {   // [lo4, hi4) in float4 units
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  constexpr int U = 4;                                                       // independent round trips in flight
+  size_t i = lo4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (U - 1) * stride < hi4; i += U * stride) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float* p = mc + (i + u * stride) * 4;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(p) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float* p = mc + (i + u * stride) * 4;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                   ::"l"(p), "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
+    }
+  }
+  for (; i < hi4; i += stride) {
+    float4 v;
+    float* p = mc + i * 4;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+  }
+}
+
+// Same exchange with plain peer loads / stores over NVLink (no switch reduction): rank r sums slice r of every
+// GPU's copy in rank order and writes the result into every copy.  W loads in flight per element hide the
+// NVLink round trip; per GPU (W-1)/W of the buffer travels in each direction.
+struct PeerPtrs { float* p[16]; };
+
+template <int W>
+__global__ void __launch_bounds__(512)
+p2p_allreduce_kernel(const PeerPtrs peers, size_t lo4, size_t hi4) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = lo4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi4; i += stride) {
+    float4 v[W];
+#pragma unroll
+    for (int r = 0; r < W; ++r)
+      asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(v[r].x), "=f"(v[r].y), "=f"(v[r].z), "=f"(v[r].w) : "l"(peers.p[r] + i * 4) : "memory");
+    float4 a = v[0];
+#pragma unroll
+    for (int r = 1; r < W; ++r) { a.x += v[r].x; a.y += v[r].y; a.z += v[r].z; a.w += v[r].w; }
+#pragma unroll
+    for (int r = 0; r < W; ++r)
+      asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                   ::"l"(peers.p[r] + i * 4), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+  }
+}
+
+}  // namespace ftrf
+
+// peer_ptrs: `world` device pointers (host array) to the same symmetric buffer on every GPU, in rank order.
+extern "C" int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int world, void* stream) {
+  if (!peer_ptrs || (world != 2 && world != 4 && world != 8) || rank < 0 || rank >= world || (n_floats & 3)) {
+    ftrf::set_error("p2p_allreduce: bad argument (world must be 2, 4 or 8)");
+    return FTRF_E_ARG;
+  }
+  ftrf::PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_ptrs[r] || (((size_t)peer_ptrs[r]) & 15)) { ftrf::set_error("p2p_allreduce: bad peer pointer %d", r); return FTRF_E_ARG; }
+    pp.p[r] = (float*)peer_ptrs[r];
+  }
+  const size_t n4 = n_floats / 4, per = (n4 + world - 1) / world;
+  const size_t lo = per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+  if (hi > lo) {
+    const size_t want = (hi - lo + 511) / 512;
+    const int grid = (int)(want < (size_t)FTRF_SMS * 4 ? want : (size_t)FTRF_SMS * 4);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (world == 2) ftrf::p2p_allreduce_kernel<2><<<grid, 512, 0, st>>>(pp, lo, hi);
+    else if (world == 4) ftrf::p2p_allreduce_kernel<4><<<grid, 512, 0, st>>>(pp, lo, hi);
+    else ftrf::p2p_allreduce_kernel<8><<<grid, 512, 0, st>>>(pp, lo, hi);
+  }
+  return ftrf::check_launch("p2p_allreduce");
+}
+
+// multicast_ptr: multicast address of the symmetric buffer; n_floats: multiple of 4; this rank reduces and
+// broadcasts slice `rank` of `world` equal slices.
+extern "C" int ftrf_multimem_allreduce(void* multicast_ptr, size_t n_floats, int rank, int world, void* stream) {
+  if (!multicast_ptr || world < 1 || rank < 0 || rank >= world || (n_floats & 3) || (((size_t)multicast_ptr) & 15)) {
+    ftrf::set_error("multimem_allreduce: bad argument");
+    return FTRF_E_ARG;
+  }
+  const size_t n4 = n_floats / 4, per = (n4 + world - 1) / world;
+  const size_t lo = per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+  if (hi > lo) {
+    const size_t want = (hi - lo + 512 * 4 - 1) / (512 * 4);
+    const int grid = (int)(want < (size_t)FTRF_SMS * 2 ? want : (size_t)FTRF_SMS * 2);
+    ftrf::multimem_allreduce_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>((float*)multicast_ptr, lo, hi);
+  }
+  return ftrf::check_launch("multimem_allreduce");
+}

@@ -301,7 +301,14 @@ class TensorBase(nn.Module):
         total = sum(p.numel() for p in params)
         # + GRAD_TAIL floats after the last parameter: slot 0 carries this rank's list-overflow flag through
         # the all-reduce of an overlapped multi-GPU step (train_step(allreduce=True))
-        buf = torch.zeros(total + GRAD_TAIL, dtype=torch.float32, device=params[0].device)
+        ext = getattr(self, "_grad_storage", None)
+        if ext is not None and not fresh:
+            if ext.numel() < total + GRAD_TAIL:
+                raise RuntimeError("external gradient storage is too small for the current parameters "
+                                   "(re-create dist.SymmetricGradients after upsample / shrink)")
+            buf = ext[:total + GRAD_TAIL]
+        else:
+            buf = torch.zeros(total + GRAD_TAIL, dtype=torch.float32, device=params[0].device)
         views, off = [], 0
         for p in params:
             n = p.numel()
@@ -317,6 +324,14 @@ class TensorBase(nn.Module):
             self._grad_cache = (key, buf, views)
             self._field_cache = {}
         return buf, views
+
+    def set_grad_storage(self, storage: Optional[torch.Tensor]) -> None:
+        """Put the flat gradient buffer into caller-provided fp32 device memory (dist.SymmetricGradients passes
+        symmetric memory so the all-reduce can go through the NVSwitch multicast address); None restores an
+        ordinary allocation."""
+        self._grad_storage = storage
+        self._grad_cache = None
+        self._gradbuf = None
 
     # ------------------------------------------------------------------ C-ABI argument marshalling
     def _fill_factor_set(self, fs, planes, lines, comps, mask, keep):

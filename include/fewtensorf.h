@@ -203,6 +203,14 @@ int ftrf_set_shade_path(int path);
 int ftrf_profile_enable(int on);
 int ftrf_profile_read(float* ms_out /* host */);
 const char* ftrf_profile_stage_name(int stage);
+/* All-reduce(sum) of a symmetric-memory fp32 buffer through its NVSwitch multicast address (NVLS): this rank
+ * reduces slice `rank` of `world` with multimem.ld_reduce and broadcasts it with multimem.st.  The caller
+ * issues a cross-GPU barrier on the stream before and after (fewtensorf_b200/dist.py).  New; the reference
+ * has no multi-GPU code. */
+int ftrf_multimem_allreduce(void* multicast_ptr, size_t n_floats, int rank, int world, void* stream);
+/* The same exchange with plain peer loads / stores over NVLink: peer_ptrs[r] is rank r's copy of the symmetric
+ * buffer (host array of `world` device pointers, world = 2, 4 or 8); same barrier contract. */
+int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int world, void* stream);
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py's gpu_launches). */
 unsigned long long ftrf_launch_count(void);
 
