@@ -102,7 +102,7 @@ extern "C" int ftrf_multimem_allreduce(void* multicast_ptr, size_t n_floats, int
   const size_t lo = per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
   if (hi > lo) {
     const size_t want = (hi - lo + 512 * 4 - 1) / (512 * 4);
-    const int grid = (int)(want < (size_t)FTRF_SMS * 2 ? want : (size_t)FTRF_SMS * 2);
+    const int grid = (int)(want < (size_t)FTRF_SMS * 4 ? want : (size_t)FTRF_SMS * 4);
     ftrf::multimem_allreduce_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>((float*)multicast_ptr, lo, hi);
   }
   return ftrf::check_launch("multimem_allreduce");
