@@ -110,6 +110,8 @@ def run_case(name, kind, args, grid, n_rays, S, *, seed=7, **kw):
     rayMarch_weight_thres may be shaded by one implementation and not by another, which
     moves rgb by ~1e-4 for reasons unrelated to kernel correctness.  Re-seed until the nearest weight
     is at least 0.2 % away from the threshold."""
+    if len(sys.argv) > 1 and name not in sys.argv[1:]:        # python make_golden.py [case ...]: only those
+        return
     for attempt in range(50):
         gap = _run_case(name, kind, args, grid, n_rays, S, seed=seed + 100 * attempt, **kw)
         if gap > 2e-3:
@@ -224,6 +226,12 @@ def main():
              is_train=True, white_bg=True, mask=cp_mask, seed=23)
     run_case("vm_fea_ndc_train", "VM", A("MLP_Fea", [8, 8, 8], [12, 12, 12], 27), (16, 16, 16), 48, 40,
              is_train=True, white_bg=False, ndc=True, seed=29, near_far=(0.0, 3.0))
+    # unequal, multiple-of-8 appearance components with per-channel decomposition masks on a non-cubic grid:
+    # the tensor-core appearance forward, the run-merging scatters and the fused MLP kernels under masks
+    tc_mask = {"encoding": {"pos": None, "view": torch.rand(12, generator=g), "fea": torch.rand(108, generator=g)},
+               "decomp": {"den": [fm(8) for _ in range(3)], "app": [fm(16), fm(8), fm(24)]}}
+    run_case("vm_fea_vecmask_tc", "VM", A("MLP_Fea", [8, 8, 8], [16, 8, 24], 27), (20, 18, 22), 96, 60,
+             is_train=True, white_bg=True, mask=tc_mask, mask_grid=(18, 20, 16), seed=37)
     run_case("vm_relu_eval", "VM", A("MLP_Fea", [8, 8, 8], [12, 12, 12], 27, act="relu"), (16, 16, 16), 48, 40,
              is_train=False, white_bg=False, seed=31)
 
