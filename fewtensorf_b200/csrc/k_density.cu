@@ -261,6 +261,103 @@ density_bwd_vm_runs_kernel(const FtrfField f, const FtrfCall c, const Ws ws, con
   }
 }
 
+// Same scatter with the per-sample work hoisted: the four lanes of a group first compute the taps of the
+// segment's samples (three samples each) into shared memory, then walk the segment once per factor pair
+// with only that pair's accumulators live.  ~70 registers instead of 128: three CTAs per SM instead of two,
+// and no lane recomputes what its neighbours compute.
+constexpr int DSEG = 12;            // longest segment (samples) a lane group walks
+constexpr int DBW_CTAS = 3;         // resident CTAs per SM the grid is sized for
+
+__global__ void __launch_bounds__(256, DBW_CTAS)
+density_bwd_vm_staged_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  __shared__ float4 s_tap[256 / GS][DSEG][3];
+  __shared__ float s_g[256 / GS][DSEG];
+  if (ws.counters[2] & 1) return;
+  const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
+  const int sub = threadIdx.x & (GS - 1), grp = threadIdx.x / GS;
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  // every lane group gets the same number of equally long segments (the grid is one resident wave)
+  const int64_t per = (n + gstride - 1) / gstride;
+  const int64_t rounds = max((int64_t)1, (per + DSEG - 1) / DSEG);
+  const int DRUN = (int)max((int64_t)1, (per + rounds - 1) / rounds);
+  const int64_t nseg = (n + DRUN - 1) / DRUN;
+  const FtrfFactorSet& d = f.den;
+  const int cmax = max(d.n_comp[0], max(d.n_comp[1], d.n_comp[2]));
+  const int64_t seg_pad = (nseg + 7) & ~(int64_t)7;        // whole warps take the same trips (__syncwarp below)
+  for (int64_t seg = g0; seg < seg_pad; seg += gstride) {
+    const int64_t s0 = seg * DRUN;
+    const int len = seg < nseg ? (int)min((int64_t)DRUN, n - s0) : 0;
+    __syncwarp();
+    for (int j = sub; j < len; j += GS) {
+      const int64_t s = s0 + j;
+      const float g = ws.s_gsig[s];
+      s_g[grp][j] = g;
+      if (g != 0.f) {
+        const Ray ray = load_ray(f, c, ws.s_ray[s]);
+        float p[3], xn[3];
+        sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+        normalize_pt(f, p, xn);
+        const Taps3 T = make_taps3(d, xn);
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+          s_tap[grp][j][a] = make_float4(__int_as_float(T.a[a].i0), __int_as_float(T.a[a].i1), T.a[a].w0, T.a[a].w1);
+      }
+    }
+    __syncwarp();
+    for (int ch = sub * 4; ch < cmax; ch += GS * 4) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int C = d.n_comp[k], W = d.plane_w[k];
+        if (ch >= C) continue;
+        float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (d.mask[k]) { const float4 m = mask4(d.mask[k], d.mask_stride[k], ch); m2 = mul4(m, m); }
+        const float* pl = d.plane[k] + ch;
+        const float* ln = d.line[k] + ch;
+        PlaneRun pr; LineRun lr;
+        pr.kx = -1; pr.ky = -1; lr.kl = -1;
+        for (int j = 0; j < len; ++j) {
+          const float g = s_g[grp][j];
+          if (g == 0.f) continue;
+          const float4 ax = s_tap[grp][j][mat0(k)], ay = s_tap[grp][j][mat1(k)], al = s_tap[grp][j][vecm(k)];
+          const int x0 = __float_as_int(ax.x), x1 = __float_as_int(ax.y), y0 = __float_as_int(ay.x), y1 = __float_as_int(ay.y);
+          const int l0 = __float_as_int(al.x), l1 = __float_as_int(al.y);
+          const float* r0 = pl + ((size_t)y0 * W) * C;
+          const float* r1 = pl + ((size_t)y1 * W) * C;
+          const float4 c00 = ld4(r0 + (size_t)x0 * C), c10 = ld4(r0 + (size_t)x1 * C);
+          const float4 c01 = ld4(r1 + (size_t)x0 * C), c11 = ld4(r1 + (size_t)x1 * C);
+          const float4 e0 = ld4(ln + (size_t)l0 * C), e1 = ld4(ln + (size_t)l1 * C);
+          const float w00 = ax.z * ay.z, w10 = ax.w * ay.z, w01 = ax.z * ay.w, w11 = ax.w * ay.w;
+          float4 pv = z4(), lv = z4();
+          pv = fma4(w00, c00, pv); pv = fma4(w10, c10, pv); pv = fma4(w01, c01, pv); pv = fma4(w11, c11, pv);
+          lv = fma4(al.z, e0, lv); lv = fma4(al.w, e1, lv);
+          const float4 gm = scale4(g, m2);
+          const float4 gp = mul4(gm, lv), gl = mul4(gm, pv);
+          const int kx = x0 | (x1 << 16), ky = y0 | (y1 << 16), kl = l0 | (l1 << 16);
+          if (kx != pr.kx || ky != pr.ky) {
+            flush_plane(pr, d.g_plane[k], W, C, ch);
+            pr.kx = kx; pr.ky = ky;
+            pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+          }
+          pr.a00 = fma4(w00, gp, pr.a00);
+          pr.a10 = fma4(w10, gp, pr.a10);
+          pr.a01 = fma4(w01, gp, pr.a01);
+          pr.a11 = fma4(w11, gp, pr.a11);
+          if (kl != lr.kl) {
+            flush_line(lr, d.g_line[k], C, ch);
+            lr.kl = kl;
+            lr.a0 = z4(); lr.a1 = z4();
+          }
+          lr.a0 = fma4(al.z, gl, lr.a0);
+          lr.a1 = fma4(al.w, gl, lr.a1);
+        }
+        flush_plane(pr, d.g_plane[k], W, C, ch);
+        flush_line(lr, d.g_line[k], C, ch);
+      }
+    }
+  }
+}
+
 static int sample_grid(int64_t n_hint) {
   int64_t blocks = (n_hint * GS + 255) / 256;
   int64_t cap = (int64_t)FTRF_SMS * 8;
@@ -275,7 +372,8 @@ int launch_density(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStre
 }
 
 int launch_density_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.model == FTRF_MODEL_VM && g_density_bwd_runs) density_bwd_vm_runs_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws, g_density_bwd_runs);
+  if (f.model == FTRF_MODEL_VM && g_density_bwd_runs == 12) density_bwd_vm_staged_kernel<<<FTRF_SMS * DBW_CTAS, 256, 0, st>>>(f, c, ws);
+  else if (f.model == FTRF_MODEL_VM && g_density_bwd_runs) density_bwd_vm_runs_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws, g_density_bwd_runs);
   else density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
   return check_launch("density_bwd");
 }

@@ -18,7 +18,7 @@ names = [lib.ftrf_profile_stage_name(i).decode() for i in range(n)]
 buf = (C.c_float * n)()
 flush = torch.empty(512 << 18, dtype=torch.float32, device=dev)
 for which in sys.argv[1:] or ["density"]:
-    for v in ((0, 4, 8, 10, 12, 16, 20, 24, 32) if which == "density" else (-2, 8, 10, 13, 16, 22, -1)):
+    for v in ((0, 8, 11, 12, 16) if which == "density" else (-2, 8, 10, 13, 16, 22, -1)):
         if which == "density":
             lib.ftrf_debug_set_runs(v)
         else:
