@@ -127,6 +127,18 @@ __device__ __forceinline__ Ray load_ray(const FtrfField& f, const FtrfCall& c, i
   return ray;
 }
 
+// Same ray with t_min read back from the workspace (the march kernel stored the value it computed, so this
+// is bit-identical and saves the six IEEE divisions per sample in every kernel downstream of stage 1).
+__device__ __forceinline__ Ray load_ray_ws(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t r) {
+  Ray ray;
+  const float* p = c.rays + r * c.ray_cols;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { ray.o[k] = __ldg(p + k); ray.d[k] = __ldg(p + 3 + k); }
+  ray.tmin = c.ndc ? 0.f : ws.tmin[r];
+  ray.u = (c.is_train && !c.ndc) ? __ldg(c.jitter + r) : 0.f;
+  return ray;
+}
+
 // alphaMask keep decision — equivalent to `grid_sample(volume, c, align_corners=True) > 0`
 // (tensorBase.py:41-48, :350-351) for a {0,1} volume: some in-bounds corner holds 1 with all three
 // 1-D weights > 0.  The lower-corner weight (x0+1-fx) is always > 0; the upper one (fx-x0) is 0

@@ -22,7 +22,7 @@ __host__ __device__ inline int app_np(const FtrfField& f) {
 
 __device__ __forceinline__ void app_point(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t s, float xn[3]) {
   int slot = ws.a_slot[s];
-  Ray ray = load_ray(f, c, ws.s_ray[slot]);
+  Ray ray = load_ray_ws(f, c, ws, ws.s_ray[slot]);
   float p[3];
   sample_pt(ray, sample_z(f, c, ray, ws.s_idx[slot]), p);
   normalize_pt(f, p, xn);

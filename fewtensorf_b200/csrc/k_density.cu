@@ -22,6 +22,46 @@ __device__ __forceinline__ float group_sum(float v) {
   return v;
 }
 
+// VM density feature of this lane's channel chunks from ready-made taps
+__device__ __forceinline__ float density_partial_vm(const FtrfField& f, const Taps3& T3, int sub) {
+  const FtrfFactorSet& d = f.den;
+  float acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int C = d.n_comp[k];
+    const Tap &tx = T3.a[mat0(k)], &ty = T3.a[mat1(k)], &tl = T3.a[vecm(k)];
+    for (int c = sub * 4; c < C; c += GS * 4) {
+      float4 p = plane4(d.plane[k], d.plane_w[k], C, tx, ty, c);
+      float4 l = line4(d.line[k], C, tl, c);
+      if (d.mask[k]) {                       // (plane*m)*(line*m), tensoRF.py:224-225
+        float4 m = mask4(d.mask[k], d.mask_stride[k], c);
+        p = mul4(p, m);
+        l = mul4(l, m);
+      }
+      acc += sum4(mul4(p, l));
+    }
+  }
+  return acc;
+}
+
+// The three taps of a sample, one axis per lane of its 4-lane group, exchanged by shuffles (every lane of
+// the warp must call this).
+__device__ __forceinline__ Taps3 taps3_group(const FtrfFactorSet& d, const float xn[3], int sub) {
+  const int a = sub < 3 ? sub : 0;
+  const int size = a == 0 ? d.plane_w[0] : (a == 1 ? d.plane_h[0] : d.line_len[0]);
+  const Tap mine = make_tap(a == 0 ? xn[0] : (a == 1 ? xn[1] : xn[2]), size);
+  const int base = lane_id() & ~(GS - 1);
+  Taps3 T;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    T.a[k].i0 = __shfl_sync(FULL_MASK, mine.i0, base + k);
+    T.a[k].i1 = __shfl_sync(FULL_MASK, mine.i1, base + k);
+    T.a[k].w0 = __shfl_sync(FULL_MASK, mine.w0, base + k);
+    T.a[k].w1 = __shfl_sync(FULL_MASK, mine.w1, base + k);
+  }
+  return T;
+}
+
 // Partial (this lane's channel chunks) density feature of one normalised point.
 __device__ __forceinline__ float density_partial(const FtrfField& f, const float xn[3], int sub) {
   const FtrfFactorSet& d = f.den;
@@ -74,9 +114,10 @@ density_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   const int64_t n_pad = (n + 7) & ~(int64_t)7;
   // the list entry and the ray of the NEXT iteration are fetched while this one gathers: without that a
   // sample is three dependent global round trips (entry -> ray -> texels) with nothing else in flight
+  const bool vm = f.model == FTRF_MODEL_VM;
   Ray ray_n = {};
   int idx_n = 0;
-  if (g0 < n) { ray_n = load_ray(f, c, ws.s_ray[g0]); idx_n = ws.s_idx[g0]; }
+  if (g0 < n) { ray_n = load_ray_ws(f, c, ws, ws.s_ray[g0]); idx_n = ws.s_idx[g0]; }
   for (int64_t s = g0; s < n_pad; s += gstride) {
     const Ray ray = ray_n;
     const int idx = idx_n;
@@ -84,13 +125,19 @@ density_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     int r2 = 0;
     if (s2 < n) { r2 = ws.s_ray[s2]; idx_n = ws.s_idx[s2]; }
     float part = 0.f;
+    float xn[3] = {0.f, 0.f, 0.f};
     if (s < n) {
-      float p[3], xn[3];
+      float p[3];
       sample_pt(ray, sample_z(f, c, ray, idx), p);
       normalize_pt(f, p, xn);
+    }
+    if (vm) {
+      const Taps3 T = taps3_group(f.den, xn, sub);       // one axis per lane, shared by shuffles
+      if (s < n) part = density_partial_vm(f, T, sub);
+    } else if (s < n) {
       part = density_partial(f, xn, sub);
     }
-    if (s2 < n) ray_n = load_ray(f, c, r2);
+    if (s2 < n) ray_n = load_ray_ws(f, c, ws, r2);
     float feat = group_sum(part);
     if (s < n && sub == 0) ws.s_sigma[s] = activate(f, feat);
   }
@@ -133,7 +180,7 @@ density_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   for (int64_t s = g0; s < n; s += gstride) {
     const float g = ws.s_gsig[s];
     if (g == 0.f) continue;
-    Ray ray = load_ray(f, c, ws.s_ray[s]);
+    Ray ray = load_ray_ws(f, c, ws, ws.s_ray[s]);
     float p[3], xn[3];
     sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
     normalize_pt(f, p, xn);
@@ -214,7 +261,7 @@ density_bwd_vm_runs_kernel(const FtrfField f, const FtrfCall c, const Ws ws, con
       for (int64_t s = s0; s < s1; ++s) {
         const float g = ws.s_gsig[s];
         if (g == 0.f) continue;
-        Ray ray = load_ray(f, c, ws.s_ray[s]);
+        Ray ray = load_ray_ws(f, c, ws, ws.s_ray[s]);
         float p[3], xn[3];
         sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
         normalize_pt(f, p, xn);
@@ -294,7 +341,7 @@ density_bwd_vm_staged_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
       const float g = ws.s_gsig[s];
       s_g[grp][j] = g;
       if (g != 0.f) {
-        const Ray ray = load_ray(f, c, ws.s_ray[s]);
+        const Ray ray = load_ray_ws(f, c, ws, ws.s_ray[s]);
         float p[3], xn[3];
         sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
         normalize_pt(f, p, xn);

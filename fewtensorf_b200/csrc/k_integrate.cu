@@ -32,7 +32,7 @@ integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
     const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
-    Ray ray = load_ray(f, c, r);
+    Ray ray = load_ray_ws(f, c, ws, r);
     const float dnorm = ray_dnorm(c, ray);
     float carry = 1.f, acc = 0.f, depth = 0.f;
     for (int j0 = 0; j0 < cnt; j0 += 32) {
@@ -131,7 +131,7 @@ integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
     const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
     if (cnt == 0) continue;
-    Ray ray = load_ray(f, c, r);
+    Ray ray = load_ray_ws(f, c, ws, r);
     const float dnorm = ray_dnorm(c, ray);
     float gm[3];
 #pragma unroll

@@ -52,7 +52,7 @@ inline InSpec make_spec(const FtrfField& f) {
 __device__ __forceinline__ void shade_geometry(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t s,
                                                float view[3], float pos[3]) {
   int slot = ws.a_slot[s];
-  Ray ray = load_ray(f, c, ws.s_ray[slot]);
+  Ray ray = load_ray_ws(f, c, ws, ws.s_ray[slot]);
   float p[3];
   sample_pt(ray, sample_z(f, c, ray, ws.s_idx[slot]), p);
   normalize_pt(f, p, pos);
