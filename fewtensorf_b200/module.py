@@ -146,7 +146,7 @@ class _Workspace:
 
 class _CallState:
     """Everything backward needs from one forward call."""
-    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield")
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen")
 
 
 class TensorBase(nn.Module):
@@ -273,11 +273,15 @@ class TensorBase(nn.Module):
     def _mlp_params(self) -> List[nn.Parameter]:
         if self.shadingMode == 'SH':
             return []
-        m = self.renderModule.mlp
-        return [m[0].weight, m[0].bias, m[2].weight, m[2].bias, m[4].weight, m[4].bias]
+        seq = self._modules['renderModule']._modules['mlp']._modules
+        out = []
+        for k in ('0', '2', '4'):
+            pr = seq[k]._parameters
+            out += [pr['weight'], pr['bias']]
+        return out
 
     def _all_params(self) -> List[nn.Parameter]:
-        return self._factor_params() + [self.basis_mat.weight] + self._mlp_params()
+        return self._factor_params() + [self._modules['basis_mat']._parameters['weight']] + self._mlp_params()
 
     def _ensure_layout(self):
         for p in self._factor_params():
@@ -332,6 +336,7 @@ class TensorBase(nn.Module):
         self._grad_storage = storage
         self._grad_cache = None
         self._gradbuf = None
+        self._grad_gen = self.__dict__.get("_grad_gen", 0) + 1
 
     # ------------------------------------------------------------------ C-ABI argument marshalling
     def _fill_factor_set(self, fs, planes, lines, comps, mask, keep):
@@ -512,10 +517,13 @@ class TensorBase(nn.Module):
         self._last_call = st
         return True
 
-    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save) -> _CallState:
-        """Forward with overflow handling: launch, sync once, repeat with larger lists if needed."""
+    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, before_sync=None) -> _CallState:
+        """Forward with overflow handling: launch, sync once, repeat with larger lists if needed.
+        `before_sync(st)` runs after the kernels are enqueued and before the host waits for them."""
         while True:
             st = self._launch_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save)
+            if before_sync is not None:
+                before_sync(st)
             if self._finish_forward(st):
                 return st
 
@@ -527,12 +535,14 @@ class TensorBase(nn.Module):
         nbytes = count * torch.empty((), dtype=dtype).element_size()
         return st.ws[o:o + nbytes].view(dtype)
 
-    def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views, part: int = 0) -> None:
-        """part 0: the whole backward; 1 / 2: its two halves (ftrf_backward_part), 2 reuses 1's arguments."""
+    def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views, part: int = 0, prepared: bool = False) -> None:
+        """part 0: the whole backward; 1 / 2: its two halves (ftrf_backward_part), 2 reuses 1's arguments.
+        prepared: st.bfield was already marshalled for these gradient views (during the forward)."""
         if part != 2:
             if g_rgb.dtype != torch.float32 or not g_rgb.is_contiguous():
                 g_rgb = g_rgb.contiguous().float()
-            st.bfield = self._fill_field(st.mask, grad_views)
+            if not prepared:
+                st.bfield = self._fill_field(st.mask, grad_views)
             st.call.g_rgb_map = g_rgb.data_ptr()
             st.keep = st.keep + (g_rgb, st.bfield)
         check(lib.ftrf_backward_part(C.byref(st.bfield), C.byref(st.call), st.ws.data_ptr(), st.ws_bytes, _stream(), part),
@@ -638,6 +648,7 @@ class TensorBase(nn.Module):
             ok = self._finish_forward(st)
             if float(flag[0]) == 0.0 and ok:
                 break
+        self._grad_gen = self.__dict__.get("_grad_gen", 0) + 1     # invalidates a pending autograd call's pre-zero
         for p, v in zip(self._all_params(), views):
             if p.grad is not v:
                 p.grad = v
@@ -739,15 +750,45 @@ class TensorBase(nn.Module):
         return all_rays[keep], all_rgbs[keep]
 
 
+class _GraphToken:
+    """Weakly tracked marker of one live autograd graph of a model (dies with the graph)."""
+    __slots__ = ("__weakref__",)
+
+
 class _RenderFn(torch.autograd.Function):
     """One autograd node for the whole per-ray path (replaces the ~60-op torch graph the reference
     builds per call).  Gradients are produced by the backward kernels, not by autograd replay."""
 
     @staticmethod
     def forward(ctx, model, rays, jitter, mask, S, is_train, ndc, add_bg, *params):
-        st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True)
+        def prepare_backward(st):
+            # While the GPU runs the forward: zero the gradient buffer and marshal the backward's arguments,
+            # so neither sits between the host sync of this call and the backward kernels.  Skipped when the
+            # buffer backs live .grad tensors (gradient accumulation); backward() re-checks with a generation
+            # counter that nothing else wrote into the buffer in between.
+            st.pre_gen = -1
+            if model.__dict__.get("_no_prepare"):
+                return
+            buf = model._gradbuf
+            aliased = buf is not None and any(
+                p.grad is not None and p.grad.untyped_storage().data_ptr() == buf.untyped_storage().data_ptr()
+                for p in params)
+            if aliased:
+                return
+            buf, views = model.grad_buffer()
+            buf.zero_()
+            st.bfield = model._fill_field(mask, views)
+            st.pre_gen = model.__dict__.get("_grad_gen", 0)
+
+        st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True, before_sync=prepare_backward)
         st.wsobj.busy = True
         ctx.model, ctx.st = model, st
+        ctx.token = _GraphToken()
+        live = model.__dict__.get("_live_graphs")
+        if live is None:
+            import weakref
+            live = model.__dict__["_live_graphs"] = weakref.WeakSet()
+        live.add(ctx.token)
         rgb, depth = st.keep[2], st.keep[3]
         n_valid = torch.tensor(st.n_valid, dtype=torch.int64)
         ctx.mark_non_differentiable(depth, n_valid)
@@ -758,16 +799,28 @@ class _RenderFn(torch.autograd.Function):
         model, st = ctx.model, ctx.st
         params = model._all_params()
         buf = model._gradbuf
-        # never zero a buffer that still backs live .grad tensors (gradient accumulation)
-        aliased = buf is not None and any(
+        # The persistent buffer may be handed out only when nothing else can still be reading it: not while it
+        # backs live .grad tensors (gradient accumulation), and not while another graph of this model is alive —
+        # in a joint backward the engine may run that graph's node before AccumulateGrad has consumed the
+        # views this one returns (chunked training calls, renderer.py:13-26 with N > chunk).
+        live = model.__dict__.get("_live_graphs")
+        others = live is not None and any(t is not ctx.token for t in live)
+        aliased = others or (buf is not None and any(
             p.grad is not None and p.grad.untyped_storage().data_ptr() == buf.untyped_storage().data_ptr()
-            for p in params)
+            for p in params))
         buf, views = model.grad_buffer(fresh=aliased)
-        if not aliased:
+        gen = model.__dict__.get("_grad_gen", 0)
+        prepared = (not aliased) and getattr(st, "pre_gen", -1) == gen and buf is model._gradbuf
+        if not aliased and not prepared:
             buf.zero_()
-        model._run_backward(st, g_rgb, views)
+        model._run_backward(st, g_rgb, views, prepared=prepared)
+        if not aliased:
+            model._grad_gen = gen + 1            # the persistent buffer now holds this call's gradients
         st.wsobj.busy = False
         ctx.st = None
+        if live is not None:
+            live.discard(ctx.token)
+        ctx.token = None
         # fresh aliases of the cached views: autograd can adopt them as .grad without a copy
         grads = tuple((v.detach() if p.requires_grad else None) for p, v in zip(params, views))
         return (None,) * 8 + grads
@@ -795,7 +848,11 @@ class TensorVMSplit(TensorBase):
         return nn.ParameterList(planes), nn.ParameterList(lines)
 
     def _factor_params(self):
-        return list(self.density_plane) + list(self.density_line) + list(self.app_plane) + list(self.app_line)
+        # straight out of the module dictionaries: nn.Module.__getattr__ / ParameterList iteration cost ~20 us
+        # per call, and the hot path asks five times per step
+        m = self._modules
+        return [*m['density_plane']._parameters.values(), *m['density_line']._parameters.values(),
+                *m['app_plane']._parameters.values(), *m['app_line']._parameters.values()]
 
     def get_optparam_groups(self, lr_init_spatialxyz=0.02, lr_init_network=0.001):
         """tensoRF.py:166-172."""
@@ -874,7 +931,8 @@ class TensorCP(TensorBase):
             for i in range(3)])
 
     def _factor_params(self):
-        return list(self.density_line) + list(self.app_line)
+        m = self._modules
+        return [*m['density_line']._parameters.values(), *m['app_line']._parameters.values()]
 
     def get_optparam_groups(self, lr_init_spatialxyz=0.02, lr_init_network=0.001):
         """tensoRF.py:350-356."""
