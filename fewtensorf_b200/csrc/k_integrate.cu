@@ -26,23 +26,36 @@ __device__ __forceinline__ float ray_dnorm(const FtrfCall& c, const Ray& ray) {
   return c.ndc ? sqrtf(ray.d[0] * ray.d[0] + ray.d[1] * ray.d[1] + ray.d[2] * ray.d[2]) : 1.f;
 }
 
+// One warp per ray.  Pass 1 scans the ray's packed samples 32 at a time (the next chunk's loads are issued
+// before this chunk's scan), writes w / T and keeps the "shaded" ballots in shared memory; then ONE atomicAdd
+// per ray allocates its run of the shaded list (a per-chunk atomic put a ~1 us round trip on the critical
+// path of every chunk of the longest ray), and pass 2 hands out the slots.
 __global__ void __launch_bounds__(INT_WARPS * 32)
 integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  extern __shared__ uint32_t s_shade[];              // [INT_WARPS][chunks]
   const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int chunks = (c.n_samples + 31) >> 5;
+  uint32_t* bal = s_shade + warp * chunks;
   const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
     const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
     Ray ray = load_ray_ws(f, c, ws, r);
     const float dnorm = ray_dnorm(c, ray);
     float carry = 1.f, acc = 0.f, depth = 0.f;
+    int n_shade = 0;
+    int i_n = 0;
+    float sg_n = 0.f;
+    if (lane < cnt) { i_n = ws.s_idx[off + lane]; sg_n = ws.s_sigma[off + lane]; }
     for (int j0 = 0; j0 < cnt; j0 += 32) {
       const int j = j0 + lane;
       const bool live = j < cnt;
+      const int i = i_n;
+      const float sg = sg_n;
+      if (j + 32 < cnt) { i_n = ws.s_idx[off + j + 32]; sg_n = ws.s_sigma[off + j + 32]; }
       float alpha = 0.f, z = 0.f;
       if (live) {
-        int i = ws.s_idx[off + j];
         z = sample_z(f, c, ray, i);
-        float sd = ws.s_sigma[off + j] * sample_dist(f, c, ray, i, z, dnorm);
+        float sd = sg * sample_dist(f, c, ray, i, z, dnorm);
         alpha = 1.f - expf(-sd);
       }
       float fac = (1.f - alpha) + 1e-10f;
@@ -57,25 +70,36 @@ integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
       float T = carry * (lane == 0 ? 1.f : excl);
       carry *= __shfl_sync(FULL_MASK, incl, 31);
       float w = alpha * T;
-      bool shade = live && (w > f.weight_thres);
-      uint32_t b = __ballot_sync(FULL_MASK, shade);
-      int base = 0;
-      if (lane == 0 && b) base = atomicAdd(ws.counters + 1, __popc(b));
-      base = __shfl_sync(FULL_MASK, base, 0);
-      int slot = -1;
-      if (shade) {
-        slot = base + __popc(b & ((1u << lane) - 1u));
-        if (slot < c.cap_app) ws.a_slot[slot] = off + j;
-        else { slot = -1; atomicOr(ws.counters + 2, 2); }
-      }
+      const bool shade = live && (w > f.weight_thres);
+      const uint32_t b = __ballot_sync(FULL_MASK, shade);
+      if (lane == 0) bal[j0 >> 5] = b;
+      n_shade += __popc(b);
       if (live) {
         ws.s_w[off + j] = w;
-        ws.s_app[off + j] = slot;
         if (c.save_for_backward) ws.s_T[off + j] = T;
         acc += w;
         depth = fmaf(w, z, depth);
       }
     }
+    int base = 0;
+    if (lane == 0 && n_shade) base = atomicAdd(ws.counters + 1, n_shade);
+    base = __shfl_sync(FULL_MASK, base, 0);
+    __syncwarp();
+    for (int j0 = 0; j0 < cnt; j0 += 32) {
+      const int j = j0 + lane;
+      const uint32_t b = bal[j0 >> 5];
+      if (j < cnt) {
+        int slot = -1;
+        if ((b >> lane) & 1u) {
+          slot = base + __popc(b & ((1u << lane) - 1u));
+          if (slot < c.cap_app) ws.a_slot[slot] = off + j;
+          else { slot = -1; atomicOr(ws.counters + 2, 2); }
+        }
+        ws.s_app[off + j] = slot;
+      }
+      base += __popc(b);
+    }
+    __syncwarp();
 #pragma unroll
     for (int d = 16; d; d >>= 1) {
       acc += __shfl_xor_sync(FULL_MASK, acc, d);
@@ -142,24 +166,43 @@ integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     const float g_acc = c.add_bg ? -(gm[0] + gm[1] + gm[2]) : 0.f;
     float suffix = 0.f;                     // sum over later samples of g_w * w
     const int last0 = ((cnt - 1) >> 5) << 5;
+    // the loads of the NEXT chunk (list entries and the shaded sample's rgb) are issued before this chunk's scan
+    struct Pre { int i, a; float sigma, T, w, q0, q1, q2; };
+    auto fetch = [&](int j0) {
+      Pre p{0, -1, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const int j = j0 + lane;
+      if (j0 >= 0 && j < cnt) {
+        p.i = ws.s_idx[off + j];
+        p.sigma = ws.s_sigma[off + j];
+        p.T = ws.s_T[off + j];
+        p.w = ws.s_w[off + j];
+        p.a = ws.s_app[off + j];
+        if (p.a >= 0) {
+          const float* q = ws.a_rgb + (size_t)p.a * 3;
+          p.q0 = q[0]; p.q1 = q[1]; p.q2 = q[2];
+        }
+      }
+      return p;
+    };
+    Pre nx = fetch(last0);
     for (int j0 = last0; j0 >= 0; j0 -= 32) {
       const int j = j0 + lane;
       const bool live = j < cnt;
+      const Pre cur = nx;
+      nx = fetch(j0 - 32);
       float gw = 0.f, w = 0.f, T = 0.f, alpha = 0.f, dist = 0.f, sigma = 0.f;
       if (live) {
-        int i = ws.s_idx[off + j];
+        const int i = cur.i;
         float z = sample_z(f, c, ray, i);
         dist = sample_dist(f, c, ray, i, z, dnorm);
-        sigma = ws.s_sigma[off + j];
+        sigma = cur.sigma;
         alpha = 1.f - expf(-sigma * dist);
-        T = ws.s_T[off + j];
-        w = ws.s_w[off + j];
+        T = cur.T;
+        w = cur.w;
         gw = g_acc;
-        int a = ws.s_app[off + j];
-        if (a >= 0) {
-          const float* q = ws.a_rgb + (size_t)a * 3;
-          gw += gm[0] * q[0] + gm[1] * q[1] + gm[2] * q[2];
-          float* o = ws.a_grgb + (size_t)a * 3;
+        if (cur.a >= 0) {
+          gw += gm[0] * cur.q0 + gm[1] * cur.q1 + gm[2] * cur.q2;
+          float* o = ws.a_grgb + (size_t)cur.a * 3;
           o[0] = w * gm[0]; o[1] = w * gm[1]; o[2] = w * gm[2];
         }
       }
@@ -192,7 +235,10 @@ static int ray_grid(int64_t n_rays) {
 
 int launch_integrate(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (c.n_rays == 0) return FTRF_OK;
-  integrate_fwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
+  const size_t smem = (size_t)INT_WARPS * ((c.n_samples + 31) / 32) * sizeof(uint32_t);
+  if (smem > 200 * 1024) { set_error("integrate: n_samples %d too large", c.n_samples); return FTRF_E_ARG; }
+  if (smem > 48 * 1024) cudaFuncSetAttribute(integrate_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  integrate_fwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, smem, st>>>(f, c, ws);
   return check_launch("integrate_fwd");
 }
 int launch_composite(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
