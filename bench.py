@@ -155,6 +155,71 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------ CPU leg
+def optim_leg(model, dev, hbm_peak, iters=20):
+    """SURVEY 8(f) rank 2, measured beside the hot path: the factor regularisers (one pass per factor set,
+    value + gradient into the flat buffer) and the one-launch Adam step over all 19 parameters.  Both are HBM
+    streams: 12 B per plane element (x, g read; g written), 28 B per parameter (p, g, m, v read; p, m, v written).
+    torch's own Adam (its default multi-tensor path) is timed on a copy of the parameters for comparison."""
+    import fewtensorf_b200 as ft
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    flush_view = flush.view(torch.int32)
+    sink = torch.zeros((), dtype=torch.int64, device=dev)
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.grad is None:
+                p.grad = torch.zeros_like(p, memory_format=torch.preserve_format)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        ms = 0.0
+        for _ in range(iters):
+            flush.zero_()                                   # 512 MB > L2: every pass streams from HBM ...
+            sink.copy_(flush[:1 << 20:4096].sum())          # ... and a read pass leaves CLEAN lines behind, so the
+            flush_view.sum()                                # timed kernel does not pay the write-back of 126 MB of
+                                                            # dirty flush lines (it did: 48 % -> of peak instead of ~75 %)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            ms += a.elapsed_time(b)
+        return ms / iters
+
+    plane_elems = sum(p.numel() for p in list(model.density_plane) + list(model.app_plane))
+    n_params = sum(p.numel() for p in model.parameters())
+    reg_ms = timed(lambda: model.add_regularizers_(L1_weight=8e-5, TV_weight_density=0.1, TV_weight_app=0.01))
+    # the same three launches through the C ABI with the argument structs prepared once (what a C caller pays)
+    import ctypes as C
+    from fewtensorf_b200._abi import lib
+    acc = torch.zeros(4, dtype=torch.float64, device=dev)
+    fs_d = model._reg_factor_set("density", [p.grad for p in model._reg_params("density")])
+    fs_a = model._reg_factor_set("app", [p.grad for p in model._reg_params("app")])
+    st = torch.cuda.current_stream().cuda_stream
+
+    def reg_abi():
+        lib.ftrf_reg_factors(C.byref(fs_d), 0, 0.1, 8e-5, None, acc.data_ptr(), 1, st)
+        lib.ftrf_reg_factors(C.byref(fs_a), 0, 0.01, 0.0, None, acc[2:].data_ptr(), 0, st)
+    reg_abi_ms = timed(reg_abi)
+    opt = ft.FusedAdam(model.get_optparam_groups(0.0, 0.0), betas=(0.9, 0.99))      # lr 0: the bench field stays put
+    adam_ms = timed(opt.step)
+    clones = [p.detach().clone().requires_grad_(True) for p in model.parameters()]
+    for c in clones:
+        c.grad = torch.zeros_like(c)
+    topt = torch.optim.Adam(clones, lr=0.0, betas=(0.9, 0.99))
+    torch_ms = timed(topt.step)
+    del clones, topt
+    reg_gbs = plane_elems * 12 / (reg_abi_ms * 1e-3) / 1e9
+    adam_gbs = n_params * 28 / (adam_ms * 1e-3) / 1e9
+    return {"regularisers": {"ms": round(reg_abi_ms, 4), "module_api_ms": round(reg_ms, 4), "launches": 3, "algorithmic_bytes": plane_elems * 12,
+                             "achieved": round(reg_gbs, 1), "unit": "GB/s", "frac": round(reg_gbs / hbm_peak, 4),
+                             "what": "TV(density planes)+L1(density planes, lines)+TV(app planes), value+gradient"},
+            "adam": {"ms": round(adam_ms, 4), "launches": 1, "algorithmic_bytes": n_params * 28,
+                     "achieved": round(adam_gbs, 1), "unit": "GB/s", "frac": round(adam_gbs / hbm_peak, 4),
+                     "torch_optim_adam_ms": round(torch_ms, 4)},
+            "l2_flush": "512 MB written then read between iterations (clean lines)"}
+
+
 def cpu_field(model=None):
     """Oracle field (CPU restatement of the reference path) holding the benchmark workload.
     With a product model: the very same parameters and alphaMask.  Without (--impl reference):
@@ -388,6 +453,7 @@ def run_gpu(args):
     e2e_fused_rps = RAYS_PER_GPU * world * args.steps / float(e2e_f)
 
     render = None if args.no_render else render_leg(dev)
+    extras = optim_leg(model, dev, load_peaks()["hbm"]) if (rank == 0 and not args.no_render) else None
 
     if rank != 0:
         if world > 1:
@@ -432,6 +498,8 @@ def run_gpu(args):
         out["render"] = {"metric": "800x800 render ms/frame (N_samples=-1, rays in HBM, rows interleaved over GPUs)",
                          "unit": "ms", "higher_is_better": False,
                          "sh": render["SH"], "mlp_fea": render["MLP_Fea"]}
+    if extras:
+        out["iteration_extras"] = extras
     if cpu:
         out["cpu_baseline"] = cpu
     print(json.dumps(out))

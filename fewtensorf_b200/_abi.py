@@ -66,13 +66,23 @@ class FtrfCall(C.Structure):
     ]
 
 
+class FtrfAdamSegment(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_int64), ("lr", C.c_float), ("pad_", C.c_int32)]
+
+
+class FtrfCamera(C.Structure):
+    _fields_ = [("H", C.c_int32), ("W", C.c_int32), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float),
+                ("cy", C.c_float), ("c2w", C.c_float * 12), ("normalize", C.c_int32), ("blender", C.c_int32)]
+
+
 # every symbol include/fewtensorf.h declares
 EXPORTS = [
     "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward", "ftrf_backward_part",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
-    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
+    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
 
@@ -120,6 +130,14 @@ def _load():
     lib.ftrf_multimem_allreduce.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
     lib.ftrf_p2p_allreduce.restype = C.c_int
     lib.ftrf_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+    lib.ftrf_reg_factors.restype = C.c_int
+    lib.ftrf_reg_factors.argtypes = [C.POINTER(FtrfFactorSet), C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
+                                     C.c_int, C.c_void_p]
+    lib.ftrf_adam_step.restype = C.c_int
+    lib.ftrf_adam_step.argtypes = [C.POINTER(FtrfAdamSegment), C.c_int, C.c_float, C.c_float, C.c_float, C.c_int,
+                                   C.c_void_p]
+    lib.ftrf_generate_rays.restype = C.c_int
+    lib.ftrf_generate_rays.argtypes = [C.POINTER(FtrfCamera), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_launch_count.restype = C.c_ulonglong
     lib.ftrf_launch_count.argtypes = []
     lib.ftrf_test_gemm3x.restype = C.c_int

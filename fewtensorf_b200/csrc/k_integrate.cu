@@ -121,13 +121,29 @@ composite_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
     const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
     float rgb[3] = {0.f, 0.f, 0.f};
-    for (int j = lane; j < cnt; j += 32) {
-      int a = ws.s_app[off + j];
-      if (a >= 0) {
-        float w = ws.s_w[off + j];
-        const float* q = ws.a_rgb + (size_t)a * 3;
-        rgb[0] = fmaf(w, q[0], rgb[0]); rgb[1] = fmaf(w, q[1], rgb[1]); rgb[2] = fmaf(w, q[2], rgb[2]);
+    // four chunks in flight: all slot loads first, then the dependent rgb gathers, then the sums
+    for (int j0 = lane; j0 < cnt; j0 += 128) {
+      int a[4];
+      float w[4], q[4][3];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + 32 * u;
+        a[u] = -1; w[u] = 0.f;
+        if (j < cnt) { a[u] = ws.s_app[off + j]; w[u] = ws.s_w[off + j]; }
       }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        q[u][0] = q[u][1] = q[u][2] = 0.f;
+        if (a[u] >= 0) {
+          const float* p = ws.a_rgb + (size_t)a[u] * 3;
+          q[u][0] = p[0]; q[u][1] = p[1]; q[u][2] = p[2];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (a[u] >= 0) {
+          rgb[0] = fmaf(w[u], q[u][0], rgb[0]); rgb[1] = fmaf(w[u], q[u][1], rgb[1]); rgb[2] = fmaf(w[u], q[u][2], rgb[2]);
+        }
     }
 #pragma unroll
     for (int d = 16; d; d >>= 1)

@@ -675,6 +675,103 @@ class TensorBase(nn.Module):
         return (lo or 0), hi
 
     # ------------------------------------------------------------------ helpers kept from the reference API
+    # ------------------------------------------------------------------ regularisers
+    def _reg_factor_set(self, which: str, grads=None) -> _abi.FtrfFactorSet:
+        """FtrfFactorSet of the density / appearance factors; `grads` = gradient tensors in
+        [planes..., lines...] order (lines only for CP), laid out like the parameters."""
+        self._ensure_layout()
+        fs = _abi.FtrfFactorSet()
+        planes = getattr(self, which + "_plane", None) if self._is_vm else None
+        lines = getattr(self, which + "_line")
+        comps = self.density_n_comp if which == "density" else self.app_n_comp
+        self._fill_factor_set(fs, planes, lines, comps, None, [])
+        if grads is not None:
+            params = (list(planes) if planes is not None else []) + list(lines)
+            for p, g in zip(params, grads):
+                if g.shape != p.shape or g.stride() != p.stride() or g.dtype != torch.float32:
+                    raise RuntimeError("regulariser gradient tensors must be laid out like their parameters")
+            if planes is not None:
+                for k in range(3):
+                    fs.g_plane[k], fs.g_line[k] = grads[k].data_ptr(), grads[3 + k].data_ptr()
+            else:
+                for k in range(3):
+                    fs.g_line[k] = grads[k].data_ptr()
+        return fs
+
+    def _reg_params(self, which: str):
+        planes = list(getattr(self, which + "_plane")) if self._is_vm else []
+        return planes + list(getattr(self, which + "_line"))
+
+    def add_regularizers_(self, L1_weight: float = 0.0, TV_weight_density: float = 0.0, TV_weight_app: float = 0.0):
+        """One pass per factor set that does what train.py:345-371 + `total_loss.backward()` do for the factor
+        regularisers: ADDS d(L1_weight * density_L1() + TV_weight_density * TV_loss_density(TVLoss())
+        + TV_weight_app * TV_loss_app(TVLoss())) / d factor into the parameters' `.grad` (the flat gradient
+        buffer after `train_step`; created as zeros when a parameter has none) and returns a device float64
+        tensor [TV_loss_density, density_L1, TV_loss_app] with the unweighted loss values for logging.
+        No host synchronisation."""
+        if not self._is_vm and (TV_weight_density or TV_weight_app):
+            raise RuntimeError("TensorCP: the reference's TV loss on lines is 0/0 (loss.py:129 with W = 1); not provided")
+        out = torch.zeros(4, dtype=torch.float64, device=self.device)
+        model = _abi.MODEL_VM if self._is_vm else _abi.MODEL_CP
+        for which, w_tv, w_l1, slot in (("density", TV_weight_density, L1_weight, 0), ("app", TV_weight_app, 0.0, 2)):
+            if not (w_tv or w_l1):
+                continue
+            params = self._reg_params(which)
+            with torch.no_grad():
+                for p in params:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p, memory_format=torch.preserve_format)
+            # the struct only depends on the parameter / gradient pointers: cached like _fill_field's
+            key = (which,) + tuple((p.data_ptr(), p.grad.data_ptr()) for p in params) + (id(self._host),)
+            cache = self.__dict__.setdefault("_reg_cache", {})
+            fs = cache.get(key)
+            if fs is None:
+                if len(cache) > 8:
+                    cache.clear()
+                fs = cache[key] = self._reg_factor_set(which, [p.grad for p in params])
+            check(lib.ftrf_reg_factors(C.byref(fs), model, float(w_tv), float(w_l1), None,
+                                       out[slot:].data_ptr(), 1 if w_l1 else 0, _stream()), "reg_factors")
+        return out[:3]
+
+    def _tv_loss(self, which: str, reg):
+        from .optim import TVLoss
+        planes = getattr(self, which + "_plane", None)
+        if planes is None:
+            raise RuntimeError("TensorCP: the reference's TV loss on lines is 0/0 (loss.py:129 with W = 1); not provided")
+        if type(reg) is not TVLoss:                      # any other callable: the reference's generic expression
+            total = 0
+            for p in planes:
+                total = total + reg(p) * 1e-2
+            return total
+        return _RegLossFn.apply(self, which, 0, *planes) * reg.TVLoss_weight
+
+    def TV_loss_density(self, reg):
+        """tensoRF.py:195-199 (planes only; the line term is commented out upstream)."""
+        return self._tv_loss("density", reg)
+
+    def TV_loss_app(self, reg):
+        """tensoRF.py:201-205."""
+        return self._tv_loss("app", reg)
+
+    def density_L1(self):
+        """tensoRF.py:189-193 (VM: planes + lines) / :468-472 (CP: lines)."""
+        return _RegLossFn.apply(self, "density", 1, *self._reg_params("density"))
+
+    def vectorDiffs(self, vector_comps):
+        """tensoRF.py:175-184: mean |off-diagonal| of each line's C x C Gram matrix (tiny; torch)."""
+        total = 0
+        for v in vector_comps:
+            n_comp, n_size = v.shape[1:-1]
+            m = v.reshape(n_comp, n_size)
+            dotp = m @ m.t()
+            non_diagonal = dotp.reshape(-1)[1:].view(n_comp - 1, n_comp + 1)[..., :-1]
+            total = total + torch.mean(torch.abs(non_diagonal))
+        return total
+
+    def vector_comp_diffs(self):
+        """tensoRF.py:186-187."""
+        return self.vectorDiffs(self.density_line) + self.vectorDiffs(self.app_line)
+
     def sample_ray(self, rays_o, rays_d, is_train=True, N_samples=-1):
         """models/tensorBase.py:189-208 (torch ops; used by filtering_rays, not by forward)."""
         S = N_samples if N_samples > 0 else self.nSamples
@@ -753,6 +850,34 @@ class TensorBase(nn.Module):
 class _GraphToken:
     """Weakly tracked marker of one live autograd graph of a model (dies with the graph)."""
     __slots__ = ("__weakref__",)
+
+
+class _RegLossFn(torch.autograd.Function):
+    """TV (kind 0) or L1 (kind 1) of one factor set as an autograd scalar: forward = loss-only pass of
+    `ftrf_reg_factors`, backward = the same kernel writing gradients scaled by the upstream gradient, which
+    it reads from device memory (no host sync)."""
+
+    @staticmethod
+    def forward(ctx, model, which, kind, *params):
+        ctx.model, ctx.which, ctx.kind = model, which, kind
+        ctx.n = len(params)
+        out = torch.zeros(2, dtype=torch.float64, device=params[0].device)
+        fs = model._reg_factor_set(which)
+        check(lib.ftrf_reg_factors(C.byref(fs), _abi.MODEL_VM if model._is_vm else _abi.MODEL_CP, 0.0, 0.0, None,
+                                   out.data_ptr(), 1 if kind == 1 else 0, _stream()), "reg_factors")
+        return out[kind].float()
+
+    @staticmethod
+    def backward(ctx, g):
+        model, which, kind = ctx.model, ctx.which, ctx.kind
+        params = model._reg_params(which)
+        grads = [torch.zeros_like(p, memory_format=torch.preserve_format) for p in params]
+        scale = g.detach().to(torch.float32).reshape(1).contiguous()
+        fs = model._reg_factor_set(which, grads)
+        check(lib.ftrf_reg_factors(C.byref(fs), _abi.MODEL_VM if model._is_vm else _abi.MODEL_CP,
+                                   1.0 if kind == 0 else 0.0, 1.0 if kind == 1 else 0.0, scale.data_ptr(), None,
+                                   1 if kind == 1 else 0, _stream()), "reg_factors")
+        return (None, None, None) + tuple(grads[:ctx.n])
 
 
 class _RenderFn(torch.autograd.Function):

@@ -19,6 +19,9 @@
  *   ftrf_pack_alpha_mask    models/tensorBase.py:30-39   (AlphaGridMask volume -> bit field)
  *   ftrf_build_coarse_mask  (none: empty-space acceleration of the alphaMask cull, same decisions)
  *   ftrf_density_at         models/tensorBase.py:298-318 compute_alpha's sigma (dense-lattice eval)
+ *   ftrf_reg_factors        models/tensoRF.py:189-205 + loss.py:120-141   TV / L1 regularisers (value + gradient)
+ *   ftrf_adam_step          train.py:272-273, :374-376   torch.optim.Adam over all parameter groups
+ *   ftrf_generate_rays      dataLoader/ray_utils.py:24-85, dataLoader/blender.py:59   camera rays from a pose
  *
  * Factor layout: CHANNEL-LAST.  A VM plane the reference holds as (1,C,H,W) is read as [H][W][C]
  * (torch.channels_last memory of the same Parameter), a line (1,C,L,1) as [L][C].  C % 4 == 0.
@@ -211,6 +214,41 @@ int ftrf_multimem_allreduce(void* multicast_ptr, size_t n_floats, int rank, int 
 /* The same exchange with plain peer loads / stores over NVLink: peer_ptrs[r] is rank r's copy of the symmetric
  * buffer (host array of `world` device pointers, world = 2, 4 or 8); same barrier contract. */
 int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int world, void* stream);
+/* Regularisers of one factor set, value and gradient in one pass.
+ *   TV : sum_k 1e-2 * TVLoss(plane_k)      models/tensoRF.py:195-205 with loss.py:120-141 (VM planes only; the
+ *        reference's CP variant, tensoRF.py:474-484, is 0/0 = NaN and is refused with FTRF_E_ARG)
+ *   L1 : sum_k mean|plane_k| (+ mean|line_k| when with_lines)      models/tensoRF.py:189-193, :468-472
+ * loss_out (device double[2], caller-zeroed, may be NULL) receives += TV and += L1, unweighted, as the reference
+ * methods return them.  Where fs->g_plane / g_line are non-NULL, d(w_tv*TV + w_l1*L1)/d factor is ADDED to them
+ * (train.py:345-371 adds the weighted losses to total_loss); dev_scale (device float, may be NULL) multiplies
+ * both weights (autograd's upstream gradient).  `model` is FTRF_MODEL_*. */
+int ftrf_reg_factors(const FtrfFactorSet* fs, int model, float w_tv, float w_l1, const float* dev_scale,
+                     double* loss_out, int with_lines, void* stream);
+/* torch.optim.Adam(betas, eps; no weight decay / amsgrad) step `step` (1-based) over a host table of segments
+ * in ONE launch (train.py:272-273 optimizer, :374-376 step; lr per segment = the param group's current lr,
+ * which train.py:389-392 decays on the host).  All four arrays of a segment share one element order. */
+typedef struct FtrfAdamSegment {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t n;
+  float lr;
+  int32_t pad_;
+} FtrfAdamSegment;
+int ftrf_adam_step(const FtrfAdamSegment* segs /* host */, int n_segs, float beta1, float beta2, float eps, int step,
+                   void* stream);
+/* Camera rays on the device: rows row0, row0+row_step, ... (n_rows of them) of an H x W
+ * pin-hole image, [n_rows*W][6] = (origin, direction).  dataLoader/ray_utils.py:24-41 get_ray_directions (pixel
+ * centre + 0.5), :44-63 blender variant (y, z negated), dataLoader/blender.py:59 normalisation,
+ * ray_utils.py:67-85 get_rays (d @ c2w[:3,:3]^T, origin c2w[:3,3]).  row_step = world size interleaves the
+ * rows of a frame over the GPUs. */
+typedef struct FtrfCamera {
+  int32_t H, W;
+  float fx, fy, cx, cy;
+  float c2w[12];            /* row-major 3x4 camera-to-world                                  */
+  int32_t normalize;        /* divide the camera-space direction by its norm (blender.py:59)  */
+  int32_t blender;          /* get_ray_directions_blender signs                               */
+} FtrfCamera;
+int ftrf_generate_rays(const FtrfCamera* cam /* host */, int32_t row0, int32_t row_step, int32_t n_rows,
+                       float* rays_out, void* stream);
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py's gpu_launches). */
 unsigned long long ftrf_launch_count(void);
 

@@ -508,6 +508,113 @@ def loss_and_grads(f: Field, rays, target, **kw):
     return loss.detach(), rgb.detach(), depth, nv, grads
 
 
+# --------------------------------------------------------------------------- regularisers / optimiser
+# SURVEY section 8(f) rank 2.  Pinned by tests/golden/optim_vm.npz (tests/golden/make_golden_optim.py runs
+# the reference's TensorVMSplit regulariser methods with its own TVLoss class, and torch.optim.Adam as
+# train.py constructs it).
+def tv_loss(x, weight: float = 1.0):
+    """loss.py:124-138 TVLoss.forward on a (B,C,H,W) tensor."""
+    b, c, h, w = x.shape
+    count_h = c * (h - 1) * w
+    count_w = c * h * (w - 1)
+    h_tv = ((x[:, :, 1:, :] - x[:, :, :h - 1, :]) ** 2).sum()
+    w_tv = ((x[:, :, :, 1:] - x[:, :, :, :w - 1]) ** 2).sum()
+    return weight * 2 * (h_tv / count_h + w_tv / count_w) / b
+
+
+def tv_loss_planes(planes):
+    """models/tensoRF.py:195-205 TV_loss_density / TV_loss_app (VM): sum_k reg(plane_k) * 1e-2."""
+    total = 0
+    for p in planes:
+        total = total + tv_loss(p) * 1e-2
+    return total
+
+
+def density_l1(planes, lines):
+    """models/tensoRF.py:189-193 (VM; pass planes=[] for CP, :468-472)."""
+    total = 0
+    for k in range(len(lines)):
+        if len(planes):
+            total = total + torch.mean(torch.abs(planes[k]))
+        total = total + torch.mean(torch.abs(lines[k]))
+    return total
+
+
+def vector_diffs(lines):
+    """models/tensoRF.py:175-184."""
+    total = 0
+    for v in lines:
+        n_comp, n_size = v.shape[1:-1]
+        m = v.reshape(n_comp, n_size)
+        dotp = m @ m.t()
+        total = total + torch.mean(torch.abs(dotp.reshape(-1)[1:].view(n_comp - 1, n_comp + 1)[..., :-1]))
+    return total
+
+
+def tv_grad(x):
+    """d tv_loss(x) / dx written out (what autograd derives from loss.py:124-138): every squared difference
+    c (a - b)^2 sends +2c(a - b) to a and -2c(a - b) to b."""
+    b, c, h, w = x.shape
+    ch = 2.0 / (c * (h - 1) * w) / b
+    cw = 2.0 / (c * h * (w - 1)) / b
+    g = torch.zeros_like(x)
+    dh = x[:, :, 1:, :] - x[:, :, :-1, :]
+    dw = x[:, :, :, 1:] - x[:, :, :, :-1]
+    g[:, :, 1:, :] += 2 * ch * dh
+    g[:, :, :-1, :] -= 2 * ch * dh
+    g[:, :, :, 1:] += 2 * cw * dw
+    g[:, :, :, :-1] -= 2 * cw * dw
+    return g
+
+
+def reg_grads(planes, lines, w_tv: float, w_l1: float):
+    """Gradient of w_tv * tv_loss_planes(planes) + w_l1 * density_l1(planes, lines) (train.py:345-371)."""
+    gp = [w_tv * 1e-2 * tv_grad(p) + w_l1 * torch.sign(p) / p.numel() for p in planes]
+    gl = [w_l1 * torch.sign(v) / v.numel() for v in lines]
+    return gp, gl
+
+
+def adam_step(p, g, m, v, lr: float, beta1: float, beta2: float, eps: float, t: int):
+    """One torch.optim.Adam update of step t (1-based), in place on p, m, v — torch/optim/adam.py
+    _single_tensor_adam with weight_decay = 0, amsgrad = False (the optimiser of train.py:272-273)."""
+    m.mul_(beta1).add_(g, alpha=1 - beta1)
+    v.mul_(beta2).addcmul_(g, g, value=1 - beta2)
+    bc1 = 1 - beta1 ** t
+    bc2 = 1 - beta2 ** t
+    denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+    p.addcdiv_(m, denom, value=-(lr / bc1))
+
+
+# --------------------------------------------------------------------------- camera rays
+# SURVEY section 8(f) rank 3.  dataLoader/ray_utils.py imports kornia (absent here), so this restatement is
+# "parity unpinned" by the reference's own code; it follows the source line by line.
+def ray_directions(H: int, W: int, focal, center=None, blender: bool = False):
+    """dataLoader/ray_utils.py:24-41 get_ray_directions / :44-63 get_ray_directions_blender.
+    kornia.create_meshgrid(H, W, normalized_coordinates=False)[0] is (x = column, y = row) per pixel."""
+    j, i = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    i, j = i + 0.5, j + 0.5
+    cent = center if center is not None else [W / 2, H / 2]
+    if blender:
+        return torch.stack([(i - cent[0]) / focal[0], -(j - cent[1]) / focal[1], -torch.ones_like(i)], -1)
+    return torch.stack([(i - cent[0]) / focal[0], (j - cent[1]) / focal[1], torch.ones_like(i)], -1)
+
+
+def get_rays(directions, c2w):
+    """dataLoader/ray_utils.py:67-85."""
+    rays_d = directions @ c2w[:3, :3].T
+    rays_o = c2w[:3, 3].expand(rays_d.shape)
+    return rays_o.reshape(-1, 3), rays_d.reshape(-1, 3)
+
+
+def camera_rays(H: int, W: int, focal, c2w, center=None, normalize: bool = True, blender: bool = False):
+    """[H*W, 6] rays of one image as the blender loader builds them (dataLoader/blender.py:57-59, :106-107)."""
+    d = ray_directions(H, W, focal, center, blender)
+    if normalize:
+        d = d / torch.norm(d, dim=-1, keepdim=True)
+    o, dd = get_rays(d, c2w)
+    return torch.cat([o, dd], 1)
+
+
 # --------------------------------------------------------------------------- synthetic inputs
 def synthetic_rays(n: int, seed: int = 0, radius: float = 4.0):
     """SURVEY.md section 8(d) synthetic training rays: origins on a sphere, aimed into the box."""

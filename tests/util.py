@@ -9,7 +9,8 @@ import torch
 from oracle import field_oracle as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
+CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
+               if not os.path.basename(p).startswith("optim_"))          # optim_*: regulariser / Adam fixtures
 
 
 class Golden:
@@ -68,3 +69,45 @@ def rel_inf(a: torch.Tensor, b: torch.Tensor, eps: float = 1e-12) -> float:
     if a.numel() == 0:
         return 0.0
     return float((a - b).abs().max() / max(float(b.abs().max()), eps))
+
+
+def pseudo_grads(shapes, steps=3, seed=5):
+    """The seeded pseudo-gradients of the Adam fixture (tests/golden/make_golden_optim.py): {t: {name: tensor}}
+    in named_parameters() order; regenerated here instead of storing 3 x all parameters in the fixture."""
+    gen = torch.Generator().manual_seed(seed)
+    out = {}
+    for t in range(1, steps + 1):
+        out[t] = {}
+        for k, shp in shapes:
+            g = torch.randn(tuple(shp), generator=gen) * (10.0 ** (-t))
+            if t == 2 and len(shp) == 4:
+                g[..., ::2, :] = 0.0                        # exact zeros keep v small next to eps
+            out[t][k] = g
+    return out
+
+
+class OptimGolden:
+    """tests/golden/optim_vm.npz: a reference TensorVMSplit's regulariser values / gradients and three
+    torch.optim.Adam steps on seeded pseudo-gradients."""
+
+    def __init__(self, name="optim_vm"):
+        d = np.load(os.path.join(GOLDEN, name + ".npz"))
+        self.t = {k: (torch.from_numpy(np.asarray(d[k])) if d[k].dtype.kind in "fiu" else d[k]) for k in d.files}
+        self.order = [str(k) for k in d["param_order"]]
+        self.grid = tuple(int(x) for x in d["grid"])
+        self.lr_factor = float(d["lr_factor"])
+        self.w_l1, self.w_tvd, self.w_tva, self.w_o = [float(x) for x in d["weights"]]
+
+    def group(self, prefix):
+        return {k[len(prefix) + 1:]: v for k, v in self.t.items() if k.startswith(prefix + "/")}
+
+    def config(self) -> O.FieldConfig:
+        return O.FieldConfig(model="VM", shading="MLP_Fea", grid=self.grid, density_n_comp=(8, 8, 8),
+                             app_n_comp=(16, 16, 16), app_dim=27)
+
+    def field(self) -> O.Field:
+        return O.Field(self.config(), {k: v.clone() for k, v in self.group("p0").items()}, None)
+
+    def lr_of(self, name, t):
+        base = 0.02 if ("plane" in name or "line" in name) else 0.001       # get_optparam_groups(0.02, 0.001)
+        return base * self.lr_factor ** (t - 1)
