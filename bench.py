@@ -60,10 +60,9 @@ def build_model(device, grid=GRID, mask_grid=MASK_GRID, shading="MLP_Fea"):
     return m
 
 
-def camera_rays(device, h=800, w=800, elev_deg=30.0, azim_deg=45.0, radius=4.0311):
-    """One 800x800 NeRF-synthetic test view: focal from camera_angle_x = 0.6911112
-    (dataLoader/blender.py:53), directions per get_ray_directions (+0.5 px, ray_utils.py:34-40) normalised
-    (blender.py:59), rotated by an OpenCV-convention c2w looking at the origin (ray_utils.py:79-85)."""
+def camera_pose(h=800, w=800, elev_deg=30.0, azim_deg=45.0, radius=4.0311):
+    """(c2w 3x4, focal) of one NeRF-synthetic test view: focal from camera_angle_x =
+    0.6911112 (dataLoader/blender.py:53), OpenCV-convention c2w looking at the origin."""
     import math
     focal = 0.5 * 800 / math.tan(0.5 * 0.6911112) * (w / 800)
     el, az = math.radians(elev_deg), math.radians(azim_deg)
@@ -72,13 +71,20 @@ def camera_rays(device, h=800, w=800, elev_deg=30.0, azim_deg=45.0, radius=4.031
     right = torch.linalg.cross(fwd, torch.tensor([0.0, 0.0, 1.0]))
     right = right / right.norm()
     down = torch.linalg.cross(fwd, right)
-    c2w = torch.stack([right, down, fwd], 1).to(device)           # columns: x right, y down, z forward
+    return torch.cat([torch.stack([right, down, fwd], 1), o[:, None]], 1), focal     # columns: x right, y down, z forward
+
+
+def camera_rays(device, h=800, w=800, elev_deg=30.0, azim_deg=45.0, radius=4.0311):
+    """The 800x800 rays of that view: directions per get_ray_directions (+0.5 px, ray_utils.py:34-40)
+    normalised (blender.py:59), rotated by c2w (ray_utils.py:79-85)."""
+    c2w, focal = camera_pose(h, w, elev_deg, azim_deg, radius)
+    c2w = c2w.to(device)
     j, i = torch.meshgrid(torch.arange(h, device=device, dtype=torch.float32) + 0.5,
                           torch.arange(w, device=device, dtype=torch.float32) + 0.5, indexing="ij")
     d = torch.stack([(i - w / 2) / focal, (j - h / 2) / focal, torch.ones_like(i)], -1)
     d = d / d.norm(dim=-1, keepdim=True)
-    rays_d = (d @ c2w.T).reshape(-1, 3)
-    rays_o = o.to(device).expand_as(rays_d)
+    rays_d = (d @ c2w[:, :3].T).reshape(-1, 3)
+    rays_o = c2w[:, 3].expand_as(rays_d)
     return torch.cat([rays_o, rays_d], -1).contiguous()
 
 
@@ -115,9 +121,31 @@ def render_leg(dev, frames=5):
         t = torch.tensor([e0.elapsed_time(e1) / frames], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        st = model._last_call
+        # end to end from the pose: rays generated on the device (ftrf_generate_rays), image read back into
+        # pinned host memory — 48 B in, 10.2 MB out per frame (rgb + depth), wall clock
+        c2w, focal = camera_pose()
+        n_mine = int(rows.numel())
+        host_rgb = torch.empty(n_mine, 800, 3).pin_memory()
+        host_depth = torch.empty(n_mine, 800).pin_memory()
+
+        def frame_e2e():
+            with torch.no_grad():
+                rgb, depth, _ = ft.render_view(model, c2w, 800, 800, focal, white_bg=True, row0=rank, row_step=world)
+            host_rgb.copy_(rgb, non_blocking=True)
+            host_depth.copy_(depth, non_blocking=True)
+            torch.cuda.synchronize()
+        frame_e2e()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            frame_e2e()
+        te = torch.tensor([(time.perf_counter() - t0) * 1e3 / frames], device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
         out[shading] = {"ms_per_frame": float(t), "shaded_samples": float(res[5]),
-                        "mean_rgb": float(res[0].mean()), "rays_this_gpu": int(mine.shape[0])}
+                        "mean_rgb": float(res[0].mean()), "rays_this_gpu": int(mine.shape[0]),
+                        "e2e_from_pose_ms": float(te), "e2e_mean_rgb": float(host_rgb.mean())}
         del model
     return out
 
@@ -163,7 +191,6 @@ def optim_leg(model, dev, hbm_peak, iters=20):
     import fewtensorf_b200 as ft
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     flush_view = flush.view(torch.int32)
-    sink = torch.zeros((), dtype=torch.int64, device=dev)
     with torch.no_grad():
         for p in model.parameters():
             if p.grad is None:
@@ -175,9 +202,8 @@ def optim_leg(model, dev, hbm_peak, iters=20):
         ms = 0.0
         for _ in range(iters):
             flush.zero_()                                   # 512 MB > L2: every pass streams from HBM ...
-            sink.copy_(flush[:1 << 20:4096].sum())          # ... and a read pass leaves CLEAN lines behind, so the
-            flush_view.sum()                                # timed kernel does not pay the write-back of 126 MB of
-                                                            # dirty flush lines (it did: 48 % -> of peak instead of ~75 %)
+            flush_view.sum()                                # ... and a read pass leaves CLEAN lines behind: the timed
+                                                            # kernel does not pay the write-back of dirty flush lines
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()

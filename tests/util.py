@@ -10,7 +10,7 @@ from oracle import field_oracle as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-               if not os.path.basename(p).startswith("optim_"))          # optim_*: regulariser / Adam fixtures
+               if not os.path.basename(p).startswith(("optim_", "sched_")))   # regulariser / Adam / schedule fixtures
 
 
 class Golden:
