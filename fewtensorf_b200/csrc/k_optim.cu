@@ -29,51 +29,61 @@ __device__ __forceinline__ float sgn(float v) { return (v > 0.f) - (v < 0.f); }
 
 // Channel-last plane [H][W][C]: one thread owns the 4 channels of one texel.  Differences are counted once
 // per pair (towards h+1 / w+1); the gradient of texel t collects both pairs it belongs to on each axis.
-// Persistent grid over 256-texel-quad tiles of the three planes taken as ONE index space (a 16-channel 300^2
-// plane is only ~1400 tiles, so per-plane grids would quantise badly); few blocks also keep the two double
-// atomics per block that publish the loss values few (same-address atomics serialise).
+// Persistent grid over tiles of T.rows image rows x 256 float4 of a row, the three planes taken as ONE tile
+// space (a 16-channel 300^2 plane alone quantises badly).  A thread walks DOWN its column of the tile with
+// the rows above / below in registers, so each plane element comes in from L2 once (+ 2/rows halo) rather
+// than three times — the per-SM L2 port, not HBM, was the limit of the flat version; left / right neighbours
+// are the neighbouring threads' centre loads (L1).  Few blocks also keep the two double atomics per block
+// that publish the loss values few (same-address atomics serialise).
 constexpr int REG_THREADS = 256;
+struct RegTiles { uint32_t first[4]; uint32_t chunks[3]; int rows; };     // tile prefix per plane, column chunks per row, rows per tile
+
 __global__ void __launch_bounds__(REG_THREADS, 6)
-reg_planes_kernel(const RegArgs a, const uint32_t tiles0, const uint32_t tiles01, const uint32_t tiles) {
+reg_planes_kernel(const RegArgs a, const RegTiles T) {
   float tv = 0.f, l1 = 0.f;
   float scale = 1.f;
   if (a.dev_scale) scale = __ldg(a.dev_scale);
-  for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int k = tile < tiles0 ? 0 : (tile < tiles01 ? 1 : 2);
+  for (uint32_t tile = blockIdx.x; tile < T.first[3]; tile += gridDim.x) {
+    const int k = tile < T.first[1] ? 0 : (tile < T.first[2] ? 1 : 2);
     const RegPlane& P = a.p[k];
-    const uint32_t q = (tile - (k == 0 ? 0u : (k == 1 ? tiles0 : tiles01))) * REG_THREADS + threadIdx.x;
+    const uint32_t lt = tile - T.first[k];
+    const uint32_t rg = lt / T.chunks[k], cc = lt - rg * T.chunks[k];
     const uint32_t c4n = P.C >> 2;
     const uint32_t rowq = (uint32_t)P.W * c4n;          // float4 per image row
-    const uint32_t n4 = (uint32_t)P.H * rowq;            // < 2^31 (checked by the launcher)
-    if (q >= n4) continue;
+    const uint32_t col = cc * REG_THREADS + threadIdx.x; // float4 index inside the row
+    if (col >= rowq) continue;
+    const int w = (int)(col / c4n);
+    const int h0 = (int)rg * T.rows;
+    const int h1 = h0 + T.rows < P.H ? h0 + T.rows : P.H;
     const float gtv = a.w_tv * scale, gl1 = a.w_l1 * scale * P.l1;
     const bool want_g = P.g != nullptr;
-    const float4* X = reinterpret_cast<const float4*>(P.x);
-    float4* G = reinterpret_cast<float4*>(P.g);
-    const int h = (int)(q / rowq);
-    const int w = (int)((q - (uint32_t)h * rowq) / c4n);
-    const bool up = h > 0 && want_g, down = h + 1 < P.H, left = w > 0 && want_g, right = w + 1 < P.W;
-    // all loads first (six independent requests in flight per thread), then the arithmetic
-    const float4 x = __ldg(X + q);
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 yd = down ? __ldg(X + q + rowq) : x;
-    const float4 yu = up ? __ldg(X + q - rowq) : x;
-    const float4 yr = right ? __ldg(X + q + c4n) : x;
-    const float4 yl = left ? __ldg(X + q - c4n) : x;
-    float4 o = want_g ? G[q] : z4;
-    const float4 dd = make_float4(x.x - yd.x, x.y - yd.y, x.z - yd.z, x.w - yd.w);
-    const float4 dr = make_float4(x.x - yr.x, x.y - yr.y, x.z - yr.z, x.w - yr.w);
-    tv = fmaf(P.ch, dd.x * dd.x + dd.y * dd.y + dd.z * dd.z + dd.w * dd.w, tv);
-    tv = fmaf(P.cw, dr.x * dr.x + dr.y * dr.y + dr.z * dr.z + dr.w * dr.w, tv);
-    l1 = fmaf(fabsf(x.x) + fabsf(x.y) + fabsf(x.z) + fabsf(x.w), P.l1, l1);
-    if (want_g) {
-      // d/dx of c (x - y)^2 is 2 c (x - y); a missing neighbour was replaced by x itself (difference 0)
-      const float ch = 2.f * gtv * P.ch, cw = 2.f * gtv * P.cw;
-      o.x += ch * (dd.x + (x.x - yu.x)) + cw * (dr.x + (x.x - yl.x)) + gl1 * sgn(x.x);
-      o.y += ch * (dd.y + (x.y - yu.y)) + cw * (dr.y + (x.y - yl.y)) + gl1 * sgn(x.y);
-      o.z += ch * (dd.z + (x.z - yu.z)) + cw * (dr.z + (x.z - yl.z)) + gl1 * sgn(x.z);
-      o.w += ch * (dd.w + (x.w - yu.w)) + cw * (dr.w + (x.w - yl.w)) + gl1 * sgn(x.w);
-      G[q] = o;
+    const bool left = w > 0 && want_g, right = w + 1 < P.W;
+    const float ch = 2.f * gtv * P.ch, cw = 2.f * gtv * P.cw;
+    const float4* X = reinterpret_cast<const float4*>(P.x) + (size_t)h0 * rowq + col;
+    float4* G = reinterpret_cast<float4*>(P.g) + (size_t)h0 * rowq + col;
+    float4 x = __ldg(X);
+    float4 yu = (h0 > 0 && want_g) ? __ldg(X - rowq) : x;     // a missing neighbour is replaced by x (difference 0)
+#pragma unroll 2
+    for (int h = h0; h < h1; ++h, X += rowq, G += rowq) {
+      const float4 yd = h + 1 < P.H ? __ldg(X + rowq) : x;
+      const float4 yr = right ? __ldg(X + c4n) : x;
+      const float4 yl = left ? __ldg(X - c4n) : x;
+      const float4 dd = make_float4(x.x - yd.x, x.y - yd.y, x.z - yd.z, x.w - yd.w);
+      const float4 dr = make_float4(x.x - yr.x, x.y - yr.y, x.z - yr.z, x.w - yr.w);
+      tv = fmaf(P.ch, dd.x * dd.x + dd.y * dd.y + dd.z * dd.z + dd.w * dd.w, tv);
+      tv = fmaf(P.cw, dr.x * dr.x + dr.y * dr.y + dr.z * dr.z + dr.w * dr.w, tv);
+      l1 = fmaf(fabsf(x.x) + fabsf(x.y) + fabsf(x.z) + fabsf(x.w), P.l1, l1);
+      if (want_g) {
+        // d/dx of c (x - y)^2 is 2 c (x - y)
+        float4 o = *G;
+        o.x += ch * (dd.x + (x.x - yu.x)) + cw * (dr.x + (x.x - yl.x)) + gl1 * sgn(x.x);
+        o.y += ch * (dd.y + (x.y - yu.y)) + cw * (dr.y + (x.y - yl.y)) + gl1 * sgn(x.y);
+        o.z += ch * (dd.z + (x.z - yu.z)) + cw * (dr.z + (x.z - yl.z)) + gl1 * sgn(x.z);
+        o.w += ch * (dd.w + (x.w - yu.w)) + cw * (dr.w + (x.w - yl.w)) + gl1 * sgn(x.w);
+        *G = o;
+      }
+      yu = x;
+      x = yd;
     }
   }
 #pragma unroll
@@ -93,30 +103,31 @@ reg_planes_kernel(const RegArgs a, const uint32_t tiles0, const uint32_t tiles01
   }
 }
 
-// L1 of the three lines [L][C] (tiny): one block per line.
+// L1 of the three lines [L][C] (tiny): one element per thread, blockIdx.y = line (a block-per-line loop made
+// ~20 dependent global round trips and took longer than the 52 MB plane pass).
 struct RegLines { const float* x[3]; float* g[3]; int n[3]; float w_l1; const float* dev_scale; double* loss; };
 __global__ void __launch_bounds__(256)
 reg_lines_kernel(const RegLines a) {
-  const int k = blockIdx.x;
+  const int k = blockIdx.y;
   const float* x = a.x[k];
-  if (!x) return;
-  float scale = a.dev_scale ? __ldg(a.dev_scale) : 1.f;
-  const float inv = 1.f / (float)a.n[k];
-  const float gl1 = a.w_l1 * scale * inv;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = x != nullptr && i < a.n[k];
+  const float inv = 1.f / (float)(a.n[k] > 0 ? a.n[k] : 1);
   float l1 = 0.f;
-  for (int i = threadIdx.x; i < a.n[k]; i += blockDim.x) {
+  if (live) {
+    const float scale = a.dev_scale ? __ldg(a.dev_scale) : 1.f;
     const float v = __ldg(x + i);
-    l1 += fabsf(v);
-    if (a.g[k]) a.g[k][i] += gl1 * sgn(v);
+    l1 = fabsf(v);
+    if (a.g[k]) a.g[k][i] += a.w_l1 * scale * inv * sgn(v);
   }
 #pragma unroll
   for (int d = 16; d; d >>= 1) l1 += __shfl_xor_sync(FULL_MASK, l1, d);
   __shared__ float s[8];
   if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = l1;
   __syncthreads();
-  if (threadIdx.x == 0 && a.loss) {
+  if (threadIdx.x == 0 && a.loss && x != nullptr && blockIdx.x * blockDim.x < a.n[k]) {
     double l = 0.0;
-    for (int i = 0; i < 8; ++i) l += s[i];
+    for (int j = 0; j < 8; ++j) l += s[j];
     atomicAdd(a.loss + 1, l * (double)inv);
   }
 }
@@ -139,23 +150,36 @@ int launch_reg_factors(const FtrfFactorSet& fs, int model, float w_tv, float w_l
       const int64_t n4 = (int64_t)P.H * P.W * (P.C >> 2);
       if (n4 >= (int64_t)1 << 31) { set_error("reg_factors: plane %d too large", k); return FTRF_E_ARG; }
     }
-    uint32_t t[3];
-    for (int k = 0; k < 3; ++k)
-      t[k] = (uint32_t)(((int64_t)a.p[k].H * a.p[k].W * (a.p[k].C >> 2) + REG_THREADS - 1) / REG_THREADS);
-    const uint32_t tiles = t[0] + t[1] + t[2];
     static int per_sm = 0;
     if (!per_sm) {
       if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reg_planes_kernel, REG_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
     }
+    // rows per tile: the walk costs rows + 2 (halo) row loads per tile, and the tiles should fill whole waves
+    RegTiles T{};
+    double best = 1e30;
+    for (int rows = 4; rows <= 32; ++rows) {
+      uint32_t tiles = 0;
+      for (int k = 0; k < 3; ++k)
+        tiles += (uint32_t)((a.p[k].W * (a.p[k].C >> 2) + REG_THREADS - 1) / REG_THREADS) * (uint32_t)((a.p[k].H + rows - 1) / rows);
+      const double waves = (double)((tiles + FTRF_SMS * per_sm - 1) / (FTRF_SMS * per_sm));
+      const double cost = waves * (rows + 2);
+      if (cost < best) { best = cost; T.rows = rows; }
+    }
+    for (int k = 0; k < 3; ++k) {
+      T.chunks[k] = (uint32_t)((a.p[k].W * (a.p[k].C >> 2) + REG_THREADS - 1) / REG_THREADS);
+      T.first[k + 1] = T.first[k] + T.chunks[k] * (uint32_t)((a.p[k].H + T.rows - 1) / T.rows);
+    }
     const uint32_t cap = (uint32_t)FTRF_SMS * per_sm;
-    reg_planes_kernel<<<tiles < cap ? tiles : cap, REG_THREADS, 0, st>>>(a, t[0], t[0] + t[1], tiles);
+    reg_planes_kernel<<<T.first[3] < cap ? T.first[3] : cap, REG_THREADS, 0, st>>>(a, T);
     if (int e = check_launch("reg_planes")) return e;
   }
   if (with_lines) {
     RegLines l{};
     l.w_l1 = w_l1; l.dev_scale = dev_scale; l.loss = loss;
     for (int k = 0; k < 3; ++k) { l.x[k] = fs.line[k]; l.g[k] = fs.g_line[k]; l.n[k] = fs.line_len[k] * fs.n_comp[k]; }
-    reg_lines_kernel<<<3, 256, 0, st>>>(l);
+    int most = 1;
+    for (int k = 0; k < 3; ++k) most = l.n[k] > most ? l.n[k] : most;
+    reg_lines_kernel<<<dim3((most + 255) / 256, 3), 256, 0, st>>>(l);
     if (int e = check_launch("reg_lines")) return e;
   }
   return FTRF_OK;
