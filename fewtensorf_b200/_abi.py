@@ -81,7 +81,8 @@ EXPORTS = [
     "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward", "ftrf_backward_part",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
-    "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_profile_enable", "ftrf_profile_read",
+    "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
+    "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_profile_enable", "ftrf_profile_read",
     "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
@@ -120,6 +121,17 @@ def _load():
     lib.ftrf_build_coarse_mask.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_density_at.restype = C.c_int
     lib.ftrf_density_at.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    i3 = [C.c_int32, C.c_int32, C.c_int32]
+    lib.ftrf_dense_alpha_bits.restype = C.c_int
+    lib.ftrf_dense_alpha_bits.argtypes = [C.POINTER(FtrfField), C.c_void_p] + i3 + [C.c_float, C.c_float, C.c_void_p,
+                                                                                   C.c_void_p, C.c_void_p]
+    lib.ftrf_dilate_alpha_mask.restype = C.c_int
+    lib.ftrf_dilate_alpha_mask.argtypes = [C.c_void_p] + i3 + [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ftrf_unpack_alpha_mask.restype = C.c_int
+    lib.ftrf_unpack_alpha_mask.argtypes = [C.c_void_p] + i3 + [C.c_void_p, C.c_void_p]
+    lib.ftrf_filter_rays.restype = C.c_int
+    lib.ftrf_filter_rays.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                     C.c_void_p, C.c_void_p]
     lib.ftrf_profile_enable.restype = C.c_int
     lib.ftrf_profile_enable.argtypes = [C.c_int]
     lib.ftrf_profile_read.restype = C.c_int

@@ -60,6 +60,8 @@ int launch_shade_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t,
 int launch_appearance_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_at(const FtrfField&, const float* xyz, int64_t n, float* out, cudaStream_t);
+int launch_dense_alpha_bits(const FtrfField&, const float* lin, int X, int Y, int Z, float length, float thres,
+                            uint32_t* raw, float* alpha_out, cudaStream_t);
 
 #ifdef __CUDACC__
 

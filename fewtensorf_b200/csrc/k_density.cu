@@ -166,6 +166,57 @@ density_at_kernel(const FtrfField f, const float* __restrict__ xyz, int64_t n, f
   }
 }
 
+// Occupancy lattice: getDenseAlpha + compute_alpha + the `>= alphaMask_thres` test of updateAlphaMask
+// (tensorBase.py:215-230, :298-318, :245) without materialising the [X,Y,Z,3] point tensor or the
+// float alpha lattice.  A warp owns one 32-texel word of the (Z,Y,X)-ordered bit field: four rounds of
+// eight lattice points (four lanes per point, as in the sample kernels), each round's verdicts
+// collected by one ballot.  Point k-coordinate = aabb0*(1-s) + aabb1*s with s = linspace(0,1,G)[i]
+// (host table `lin` = the three linspaces back to back), every operation rounded separately as in
+// torch.  alpha = clamp(1 - exp(-sigma*length), 0, 1); raw bit = alpha >= thres (the 3^3 max-pool
+// that follows is a dilation of these bits because max(.) >= t <=> any(. >= t)).
+__global__ void __launch_bounds__(256)
+dense_alpha_bits_kernel(const FtrfField f, const float* __restrict__ lin, const int X, const int Y, const int Z,
+                        const float length, const float thres, uint32_t* __restrict__ raw, float* __restrict__ alpha_out) {
+  const int sub = threadIdx.x & (GS - 1), grp = lane_id() >> 2;
+  const int xw = (X + 31) >> 5;
+  const int64_t words = (int64_t)xw * Y * Z;
+  const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t wstride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = w0; w < words; w += wstride) {
+    const int xb = (int)(w % xw) << 5;
+    const int y = (int)((w / xw) % Y), z = (int)(w / ((int64_t)xw * Y));
+    const float sy = __ldg(lin + X + y), sz = __ldg(lin + X + Y + z);
+    uint32_t word = 0u;
+#pragma unroll 1
+    for (int j = 0; j < 4; ++j) {
+      const int x = xb + j * 8 + grp;
+      float part = 0.f;
+      bool keep = false;
+      if (x < X) {
+        const float s[3] = {__ldg(lin + x), sy, sz};
+        float p[3], xn[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          p[k] = __fadd_rn(__fmul_rn(f.aabb[k], __fsub_rn(1.f, s[k])), __fmul_rn(f.aabb[3 + k], s[k]));
+        keep = f.has_alpha_mask ? alpha_mask_keep(f, p) : true;
+        if (keep) {
+          normalize_pt(f, p, xn);
+          part = density_partial(f, xn, sub);
+        }
+      }
+      const float feat = group_sum(part);
+      const float sigma = keep ? activate(f, feat) : 0.f;
+      float a = __fsub_rn(1.f, expf(__fmul_rn(-sigma, length)));
+      a = fminf(fmaxf(a, 0.f), 1.f);
+      if (alpha_out && sub == 0 && x < X) alpha_out[((size_t)z * Y + y) * X + x] = a;
+      const uint32_t b = __ballot_sync(FULL_MASK, sub == 0 && x < X && a >= thres);
+#pragma unroll
+      for (int g = 0; g < 8; ++g) word |= ((b >> (4 * g)) & 1u) << (j * 8 + g);
+    }
+    if (lane_id() == 0) raw[w] = word;
+  }
+}
+
 // ------------------------------------------------------------------------------------ backward
 // d sigma_feature arrives in ws.s_gsig.  Each lane scatters its own channel chunks with
 // red.global.add.v4.f32 (one 16-byte reduction per corner per chunk).
@@ -423,6 +474,15 @@ int launch_density_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   else if (f.model == FTRF_MODEL_VM && g_density_bwd_runs) density_bwd_vm_runs_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws, g_density_bwd_runs);
   else density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
   return check_launch("density_bwd");
+}
+
+int launch_dense_alpha_bits(const FtrfField& f, const float* lin, int X, int Y, int Z, float length, float thres,
+                            uint32_t* raw, float* alpha_out, cudaStream_t st) {
+  const int64_t words = (int64_t)((X + 31) / 32) * Y * Z;
+  const int64_t blocks = (words + 7) / 8;                       // 8 warps (words) per CTA
+  const int64_t cap = (int64_t)FTRF_SMS * 8 * 4;
+  dense_alpha_bits_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(f, lin, X, Y, Z, length, thres, raw, alpha_out);
+  return check_launch("dense_alpha_bits");
 }
 
 int launch_density_at(const FtrfField& f, const float* xyz, int64_t n, float* out, cudaStream_t st) {

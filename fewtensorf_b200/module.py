@@ -55,27 +55,64 @@ class AlphaGridMask(nn.Module):
         self.aabb = aabb.to(self.device)
         self.aabbSize = self.aabb[1] - self.aabb[0]
         self.invgridSize = 1.0 / self.aabbSize * 2
-        self.alpha_volume = alpha_volume.view(1, 1, *alpha_volume.shape[-3:])
+        self._volume = alpha_volume.view(1, 1, *alpha_volume.shape[-3:])
         self.gridSize = torch.LongTensor(
             [alpha_volume.shape[-1], alpha_volume.shape[-2], alpha_volume.shape[-3]]).to(self.device)
         self._bits = None
         self._host = None
 
+    @classmethod
+    def from_bits(cls, device, aabb, bits: torch.Tensor, dims):
+        """Mask that only exists bit-packed (updateAlphaMask's kernels write it that way); the float volume
+        the reference exposes is unpacked on first access of `.alpha_volume`."""
+        self = cls.__new__(cls)
+        nn.Module.__init__(self)
+        self.device = device
+        self.aabb = aabb.to(device)
+        self.aabbSize = self.aabb[1] - self.aabb[0]
+        self.invgridSize = 1.0 / self.aabbSize * 2
+        self._volume = None
+        self.gridSize = torch.LongTensor([int(d) for d in dims]).to(device)
+        self._bits = None
+        self._host = None
+        self._finish_packed(bits, [int(d) for d in dims])
+        return self
+
+    @property
+    def alpha_volume(self):
+        if self._volume is None:
+            x, y, z = self._host[0]
+            vol = torch.empty((1, 1, z, y, x), dtype=torch.float32, device=self._bits.device)
+            check(lib.ftrf_unpack_alpha_mask(self._bits.data_ptr(), x, y, z, vol.data_ptr(), _stream()), "unpack_alpha_mask")
+            self._volume = vol
+        return self._volume
+
+    @alpha_volume.setter
+    def alpha_volume(self, vol):
+        self._volume = vol.view(1, 1, *vol.shape[-3:])
+        self.gridSize = torch.LongTensor([vol.shape[-1], vol.shape[-2], vol.shape[-3]]).to(self.device)
+        self._bits = None
+        self._host = None
+
+    def _finish_packed(self, bits, dims):
+        x, y, z = dims
+        self._bits = bits
+        coarse = torch.empty(lib.ftrf_alpha_mask_coarse_words(x, y, z), dtype=torch.int32, device=bits.device)
+        check(lib.ftrf_build_coarse_mask(bits.data_ptr(), x, y, z, coarse.data_ptr(), _stream()), "build_coarse_mask")
+        self._coarse = coarse
+        a = self.aabb.detach().float().cpu()
+        inv = (1.0 / (a[1] - a[0]) * 2)          # same fp32 ops as :36-37
+        self._host = ([x, y, z], a[0].tolist(), inv.tolist())
+
     def packed(self):
         """(bits tensor, dims [X,Y,Z], aabb0 list, invgrid list) — built once per mask."""
         if self._bits is None:
-            vol = self.alpha_volume.detach().to(device=self.device, dtype=torch.float32).contiguous()
+            vol = self._volume.detach().to(device=self.device, dtype=torch.float32).contiguous()
             z, y, x = vol.shape[-3:]
             words = lib.ftrf_alpha_mask_words(x, y, z)
             bits = torch.empty(words, dtype=torch.int32, device=vol.device)
             check(lib.ftrf_pack_alpha_mask(vol.data_ptr(), x, y, z, bits.data_ptr(), _stream()), "pack_alpha_mask")
-            self._bits = bits
-            coarse = torch.empty(lib.ftrf_alpha_mask_coarse_words(x, y, z), dtype=torch.int32, device=vol.device)
-            check(lib.ftrf_build_coarse_mask(bits.data_ptr(), x, y, z, coarse.data_ptr(), _stream()), "build_coarse_mask")
-            self._coarse = coarse
-            a = self.aabb.detach().float().cpu()
-            inv = (1.0 / (a[1] - a[0]) * 2)          # same fp32 ops as :36-37
-            self._host = ([x, y, z], a[0].tolist(), inv.tolist())
+            self._finish_packed(bits, [x, y, z])
         return (self._bits,) + self._host
 
     def sample_alpha(self, xyz_sampled):
@@ -814,36 +851,56 @@ class TensorBase(nn.Module):
 
     @torch.no_grad()
     def updateAlphaMask(self, gridSize=(200, 200, 200), mask=None):
-        """models/tensorBase.py:233-256."""
-        gridSize = tuple(int(g) for g in gridSize)
-        alpha, dense_xyz = self.getDenseAlpha(gridSize, mask)
-        dense_xyz = dense_xyz.transpose(0, 2).contiguous()
-        alpha = alpha.clamp(0, 1).transpose(0, 2).contiguous()[None, None]
-        alpha = F.max_pool3d(alpha, kernel_size=3, padding=1, stride=1).view(gridSize[::-1])
-        alpha[alpha >= self.alphaMask_thres] = 1
-        alpha[alpha < self.alphaMask_thres] = 0
-        self.alphaMask = AlphaGridMask(self.device, self.aabb, alpha)
-        occ = dense_xyz[alpha > 0.5]
-        return torch.stack((occ.amin(0), occ.amax(0)))
+        """models/tensorBase.py:233-256 on the occupancy kernels: lattice alpha -> threshold bits ->
+        3^3 dilation (the max-pool) -> bit-packed AlphaGridMask, bounding box and count reduced on the
+        device.  Neither the [X,Y,Z,3] point lattice nor a float alpha volume is materialised."""
+        X, Y, Z = (int(g) for g in gridSize)
+        lin = torch.cat([torch.linspace(0, 1, n) for n in (X, Y, Z)]).to(self.device)     # :218-222 (CPU linspace, as there)
+        den_mask = None if mask is None else {"encoding": {"pos": None, "view": None, "fea": None},
+                                              "decomp": {"den": mask, "app": None}}
+        field = self._fill_field(den_mask)
+        words = lib.ftrf_alpha_mask_words(X, Y, Z)
+        raw = torch.empty(words, dtype=torch.int32, device=self.device)
+        bits = torch.empty(words, dtype=torch.int32, device=self.device)
+        stats = torch.empty(8, dtype=torch.int32, device=self.device)
+        check(lib.ftrf_dense_alpha_bits(C.byref(field), lin.data_ptr(), X, Y, Z, float(self.stepSize),
+                                        float(self.alphaMask_thres), raw.data_ptr(), None, _stream()), "dense_alpha_bits")
+        check(lib.ftrf_dilate_alpha_mask(raw.data_ptr(), X, Y, Z, bits.data_ptr(), stats.data_ptr(), _stream()),
+              "dilate_alpha_mask")
+        st = stats.cpu()                                                                # the call's one host sync
+        total = int(st[6:8].view(torch.int64))
+        self.alphaMask = AlphaGridMask.from_bits(self.device, self.aabb, bits, (X, Y, Z))
+        self.last_alpha_rest = total / float(X * Y * Z)
+        if total == 0:
+            raise RuntimeError("updateAlphaMask: no lattice point reaches alphaMask_thres (the reference's "
+                               "valid_xyz.amin(0) fails on the empty selection, tensorBase.py:250)")
+        # :248-253 — the lattice is monotone in the index, so the extreme points are the points at the extreme indices
+        lin = lin.cpu()
+        off = (0, X, X + Y)
+        s_lo = torch.stack([lin[off[k] + int(st[k])] for k in range(3)]).to(self.device)
+        s_hi = torch.stack([lin[off[k] + int(st[3 + k])] for k in range(3)]).to(self.device)
+        xyz_min = self.aabb[0] * (1 - s_lo) + self.aabb[1] * s_lo
+        xyz_max = self.aabb[0] * (1 - s_hi) + self.aabb[1] * s_hi
+        return torch.stack((xyz_min, xyz_max))
 
     @torch.no_grad()
     def filtering_rays(self, all_rays, all_rgbs, N_samples=256, chunk=10240 * 5, bbox_only=False):
-        """models/tensorBase.py:259-288."""
+        """models/tensorBase.py:259-288 on filter_rays_kernel: one launch per host chunk (one launch in all
+        when the rays already live on the device); `chunk` only bounds the staging copy."""
         n = int(torch.tensor(all_rays.shape[:-1]).prod())
         flat = all_rays.reshape(n, all_rays.shape[-1])
-        keep = []
-        for lo in range(0, n, chunk):
-            rc = flat[lo:lo + chunk].to(self.device)
-            o, d = rc[..., :3], rc[..., 3:6]
-            if bbox_only:
-                v = torch.where(d == 0, torch.full_like(d, 1e-6), d)
-                ra, rb = (self.aabb[1] - o) / v, (self.aabb[0] - o) / v
-                ok = torch.maximum(ra, rb).amin(-1) > torch.minimum(ra, rb).amax(-1)
-            else:
-                pts, _, _ = self.sample_ray(o, d, N_samples=N_samples, is_train=False)
-                ok = (self.alphaMask.sample_alpha(pts).view(pts.shape[:-1]) > 0).any(-1)
-            keep.append(ok.cpu())
-        keep = torch.cat(keep).view(all_rgbs.shape[:-1])
+        if flat.dtype != torch.float32:
+            flat = flat.float()
+        if not bbox_only and self.alphaMask is None:
+            raise AttributeError("filtering_rays(bbox_only=False) needs an alphaMask (tensorBase.py:286)")
+        field = self._fill_field(None)
+        keep = torch.empty(n, dtype=torch.uint8, device=self.device)
+        step = n if flat.is_cuda else max(int(chunk), 1 << 20)
+        for lo in range(0, n, max(step, 1)):
+            rc = flat[lo:lo + step].to(self.device).contiguous()
+            check(lib.ftrf_filter_rays(C.byref(field), rc.data_ptr(), rc.shape[1], rc.shape[0], int(N_samples),
+                                       int(bool(bbox_only)), keep.data_ptr() + lo, _stream()), "filter_rays")
+        keep = keep.bool().to(all_rays.device).view(all_rgbs.shape[:-1])
         return all_rays[keep], all_rgbs[keep]
 
 

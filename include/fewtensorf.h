@@ -19,6 +19,9 @@
  *   ftrf_pack_alpha_mask    models/tensorBase.py:30-39   (AlphaGridMask volume -> bit field)
  *   ftrf_build_coarse_mask  (none: empty-space acceleration of the alphaMask cull, same decisions)
  *   ftrf_density_at         models/tensorBase.py:298-318 compute_alpha's sigma (dense-lattice eval)
+ *   ftrf_dense_alpha_bits, ftrf_dilate_alpha_mask, ftrf_unpack_alpha_mask
+ *                           models/tensorBase.py:215-256 getDenseAlpha / updateAlphaMask
+ *   ftrf_filter_rays        models/tensorBase.py:259-288 filtering_rays
  *   ftrf_reg_factors        models/tensoRF.py:189-205 + loss.py:120-141   TV / L1 regularisers (value + gradient)
  *   ftrf_adam_step          train.py:272-273, :374-376   torch.optim.Adam over all parameter groups
  *   ftrf_generate_rays      dataLoader/ray_utils.py:24-85, dataLoader/blender.py:59   camera rays from a pose
@@ -182,6 +185,28 @@ int ftrf_build_coarse_mask(const uint32_t* bits, int32_t x, int32_t y, int32_t z
 /* sigma_out[i] = feature2density(compute_densityfeature(normalize(xyz[i]))) for n world-space points,
  * or 0 where the field's alphaMask rejects the point (tensorBase.py:298-313). */
 int ftrf_density_at(const FtrfField* field, const float* xyz, int64_t n, float* sigma_out, void* stream);
+
+/* Occupancy rebuild, all bit-packed like ftrf_pack_alpha_mask's output.
+ * ftrf_dense_alpha_bits: getDenseAlpha + compute_alpha + the threshold of updateAlphaMask
+ *   (models/tensorBase.py:215-230, :298-318, :245).  lin (device) = linspace(0,1,x), linspace(0,1,y),
+ *   linspace(0,1,z) back to back; lattice point = aabb0*(1-s) + aabb1*s; raw bit (x,y,z) =
+ *   clamp(1 - exp(-sigma*length), 0, 1) >= thres, sigma as ftrf_density_at.  alpha_out (NULL or float
+ *   [z][y][x]) additionally receives the clamped alpha lattice (getDenseAlpha's first result, transposed
+ *   as updateAlphaMask :237 does).
+ * ftrf_dilate_alpha_mask: max_pool3d(kernel 3, padding 1) + threshold assignments (:243-246) = 3^3
+ *   dilation of the raw bits.  stats (device int32[8]) receives min x,y,z / max x,y,z of the set texels
+ *   (INT_MAX / -1 when none) and their count as a 64-bit value in [6..7] (:248-257).
+ * ftrf_unpack_alpha_mask: bits -> float (Z,Y,X) volume of {0,1} (AlphaGridMask.alpha_volume, :31-39). */
+int ftrf_dense_alpha_bits(const FtrfField* field, const float* lin, int32_t x, int32_t y, int32_t z, float length,
+                          float thres, uint32_t* raw_bits, float* alpha_out, void* stream);
+int ftrf_dilate_alpha_mask(const uint32_t* raw_bits, int32_t x, int32_t y, int32_t z, uint32_t* bits, int32_t* stats,
+                           void* stream);
+int ftrf_unpack_alpha_mask(const uint32_t* bits, int32_t x, int32_t y, int32_t z, float* volume, void* stream);
+/* filtering_rays (models/tensorBase.py:259-288): keep[i] = 1 iff ray i ([n][ray_cols] floats, origin then
+ * direction) survives.  bbox_only = 0: any of the n_samples un-jittered march points of sample_ray(:189-208)
+ * reads alphaMask > 0 (:285-286; needs field->has_alpha_mask); bbox_only != 0: slab test t_max > t_min (:277-283). */
+int ftrf_filter_rays(const FtrfField* field, const float* rays, int32_t ray_cols, int64_t n, int32_t n_samples,
+                     int32_t bbox_only, uint8_t* keep, void* stream);
 
 /* Bring-up / unit-test entry of the tensor-core contraction used by the shading MLP (tcgen05.mma
  * kind::tf32, 3xTF32 split): out[M][N] = epi(A[M][K] * B^T), B element (n,k) at B[n*sn + k*sk].

@@ -455,6 +455,19 @@ def build_alpha_mask(f: Field, grid=(200, 200, 200), dmask=None) -> torch.Tensor
         return torch.stack((occ.amin(0), occ.amax(0)))
 
 
+def filter_rays(f: Field, rays, n_samples: int = 256, bbox_only: bool = False) -> torch.Tensor:
+    """Ray pre-filter — models/tensorBase.py:259-288 (filtering_rays); returns the boolean keep mask the
+    reference indexes all_rays / all_rgbs with (its chunking does not change the result)."""
+    o, d = rays[..., :3], rays[..., 3:6]
+    if bbox_only:                                                         # :277-283
+        vec = torch.where(d == 0, torch.full_like(d, 1e-6), d)
+        ra = (f.aabb[1] - o) / vec
+        rb = (f.aabb[0] - o) / vec
+        return torch.maximum(ra, rb).amin(-1) > torch.minimum(ra, rb).amax(-1)
+    pts, _, _ = march(f, o, d, None, n_samples)                           # :285 sample_ray(is_train=False)
+    return (alpha_mask_values(f.alpha_mask, pts).view(pts.shape[:-1]) > 0).any(-1)   # :286
+
+
 def freq_mask_shipped(lengths, it, total, ratio):
     """utils.py:11-36 AS SHIPPED: returns from inside the loop, i.e. ONE tensor for lengths[0]."""
     n = lengths[0]

@@ -64,3 +64,21 @@ def test_free_mask_shipped_is_scalar_one():
     assert mi["encoding"]["fea"].shape == (108,)
     assert len(mi["decomp"]["app"]) == 3 and mi["decomp"]["app"][2].shape == (48,)
     assert 0 < float(mi["encoding"]["fea"][-1]) < 1e-7
+
+
+# ------------------------------------------------------------------ occupancy rebuild + ray pre-filter
+@pytest.mark.parametrize("kind", ["vm", "cp"])
+def test_occupancy_rebuild_and_ray_filter_match_reference(kind):
+    from tests.util import OccGolden
+    g = OccGolden(kind)
+    f = g.field()
+    box1 = O.build_alpha_mask(f, (24, 20, 22))                         # no mask yet: every lattice point evaluated
+    assert torch.equal(f.alpha_mask.volume.bool(), g.t["am1_volume"])
+    assert torch.equal(box1, g.t["am1_box"])
+    assert torch.equal(O.filter_rays(f, g.rays, 48), g.t["keep1_s48"])
+    assert torch.equal(O.filter_rays(f, g.rays, 24), g.t["keep1_s24"])
+    assert torch.equal(O.filter_rays(f, g.rays, bbox_only=True), g.t["keep_bbox"])
+    box2 = O.build_alpha_mask(f, (30, 26, 21))                         # rebuild under the first mask (compute_alpha :300-304)
+    assert torch.equal(f.alpha_mask.volume.bool(), g.t["am2_volume"])
+    assert torch.equal(box2, g.t["am2_box"])
+    assert torch.equal(O.filter_rays(f, g.rays, 48), g.t["keep2_s48"])

@@ -10,7 +10,7 @@ from oracle import field_oracle as O
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-               if not os.path.basename(p).startswith(("optim_", "sched_")))   # regulariser / Adam / schedule fixtures
+               if not os.path.basename(p).startswith(("optim_", "sched_", "occ_")))   # regulariser / Adam / schedule fixtures
 
 
 class Golden:
@@ -84,6 +84,24 @@ def pseudo_grads(shapes, steps=3, seed=5):
                 g[..., ::2, :] = 0.0                        # exact zeros keep v small next to eps
             out[t][k] = g
     return out
+
+
+class OccGolden:
+    """tests/golden/occ_<kind>.npz (make_golden_occupancy.py): a reference model, the masks two successive
+    updateAlphaMask calls built, the boxes they returned and filtering_rays' keep masks."""
+
+    def __init__(self, kind):
+        d = np.load(os.path.join(GOLDEN, f"occ_{kind}.npz"))
+        self.meta = ast.literal_eval(str(d["meta"]))
+        self.t = {k: torch.from_numpy(np.asarray(d[k])) for k in d.files if k != "meta"}
+        self.params = {k[2:]: v for k, v in self.t.items() if k.startswith("p:")}
+        self.rays = self.t["rays"]
+        self.aabb = torch.tensor([[-1.5, -1.5, -1.5], [1.5, 1.5, 1.5]])
+    config = Golden.config
+
+    def field(self, mask=0) -> O.Field:
+        am = None if not mask else O.AlphaMask(self.t[f"am{mask}_volume"].float(), self.aabb.clone())
+        return O.Field(self.config(), {k: v.clone() for k, v in self.params.items()}, am)
 
 
 class OptimGolden:
