@@ -235,6 +235,28 @@ def optim_leg(model, dev, hbm_peak, iters=20):
     topt = torch.optim.Adam(clones, lr=0.0, betas=(0.9, 0.99))
     torch_ms = timed(topt.step)
     del clones, topt
+    # the occupancy rebuild (lattice alpha -> bits -> dilation -> coarse levels; includes its one
+    # host sync) under the current mask, and filtering_rays over one 800x800 frame of device-resident rays
+    occ = None
+    if model.alphaMask is not None:
+        keep_mask = model.alphaMask
+        mg = tuple(int(v) for v in keep_mask.gridSize.tolist())
+        occ_ms = timed(lambda: model.updateAlphaMask(mg))
+        same = bool(torch.equal(model.alphaMask.packed()[0], keep_mask.packed()[0]))
+        model.alphaMask = keep_mask
+        frame = camera_rays(dev)
+        tag = torch.empty(frame.shape[0], 1, device=dev)
+        kept = [0]
+
+        def filt():
+            kept[0] = model.filtering_rays(frame, tag, N_samples=256)[0].shape[0]
+        filt_ms = timed(filt)
+        pts = mg[0] * mg[1] * mg[2]
+        occ = {"update_alpha_mask_ms": round(occ_ms, 4), "lattice": list(mg), "launches": 5,
+               "lattice_points_per_s": round(pts / (occ_ms * 1e-3), 1), "idempotent": same,
+               "filtering_rays_ms": round(filt_ms, 4), "rays": int(frame.shape[0]), "rays_kept": int(kept[0]),
+               "what": "updateAlphaMask under the current mask (host sync included); filtering_rays(N_samples=256) "
+                       "over one 800x800 frame of device rays incl. the boolean compaction"}
     reg_gbs = plane_elems * 12 / (reg_abi_ms * 1e-3) / 1e9
     adam_gbs = n_params * 28 / (adam_ms * 1e-3) / 1e9
     return {"regularisers": {"ms": round(reg_abi_ms, 4), "module_api_ms": round(reg_ms, 4), "launches": 3, "algorithmic_bytes": plane_elems * 12,
@@ -243,6 +265,7 @@ def optim_leg(model, dev, hbm_peak, iters=20):
             "adam": {"ms": round(adam_ms, 4), "launches": 1, "algorithmic_bytes": n_params * 28,
                      "achieved": round(adam_gbs, 1), "unit": "GB/s", "frac": round(adam_gbs / hbm_peak, 4),
                      "torch_optim_adam_ms": round(torch_ms, 4)},
+            "occupancy": occ,
             "l2_flush": "512 MB written then read between iterations (clean lines)"}
 
 

@@ -18,6 +18,8 @@ import ctypes as C
 import math
 from typing import List, Optional
 
+import itertools
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -28,6 +30,9 @@ from ._abi import FtrfCall, FtrfField, check, lib
 
 GRAD_TAIL = 4
 MAX_CANDIDATES = 1 << 30      # rays * samples per launch sequence (int32 sample cursors); an 800x800 frame is one sequence
+
+
+_SERIAL = itertools.count(1)      # identity of replaceable host-side state in cache keys (id() values are reused)
 
 
 def _stream() -> int:
@@ -103,6 +108,7 @@ class AlphaGridMask(nn.Module):
         a = self.aabb.detach().float().cpu()
         inv = (1.0 / (a[1] - a[0]) * 2)          # same fp32 ops as :36-37
         self._host = ([x, y, z], a[0].tolist(), inv.tolist())
+        self._serial = next(_SERIAL)
 
     def packed(self):
         """(bits tensor, dims [X,Y,Z], aabb0 list, invgrid list) — built once per mask."""
@@ -263,7 +269,7 @@ class TensorBase(nn.Module):
         self.aabbDiag = diag.to(self.device)
         self.nSamples = int((diag / step).item()) + 1
         self._host = dict(aabb=a.reshape(-1).tolist(), inv=inv.tolist(), step=float(step),
-                          grid=[int(v) for v in gridSize])
+                          grid=[int(v) for v in gridSize], serial=next(_SERIAL))
 
     def init_svd_volume(self, res, device):
         pass
@@ -412,7 +418,7 @@ class TensorBase(nn.Module):
         """FtrfField for this call.  Without FreeNeRF masks the struct only depends on the parameter
         pointers, the alphaMask and the derived constants, so it is cached on exactly those."""
         if mask is None:
-            key = (tuple(p.data_ptr() for p in self._all_params()), id(self.alphaMask), id(self._host),
+            key = (tuple(p.data_ptr() for p in self._all_params()), self._mask_serial(), self._host["serial"],
                    self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr())
             cache = self.__dict__.setdefault("_field_cache", {})
             f = cache.get(key)
@@ -422,6 +428,12 @@ class TensorBase(nn.Module):
                 f = cache[key] = self._build_field(None, grad_views)
             return f
         return self._build_field(mask, grad_views)
+
+    def _mask_serial(self) -> int:
+        if self.alphaMask is None:
+            return 0
+        self.alphaMask.packed()
+        return self.alphaMask._serial
 
     def _build_field(self, mask, grad_views=None) -> FtrfField:
         self._ensure_layout()
@@ -759,7 +771,7 @@ class TensorBase(nn.Module):
                     if p.grad is None:
                         p.grad = torch.zeros_like(p, memory_format=torch.preserve_format)
             # the struct only depends on the parameter / gradient pointers: cached like _fill_field's
-            key = (which,) + tuple((p.data_ptr(), p.grad.data_ptr()) for p in params) + (id(self._host),)
+            key = (which,) + tuple((p.data_ptr(), p.grad.data_ptr()) for p in params) + (self._host["serial"],)
             cache = self.__dict__.setdefault("_reg_cache", {})
             fs = cache.get(key)
             if fs is None:

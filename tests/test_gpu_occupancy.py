@@ -82,3 +82,21 @@ def test_update_alpha_mask_empty_scene_raises_like_reference():
         import ctypes as C
         from fewtensorf_b200._abi import lib, check
         check(lib.ftrf_filter_rays(C.byref(m._fill_field(None)), None, 6, 4, 8, 1, None, None), "filter_rays")
+
+
+def test_repeated_rebuilds_never_see_a_stale_mask():
+    """The cached call descriptor is keyed on a serial number of the mask, not on id(): masks replaced in a loop
+    reuse Python object addresses, and a stale descriptor would point at a freed bit field."""
+    from tests.gpu_util import model_from_field
+    cfg = O.FieldConfig(grid=(40, 40, 40), density_n_comp=(16, 16, 16), app_n_comp=(8, 8, 8))
+    p = O.init_params(cfg, seed=5)
+    O.plant_box(cfg, p)
+    m = model_from_field(O.Field(cfg, p), "cuda")
+    m.updateAlphaMask((64, 64, 64))
+    m.updateAlphaMask((64, 64, 64))
+    want = m.alphaMask.packed()[0].clone()
+    for _ in range(8):
+        junk = torch.randint(0, 2 ** 31 - 1, (1 << 16,), dtype=torch.int32, device="cuda")     # recycle freed blocks
+        m.updateAlphaMask((64, 64, 64))
+        assert torch.equal(m.alphaMask.packed()[0], want)
+        del junk
