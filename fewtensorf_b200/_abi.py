@@ -78,7 +78,7 @@ class FtrfCamera(C.Structure):
 
 # every symbol include/fewtensorf.h declares
 EXPORTS = [
-    "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_backward", "ftrf_backward_part",
+    "ftrf_abi_version", "ftrf_last_error", "ftrf_workspace_layout", "ftrf_forward", "ftrf_forward_ex", "ftrf_backward", "ftrf_backward_part",
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
@@ -109,6 +109,8 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = C.c_int
         fn.argtypes = stage_args
+    lib.ftrf_forward_ex.restype = C.c_int
+    lib.ftrf_forward_ex.argtypes = stage_args + [C.c_void_p, C.c_void_p]
     lib.ftrf_mse_loss.restype = C.c_int
     lib.ftrf_mse_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ftrf_alpha_mask_words.restype = C.c_size_t

@@ -239,7 +239,8 @@ STAGE_FN(ftrf_stage_appearance, launch_appearance)
 STAGE_FN(ftrf_stage_shade, launch_shade)
 STAGE_FN(ftrf_stage_composite, launch_composite)
 
-extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+extern "C" int ftrf_forward_ex(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream,
+                               int32_t* counters_host, void* counters_event) {
   Ws ws;
   if (int e = check_args(f, c, wsb, ws_bytes, false, &ws)) return e;
   cudaStream_t st = (cudaStream_t)stream;
@@ -249,7 +250,13 @@ extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, si
   if (int e = launch_density(*f, *c, ws, st)) return e;
   prof_end(1, st); prof_begin(2, st);
   if (int e = launch_integrate(*f, *c, ws, st)) return e;
-  prof_end(2, st); prof_begin(3, st);
+  prof_end(2, st);
+  // the list counters and overflow flags are final here: hand them to the host now, so that its one wait
+  // of the call ends while the appearance / shading / compositing kernels are still running
+  if (counters_host && cudaMemcpyAsync(counters_host, ws.counters, 32, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+    return check_launch("counters copy");
+  if (counters_event && cudaEventRecord((cudaEvent_t)counters_event, st) != cudaSuccess) return check_launch("counters event");
+  prof_begin(3, st);
   if (int e = launch_appearance(*f, *c, ws, st)) return e;
   prof_end(3, st); prof_begin(4, st);
   if (int e = launch_shade(*f, *c, ws, st)) return e;
@@ -257,6 +264,10 @@ extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, si
   int e = launch_composite(*f, *c, ws, st);
   prof_end(5, st);
   return e;
+}
+
+extern "C" int ftrf_forward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
+  return ftrf_forward_ex(f, c, wsb, ws_bytes, stream, nullptr, nullptr);
 }
 
 // part 1: everything but the density backward (after it every gradient except the density factors' is

@@ -502,12 +502,24 @@ class TensorBase(nn.Module):
         f._keep = keep          # python-side keep-alive of mask tensors
         return f
 
-    def _read_counters(self, ws: torch.Tensor):
+    def _counter_slots(self):
+        """Pinned int32[8] the forward copies its counters into + the event recorded behind that copy."""
         if self._counters_host is None:
             self._counters_host = torch.empty(8, dtype=torch.int32).pin_memory()
-        self._counters_host.copy_(ws[:32].view(torch.int32), non_blocking=True)
-        torch.cuda.current_stream().synchronize()        # the one host sync of a forward call
-        c = self._counters_host
+            with torch.cuda.device(torch.device(self.device)):
+                self._counters_event = torch.cuda.Event()
+                self._counters_event.record()          # materialises the cudaEvent_t the C side records
+        return self._counters_host, self._counters_event
+
+    def _read_counters(self, whole_stream: bool):
+        """The one host wait of a forward call.  The counters are final after the integration stage and
+        ftrf_forward_ex copies them out right there: waiting on its event returns while appearance / shading /
+        compositing still run (stream order keeps every later use of their outputs correct)."""
+        c, ev = self._counter_slots()
+        if whole_stream:
+            torch.cuda.current_stream().synchronize()
+        else:
+            ev.synchronize()
         return int(c[0]), int(c[1]), int(c[2])
 
     def _launch_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, caps=None) -> _CallState:
@@ -537,7 +549,9 @@ class TensorBase(nn.Module):
             nbytes = lib.ftrf_workspace_layout(C.byref(field), C.byref(call), None)
             self.__dict__.setdefault("_layout_cache", {})[lkey] = nbytes
         ws = wsobj.get(nbytes, rays.device)
-        check(lib.ftrf_forward(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream()), "forward")
+        chost, cev = self._counter_slots()
+        check(lib.ftrf_forward_ex(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream(), chost.data_ptr(),
+                                  cev.cuda_event), "forward")
         st = _CallState()
         st.field, st.call, st.ws, st.ws_bytes, st.wsobj = field, call, ws, ws.numel(), wsobj
         st.keep = (rays, jitter, rgb, depth)
@@ -545,10 +559,11 @@ class TensorBase(nn.Module):
         st.n_samples = st.n_valid = -1
         return st
 
-    def _finish_forward(self, st: _CallState) -> bool:
+    def _finish_forward(self, st: _CallState, whole_stream: bool = False) -> bool:
         """The one host sync of a call: read the counters; returns False (and grows the capacity hints)
-        if a packed list overflowed and the call has to be repeated."""
-        need_s, need_a, flags = self._read_counters(st.ws)
+        if a packed list overflowed and the call has to be repeated.  whole_stream: wait for everything
+        enqueued so far (train_step, which also launched the backward) instead of the counters alone."""
+        need_s, need_a, flags = self._read_counters(whole_stream)
         N, S = st.call.n_rays, st.call.n_samples
         key = (N, S, bool(st.call.save_for_backward))
         cap_s, cap_a = st.call.cap_samples, st.call.cap_app
@@ -681,7 +696,7 @@ class TensorBase(nn.Module):
                 g_rgb.mul_(grad_scale)
             if not reduce_on:
                 self._run_backward(st, g_rgb, views)
-                if self._finish_forward(st):
+                if self._finish_forward(st, whole_stream=True):
                     break
                 continue
             # this rank's overflow flag (final after the forward) rides in the tail slot
@@ -694,7 +709,7 @@ class TensorBase(nn.Module):
             for w in works:
                 w.wait()                      # stream-level: the current stream waits for the collectives
             flag = self._tail_flag(buf)       # async copy; _finish_forward's sync completes it
-            ok = self._finish_forward(st)
+            ok = self._finish_forward(st, whole_stream=True)
             if float(flag[0]) == 0.0 and ok:
                 break
         self._grad_gen = self.__dict__.get("_grad_gen", 0) + 1     # invalidates a pending autograd call's pre-zero

@@ -155,6 +155,14 @@ const char* ftrf_last_error(void);          /* host string, thread-local */
 size_t ftrf_workspace_layout(const FtrfField* field, const FtrfCall* call, int64_t* offsets_out);
 
 int ftrf_forward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
+/* ftrf_forward that also hands the call's counters to the host as soon as they are final (after the
+ * integration stage; the appearance / shading / compositing kernels follow on the stream): counters_host
+ * (pinned int32[8], may be NULL) receives {valid samples needed, shaded samples needed, overflow flags, ...} by
+ * an async copy and counters_event (a cudaEvent_t, may be NULL) is recorded behind it.  The Python wrapper
+ * waits on that event instead of the stream: the float the reference's renderer returns (renderer.py:24) no
+ * longer costs the tail of the forward. */
+int ftrf_forward_ex(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream,
+                    int32_t* counters_host, void* counters_event);
 int ftrf_backward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
 /* The same work in two halves, for callers that overlap a gradient all-reduce with it (dist.py):
  * part 1 = everything but the density backward (all gradients except the density factors' are final after
