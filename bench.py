@@ -269,6 +269,61 @@ def optim_leg(model, dev, hbm_peak, iters=20):
             "l2_flush": "512 MB written then read between iterations (clean lines)"}
 
 
+def other_configs_leg(dev, iters=20):
+    """BASELINE.json configs 3 and 4 on the same kernels (not bench lines of their own: reported so that every
+    named configuration has a measured number).  Same timing rules: CUDA events, L2 flushed between steps.
+      cp_96_288     TensorCP, n_lamb 96 / 288, 300^3, MLP_Fea, 4096 rays x S=1039
+      fewshot_free  configs/free_tensorf_human.txt: TensorVMSplit 32/48, shadingMode MLP, pos_pe 8, 1024-ray batch,
+                    FreeNeRF encoding + decomposition masks (vector form) at 30 % of the schedule"""
+    import fewtensorf_b200 as ft
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    aabb = torch.tensor([[-1.5] * 3, [1.5] * 3], device=dev)
+    ind = (torch.linspace(-1.5, 1.5, GRID).abs() < 0.6).float().to(dev)
+    out = {}
+
+    def run(name, model, n_rays, mask):
+        model.updateAlphaMask((MASK_GRID,) * 3)
+        rays_h, target_h = synthetic_rays(n_rays, seed=0)
+        rays, target = rays_h.to(dev), target_h.to(dev)
+        torch.manual_seed(1)
+        for _ in range(3):
+            model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+        ms = 0.0
+        for _ in range(iters):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            loss, nv = model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+            b.record()
+            b.synchronize()
+            ms += a.elapsed_time(b)
+        ms /= iters
+        st = model._last_call
+        out[name] = {"ms_per_step": round(ms, 4), "rays_per_s": round(n_rays / (ms * 1e-3), 1), "rays": n_rays,
+                     "valid_per_step": int(st.n_samples), "shaded_per_step": int(st.n_valid), "loss": float(loss)}
+
+    torch.manual_seed(20211202)
+    cp = ft.TensorCP(dict(ARGS, density_n_comp=[96, 96, 96], app_n_comp=[288, 288, 288]), aabb, [GRID] * 3, dev,
+                     near_far=[2.0, 6.0])
+    with torch.no_grad():                             # planted box, CP form (SURVEY section 8d)
+        cp.density_line[0][0, 0, :, 0] = 11.0 * ind
+        cp.density_line[1][0, 0, :, 0] = ind
+        cp.density_line[2][0, 0, :, 0] = ind
+    run("cp_96_288", cp, RAYS_PER_GPU, None)
+    del cp
+    torch.manual_seed(20211202)
+    few_args = dict(ARGS, density_n_comp=[32, 32, 32], app_n_comp=[48, 48, 48], shadingMode='MLP', pos_pe=8)
+    vm = ft.TensorVMSplit(few_args, aabb, [GRID] * 3, [2.0, 6.0], dev)
+    with torch.no_grad():
+        vm.density_plane[0][0, 0] = 11.0 * ind[:, None] * ind[None, :]
+        vm.density_line[0][0, 0, :, 0] = ind
+    from fewtensorf_b200.schedule import get_free_mask
+    mask = get_free_mask(pos_bl=[2 * 8 * 3], view_bl=[2 * 2 * 3], fea_bl=[2 * 2 * 27], den_bl=[32] * 3, app_bl=[48] * 3,
+                            step=900, total_step=3000, ratio=0.65, device=dev, intended=True)
+    run("fewshot_free", vm, 1024, mask)
+    return out
+
+
 def cpu_field(model=None):
     """Oracle field (CPU restatement of the reference path) holding the benchmark workload.
     With a product model: the very same parameters and alphaMask.  Without (--impl reference):
@@ -503,6 +558,7 @@ def run_gpu(args):
 
     render = None if args.no_render else render_leg(dev)
     extras = optim_leg(model, dev, load_peaks()["hbm"]) if (rank == 0 and not args.no_render) else None
+    others = other_configs_leg(dev) if (world == 1 and not args.no_render) else None
 
     if rank != 0:
         if world > 1:
@@ -549,6 +605,8 @@ def run_gpu(args):
                          "sh": render["SH"], "mlp_fea": render["MLP_Fea"]}
     if extras:
         out["iteration_extras"] = extras
+    if others:
+        out["other_configs"] = others
     if cpu:
         out["cpu_baseline"] = cpu
     print(json.dumps(out))

@@ -15,6 +15,7 @@ struct Gemm3xArgs {
   int relu;                              // out = max(acc, 0)
   float* out; int ldo;
   int variant;                           // debug: bit0 swaps the LBO/SBO roles
+  int accumulate;                        // acc += out[m][n] before bias / ReLU / mask (second half of a K-split layer)
 };
 
 // dW[o][k] += sum_s G[s][o] * A[s][k]   (o < 128, k < K);  dbias[o] += sum_s G[s][o] if dbias

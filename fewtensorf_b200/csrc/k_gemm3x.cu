@@ -122,15 +122,16 @@ gemm3x_kernel(const Gemm3xArgs a) {
             } else
               for (int e = 0; e < 4 && col + e < a.N; ++e) mk[e] = __ldg(a.mask + row * a.ldm + col + e);
           }
+          float* dst = a.out + row * a.ldo + col;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             float x = acc[j + e];
+            if (a.accumulate && col + e < a.N) x += dst[e];
             x += s_bias[col + e];
             if (a.relu) x = fmaxf(x, 0.f);
             if (!(mk[e] > 0.f)) x = 0.f;
             o[e] = x;
           }
-          float* dst = a.out + row * a.ldo + col;
           if (col + 3 < a.N && (a.ldo & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
           else
             for (int e = 0; e < 4 && col + e < a.N; ++e) dst[e] = o[e];

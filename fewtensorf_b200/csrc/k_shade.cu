@@ -155,11 +155,16 @@ size_t shade_fwd_smem(const InSpec& sp) {
   return fl * sizeof(float);
 }
 
-int shade_check(const FtrfField& f, const InSpec& sp) {
+// cuda_core: the fp32 CUDA-core kernels keep W1 and W2 whole in shared memory, which bounds the input width;
+// the tcgen05 back ends split a wide first layer instead (k_shade_tc.cu).
+int shade_check(const FtrfField& f, const InSpec& sp, bool cuda_core) {
   if (f.feature_c != FC) { set_error("shade: featureC must be %d (got %d)", FC, f.feature_c); return FTRF_E_ARG; }
   if (sp.in_dim != f.in_dim) { set_error("shade: in_dim %d does not match the shading mode (%d)", f.in_dim, sp.in_dim); return FTRF_E_ARG; }
   if (sp.D + 6 > HS) { set_error("shade: unsupported input width %d", sp.in_dim); return FTRF_E_ARG; }
-  if (shade_fwd_smem(sp) > 227 * 1024) { set_error("shade: input width %d needs too much shared memory", sp.in_dim); return FTRF_E_ARG; }
+  if (cuda_core && shade_fwd_smem(sp) > 227 * 1024) {
+    set_error("shade: input width %d needs too much shared memory on the CUDA-core back end (use the tensor-core one)", sp.in_dim);
+    return FTRF_E_ARG;
+  }
   return FTRF_OK;
 }
 
@@ -171,7 +176,7 @@ int launch_shade_sh(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStr
 
 int launch_shade_v1(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp)) return e;
+  if (int e = shade_check(f, sp, true)) return e;
   size_t smem = shade_fwd_smem(sp);
   cudaFuncSetAttribute(shade_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   shade_mlp_fwd_kernel<<<FTRF_SMS, 256, smem, st>>>(f, c, ws, sp);

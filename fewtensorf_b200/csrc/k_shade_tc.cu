@@ -239,7 +239,7 @@ pe_bwd_internal_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const I
 }
 
 // ---------------------------------------------------------------------------------------- drivers
-int shade_check(const FtrfField& f, const InSpec& sp);
+int shade_check(const FtrfField& f, const InSpec& sp, bool cuda_core);
 int launch_shade_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_bwd_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_sh(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
@@ -254,11 +254,50 @@ static Gemm3xArgs gemm_args(const Ws& ws, const FtrfCall& c) {
   return g;
 }
 
+size_t gemm3x_smem(int N, int K);
+constexpr size_t SMEM_MAX = 227 * 1024;
+
+// A layer whose resident weight operand does not fit shared memory (first layer of a wide input: MLP shading
+// with pos_pe 8 is 198 columns, configs/free_tensorf_human.txt) runs as two launches.
+//   split along K (forward): the second launch adds the first one's partial sums in its epilogue
+static int launch_gemm3x_ksplit(Gemm3xArgs g, cudaStream_t st) {
+  if (gemm3x_smem(g.N, g.K) <= SMEM_MAX) return launch_gemm3x(g, st);
+  const int k1 = ((g.K / 2) + 31) & ~31;             // whole A chunks in the first half
+  Gemm3xArgs a = g, b = g;
+  a.K = k1; a.ka = k1; a.bias = nullptr; a.relu = 0; a.mask = nullptr;
+  if (int e = launch_gemm3x(a, st)) return e;
+  b.A = g.A + k1; b.ka = g.ka - k1; b.B = g.B + (int64_t)k1 * g.sk; b.K = g.K - k1; b.accumulate = 1;
+  return launch_gemm3x(b, st);
+}
+//   split along N (dgrad into the input columns): two independent column ranges of the output
+static int launch_gemm3x_nsplit(Gemm3xArgs g, cudaStream_t st) {
+  if (gemm3x_smem(g.N, g.K) <= SMEM_MAX) return launch_gemm3x(g, st);
+  const int n1 = ((g.N / 2) + 15) & ~15;
+  Gemm3xArgs a = g, b = g;
+  a.N = n1;
+  if (int e = launch_gemm3x(a, st)) return e;
+  b.B = g.B + (int64_t)n1 * g.sn; b.N = g.N - n1; b.out = g.out + n1;
+  if (g.bias) b.bias = g.bias + n1;
+  if (g.mask) b.mask = g.mask + n1;
+  return launch_gemm3x(b, st);
+}
+//   weight gradient of a wide layer: two column ranges of dW (the bias gradient rides with the first)
+static int launch_wgrad3x_split(Wgrad3xArgs w, cudaStream_t st) {
+  if (g_np(w.K + (w.dbias ? 1 : 0)) <= 192) return launch_wgrad3x(w, st);
+  const int k1 = ((w.K / 2) + 15) & ~15;
+  Wgrad3xArgs a = w, b = w;
+  a.K = k1;
+  if (w.use_perm) return launch_wgrad3x(w, st);      // (the permuted internal layout never gets this wide)
+  if (int e = launch_wgrad3x(a, st)) return e;
+  b.A = w.A + k1; b.K = w.K - k1; b.dW = w.dW + k1; b.dbias = nullptr;
+  return launch_wgrad3x(b, st);
+}
+
 int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (f.shading == FTRF_SHADE_SH) return launch_shade_sh(f, c, ws, st);
   if (!g_shade_path) return launch_shade_v1(f, c, ws, st);
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp)) return e;
+  if (int e = shade_check(f, sp, false)) return e;
   if (c.cap_app == 0) return FTRF_OK;
   if (g_shade_path == 2) {
     bool handled = false;
@@ -271,7 +310,7 @@ int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream
   Gemm3xArgs g = gemm_args(ws, c);
   g.A = ws.a_x; g.lda = ws.ldx; g.ka = ws.ldx; g.B = f.w1; g.sn = sp.in_dim; g.sk = 1; g.N = FC; g.K = sp.in_dim;
   g.bias = f.b1; g.relu = 1; g.out = ws.a_h1; g.ldo = FC;
-  if (int e = launch_gemm3x(g, st)) return e;
+  if (int e = launch_gemm3x_ksplit(g, st)) return e;
   g.A = ws.a_h1; g.lda = FC; g.ka = FC; g.B = f.w2; g.sn = FC; g.sk = 1; g.N = FC; g.K = FC;
   g.bias = f.b2; g.out = ws.a_h2;
   if (int e = launch_gemm3x(g, st)) return e;
@@ -286,7 +325,7 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   if (f.shading == FTRF_SHADE_SH) return part == 2 ? FTRF_OK : launch_shade_sh_bwd(f, c, ws, st);
   if (!g_shade_path) return part == 2 ? FTRF_OK : launch_shade_bwd_v1(f, c, ws, st);
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp)) return e;
+  if (int e = shade_check(f, sp, false)) return e;
   if (c.cap_app == 0) return FTRF_OK;
   FusedSpec fs;
   const bool internal = g_shade_path == 2 && make_fused_spec(f, sp, fs) && fs.kp <= ws.ldx && ws.wimg;   // X saved by the fused forward
@@ -322,7 +361,7 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     g.A = ws.a_gh1; g.lda = FC; g.ka = FC; g.B = f.w1; g.sn = 1; g.sk = sp.in_dim; g.N = sp.in_dim; g.K = FC;
     if (internal) { g.B = w1p; g.sk = fs.kp; g.N = fs.kp; }
     g.out = ws.a_gx; g.ldo = ws.ldx;
-    if (int e = launch_gemm3x(g, st)) return e;
+    if (int e = launch_gemm3x_nsplit(g, st)) return e;
     if (internal) pe_bwd_internal_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp, fs.blk_icol0[0], fs.blk_icol0[1], fs.blk_icol0[2]);
     else pe_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws, sp);
     if (int e = check_launch("pe_bwd")) return e;
@@ -340,7 +379,7 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     w.K = fs.kp; w.use_perm = 1;
     for (int k = 0; k < fs.kp; ++k) w.perm[k] = fs.orig[k];
   }
-  int e = launch_wgrad3x(w, st);
+  int e = launch_wgrad3x_split(w, st);
   prof_end(10, st);
   return e;
 }
