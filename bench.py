@@ -299,7 +299,21 @@ def other_configs_leg(dev, iters=20):
             ms += a.elapsed_time(b)
         ms /= iters
         st = model._last_call
-        out[name] = {"ms_per_step": round(ms, 4), "rays_per_s": round(n_rays / (ms * 1e-3), 1), "rays": n_rays,
+        import ctypes as C
+        from fewtensorf_b200._abi import lib, PROF_STAGES
+        lib.ftrf_profile_enable(1)
+        buf = (C.c_float * PROF_STAGES)()
+        stage = [0.0] * PROF_STAGES
+        for _ in range(5):
+            flush.zero_()
+            model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+            torch.cuda.synchronize()
+            lib.ftrf_profile_read(buf)
+            for i in range(PROF_STAGES):
+                stage[i] += max(buf[i], 0.0) / 5
+        lib.ftrf_profile_enable(0)
+        stages_us = {lib.ftrf_profile_stage_name(i).decode(): round(stage[i] * 1e3, 1) for i in range(PROF_STAGES)}
+        out[name] = {"stages_us": stages_us, "ms_per_step": round(ms, 4), "rays_per_s": round(n_rays / (ms * 1e-3), 1), "rays": n_rays,
                      "valid_per_step": int(st.n_samples), "shaded_per_step": int(st.n_valid), "loss": float(loss)}
 
     torch.manual_seed(20211202)
