@@ -82,7 +82,7 @@ EXPORTS = [
     "ftrf_stage_march", "ftrf_stage_density", "ftrf_stage_integrate", "ftrf_stage_appearance",
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
-    "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_profile_enable", "ftrf_profile_read",
+    "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_event_record", "ftrf_stream_wait_event", "ftrf_zero_after", "ftrf_profile_enable", "ftrf_profile_read",
     "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
 ]
 PROF_STAGES = 13
@@ -134,6 +134,12 @@ def _load():
     lib.ftrf_filter_rays.restype = C.c_int
     lib.ftrf_filter_rays.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                      C.c_void_p, C.c_void_p]
+    lib.ftrf_event_record.restype = C.c_int
+    lib.ftrf_event_record.argtypes = [C.c_void_p, C.c_void_p]
+    lib.ftrf_stream_wait_event.restype = C.c_int
+    lib.ftrf_stream_wait_event.argtypes = [C.c_void_p, C.c_void_p]
+    lib.ftrf_zero_after.restype = C.c_int
+    lib.ftrf_zero_after.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.ftrf_profile_enable.restype = C.c_int
     lib.ftrf_profile_enable.argtypes = [C.c_int]
     lib.ftrf_profile_read.restype = C.c_int

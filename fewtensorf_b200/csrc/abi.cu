@@ -310,6 +310,27 @@ extern "C" int ftrf_mse_loss(const float* rgb, const float* target, int64_t n, f
   return check_launch("mse_loss");
 }
 
+// Stream plumbing of the gradient-buffer memset (runs beside the forward on a side stream): thin wrappers so the
+// Python wrapper pays ~1 us per call instead of torch's stream context manager.
+extern "C" int ftrf_event_record(void* event, void* stream) {
+  if (!event) { set_error("event_record: null event"); return FTRF_E_ARG; }
+  if (cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream) != cudaSuccess) return check_launch("event_record");
+  return FTRF_OK;
+}
+extern "C" int ftrf_stream_wait_event(void* stream, void* event) {
+  if (!event) { set_error("stream_wait_event: null event"); return FTRF_E_ARG; }
+  if (cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0) != cudaSuccess) return check_launch("stream_wait_event");
+  return FTRF_OK;
+}
+extern "C" int ftrf_zero_after(void* ptr, size_t bytes, void* side_stream, void* wait_event, void* done_event) {
+  if (!ptr || !wait_event || !done_event) { set_error("zero_after: null argument"); return FTRF_E_ARG; }
+  cudaStream_t ss = (cudaStream_t)side_stream;
+  if (cudaStreamWaitEvent(ss, (cudaEvent_t)wait_event, 0) != cudaSuccess) return check_launch("zero_after wait");
+  if (cudaMemsetAsync(ptr, 0, bytes, ss) != cudaSuccess) return check_launch("zero_after memset");
+  if (cudaEventRecord((cudaEvent_t)done_event, ss) != cudaSuccess) return check_launch("zero_after record");
+  return FTRF_OK;
+}
+
 extern "C" int ftrf_density_at(const FtrfField* f, const float* xyz, int64_t n, float* sigma_out, void* stream) {
   if (!f || !xyz || !sigma_out || n < 0) { set_error("density_at: bad argument"); return FTRF_E_ARG; }
   if (int e = check_factor_set(f->den, f->model, "density", false)) return e;

@@ -35,6 +35,10 @@ MAX_CANDIDATES = 1 << 30      # rays * samples per launch sequence (int32 sample
 _SERIAL = itertools.count(1)      # identity of replaceable host-side state in cache keys (id() values are reused)
 
 
+def rays_device(st) -> torch.device:
+    return st.keep[0].device
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -189,7 +193,7 @@ class _Workspace:
 
 class _CallState:
     """Everything backward needs from one forward call."""
-    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen")
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen", "zeroing")
 
 
 class TensorBase(nn.Module):
@@ -371,6 +375,34 @@ class TensorBase(nn.Module):
             self._grad_cache = (key, buf, views)
             self._field_cache = {}
         return buf, views
+
+    def _zero_plumbing(self, device):
+        """(side stream handle, fork event handle, done event handle) of the gradient-buffer memset."""
+        z = self.__dict__.get("_zero_objs")
+        if z is None:
+            with torch.cuda.device(device):
+                side = torch.cuda.Stream(device=device)
+                fork, done = torch.cuda.Event(), torch.cuda.Event()
+                fork.record()
+                done.record()                          # materialise both cudaEvent_t handles
+            z = self.__dict__["_zero_objs"] = (side, fork, done, side.cuda_stream, fork.cuda_event, done.cuda_event)
+        return z
+
+    def _zero_fork(self, device) -> None:
+        """Mark the point on the current stream after which the gradient buffer may be zeroed."""
+        z = self._zero_plumbing(device)
+        check(lib.ftrf_event_record(z[4], _stream()), "event_record")
+
+    def _zero_grad_buffer_async(self, buf: torch.Tensor) -> None:
+        """Zero the flat gradient buffer on a side stream, ordered after the last `_zero_fork`: the 71 MB memset
+        runs beside the forward kernels (issue- and latency-bound) instead of in front of them.  The backward's
+        stream joins with `_zero_join`."""
+        z = self._zero_plumbing(buf.device)
+        check(lib.ftrf_zero_after(buf.data_ptr(), buf.numel() * buf.element_size(), z[3], z[4], z[5]), "zero_after")
+
+    def _zero_join(self, device) -> None:
+        z = self._zero_plumbing(device)
+        check(lib.ftrf_stream_wait_event(_stream(), z[5]), "stream_wait_event")
 
     def set_grad_storage(self, storage: Optional[torch.Tensor]) -> None:
         """Put the flat gradient buffer into caller-provided fp32 device memory (dist.SymmetricGradients passes
@@ -687,13 +719,15 @@ class TensorBase(nn.Module):
         while True:
             # everything is enqueued back to back (the kernels read the sample counts from device memory);
             # the single host sync comes at the end and only decides whether a list overflowed
-            buf.zero_()
+            self._zero_fork(buf.device)
+            self._zero_grad_buffer_async(buf)
             st = self._launch_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
             rgb = st.keep[2]
             check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
                                     _stream()), "mse_loss")
             if grad_scale != 1.0:
                 g_rgb.mul_(grad_scale)
+            self._zero_join(buf.device)
             if not reduce_on:
                 self._run_backward(st, g_rgb, views)
                 if self._finish_forward(st, whole_stream=True):
@@ -985,10 +1019,12 @@ class _RenderFn(torch.autograd.Function):
             if aliased:
                 return
             buf, views = model.grad_buffer()
-            buf.zero_()
+            model._zero_grad_buffer_async(buf)
+            st.zeroing = True
             st.bfield = model._fill_field(mask, views)
             st.pre_gen = model.__dict__.get("_grad_gen", 0)
 
+        model._zero_fork(rays.device)       # the memset may start here, beside the forward kernels
         st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True, before_sync=prepare_backward)
         st.wsobj.busy = True
         ctx.model, ctx.st = model, st
@@ -1020,6 +1056,8 @@ class _RenderFn(torch.autograd.Function):
         buf, views = model.grad_buffer(fresh=aliased)
         gen = model.__dict__.get("_grad_gen", 0)
         prepared = (not aliased) and getattr(st, "pre_gen", -1) == gen and buf is model._gradbuf
+        if getattr(st, "zeroing", False):        # the side-stream memset of this call's forward, used or not
+            model._zero_join(buf.device if buf is not None else rays_device(st))
         if not aliased and not prepared:
             buf.zero_()
         model._run_backward(st, g_rgb, views, prepared=prepared)

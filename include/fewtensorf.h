@@ -25,6 +25,7 @@
  *   ftrf_reg_factors        models/tensoRF.py:189-205 + loss.py:120-141   TV / L1 regularisers (value + gradient)
  *   ftrf_adam_step          train.py:272-273, :374-376   torch.optim.Adam over all parameter groups
  *   ftrf_generate_rays      dataLoader/ray_utils.py:24-85, dataLoader/blender.py:59   camera rays from a pose
+ *   ftrf_zero_after (+ ftrf_event_record, ftrf_stream_wait_event)   train.py:374 optimizer.zero_grad()
  *
  * Factor layout: CHANNEL-LAST.  A VM plane the reference holds as (1,C,H,W) is read as [H][W][C]
  * (torch.channels_last memory of the same Parameter), a line (1,C,L,1) as [L][C].  C % 4 == 0.
@@ -282,6 +283,13 @@ typedef struct FtrfCamera {
 } FtrfCamera;
 int ftrf_generate_rays(const FtrfCamera* cam /* host */, int32_t row0, int32_t row_step, int32_t n_rows,
                        float* rays_out, void* stream);
+/* Side-stream zeroing of the flat gradient buffer (new; the reference's optimizer.zero_grad(), train.py:374, is a
+ * per-tensor loop).  ftrf_event_record marks the fork point on the caller's stream; ftrf_zero_after makes
+ * side_stream wait for it, memsets `bytes` at ptr there and records done_event; ftrf_stream_wait_event joins
+ * (the backward's stream waits for done_event).  The memset thus runs beside the forward kernels. */
+int ftrf_event_record(void* event, void* stream);
+int ftrf_stream_wait_event(void* stream, void* event);
+int ftrf_zero_after(void* ptr, size_t bytes, void* side_stream, void* wait_event, void* done_event);
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py's gpu_launches). */
 unsigned long long ftrf_launch_count(void);
 
