@@ -39,8 +39,7 @@ def rays_device(st) -> torch.device:
     return st.keep[0].device
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+_stream = _abi.current_stream_handle
 
 
 def _channels_last_param(t: torch.Tensor, device) -> nn.Parameter:
@@ -193,7 +192,7 @@ class _Workspace:
 
 class _CallState:
     """Everything backward needs from one forward call."""
-    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen", "zeroing")
+    __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen", "zeroing", "gradbuf")
 
 
 class TensorBase(nn.Module):
@@ -345,10 +344,12 @@ class TensorBase(nn.Module):
         `_all_params()` order; factor views are channels-last like the parameters.  The persistent
         buffer and its views are cached until the parameter set changes (upsample / shrink)."""
         params = self._all_params()
-        key = tuple((id(p), tuple(p.shape)) for p in params)
         cache = getattr(self, "_grad_cache", None)
-        if not fresh and cache is not None and cache[0] == key and cache[1].device == params[0].device:
+        if not fresh and cache is not None and len(cache[0][0]) == len(params) \
+                and all(a is b for a, b in zip(cache[0][0], params)) and cache[0][1] == [p.shape for p in params] \
+                and cache[1].device == params[0].device:
             return cache[1], cache[2]
+        key = (list(params), [p.shape for p in params])
         total = sum(p.numel() for p in params)
         # + GRAD_TAIL floats after the last parameter: slot 0 carries this rank's list-overflow flag through
         # the all-reduce of an overlapped multi-GPU step (train_step(allreduce=True))
@@ -581,9 +582,12 @@ class TensorBase(nn.Module):
             nbytes = lib.ftrf_workspace_layout(C.byref(field), C.byref(call), None)
             self.__dict__.setdefault("_layout_cache", {})[lkey] = nbytes
         ws = wsobj.get(nbytes, rays.device)
-        chost, cev = self._counter_slots()
-        check(lib.ftrf_forward_ex(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream(), chost.data_ptr(),
-                                  cev.cuda_event), "forward")
+        cptr = self.__dict__.get("_counter_ptrs")
+        if cptr is None:
+            chost, cev = self._counter_slots()
+            cptr = self.__dict__["_counter_ptrs"] = (chost.data_ptr(), cev.cuda_event)
+        check(lib.ftrf_forward_ex(C.byref(field), C.byref(call), ws.data_ptr(), ws.numel(), _stream(), cptr[0], cptr[1]),
+              "forward")
         st = _CallState()
         st.field, st.call, st.ws, st.ws_bytes, st.wsobj = field, call, ws, ws.numel(), wsobj
         st.keep = (rays, jitter, rgb, depth)
@@ -656,7 +660,14 @@ class TensorBase(nn.Module):
                 z = z + torch.rand_like(z) * ((far - near) / S)
             jitter = z.reshape(-1)
         elif is_train:
-            jitter = torch.rand(n_rays, 1).reshape(-1)
+            # tensorBase.py:201 draws torch.rand(n_rays, 1): the same n_rays values of the CPU generator, written
+            # straight into the pinned staging buffer
+            pin = getattr(self, "_jitter_pin", None)
+            if pin is None or pin.numel() < n_rays:
+                pin = self._jitter_pin = torch.empty(max(n_rays, 1 << 16), dtype=torch.float32).pin_memory()
+            torch.rand(n_rays, out=pin[:n_rays])
+            add_bg = bool(white_bg or bool(torch.rand((1,)) < 0.5))
+            return pin[:n_rays].to(device, non_blocking=True), add_bg
         add_bg = bool(white_bg or (is_train and bool(torch.rand((1,)) < 0.5)))
         if jitter is not None:
             # staged through a persistent pinned buffer; every call ends with a stream sync before the
@@ -1018,7 +1029,7 @@ class _RenderFn(torch.autograd.Function):
                 for p in params)
             if aliased:
                 return
-            buf, views = model.grad_buffer()
+            buf, views = st.gradbuf = model.grad_buffer()
             model._zero_grad_buffer_async(buf)
             st.zeroing = True
             st.bfield = model._fill_field(mask, views)
@@ -1053,8 +1064,13 @@ class _RenderFn(torch.autograd.Function):
         aliased = others or (buf is not None and any(
             p.grad is not None and p.grad.untyped_storage().data_ptr() == buf.untyped_storage().data_ptr()
             for p in params))
-        buf, views = model.grad_buffer(fresh=aliased)
         gen = model.__dict__.get("_grad_gen", 0)
+        pre = getattr(st, "gradbuf", None)
+        if (not aliased) and pre is not None and getattr(st, "pre_gen", -1) == gen and pre[0] is model._gradbuf \
+                and all(a is b for a, b in zip(model._grad_cache[0][0], params)):
+            buf, views = pre                     # fetched (and zeroed) while the forward ran; parameters unchanged
+        else:
+            buf, views = model.grad_buffer(fresh=aliased)
         prepared = (not aliased) and getattr(st, "pre_gen", -1) == gen and buf is model._gradbuf
         if getattr(st, "zeroing", False):        # the side-stream memset of this call's forward, used or not
             model._zero_join(buf.device if buf is not None else rays_device(st))

@@ -16,8 +16,7 @@ import torch.nn as nn
 from ._abi import FtrfAdamSegment, check, lib
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+from ._abi import current_stream_handle as _stream  # noqa: E402
 
 
 class TVLoss(nn.Module):

@@ -15,8 +15,7 @@ import torch
 from ._abi import FtrfCamera, check, lib
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+from ._abi import current_stream_handle as _stream  # noqa: E402
 
 
 def generate_rays(H: int, W: int, focal, c2w, center=None, normalize: bool = True, blender: bool = False,

@@ -77,3 +77,43 @@ def test_stale_prepared_backward_is_detected(small):
     _zero(model)
     la.backward()
     _close(_grads(model), g1)
+
+
+def test_rng_draws_follow_the_reference_order_and_values():
+    """SURVEY 0.8 / tensorBase.py:201, :380 and :183: per-ray jitter first, then the background coin, from the CPU
+    generator — a seeded run samples exactly the reference's points (the jitter is drawn straight into the pinned
+    staging buffer; that must not change the values)."""
+    from tests.util import Golden
+    g = Golden("vm_fea_train_mask")
+    from tests.gpu_util import model_from_field
+    m = model_from_field(g.field(), "cuda")
+    for n in (1, 96, 5000):
+        torch.manual_seed(123)
+        want_j = torch.rand(n, 1).reshape(-1)
+        want_coin = bool(torch.rand((1,)) < 0.5)
+        after = torch.rand(3)
+        torch.manual_seed(123)
+        j, add_bg = m._draw_rng(n, 70, True, False, False, torch.device("cuda"))
+        assert torch.equal(j.cpu(), want_j) and add_bg == want_coin
+        assert torch.equal(torch.rand(3), after)            # the generator is left where the reference leaves it
+        torch.manual_seed(123)
+        j, add_bg = m._draw_rng(n, 70, True, False, True, torch.device("cuda"))   # white_bg: no coin is drawn
+        assert torch.equal(j.cpu(), want_j) and add_bg is True
+        nxt = torch.rand(1)
+        assert torch.equal(nxt, _nth_rand(123, n))          # exactly n values consumed
+    near, far = m.near_far
+    torch.manual_seed(7)
+    z = torch.linspace(near, far, 70).unsqueeze(0)
+    want = (z + torch.rand_like(z) * ((far - near) / 70)).reshape(-1)
+    torch.manual_seed(7)
+    j, _ = m._draw_rng(5, 70, True, True, True, torch.device("cuda"))
+    assert torch.equal(j.cpu(), want)
+    j, add_bg = m._draw_rng(5, 70, False, False, False, torch.device("cuda"))
+    assert j is None and add_bg is False
+
+
+def _nth_rand(seed, skip):
+    """First value the CPU generator yields after `skip` uniform draws."""
+    torch.manual_seed(seed)
+    torch.rand(skip)
+    return torch.rand(1)
