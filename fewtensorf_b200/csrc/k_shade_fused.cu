@@ -780,6 +780,61 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
 size_t fused_bwd_wimg_floats() { return (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)8 * BZ_W1_SUB_FLOATS; }
 
 // g_h2 (from layer3_bwd) -> g_h1 (saved) and g_feat.  *handled = false: configuration not covered.
+// Which fused dgrad build covers this field (-1: none, the per-layer GEMMs run instead).
+static int dgrad_variant(const FtrfField& f, const FusedSpec& fs) {
+  using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
+  using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
+  const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
+  if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) return 0;
+  if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) return 1;
+  return -1;                                     // (MLP: kp = 168 > 160 rows of the W1^T chunk; generic path)
+}
+
+// The weight images only depend on the parameters, not on anything the step computes, so ftrf_forward_ex builds
+// them on a side stream at the very start of the call (beside march / density) instead of in front of the fused
+// forward and dgrad kernels, where the two ~7 us latency-bound launches sat on the step's serial chain.
+// Thread-local: entry points stay re-entrant; the hints are keyed by the image address inside the workspace.
+struct PrepAhead {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, done = nullptr;
+  const float* img_fwd = nullptr;      // forward image built ahead, join pending
+  const float* img_bwd = nullptr;      // backward image built ahead by the same call
+};
+static thread_local PrepAhead g_prep;
+
+int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  g_prep.img_fwd = g_prep.img_bwd = nullptr;
+  if (f.shading == FTRF_SHADE_SH || c.cap_app == 0 || !ws.wimg) return FTRF_OK;
+  InSpec sp = make_spec(f);
+  FusedSpec fs;
+  if (sp.in_dim != f.in_dim || !make_fused_spec(f, sp, fs) || fs.kp > ws.ldx) return FTRF_OK;
+  if (!g_prep.side) {
+    if (cudaStreamCreateWithFlags(&g_prep.side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&g_prep.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&g_prep.done, cudaEventDisableTiming) != cudaSuccess) {
+      g_prep.side = nullptr;
+      cudaGetLastError();
+      return FTRF_OK;                            // no side stream: the launchers build the images in line
+    }
+  }
+  // after everything already on the caller's stream (the previous call's kernels still read the images)
+  if (cudaEventRecord(g_prep.fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_prep.fork, 0) != cudaSuccess)
+    return check_launch("prep_ahead fork");
+  float* img = ws.wimg;
+  float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
+  prep_weights_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, img, w1p, sp.in_dim);
+  if (int e = check_launch("prep_weights")) return e;
+  g_prep.img_fwd = img;
+  if (c.save_for_backward && dgrad_variant(f, fs) >= 0) {
+    float* bimg = ws.wimg + fused_bwd_offset_floats();
+    prep_weights_bwd_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, bimg, sp.in_dim);
+    if (int e = check_launch("prep_weights_bwd")) return e;
+    g_prep.img_bwd = bimg;
+  }
+  if (cudaEventRecord(g_prep.done, g_prep.side) != cudaSuccess) return check_launch("prep_ahead done");
+  return FTRF_OK;
+}
+
 int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, bool* handled) {
   *handled = false;
   InSpec sp = make_spec(f);
@@ -787,18 +842,17 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
   if (!make_fused_spec(f, sp, fs) || fs.kp > ws.ldx || !ws.wimg) return FTRF_OK;
   using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
   using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
-  using SMlp = StaticSpec<FTRF_SHADE_MLP, 27, 2, 2, 2>;
-  const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
-  int which = -1;
-  if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) which = 0;
-  else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) which = 1;
-  if (which < 0) return FTRF_OK;                 // (MLP: kp = 168 > 160 rows of the W1^T chunk; generic path)
-  (void)sizeof(SMlp);
+  const int which = dgrad_variant(f, fs);
+  if (which < 0) return FTRF_OK;
   *handled = true;
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg + fused_bwd_offset_floats();
-  prep_weights_bwd_kernel<<<32, 256, 0, st>>>(f, fs, img, sp.in_dim);
-  if (int e = check_launch("prep_weights_bwd")) return e;
+  if (g_prep.img_bwd == img) {
+    g_prep.img_bwd = nullptr;        // built by this call's forward on the side stream, which the forward joined
+  } else {
+    prep_weights_bwd_kernel<<<72, 128, 0, st>>>(f, fs, img, sp.in_dim);
+    if (int e = check_launch("prep_weights_bwd")) return e;
+  }
   const size_t smem = ((size_t)BZ_GROUPS * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS + (size_t)BZ_W_STAGES * BZ_WSTAGE_FLOATS) * 4 +
                       (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 24 * 8 + 16;
   int64_t tiles = (c.cap_app + 127) / 128;
@@ -827,8 +881,14 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg;
   float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
-  prep_weights_kernel<<<32, 256, 0, st>>>(f, fs, img, w1p, sp.in_dim);
-  if (int e = check_launch("prep_weights")) return e;
+  if (g_prep.img_fwd == img) {
+    g_prep.img_fwd = nullptr;        // built at the start of this call on the side stream: join
+    if (cudaStreamWaitEvent(st, g_prep.done, 0) != cudaSuccess) return check_launch("prep_ahead join");
+  } else {
+    g_prep.img_bwd = nullptr;        // (stage-level call: nothing was built ahead, a stale hint must not survive)
+    prep_weights_kernel<<<72, 128, 0, st>>>(f, fs, img, w1p, sp.in_dim);
+    if (int e = check_launch("prep_weights")) return e;
+  }
   const size_t smem = fused_fwd_smem();
   int64_t pairs = (c.cap_app + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
   int grid = (int)(pairs < FTRF_SMS ? pairs : FTRF_SMS);

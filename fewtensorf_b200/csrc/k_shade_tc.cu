@@ -293,6 +293,8 @@ static int launch_wgrad3x_split(Wgrad3xArgs w, cudaStream_t st) {
   return launch_wgrad3x(b, st);
 }
 
+bool shade_path_is_fused() { return g_shade_path == 2; }
+
 int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (f.shading == FTRF_SHADE_SH) return launch_shade_sh(f, c, ws, st);
   if (!g_shade_path) return launch_shade_v1(f, c, ws, st);
