@@ -89,6 +89,8 @@ inline size_t fused_wimg_bytes() { return (fused_bwd_offset_floats() + (size_t)4
 int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 int launch_shade_dgrad_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 bool shade_path_is_fused();
+bool prep_ahead_take_scratch(const float* scratch);   // true: this call's forward already zeroed the wgrad scratch
+size_t wgrad_fused_scratch_bytes();
 int shade_prep_ahead(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);   // weight images on a side stream
 
 // argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)

@@ -799,11 +799,18 @@ struct PrepAhead {
   cudaEvent_t fork = nullptr, done = nullptr;
   const float* img_fwd = nullptr;      // forward image built ahead, join pending
   const float* img_bwd = nullptr;      // backward image built ahead by the same call
+  const float* scratch = nullptr;      // wgrad scratch zeroed ahead by the same call
 };
 static thread_local PrepAhead g_prep;
 
+bool prep_ahead_take_scratch(const float* scratch) {
+  if (g_prep.scratch != scratch) return false;
+  g_prep.scratch = nullptr;
+  return true;
+}
+
 int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  g_prep.img_fwd = g_prep.img_bwd = nullptr;
+  g_prep.img_fwd = g_prep.img_bwd = g_prep.scratch = nullptr;
   if (f.shading == FTRF_SHADE_SH || c.cap_app == 0 || !ws.wimg) return FTRF_OK;
   InSpec sp = make_spec(f);
   FusedSpec fs;
@@ -830,6 +837,10 @@ int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     prep_weights_bwd_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, bimg, sp.in_dim);
     if (int e = check_launch("prep_weights_bwd")) return e;
     g_prep.img_bwd = bimg;
+    // the weight-gradient kernel's zeroed dW1 scratch (read by nothing before it): same side stream
+    float* scratch = ws.wimg + fused_scratch_offset_floats();
+    if (cudaMemsetAsync(scratch, 0, wgrad_fused_scratch_bytes(), g_prep.side) != cudaSuccess) return check_launch("wgrad scratch memset");
+    g_prep.scratch = scratch;
   }
   if (cudaEventRecord(g_prep.done, g_prep.side) != cudaSuccess) return check_launch("prep_ahead done");
   return FTRF_OK;
@@ -885,7 +896,7 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
     g_prep.img_fwd = nullptr;        // built at the start of this call on the side stream: join
     if (cudaStreamWaitEvent(st, g_prep.done, 0) != cudaSuccess) return check_launch("prep_ahead join");
   } else {
-    g_prep.img_bwd = nullptr;        // (stage-level call: nothing was built ahead, a stale hint must not survive)
+    g_prep.img_bwd = g_prep.scratch = nullptr;   // (stage-level call: nothing was built ahead, stale hints must not survive)
     prep_weights_kernel<<<72, 128, 0, st>>>(f, fs, img, w1p, sp.in_dim);
     if (int e = check_launch("prep_weights")) return e;
   }

@@ -237,7 +237,8 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
   a.variant = g_wgrad_variant;
   if (a.kp < 4 || a.ngt > WG_NGX_MAX || (a.kp & 3) || (a.ldx & 3) || a.cap < 0) { set_error("wgrad_fused: bad shape kp=%d ldx=%d", a.kp, a.ldx); return FTRF_E_ARG; }
   if (a.cap == 0) return FTRF_OK;
-  if (cudaMemsetAsync(a.dw1i, 0, wgrad_fused_scratch_bytes(), st) != cudaSuccess) return check_launch("wgrad scratch memset");
+  if (!prep_ahead_take_scratch(a.dw1i) &&
+      cudaMemsetAsync(a.dw1i, 0, wgrad_fused_scratch_bytes(), st) != cudaSuccess) return check_launch("wgrad scratch memset");
   const size_t smem = (size_t)WG_STAGES * 2 * (3 * WG_G_FLOATS + WG_KS * a.ngt * 4) * 4 + 16 * 8;
   cudaFuncSetAttribute(wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int64_t chunks = (a.cap + WG_KS - 1) / WG_KS;
