@@ -271,8 +271,8 @@ def optim_leg(model, dev, hbm_peak, iters=20):
 
 
 def other_configs_leg(dev, iters=20):
-    """BASELINE.json configs 3 and 4 on the same kernels (not bench lines of their own: reported so that every
-    named configuration has a measured number).  Same timing rules: CUDA events, L2 flushed between steps.
+    """BASELINE.json configs 3 and 4 and SURVEY 8(d)'s other regimes on the same kernels (not bench lines of their
+    own: reported so that every named configuration has a measured number).  Same timing rules: CUDA events, L2 flushed between steps.
       cp_96_288     TensorCP, n_lamb 96 / 288, 300^3, MLP_Fea, 4096 rays x S=1039
       fewshot_free  configs/free_tensorf_human.txt: TensorVMSplit 32/48, shadingMode MLP, pos_pe 8, 1024-ray batch,
                     FreeNeRF encoding + decomposition masks (vector form) at 30 % of the schedule"""
@@ -282,19 +282,21 @@ def other_configs_leg(dev, iters=20):
     ind = (torch.linspace(-1.5, 1.5, GRID).abs() < 0.6).float().to(dev)
     out = {}
 
-    def run(name, model, n_rays, mask):
-        model.updateAlphaMask((MASK_GRID,) * 3)
+    def run(name, model, n_rays, mask, mask_grid=MASK_GRID, n_samples=N_SAMPLES):
+        if mask_grid:
+            model.updateAlphaMask((mask_grid,) * 3)
         rays_h, target_h = synthetic_rays(n_rays, seed=0)
         rays, target = rays_h.to(dev), target_h.to(dev)
         torch.manual_seed(1)
         for _ in range(3):
-            model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+            model.train_step(rays, target, mask, white_bg=True, N_samples=n_samples)
         ms = 0.0
         for _ in range(iters):
             flush.zero_()
+            torch.cuda._sleep(SPIN_CYCLES)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            loss, nv = model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+            loss, nv = model.train_step(rays, target, mask, white_bg=True, N_samples=n_samples)
             b.record()
             b.synchronize()
             ms += a.elapsed_time(b)
@@ -307,7 +309,7 @@ def other_configs_leg(dev, iters=20):
         stage = [0.0] * PROF_STAGES
         for _ in range(5):
             flush.zero_()
-            model.train_step(rays, target, mask, white_bg=True, N_samples=N_SAMPLES)
+            model.train_step(rays, target, mask, white_bg=True, N_samples=n_samples)
             torch.cuda.synchronize()
             lib.ftrf_profile_read(buf)
             for i in range(PROF_STAGES):
@@ -336,6 +338,16 @@ def other_configs_leg(dev, iters=20):
     mask = get_free_mask(pos_bl=[2 * 8 * 3], view_bl=[2 * 2 * 3], fea_bl=[2 * 2 * 27], den_bl=[32] * 3, app_bl=[48] * 3,
                             step=900, total_step=3000, ratio=0.65, device=dev, intended=True)
     run("fewshot_free", vm, 1024, mask)
+    del vm
+    # SURVEY 8(d)'s other regimes of the benchmark model: the 128^3 stage of the schedule (S = 443), the first 2000
+    # iterations without an alphaMask (config.yaml:47), and the reference-scale init without the planted box
+    # (sigma ~ softplus(-10): every in-box sample is valid, none is shaded)
+    run("vm_128_mask128", build_model(dev, grid=128, mask_grid=0), RAYS_PER_GPU, None, mask_grid=128, n_samples=443)
+    run("vm_128_nomask", build_model(dev, grid=128, mask_grid=0), RAYS_PER_GPU, None, mask_grid=0, n_samples=443)
+    run("vm_300_nomask", build_model(dev, grid=GRID, mask_grid=0), RAYS_PER_GPU, None, mask_grid=0)
+    torch.manual_seed(20211202)
+    plain = ft.TensorVMSplit(dict(ARGS), aabb, [GRID] * 3, [2.0, 6.0], dev)
+    run("vm_300_reference_init_nomask", plain, RAYS_PER_GPU, None, mask_grid=0)
     return out
 
 
