@@ -244,10 +244,13 @@ extern "C" int ftrf_forward_ex(const FtrfField* f, const FtrfCall* c, void* wsb,
   Ws ws;
   if (int e = check_args(f, c, wsb, ws_bytes, false, &ws)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  if (shade_path_is_fused())
-    if (int e = shade_prep_ahead(*f, *c, ws, st)) return e;
+  const bool ahead = shade_path_is_fused();
+  if (ahead)
+    if (int e = shade_prep_ahead(*f, *c, ws, st, 0)) return e;
   prof_begin(0, st);
   if (int e = march_with_reset(*f, *c, ws, st)) return e;
+  if (ahead)
+    if (int e = shade_prep_ahead(*f, *c, ws, st, 1)) return e;
   prof_end(0, st); prof_begin(1, st);
   if (int e = launch_density(*f, *c, ws, st)) return e;
   prof_end(1, st); prof_begin(2, st);

@@ -800,6 +800,7 @@ struct PrepAhead {
   const float* img_fwd = nullptr;      // forward image built ahead, join pending
   const float* img_bwd = nullptr;      // backward image built ahead by the same call
   const float* scratch = nullptr;      // wgrad scratch zeroed ahead by the same call
+  bool forked = false;                 // phase 0 recorded the fork event of this call
 };
 static thread_local PrepAhead g_prep;
 
@@ -809,8 +810,15 @@ bool prep_ahead_take_scratch(const float* scratch) {
   return true;
 }
 
-int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  g_prep.img_fwd = g_prep.img_bwd = g_prep.scratch = nullptr;
+// phase 0 (before the call's first kernel is launched): mark the fork point on the caller's stream; phase 1 (after
+// that launch, so the host work below does not delay it): build the images on the side stream behind the mark.
+int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, int phase) {
+  if (phase == 0) {
+    g_prep.img_fwd = g_prep.img_bwd = g_prep.scratch = nullptr;
+    g_prep.forked = false;
+  } else if (!g_prep.forked) {
+    return FTRF_OK;
+  }
   if (f.shading == FTRF_SHADE_SH || c.cap_app == 0 || !ws.wimg) return FTRF_OK;
   InSpec sp = make_spec(f);
   FusedSpec fs;
@@ -825,8 +833,13 @@ int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     }
   }
   // after everything already on the caller's stream (the previous call's kernels still read the images)
-  if (cudaEventRecord(g_prep.fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_prep.fork, 0) != cudaSuccess)
-    return check_launch("prep_ahead fork");
+  if (phase == 0) {
+    if (cudaEventRecord(g_prep.fork, st) != cudaSuccess) return check_launch("prep_ahead fork");
+    g_prep.forked = true;
+    return FTRF_OK;
+  }
+  g_prep.forked = false;
+  if (cudaStreamWaitEvent(g_prep.side, g_prep.fork, 0) != cudaSuccess) return check_launch("prep_ahead fork wait");
   float* img = ws.wimg;
   float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
   prep_weights_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, img, w1p, sp.in_dim);
