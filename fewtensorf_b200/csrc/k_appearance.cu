@@ -722,6 +722,298 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
   return check_launch("app_fwd");
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Appearance backward with both small contractions on the tensor cores (VM).  app_bwd_vm_kernel above spends most
+// of its instructions in two CUDA-core mini GEMMs over shared memory (GQ = G Wb and dWb += G^T P); here
+//   GQ [64 x NP]  = G [64 x 32] Wb [32 x NP]           one tcgen05 batch per tile (M = 128 with rows 64.. zero)
+//   dWb^T [NP x 32] += P^T [NP x 64] G [64 x 32]       accumulated in TMEM over all tiles of the CTA, two M = 128
+//                                                       tiles of component rows (0..127 and NP-128..NP-1)
+// both 3xTF32 (operands split into tf32 hi / lo, three products), fp32 accumulation: fp32-grade like everything else.
+// The gather / run-merging scatter pass in between is the one of app_bwd_vm_kernel; it reads GQ from shared memory
+// (copied out of TMEM) and writes the products straight into the K-major operand tile of the second contraction
+// (four consecutive samples of one component per 16-byte store; the row-group stride is skewed by 16 bytes so the
+// eight lanes of a store phase hit different bank groups).  One CTA of 576 threads per SM.
+constexpr int BT = 64;                 // samples per tile
+constexpr int BT_WORK = 576;            // threads of the gather / scatter pass: one (4-sample segment, 4-component group) each
+constexpr int BT_THREADS = BT_WORK + 64;   // + two warps that compute the NEXT tile's taps meanwhile
+constexpr int BT_RUN = 4;              // samples per scatter segment = one 16-byte K unit of the product operand
+constexpr int BT_PT_SBO_F = 16 * 32 + 4;   // floats between 8-row groups of the product operand (2048 B + 16 B skew)
+int g_app_bwd_tc = 1;                  // ftrf_debug_set_app_bwd_tc
+
+struct AppBwdTcLayout { int np, rows_pt, qcols, tmem_cols; size_t wbi, g, gt, pt, q, tap, gf, bars, total; };
+static __host__ __device__ inline AppBwdTcLayout app_bwd_tc_layout(int NP) {
+  AppBwdTcLayout L;
+  L.np = NP;
+  L.rows_pt = NP > 128 ? NP : 128;
+  L.qcols = (NP + 31) & ~31;
+  int need = L.qcols + 64, cols = 32;
+  while (cols < need) cols <<= 1;
+  L.tmem_cols = cols;
+  size_t off = 0;
+  L.wbi = off; off += (size_t)2 * NP * 32;                        // Wb image  [NP rows][K 32] hi, lo
+  L.g = off; off += (size_t)2 * 128 * 32;                          // G         [128 rows][K 32] hi, lo (rows 64.. zero)
+  L.gt = off; off += (size_t)2 * 2 * 32 * BT;                      // G^T       [32 rows][K 64] hi, lo, two tile buffers
+  L.pt = off; off += (size_t)2 * (L.rows_pt / 8) * BT_PT_SBO_F;    // P^T       [rows_pt][K 64] hi, lo, skewed
+  L.q = off; off += (size_t)BT * (NP + 4);                         // GQ fp32   [64][NP + 4]
+  L.tap = off; off += (size_t)2 * BT * 3 * 4;                      // taps      [64][3] float4, two tile buffers
+  L.gf = off; off += (size_t)BT * 32;                              // next tile's g_feat block (fp32, prefetched)
+  L.bars = off; off += 8;
+  L.total = off * sizeof(float);
+  return L;
+}
+
+__global__ void __launch_bounds__(BT_THREADS, 1)
+app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  extern __shared__ __align__(1024) float bsm[];
+  const FtrfFactorSet& a = f.app;
+  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, n_kg = NP / 4;
+  const AppBwdTcLayout L = app_bwd_tc_layout(NP);
+  float* WbH = bsm + L.wbi; float* WbL = WbH + (size_t)NP * 32;
+  float* GH = bsm + L.g;    float* GL = GH + 128 * 32;
+  float* GT0 = bsm + L.gt;                                         // buffer b: hi at GT0 + b * 2 * 32 * BT, lo 32 * BT after it
+  const int pt_half = (L.rows_pt / 8) * BT_PT_SBO_F;
+  float* PTH = bsm + L.pt;  float* PTL = PTH + pt_half;
+  float* Q = bsm + L.q;
+  float4* TAP0 = reinterpret_cast<float4*>(bsm + L.tap);
+  float* GF = bsm + L.gf;                                          // [64 * D] contiguous copy of the tile's g_feat rows
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bsm + L.bars);      // [0] GQ batch done, [1] dWb batch done
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  if ((int64_t)blockIdx.x * BT >= n) return;
+
+  // resident operands: Wb image (row = component, k = output o, zero for o >= D); zero G rows 64..127 and P^T
+  for (int e = tid; e < NP * 8; e += BT_THREADS) {
+    const int nrow = e >> 3, ku = e & 7;
+    float h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int o = ku * 4 + j;
+      tc::split_tf32(o < D ? __ldg(f.basis + (size_t)o * NP + nrow) : 0.f, h[j], l[j]);
+    }
+    const int off = tc::canon_off(nrow, ku, 8);
+    *reinterpret_cast<float4*>(WbH + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(WbL + off) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+  for (int e = tid * 4; e < 2 * 128 * 32; e += BT_THREADS * 4) *reinterpret_cast<float4*>(GH + e) = z4();
+  for (int e = tid * 4; e < 2 * pt_half; e += BT_THREADS * 4) *reinterpret_cast<float4*>(PTH + e) = z4();
+  if (tid == 0) { tc::mbar_init(bars, 1); tc::mbar_init(bars + 1, 1); tc::fence_barrier_init(); }
+  if (warp == 0) tc::tmem_alloc(tslot, (uint32_t)L.tmem_cols);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tslot;
+  const uint32_t idesc_q = tc::idesc_tf32(128, NP), idesc_w = tc::idesc_tf32(128, 32);
+  const uint32_t tq = tmem, tw0 = tmem + (uint32_t)L.qcols, tw1 = tw0 + 32u;
+  const bool two_m = NP > 128;
+  uint32_t ph_q = 0, ph_w = 0;
+  bool first = true;
+  int gtb = 0;
+  // taps of one tile (slot -> ray -> position: three dependent global round trips) — computed one tile ahead by
+  // the two extra warps while the others run the gather / scatter pass
+  auto make_taps = [&](int64_t tbase, float4* dst, int r) {
+    const int64_t st = tbase + r;
+    float4 tp[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) tp[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (st < n) {
+      float xn[3];
+      app_point(f, c, ws, st, xn);
+      const Taps3 T = make_taps3(a, xn);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) dst[r * 3 + j] = tp[j];
+    // the tile's g_feat rows are one contiguous block: coalesced copy into shared memory
+    const int64_t lim = min((int64_t)BT, n - tbase) * D;
+    for (int e = r; e < BT * D; e += 64) GF[e] = e < lim ? __ldg(ws.a_gfeat + tbase * D + e) : 0.f;
+  };
+  if (tid >= BT_WORK) make_taps((int64_t)blockIdx.x * BT, TAP0, tid - BT_WORK);
+  __syncthreads();                        // the first tile's staging reads the g_feat block
+
+  for (int64_t t0 = (int64_t)blockIdx.x * BT; t0 < n; t0 += (int64_t)gridDim.x * BT) {
+    const int tile_n = (int)min((int64_t)BT, n - t0);
+    // ---- stage g_feat as both operands, and the taps.  The previous tile's dWb products may still be running:
+    // they read the other G^T buffer and P^T, which is not written before the wait below.
+    float* GTH = GT0 + (size_t)gtb * (2 * 32 * BT);           // gtb = parity of this tile: selects its G^T and tap buffers
+    float* GTL = GTH + 32 * BT;
+    for (int e = tid; e < BT * 8; e += BT_THREADS) {
+      const int sl = e >> 3, ku = e & 7;
+      float h[4], l[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int o = ku * 4 + j;
+        const float g = o < D ? GF[sl * D + o] : 0.f;          // (rows past the end were stored as zeros)
+        tc::split_tf32(g, h[j], l[j]);
+        const int offt = tc::canon_off(o, sl >> 2, BT / 4) + (sl & 3);
+        GTH[offt] = h[j];
+        GTL[offt] = l[j];
+      }
+      const int off = tc::canon_off(sl, ku, 8);
+      *reinterpret_cast<float4*>(GH + off) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(GL + off) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    // ---- GQ = G Wb
+    if (tid == 0) {
+      tc::fence_after_sync();
+      const uint32_t hi = tc::desc_hi(8u * 128u);
+      const uint32_t ah = tc::desc_lo(tc::smem_u32(GH), 128), al = tc::desc_lo(tc::smem_u32(GL), 128);
+      const uint32_t bh = tc::desc_lo(tc::smem_u32(WbH), 128), bl = tc::desc_lo(tc::smem_u32(WbL), 128);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint32_t o = (uint32_t)ks * 16u;
+        tc::mma_tf32_ss_lo(tq, al + o, bh + o, hi, idesc_q, ks ? 1u : 0u);
+        tc::mma_tf32_ss_lo(tq, ah + o, bl + o, hi, idesc_q, 1u);
+        tc::mma_tf32_ss_lo(tq, ah + o, bh + o, hi, idesc_q, 1u);
+      }
+      tc::mma_commit(bars);
+    }
+    tc::mbar_wait(bars, ph_q);
+    ph_q ^= 1;
+    if (!first) {                         // issued before this tile's GQ batch by the same thread: complete as well
+      tc::mbar_wait(bars + 1, ph_w);
+      ph_w ^= 1;
+    }
+    tc::fence_after_sync();
+    if ((warp & 3) < 2) {                 // rows 0..63 live in TMEM lanes 0..63: warps 0,1 (mod 4) can read them
+      const int q = warp & 3, row = q * 32 + lane;
+      for (int cc = warp >> 2; cc * 32 < NP; cc += (BT_THREADS / 32 + 3) / 4) {
+        float acc[32];
+        tc::tmem_ld32(tq + ((uint32_t)(q * 32) << 16) + (uint32_t)(cc * 32), acc);
+        tc::tmem_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          if (cc * 32 + j < NP)
+            *reinterpret_cast<float4*>(Q + (size_t)row * NPs + cc * 32 + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+      }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    // ---- gather once: products into the dWb operand, plane / line gradients with run merging
+    const float4* TAP = TAP0 + (size_t)gtb * (BT * 3);
+    if (tid >= BT_WORK) {
+      const int64_t tn = t0 + (int64_t)gridDim.x * BT;
+      if (tn < n) make_taps(tn, TAP0 + (size_t)(gtb ^ 1) * (BT * 3), tid - BT_WORK);
+    }
+    for (int item = tid; item < (BT / BT_RUN) * n_kg && tid < BT_WORK; item += BT_WORK) {
+      const int seg = item / n_kg, q = item - seg * n_kg;
+      int k = 0, base = 0;
+      while (k < 2 && 4 * q >= base + a.n_comp[k]) { base += a.n_comp[k]; ++k; }
+      const int ch = 4 * q - base, C = a.n_comp[k], W = a.plane_w[k];
+      const int m0 = mat0(k), m1 = mat1(k), mv = vecm(k);
+      float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (a.mask[k]) { const float4 m = mask4(a.mask[k], a.mask_stride[k], ch); m2 = mul4(m, m); }
+      const float* pl = a.plane[k] + ch;
+      const float* ln = a.line[k] + ch;
+      PlaneRun pr; LineRun lr;
+      pr.kx = -1; pr.ky = -1; lr.kl = -1;
+      float pq[BT_RUN][4];
+#pragma unroll
+      for (int u = 0; u < BT_RUN; ++u) {
+        const int i = seg * BT_RUN + u;
+        pq[u][0] = pq[u][1] = pq[u][2] = pq[u][3] = 0.f;
+        if (i >= tile_n) continue;
+        const float4 ax = TAP[i * 3 + m0], ay = TAP[i * 3 + m1], al = TAP[i * 3 + mv];
+        const int x0 = __float_as_int(ax.x), x1 = __float_as_int(ax.y), y0 = __float_as_int(ay.x), y1 = __float_as_int(ay.y);
+        const int l0 = __float_as_int(al.x), l1 = __float_as_int(al.y);
+        const float* r0 = pl + ((size_t)y0 * W) * C;
+        const float* r1 = pl + ((size_t)y1 * W) * C;
+        const float4 c00 = ld4(r0 + (size_t)x0 * C), c10 = ld4(r0 + (size_t)x1 * C);
+        const float4 c01 = ld4(r1 + (size_t)x0 * C), c11 = ld4(r1 + (size_t)x1 * C);
+        const float4 e0 = ld4(ln + (size_t)l0 * C), e1 = ld4(ln + (size_t)l1 * C);
+        const float w00 = ax.z * ay.z, w10 = ax.w * ay.z, w01 = ax.z * ay.w, w11 = ax.w * ay.w;
+        float4 pv = z4(), lv = z4();
+        pv = fma4(w00, c00, pv); pv = fma4(w10, c10, pv); pv = fma4(w01, c01, pv); pv = fma4(w11, c11, pv);
+        lv = fma4(al.z, e0, lv); lv = fma4(al.w, e1, lv);
+        const float4 prod = mul4(mul4(pv, lv), m2);
+        pq[u][0] = prod.x; pq[u][1] = prod.y; pq[u][2] = prod.z; pq[u][3] = prod.w;
+        const float4 gq = mul4(*reinterpret_cast<const float4*>(Q + (size_t)i * NPs + 4 * q), m2);
+        const float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
+        const int kx = x0 | (x1 << 16), ky = y0 | (y1 << 16), kl = l0 | (l1 << 16);
+        if (kx != pr.kx || ky != pr.ky) {
+          flush_plane(pr, a.g_plane[k], W, C, ch);
+          pr.kx = kx; pr.ky = ky;
+          pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+        }
+        pr.a00 = fma4(w00, gp, pr.a00);
+        pr.a10 = fma4(w10, gp, pr.a10);
+        pr.a01 = fma4(w01, gp, pr.a01);
+        pr.a11 = fma4(w11, gp, pr.a11);
+        if (kl != lr.kl) {
+          flush_line(lr, a.g_line[k], C, ch);
+          lr.kl = kl;
+          lr.a0 = z4(); lr.a1 = z4();
+        }
+        lr.a0 = fma4(al.z, gl, lr.a0);
+        lr.a1 = fma4(al.w, gl, lr.a1);
+      }
+      flush_plane(pr, a.g_plane[k], W, C, ch);
+      flush_line(lr, a.g_line[k], C, ch);
+      // rows 4q..4q+3 (components), K unit `seg` (samples 4 seg .. 4 seg + 3)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int row = 4 * q + j;
+        float h[4], l[4];
+#pragma unroll
+        for (int u = 0; u < BT_RUN; ++u) tc::split_tf32(pq[u][j], h[u], l[u]);
+        const int off = (row >> 3) * BT_PT_SBO_F + seg * 32 + (row & 7) * 4;
+        *reinterpret_cast<float4*>(PTH + off) = make_float4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<float4*>(PTL + off) = make_float4(l[0], l[1], l[2], l[3]);
+      }
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    // ---- dWb^T += P^T G
+    if (tid == 0) {
+      tc::fence_after_sync();
+      const uint32_t hi_a = tc::desc_hi((uint32_t)BT_PT_SBO_F * 4u), hi_b = tc::desc_hi((uint32_t)(BT / 4) * 128u);
+      const uint32_t bh = tc::desc_lo(tc::smem_u32(GTH), 128), bl = tc::desc_lo(tc::smem_u32(GTL), 128);
+      for (int mt = 0; mt < (two_m ? 2 : 1); ++mt) {
+        const int row0 = mt ? NP - 128 : 0;
+        const uint32_t ah = tc::desc_lo(tc::smem_u32(PTH + (row0 >> 3) * BT_PT_SBO_F), 128);
+        const uint32_t al = tc::desc_lo(tc::smem_u32(PTL + (row0 >> 3) * BT_PT_SBO_F), 128);
+        const uint32_t td = mt ? tw1 : tw0;
+#pragma unroll
+        for (int ks = 0; ks < BT / 8; ++ks) {
+          const uint32_t o = (uint32_t)ks * 16u;
+          tc::mma_tf32_ss_lo2(td, al + o, hi_a, bh + o, hi_b, idesc_w, (first && ks == 0) ? 0u : 1u);
+          tc::mma_tf32_ss_lo2(td, ah + o, hi_a, bl + o, hi_b, idesc_w, 1u);
+          tc::mma_tf32_ss_lo2(td, ah + o, hi_a, bh + o, hi_b, idesc_w, 1u);
+        }
+      }
+      tc::mma_commit(bars + 1);
+    }
+    first = false;
+    gtb ^= 1;
+  }
+  // ---- flush the basis gradient: TMEM row = component, column = output
+  tc::mbar_wait(bars + 1, ph_w);
+  tc::fence_after_sync();
+  if (warp < 8) {
+    const int mt = warp >> 2, q = warp & 3;
+    if (mt == 0 || two_m) {
+      const int m = q * 32 + lane, comp = mt ? NP - 128 + m : m;
+      float acc[32];
+      tc::tmem_ld32((mt ? tw1 : tw0) + ((uint32_t)(q * 32) << 16), acc);
+      tc::tmem_wait_ld();
+      const bool mine = mt ? comp >= 128 : comp < NP;      // the second tile repeats rows NP-128 .. 127
+      if (mine)
+#pragma unroll
+        for (int o = 0; o < 32; ++o)
+          if (o < D && acc[o] != 0.f) atomicAdd(f.g_basis + (size_t)o * NP + comp, acc[o]);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, (uint32_t)L.tmem_cols);
+}
+
 int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   int NPs = app_np(f) + 4, Dp = (f.app_dim + 3) & ~3;
   size_t smem = ((size_t)f.app_dim * NPs + (size_t)ATILE * NPs + (size_t)ATILE * Dp + (size_t)Dp * LDP + (size_t)ATILE * 3) * sizeof(float);
@@ -733,6 +1025,15 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
   if (arun < 0) {
     arun = 4;
     while (arun < ATILE && ((ATILE + arun - 1) / arun) * (app_np(f) / 4) > 256) ++arun;
+  }
+  if (f.model == FTRF_MODEL_VM && g_app_bwd_tc && arun != 0) {
+    const int NP = app_np(f);
+    const AppBwdTcLayout L = app_bwd_tc_layout(NP);
+    if (NP % 16 == 0 && NP >= 16 && NP <= 256 && f.app_dim <= 32 && L.total + 1024 <= 227 * 1024 && L.tmem_cols <= 512) {
+      cudaFuncSetAttribute(app_bwd_vm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+      app_bwd_vm_tc_kernel<<<FTRF_SMS, BT_THREADS, L.total, st>>>(f, c, ws);
+      return check_launch("app_bwd_vm_tc");
+    }
   }
   if (arun > 0 && g_app_bwd_onegather) {
     const size_t sm2 = smem + ((size_t)ATILE * NPs + (size_t)ATILE * 3 * 4) * sizeof(float);
@@ -748,6 +1049,11 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
 
 extern "C" int ftrf_debug_set_app_tc(int on) {
   ftrf::g_app_fwd_tc = on;
+  return 0;
+}
+
+extern "C" int ftrf_debug_set_app_bwd_tc(int on) {
+  ftrf::g_app_bwd_tc = on;
   return 0;
 }
 
