@@ -52,7 +52,7 @@ STAGE_OF = {'march_kernel': 'march', 'density_fwd_kernel': 'density_fwd', 'integ
             'shade_fused_fwd_kernel': 'shade_fwd', 'composite_kernel': 'composite', 'integrate_bwd_kernel': 'integrate_bwd',
             'layer3_bwd_kernel': 'shade_bwd_out', 'prep_weights_bwd_kernel': 'shade_bwd_dgrad',
             'shade_fused_dgrad_kernel': 'shade_bwd_dgrad', 'wgrad_fused_kernel': 'shade_wgrad',
-            'wgrad_unpermute_kernel': 'shade_wgrad', 'app_bwd_vm_kernel': 'app_bwd', 'app_bwd_kernel': 'app_bwd',
+            'wgrad_unpermute_kernel': 'shade_wgrad', 'app_bwd_vm_kernel': 'app_bwd', 'app_bwd_vm_tc_kernel': 'app_bwd', 'app_bwd_kernel': 'app_bwd',
             'density_bwd_vm_runs_kernel': 'density_bwd', 'density_bwd_vm_staged_kernel': 'density_bwd', 'density_bwd_kernel': 'density_bwd'}
 
 
