@@ -736,6 +736,8 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
 constexpr int BT = 64;                 // samples per tile
 constexpr int BT_WORK = 576;            // threads of the gather / scatter pass: one (4-sample segment, 4-component group) each
 constexpr int BT_THREADS = BT_WORK + 64;   // + two warps that compute the NEXT tile's taps meanwhile
+constexpr int BT_ISSUER = BT_WORK + 32;  // the thread that issues the MMA batches: lane 0 of the second extra warp, so the
+                                         // dWb batch of a tile is issued while the 576 workers already stage the next one
 constexpr int BT_RUN = 4;              // samples per scatter segment = one 16-byte K unit of the product operand
 constexpr int BT_PT_SBO_F = 16 * 32 + 4;   // floats between 8-row groups of the product operand (2048 B + 16 B skew)
 int g_app_bwd_tc = 1;                  // ftrf_debug_set_app_bwd_tc
@@ -859,7 +861,7 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     tc::fence_before_sync();
     __syncthreads();
     // ---- GQ = G Wb
-    if (tid == 0) {
+    if (tid == BT_ISSUER) {
       tc::fence_after_sync();
       const uint32_t hi = tc::desc_hi(8u * 128u);
       const uint32_t ah = tc::desc_lo(tc::smem_u32(GH), 128), al = tc::desc_lo(tc::smem_u32(GL), 128);
@@ -970,7 +972,7 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     tc::fence_before_sync();
     __syncthreads();
     // ---- dWb^T += P^T G
-    if (tid == 0) {
+    if (tid == BT_ISSUER) {
       tc::fence_after_sync();
       const uint32_t hi_a = tc::desc_hi((uint32_t)BT_PT_SBO_F * 4u), hi_b = tc::desc_hi((uint32_t)(BT / 4) * 128u);
       const uint32_t bh = tc::desc_lo(tc::smem_u32(GTH), 128), bl = tc::desc_lo(tc::smem_u32(GTL), 128);
