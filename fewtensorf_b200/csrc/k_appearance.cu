@@ -176,11 +176,12 @@ app_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 // the accumulator rows back and stores app_dim features per sample.  Two CTAs per SM overlap one CTA's
 // gathers with the other's products.
 constexpr int TCT = 128;
+constexpr int TC_THREADS = 256 + 64;   // 256 workers + two warps computing the next tile's taps
 constexpr int TC_LBO_F = 36;      // operand tile: 144 B between K-adjacent core matrices (128 B + 16 B skew: the 12 lanes that
                                   // write the chunks of one sample row then hit different banks)
 int g_app_fwd_tc = 1;           // bring-up switch (ftrf_debug_set_app_tc)
 
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(TC_THREADS, 2)
 app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM) {
   extern __shared__ __align__(1024) uint8_t app_raw[];
   const FtrfFactorSet& a = f.app;
@@ -188,8 +189,8 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
   float* Bimg = reinterpret_cast<float*>(app_raw);             // per pair k: hi [32 x C_k] then lo [32 x C_k]
   float* Phi = Bimg + (size_t)2 * 32 * NP;                      // [128 x CM]
   float* Plo = Phi + (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F;
-  float4* TAP = reinterpret_cast<float4*>(Plo + (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F);   // [128][3] (i0, i1, w0, w1) per axis
-  uint64_t* bar = reinterpret_cast<uint64_t*>(TAP + TCT * 3);
+  float4* TAP0 = reinterpret_cast<float4*>(Plo + (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F);   // 2 x [128][3] (i0, i1, w0, w1) per axis
+  uint64_t* bar = reinterpret_cast<uint64_t*>(TAP0 + 2 * TCT * 3);
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar + 1);
   const int tid = threadIdx.x, warp = tid >> 5;
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
@@ -199,7 +200,7 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
     int base = 0, kb = 0;
     for (int k = 0; k < 3; ++k) {
       const int Ck = a.n_comp[k], nq = Ck >> 2;
-      for (int e = tid; e < 32 * nq; e += 256) {
+      for (int e = tid; e < 32 * nq; e += TC_THREADS) {
         const int o = e / nq, ku = e - o * nq;
         float4 w = make_float4(0.f, 0.f, 0.f, 0.f), h, l;
         if (o < D) w = ld4(f.basis + (size_t)o * NP + kb + ku * 4);
@@ -213,19 +214,13 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
       kb += Ck;
     }
   }
-  if (tid == 0) { tc::mbar_init(bar, 1); tc::fence_barrier_init(); }
-  if (warp == 0) tc::tmem_alloc(tslot, 32);
-  tc::fence_async_smem();
-  tc::fence_before_sync();
-  __syncthreads();
-  tc::fence_after_sync();
-  const uint32_t tmem = *tslot;
-  const uint32_t idesc = tc::idesc_tf32(128, 32);
-  uint32_t ph = 0;
-
-  for (int64_t t0 = (int64_t)blockIdx.x * TCT; t0 < n; t0 += (int64_t)gridDim.x * TCT) {
-    if (tid < TCT) {
-      const int64_t s = t0 + tid;
+  // Taps of a tile: slot -> ray -> position is three dependent global round trips.  Two extra warps compute them
+  // one tile ahead (two samples per thread) while the 256 workers gather; nobody waits for the chain any more.
+  auto make_taps = [&](int64_t tbase, float4* dst) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int r = (tid - 256) * 2 + u;
+      const int64_t s = tbase + r;
       float4 tp[3];
 #pragma unroll
       for (int j = 0; j < 3; ++j) tp[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // index 0, weight 0
@@ -237,9 +232,27 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
         for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
       }
 #pragma unroll
-      for (int j = 0; j < 3; ++j) TAP[tid * 3 + j] = tp[j];
+      for (int j = 0; j < 3; ++j) dst[r * 3 + j] = tp[j];
     }
-    __syncthreads();
+  };
+  if (tid >= 256) make_taps((int64_t)blockIdx.x * TCT, TAP0);
+  if (tid == 0) { tc::mbar_init(bar, 1); tc::fence_barrier_init(); }
+  if (warp == 0) tc::tmem_alloc(tslot, 32);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tslot;
+  const uint32_t idesc = tc::idesc_tf32(128, 32);
+  uint32_t ph = 0;
+  int par = 0;                      // tap buffer of the current tile
+
+  for (int64_t t0 = (int64_t)blockIdx.x * TCT; t0 < n; t0 += (int64_t)gridDim.x * TCT) {
+    const float4* TAP = TAP0 + (size_t)par * (TCT * 3);
+    if (tid >= 256) {
+      const int64_t tn = t0 + (int64_t)gridDim.x * TCT;
+      if (tn < n) make_taps(tn, TAP0 + (size_t)(par ^ 1) * (TCT * 3));
+    }
     int bbase = 0;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -250,7 +263,7 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
         tc::fence_after_sync();
       }
       // two items per iteration, all twelve gathers issued before the first use
-      for (int item = tid; item < TCT * nq; item += 512) {
+      for (int item = tid; item < TCT * nq && tid < 256; item += 512) {
         float4 pv[2], lv[2];
         int off[2];
         bool on[2];
@@ -323,16 +336,17 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
       const int total = rows * D;                       // floats; the block starts 16-byte aligned (t0 % 128 == 0)
       float* dst = ws.a_feat + t0 * D;
       if ((((size_t)dst) & 15) == 0) {
-        for (int e = tid * 4; e < total; e += 256 * 4) {
+        for (int e = tid * 4; e < total && tid < 256; e += 256 * 4) {
           if (e + 4 <= total) *reinterpret_cast<float4*>(dst + e) = *reinterpret_cast<const float4*>(stage + e);
           else for (int j = e; j < total; ++j) dst[j] = stage[j];
         }
       } else {
-        for (int e = tid; e < total; e += 256) dst[e] = stage[e];
+        for (int e = tid; e < total && tid < 256; e += 256) dst[e] = stage[e];
       }
     }
     tc::fence_before_sync();
-    __syncthreads();                    // accumulator read, TAP / operand tile free for the next tile
+    __syncthreads();                    // accumulator read, operand tile free, the next tile's taps written
+    par ^= 1;
   }
   if (warp == 0) tc::tmem_dealloc(tmem, 32);
 }
@@ -710,9 +724,9 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
   const FtrfFactorSet& a = f.app;
   const int cm = f.model == FTRF_MODEL_VM ? (a.n_comp[0] > a.n_comp[1] ? (a.n_comp[0] > a.n_comp[2] ? a.n_comp[0] : a.n_comp[2]) : (a.n_comp[1] > a.n_comp[2] ? a.n_comp[1] : a.n_comp[2])) : 0;
   if (g_app_fwd_tc && f.model == FTRF_MODEL_VM && a.n_comp[0] % 8 == 0 && a.n_comp[1] % 8 == 0 && a.n_comp[2] % 8 == 0 && cm <= 64) {
-    const size_t sm = ((size_t)2 * 32 * app_np(f) + (size_t)2 * (TCT / 8) * (cm / 4) * TC_LBO_F) * sizeof(float) + (size_t)TCT * 3 * sizeof(float4) + 32;
+    const size_t sm = ((size_t)2 * 32 * app_np(f) + (size_t)2 * (TCT / 8) * (cm / 4) * TC_LBO_F) * sizeof(float) + (size_t)2 * TCT * 3 * sizeof(float4) + 32;
     cudaFuncSetAttribute(app_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    app_fwd_tc_kernel<<<FTRF_SMS * 2, 256, sm, st>>>(f, c, ws, cm);
+    app_fwd_tc_kernel<<<FTRF_SMS * 2, TC_THREADS, sm, st>>>(f, c, ws, cm);
     return check_launch("app_fwd_tc");
   }
   size_t smem = ((size_t)app_np(f) * 32 + (size_t)app_np(f) * LDP) * sizeof(float);

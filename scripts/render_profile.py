@@ -31,6 +31,7 @@ for it in range(frames + 2):
         with torch.no_grad():
             model(rays[lo:lo + step], None, white_bg=True, is_train=False, N_samples=-1)
         if it >= 2:
+            torch.cuda.synchronize()          # forward() returns once the counters are final; the stage events need the tail
             lib.ftrf_profile_read(buf)
             for i in range(n):
                 acc[i] += max(buf[i], 0.0) / frames
