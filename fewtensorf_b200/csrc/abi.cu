@@ -295,9 +295,9 @@ extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* w
     prof_begin(12, st);
     int e = launch_density_bwd(*f, *c, ws, st);
     prof_end(12, st);
-    return e;
+    if (e) return e;
   }
-  return FTRF_OK;
+  return side_tail_join(st);     // the un-permute of the first-layer weight gradient ran beside the kernels above
 }
 
 extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {

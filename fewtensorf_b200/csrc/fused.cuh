@@ -91,6 +91,9 @@ int launch_shade_dgrad_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaS
 bool shade_path_is_fused();
 bool prep_ahead_take_scratch(const float* scratch);   // true: this call's forward already zeroed the wgrad scratch
 size_t wgrad_fused_scratch_bytes();
+cudaStream_t side_tail_begin(cudaStream_t st);        // side stream ordered after `st`, or nullptr
+void side_tail_end();
+int side_tail_join(cudaStream_t st);                  // `st` waits for the tail (no-op when none is pending)
 int shade_prep_ahead(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int phase);   // weight images on a side stream
 
 // argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)

@@ -804,6 +804,38 @@ struct PrepAhead {
 };
 static thread_local PrepAhead g_prep;
 
+// A tail that nothing later in the backward reads (the un-permute of the dW1 scratch into g_w1 / g_b1) runs on the
+// side stream beside the appearance and density backward kernels: side_tail_begin() orders the side stream after
+// everything enqueued on `st` so far and returns it (nullptr: no side stream, run in line); side_tail_end() records
+// its completion; side_tail_join() makes `st` wait for it (end of the backward call).
+static thread_local cudaEvent_t g_tail_fork = nullptr, g_tail_done = nullptr;
+static thread_local bool g_tail_pending = false;
+cudaStream_t side_tail_begin(cudaStream_t st) {
+  if (!g_prep.side) return nullptr;
+  if (!g_tail_fork) {
+    if (cudaEventCreateWithFlags(&g_tail_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&g_tail_done, cudaEventDisableTiming) != cudaSuccess) {
+      g_tail_fork = g_tail_done = nullptr;
+      cudaGetLastError();
+      return nullptr;
+    }
+  }
+  if (cudaEventRecord(g_tail_fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_tail_fork, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return g_prep.side;
+}
+void side_tail_end() {
+  if (cudaEventRecord(g_tail_done, g_prep.side) == cudaSuccess) g_tail_pending = true;
+}
+int side_tail_join(cudaStream_t st) {
+  if (!g_tail_pending) return FTRF_OK;
+  g_tail_pending = false;
+  if (cudaStreamWaitEvent(st, g_tail_done, 0) != cudaSuccess) return check_launch("side tail join");
+  return FTRF_OK;
+}
+
 bool prep_ahead_take_scratch(const float* scratch) {
   if (g_prep.scratch != scratch) return false;
   g_prep.scratch = nullptr;

@@ -245,7 +245,10 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
   int grid = (int)(chunks < FTRF_SMS ? chunks : FTRF_SMS);
   wgrad_fused_kernel<<<grid, WG_THREADS, smem, st>>>(a);
   if (int e = check_launch("wgrad_fused")) return e;
-  wgrad_unpermute_kernel<<<(128 * a.ngt * 4 + 255) / 256, 256, 0, st>>>(a.dw1i, fs, a.ngt * 4, g_w1, ldw, g_b1);
+  // nothing later in the backward reads g_w1 / g_b1: off the serial chain, joined at the end of the call
+  cudaStream_t tail = side_tail_begin(st);
+  wgrad_unpermute_kernel<<<(128 * a.ngt * 4 + 255) / 256, 256, 0, tail ? tail : st>>>(a.dw1i, fs, a.ngt * 4, g_w1, ldw, g_b1);
+  if (tail) side_tail_end();
   return check_launch("wgrad_unpermute");
 }
 
