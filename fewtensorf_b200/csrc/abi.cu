@@ -284,7 +284,16 @@ extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* w
   cudaStream_t st = (cudaStream_t)stream;
   if (part != 2) {
     prof_begin(6, st);
-    if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
+    // MLP shading on the fused path: the MLP backward only needs dL/d rgb of the shaded samples (one small kernel);
+    // the reverse scan, whose sigma gradients only the density backward reads, runs beside it on the side stream
+    cudaStream_t scan = (f->shading != FTRF_SHADE_SH && shade_path_is_fused() && !g_prof_on) ? side_scan_begin(st) : nullptr;
+    if (scan) {
+      if (int e = launch_integrate_bwd_sigma(*f, *c, ws, scan)) return e;
+      side_scan_end();
+      if (int e = launch_grgb(*f, *c, ws, st)) return e;
+    } else {
+      if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
+    }
     prof_end(6, st);
     if (int e = launch_shade_bwd(*f, *c, ws, st, 0)) return e;     // stages 7-10 marked inside
     prof_begin(11, st);
@@ -292,6 +301,7 @@ extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* w
     prof_end(11, st);
   }
   if (part != 1) {
+    if (int e = side_scan_join(st)) return e;
     prof_begin(12, st);
     int e = launch_density_bwd(*f, *c, ws, st);
     prof_end(12, st);

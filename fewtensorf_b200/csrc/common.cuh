@@ -56,6 +56,8 @@ int launch_appearance(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t
 int launch_shade(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_composite(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_integrate_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_grgb(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
+int launch_integrate_bwd_sigma(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int part = 0);
 int launch_appearance_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);

@@ -93,6 +93,9 @@ bool prep_ahead_take_scratch(const float* scratch);   // true: this call's forwa
 size_t wgrad_fused_scratch_bytes();
 cudaStream_t side_tail_begin(cudaStream_t st);        // side stream ordered after `st`, or nullptr
 void side_tail_end();
+cudaStream_t side_scan_begin(cudaStream_t st);        // the same pair for the integration backward's reverse scan
+void side_scan_end();
+int side_scan_join(cudaStream_t st);
 int side_tail_join(cudaStream_t st);                  // `st` waits for the tail (no-op when none is pending)
 int shade_prep_ahead(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int phase);   // weight images on a side stream
 

@@ -165,7 +165,7 @@ composite_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 //   g_alpha_i = T_i g_w_i - (sum_{j>i} g_w_j w_j) / (1 - alpha_i + 1e-10)
 //   g_sigma_i = g_alpha_i * dist_i * (1 - alpha_i);  g_feat_i = g_sigma_i * act'(.)
 __global__ void __launch_bounds__(INT_WARPS * 32)
-integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const bool write_grgb) {
   const int warp = threadIdx.x >> 5, lane = lane_id();
   const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
@@ -218,8 +218,10 @@ integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
         gw = g_acc;
         if (cur.a >= 0) {
           gw += gm[0] * cur.q0 + gm[1] * cur.q1 + gm[2] * cur.q2;
-          float* o = ws.a_grgb + (size_t)cur.a * 3;
-          o[0] = w * gm[0]; o[1] = w * gm[1]; o[2] = w * gm[2];
+          if (write_grgb) {
+            float* o = ws.a_grgb + (size_t)cur.a * 3;
+            o[0] = w * gm[0]; o[1] = w * gm[1]; o[2] = w * gm[2];
+          }
         }
       }
       // exclusive suffix sum of gw*w across lanes (higher lanes = later samples)
@@ -262,9 +264,40 @@ int launch_composite(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   composite_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
   return check_launch("composite");
 }
+// dL/d rgb of every shaded sample on its own: a_grgb[a] = w * (clamp-masked g_rgb_map of the sample's ray), the
+// same values integrate_bwd_kernel writes.  The MLP backward only needs these, so with this kernel in front of it
+// the reverse scan (whose sigma gradients nothing reads before the density backward) can run on a side stream.
+__global__ void __launch_bounds__(256)
+grgb_kernel(const FtrfCall c, const Ws ws) {
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < n; a += (int64_t)gridDim.x * blockDim.x) {
+    const int slot = ws.a_slot[a];
+    const int r = ws.s_ray[slot];
+    const float w = ws.s_w[slot];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float pre = ws.rgb_pre[(int64_t)r * 3 + k];
+      const float gm = (pre >= 0.f && pre <= 1.f) ? __ldg(c.g_rgb_map + (int64_t)r * 3 + k) : 0.f;   // clamp backward
+      ws.a_grgb[a * 3 + k] = w * gm;
+    }
+  }
+}
+
 int launch_integrate_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (c.n_rays == 0) return FTRF_OK;
-  integrate_bwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws);
+  integrate_bwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws, true);
+  return check_launch("integrate_bwd");
+}
+
+// the two halves of that kernel's job as separate launches (see grgb_kernel)
+int launch_grgb(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (c.n_rays == 0 || c.cap_app == 0) return FTRF_OK;
+  grgb_kernel<<<FTRF_SMS * 4, 256, 0, st>>>(c, ws);
+  return check_launch("grgb");
+}
+int launch_integrate_bwd_sigma(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
+  if (c.n_rays == 0) return FTRF_OK;
+  integrate_bwd_kernel<<<ray_grid(c.n_rays), INT_WARPS * 32, 0, st>>>(f, c, ws, false);
   return check_launch("integrate_bwd");
 }
 

@@ -836,6 +836,35 @@ int side_tail_join(cudaStream_t st) {
   return FTRF_OK;
 }
 
+// Same for the reverse scan of the integration backward (only the density backward reads its sigma gradients).
+static thread_local cudaEvent_t g_scan_fork = nullptr, g_scan_done = nullptr;
+static thread_local bool g_scan_pending = false;
+cudaStream_t side_scan_begin(cudaStream_t st) {
+  if (!g_prep.side) return nullptr;
+  if (!g_scan_fork) {
+    if (cudaEventCreateWithFlags(&g_scan_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&g_scan_done, cudaEventDisableTiming) != cudaSuccess) {
+      g_scan_fork = g_scan_done = nullptr;
+      cudaGetLastError();
+      return nullptr;
+    }
+  }
+  if (cudaEventRecord(g_scan_fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_scan_fork, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return g_prep.side;
+}
+void side_scan_end() {
+  if (cudaEventRecord(g_scan_done, g_prep.side) == cudaSuccess) g_scan_pending = true;
+}
+int side_scan_join(cudaStream_t st) {
+  if (!g_scan_pending) return FTRF_OK;
+  g_scan_pending = false;
+  if (cudaStreamWaitEvent(st, g_scan_done, 0) != cudaSuccess) return check_launch("side scan join");
+  return FTRF_OK;
+}
+
 bool prep_ahead_take_scratch(const float* scratch) {
   if (g_prep.scratch != scratch) return false;
   g_prep.scratch = nullptr;
