@@ -801,8 +801,26 @@ struct PrepAhead {
   const float* img_bwd = nullptr;      // backward image built ahead by the same call
   const float* scratch = nullptr;      // wgrad scratch zeroed ahead by the same call
   bool forked = false;                 // phase 0 recorded the fork event of this call
+  int dev = -1;                        // device the side stream lives on
 };
 static thread_local PrepAhead g_prep;
+
+// The calling thread's side stream (created on first use; an autograd engine runs the backward on its own thread,
+// which gets its own).
+static bool ensure_side() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (g_prep.side) return g_prep.dev == dev;     // (one process per GPU; a thread that switches devices runs in line)
+  g_prep.dev = dev;
+  if (cudaStreamCreateWithFlags(&g_prep.side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&g_prep.fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&g_prep.done, cudaEventDisableTiming) != cudaSuccess) {
+    g_prep.side = nullptr;
+    cudaGetLastError();
+    return false;
+  }
+  return true;
+}
 
 // A tail that nothing later in the backward reads (the un-permute of the dW1 scratch into g_w1 / g_b1) runs on the
 // side stream beside the appearance and density backward kernels: side_tail_begin() orders the side stream after
@@ -811,7 +829,7 @@ static thread_local PrepAhead g_prep;
 static thread_local cudaEvent_t g_tail_fork = nullptr, g_tail_done = nullptr;
 static thread_local bool g_tail_pending = false;
 cudaStream_t side_tail_begin(cudaStream_t st) {
-  if (!g_prep.side) return nullptr;
+  if (!ensure_side()) return nullptr;
   if (!g_tail_fork) {
     if (cudaEventCreateWithFlags(&g_tail_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&g_tail_done, cudaEventDisableTiming) != cudaSuccess) {
@@ -840,7 +858,7 @@ int side_tail_join(cudaStream_t st) {
 static thread_local cudaEvent_t g_scan_fork = nullptr, g_scan_done = nullptr;
 static thread_local bool g_scan_pending = false;
 cudaStream_t side_scan_begin(cudaStream_t st) {
-  if (!g_prep.side) return nullptr;
+  if (!ensure_side()) return nullptr;
   if (!g_scan_fork) {
     if (cudaEventCreateWithFlags(&g_scan_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&g_scan_done, cudaEventDisableTiming) != cudaSuccess) {
@@ -884,15 +902,7 @@ int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   InSpec sp = make_spec(f);
   FusedSpec fs;
   if (sp.in_dim != f.in_dim || !make_fused_spec(f, sp, fs) || fs.kp > ws.ldx) return FTRF_OK;
-  if (!g_prep.side) {
-    if (cudaStreamCreateWithFlags(&g_prep.side, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&g_prep.fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&g_prep.done, cudaEventDisableTiming) != cudaSuccess) {
-      g_prep.side = nullptr;
-      cudaGetLastError();
-      return FTRF_OK;                            // no side stream: the launchers build the images in line
-    }
-  }
+  if (!ensure_side()) return FTRF_OK;            // no side stream: the launchers build the images in line
   // after everything already on the caller's stream (the previous call's kernels still read the images)
   if (phase == 0) {
     if (cudaEventRecord(g_prep.fork, st) != cudaSuccess) return check_launch("prep_ahead fork");
