@@ -15,6 +15,7 @@
 //              (TMA), completion on mbarriers.  Each weight chunk serves both sub-tiles.
 // Roles meet only through mbarriers: a_full / a_empty (operand ring), w_full / w_empty (weight
 // ring), acc1_full / acc2_full (tcgen05.commit).  TMEM: acc1[a,b] columns 0-255, acc2[a,b] 256-511.
+#include <atomic>
 #include "fused.cuh"
 #include "tc.cuh"
 
@@ -798,12 +799,18 @@ struct PrepAhead {
   cudaStream_t side = nullptr;
   cudaEvent_t fork = nullptr, done = nullptr;
   const float* img_fwd = nullptr;      // forward image built ahead, join pending
-  const float* img_bwd = nullptr;      // backward image built ahead by the same call
-  const float* scratch = nullptr;      // wgrad scratch zeroed ahead by the same call
   bool forked = false;                 // phase 0 recorded the fork event of this call
   int dev = -1;                        // device the side stream lives on
 };
 static thread_local PrepAhead g_prep;
+// The two hints the BACKWARD consumes are process-wide: an autograd engine runs it on another host thread than the
+// forward.  They are keyed by the address inside the workspace and taken with an exchange, so concurrent hosts can
+// at worst lose a hint (and prepare in line), never see a wrong one.
+static std::atomic<const float*> g_hint_img_bwd{nullptr}, g_hint_scratch{nullptr};
+static bool take_hint(std::atomic<const float*>& h, const float* want) {
+  const float* expect = want;
+  return h.compare_exchange_strong(expect, nullptr);
+}
 
 // The calling thread's side stream (created on first use; an autograd engine runs the backward on its own thread,
 // which gets its own).
@@ -884,16 +891,16 @@ int side_scan_join(cudaStream_t st) {
 }
 
 bool prep_ahead_take_scratch(const float* scratch) {
-  if (g_prep.scratch != scratch) return false;
-  g_prep.scratch = nullptr;
-  return true;
+  return take_hint(g_hint_scratch, scratch);
 }
 
 // phase 0 (before the call's first kernel is launched): mark the fork point on the caller's stream; phase 1 (after
 // that launch, so the host work below does not delay it): build the images on the side stream behind the mark.
 int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, int phase) {
   if (phase == 0) {
-    g_prep.img_fwd = g_prep.img_bwd = g_prep.scratch = nullptr;
+    g_prep.img_fwd = nullptr;
+    g_hint_img_bwd.store(nullptr);
+    g_hint_scratch.store(nullptr);
     g_prep.forked = false;
   } else if (!g_prep.forked) {
     return FTRF_OK;
@@ -920,11 +927,11 @@ int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     float* bimg = ws.wimg + fused_bwd_offset_floats();
     prep_weights_bwd_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, bimg, sp.in_dim);
     if (int e = check_launch("prep_weights_bwd")) return e;
-    g_prep.img_bwd = bimg;
+    g_hint_img_bwd.store(bimg);
     // the weight-gradient kernel's zeroed dW1 scratch (read by nothing before it): same side stream
     float* scratch = ws.wimg + fused_scratch_offset_floats();
     if (cudaMemsetAsync(scratch, 0, wgrad_fused_scratch_bytes(), g_prep.side) != cudaSuccess) return check_launch("wgrad scratch memset");
-    g_prep.scratch = scratch;
+    g_hint_scratch.store(scratch);
   }
   if (cudaEventRecord(g_prep.done, g_prep.side) != cudaSuccess) return check_launch("prep_ahead done");
   return FTRF_OK;
@@ -942,8 +949,8 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
   *handled = true;
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg + fused_bwd_offset_floats();
-  if (g_prep.img_bwd == img) {
-    g_prep.img_bwd = nullptr;        // built by this call's forward on the side stream, which the forward joined
+  if (take_hint(g_hint_img_bwd, img)) {
+    // built by this call's forward on the side stream, which the forward joined
   } else {
     prep_weights_bwd_kernel<<<72, 128, 0, st>>>(f, fs, img, sp.in_dim);
     if (int e = check_launch("prep_weights_bwd")) return e;
@@ -980,7 +987,8 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
     g_prep.img_fwd = nullptr;        // built at the start of this call on the side stream: join
     if (cudaStreamWaitEvent(st, g_prep.done, 0) != cudaSuccess) return check_launch("prep_ahead join");
   } else {
-    g_prep.img_bwd = g_prep.scratch = nullptr;   // (stage-level call: nothing was built ahead, stale hints must not survive)
+    g_hint_img_bwd.store(nullptr);               // (stage-level call: nothing was built ahead, stale hints must not survive)
+    g_hint_scratch.store(nullptr);
     prep_weights_kernel<<<72, 128, 0, st>>>(f, fs, img, w1p, sp.in_dim);
     if (int e = check_launch("prep_weights")) return e;
   }
