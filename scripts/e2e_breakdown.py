@@ -121,7 +121,6 @@ wrap(M.TensorBase, "grad_buffer", "grad_buffer")
 wrap(M.TensorBase, "_run_backward", "run_backward")
 wrap(M.TensorBase, "forward", "module.forward")
 wrap(M.TensorBase, "_all_params", "all_params")
-wrap(ft.renderer if hasattr(ft, "renderer") else M, "OctreeRender_trilinear_fast", "renderer") if False else None
 for it in range(100):
     step()
 print("pieces:", {k: round(v / 100 * 1e3, 4) for k, v in marks.items()})
