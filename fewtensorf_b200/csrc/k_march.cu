@@ -202,7 +202,8 @@ __global__ void pack_mask_kernel(const float* __restrict__ vol, int X, int Y, in
   for (int64_t w = gw; w < words; w += wstride) {
     int64_t row = w / xw;
     int x = (int)(w % xw) * 32 + lane;
-    bool on = x < X && vol[row * X + x] > 0.5f;
+    // grid_sample(volume) > 0 on a NON-NEGATIVE volume <=> some touched texel is > 0 (the wrapper rejects negatives)
+    bool on = x < X && vol[row * X + x] > 0.f;
     uint32_t b = __ballot_sync(FULL_MASK, on);
     if (lane == 0) bits[w] = b;
   }

@@ -60,16 +60,29 @@ class SymmetricGradients:
     """
 
     def __init__(self, model, group=None):
-        import torch.distributed._symmetric_memory as symm_mem
         from ._abi import lib
         self._lib = lib
         pg = group if group is not None else dist.group.WORLD
         self.rank, self.world = dist.get_rank(pg), dist.get_world_size(pg)
-        flat, _ = model.grad_buffer(fresh=True)
-        n = (flat.numel() + 127) // 128 * 128
-        del flat
-        self.storage = symm_mem.empty(n, dtype=torch.float32, device=model.basis_mat.weight.device)
-        self.storage.zero_()
+        dev = model.basis_mat.weight.device
+        # Phase 1, local only (may fail on one rank alone: torch without symmetric memory, allocation failure).
+        # The ranks agree on the outcome BEFORE the first collective of this constructor, so a rank that failed
+        # never leaves the others blocked in rendezvous.
+        symm_mem, err = None, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            flat, _ = model.grad_buffer(fresh=True)
+            n = (flat.numel() + 127) // 128 * 128
+            del flat
+            self.storage = symm_mem.empty(n, dtype=torch.float32, device=dev)
+            self.storage.zero_()
+        except Exception as e:                               # noqa: BLE001
+            err = e
+        ok = torch.tensor([0 if err is not None else 1], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok) == 0:
+            raise RuntimeError(f"symmetric gradient storage unavailable on some rank ({err!r})")
+        # Phase 2, collective on every rank
         self.handle = symm_mem.rendezvous(self.storage, pg.group_name)
         import ctypes as C
         self.group = group
@@ -83,9 +96,10 @@ class SymmetricGradients:
         """Collective.  None if any rank cannot set up multicast symmetric memory (all ranks agree)."""
         ok, sg = 1, None
         try:
-            sg = cls(model, group)
+            sg = cls(model, group)      # raises on every rank together when phase 1 failed anywhere (see __init__)
         except Exception:                                    # noqa: BLE001 — old driver / no NVSwitch / torch without symm_mem
             ok = 0
+        # rendezvous / autotune failures (driver without multicast) are symmetric, but agree once more before use
         flag = torch.tensor([ok], device=model.basis_mat.weight.device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
         if int(flag) == 0:

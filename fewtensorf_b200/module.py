@@ -42,6 +42,25 @@ def rays_device(st) -> torch.device:
 _stream = _abi.current_stream_handle
 
 
+def _on_device(fn):
+    """Run a public entry point with the module's device current: the library launches on the CUDA current device
+    and `_stream()` returns that device's stream, while the reference accepts a model on any device
+    (`TensorVMSplit(..., device='cuda:1')` with cuda:0 current).  A plain 'cuda' device follows the current one."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *args, **kwargs):
+        idx = self.__dict__.get("_dev_index")
+        if idx is None:
+            d = torch.device(self.device)
+            idx = self.__dict__["_dev_index"] = d.index if (d.type == "cuda" and d.index is not None) else -1
+        if idx < 0 or torch.cuda.current_device() == idx:
+            return fn(self, *args, **kwargs)
+        with torch.cuda.device(idx):
+            return fn(self, *args, **kwargs)
+    return wrapper
+
+
 def _channels_last_param(t: torch.Tensor, device) -> nn.Parameter:
     """(1,C,H,W) values -> Parameter of the same shape whose memory is [H][W][C]."""
     buf = t.to(device).permute(0, 2, 3, 1).contiguous()
@@ -117,6 +136,10 @@ class AlphaGridMask(nn.Module):
         """(bits tensor, dims [X,Y,Z], aabb0 list, invgrid list) — built once per mask."""
         if self._bits is None:
             vol = self._volume.detach().to(device=self.device, dtype=torch.float32).contiguous()
+            # the kernels decide "interpolated alpha > 0" from per-texel bits, which equals the reference's
+            # grid_sample(volume) > 0 (tensorBase.py:41-48, :350-351) for every non-negative volume
+            if vol.numel() and float(vol.min()) < 0:
+                raise ValueError("AlphaGridMask: alpha_volume must be non-negative (occupancy values)")
             z, y, x = vol.shape[-3:]
             words = lib.ftrf_alpha_mask_words(x, y, z)
             bits = torch.empty(words, dtype=torch.int32, device=vol.device)
@@ -451,8 +474,12 @@ class TensorBase(nn.Module):
         """FtrfField for this call.  Without FreeNeRF masks the struct only depends on the parameter
         pointers, the alphaMask and the derived constants, so it is cached on exactly those."""
         if mask is None:
+            # every input of _build_field: parameter pointers, mask / derived-constant serials and the plain
+            # attributes a caller may change between calls
             key = (tuple(p.data_ptr() for p in self._all_params()), self._mask_serial(), self._host["serial"],
-                   self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr())
+                   self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr(),
+                   bool(self.use_coarse_mask), float(self.near_far[0]), float(self.near_far[1]),
+                   float(self.distance_scale), float(self.density_shift), self.fea2denseAct, self.shadingMode)
             cache = self.__dict__.setdefault("_field_cache", {})
             f = cache.get(key)
             if f is None:
@@ -680,6 +707,7 @@ class TensorBase(nn.Module):
             jitter = pin[:n].to(device, non_blocking=True)
         return jitter, add_bg
 
+    @_on_device
     def forward(self, rays_chunk, mask, white_bg=True, is_train=False, ndc_ray=False, N_samples=-1):
         """models/tensorBase.py:321-395.  Returns (rgb_map [N,3], depth_map [N], num_valid_samples)."""
         S = int(N_samples) if N_samples > 0 else int(self.nSamples)
@@ -702,6 +730,7 @@ class TensorBase(nn.Module):
             return outs[0]
         return (torch.cat([o[0] for o in outs]), torch.cat([o[1] for o in outs]), sum(o[2] for o in outs))
 
+    @_on_device
     def train_step(self, rays, rgb_target, mask=None, white_bg=True, ndc_ray=False, N_samples=-1, grad_scale=1.0,
                    allreduce=False, group=None):
         """Fused training step without the autograd engine: forward, MSE loss (train.py:338) and
@@ -811,6 +840,7 @@ class TensorBase(nn.Module):
         planes = list(getattr(self, which + "_plane")) if self._is_vm else []
         return planes + list(getattr(self, which + "_line"))
 
+    @_on_device
     def add_regularizers_(self, L1_weight: float = 0.0, TV_weight_density: float = 0.0, TV_weight_app: float = 0.0):
         """One pass per factor set that does what train.py:345-371 + `total_loss.backward()` do for the factor
         regularisers: ADDS d(L1_weight * density_L1() + TV_weight_density * TV_loss_density(TVLoss())
@@ -896,6 +926,7 @@ class TensorBase(nn.Module):
         inside = ~((self.aabb[0] > pts) | (pts > self.aabb[1])).any(dim=-1)
         return pts, z, inside
 
+    @_on_device
     @torch.no_grad()
     def sigma_at(self, xyz: torch.Tensor, mask=None) -> torch.Tensor:
         """sigma of compute_alpha (tensorBase.py:298-313) for world-space points, on the GPU kernels."""
@@ -911,6 +942,7 @@ class TensorBase(nn.Module):
         sigma = self.sigma_at(xyz_locs, mask)
         return 1 - torch.exp(-sigma * length)
 
+    @_on_device
     @torch.no_grad()
     def getDenseAlpha(self, gridSize=None, mask=None):
         """models/tensorBase.py:215-230 — the whole lattice in one kernel launch per x-slab batch."""
@@ -921,6 +953,7 @@ class TensorBase(nn.Module):
         alpha = self.compute_alpha(dense_xyz.view(-1, 3), mask, self.stepSize).view(dense_xyz.shape[:-1])
         return alpha, dense_xyz
 
+    @_on_device
     @torch.no_grad()
     def updateAlphaMask(self, gridSize=(200, 200, 200), mask=None):
         """models/tensorBase.py:233-256 on the occupancy kernels: lattice alpha -> threshold bits ->
@@ -955,6 +988,7 @@ class TensorBase(nn.Module):
         xyz_max = self.aabb[0] * (1 - s_hi) + self.aabb[1] * s_hi
         return torch.stack((xyz_min, xyz_max))
 
+    @_on_device
     @torch.no_grad()
     def filtering_rays(self, all_rays, all_rgbs, N_samples=256, chunk=10240 * 5, bbox_only=False):
         """models/tensorBase.py:259-288 on filter_rays_kernel: one launch per host chunk (one launch in all
@@ -979,6 +1013,10 @@ class TensorBase(nn.Module):
 class _GraphToken:
     """Weakly tracked marker of one live autograd graph of a model (dies with the graph)."""
     __slots__ = ("__weakref__",)
+
+
+def _release_workspace(wsobj) -> None:
+    wsobj.busy = False
 
 
 class _RegLossFn(torch.autograd.Function):
@@ -1040,6 +1078,9 @@ class _RenderFn(torch.autograd.Function):
         st.wsobj.busy = True
         ctx.model, ctx.st = model, st
         ctx.token = _GraphToken()
+        # a graph dropped without backward (output discarded) must not keep the cached workspace "busy" for good
+        import weakref
+        weakref.finalize(ctx.token, _release_workspace, st.wsobj)
         live = model.__dict__.get("_live_graphs")
         if live is None:
             import weakref
@@ -1053,6 +1094,9 @@ class _RenderFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_rgb, g_depth, g_nv):
         model, st = ctx.model, ctx.st
+        if st is None:
+            raise RuntimeError("fewtensorf_b200: backward through a render call a second time — its workspace (the "
+                               "saved activations) was released by the first backward; call the model again")
         params = model._all_params()
         buf = model._gradbuf
         # The persistent buffer may be handed out only when nothing else can still be reading it: not while it

@@ -96,5 +96,6 @@ class FusedAdam(torch.optim.Optimizer):
             table = self._table
             for s, it in zip(table, items):
                 s.lr = it[3]
-            check(lib.ftrf_adam_step(table, len(items), b1, b2, eps, t, _stream()), "adam_step")
+            with torch.cuda.device(items[0][0].device):        # launch where the parameters live
+                check(lib.ftrf_adam_step(table, len(items), b1, b2, eps, t, _stream()), "adam_step")
         return loss

@@ -37,8 +37,9 @@ def generate_rays(H: int, W: int, focal, c2w, center=None, normalize: bool = Tru
     if n_rows is None:
         n_rows = max(0, (H - row0 + row_step - 1) // row_step)
     out = torch.empty(n_rows * W, 6, dtype=torch.float32, device=device)
-    check(lib.ftrf_generate_rays(C.byref(cam), int(row0), int(row_step), int(n_rows), out.data_ptr(), _stream()),
-          "generate_rays")
+    with torch.cuda.device(out.device):
+        check(lib.ftrf_generate_rays(C.byref(cam), int(row0), int(row_step), int(n_rows), out.data_ptr(), _stream()),
+              "generate_rays")
     return out
 
 

@@ -176,6 +176,8 @@ def test_coarse_occupancy_keeps_sample_lists_bit_exact(workload):
         finally:
             model.use_coarse_mask = True
         st = model._last_call
+        # the call really ran with / without the coarse levels (the field descriptor is cached per setting)
+        assert bool(st.field.am_coarse) == use
         n = st.n_samples
         ray = model.workspace_section(st, "S_RAY", torch.int32, n).long()
         idx = model.workspace_section(st, "S_IDX", torch.int32, n).long()
