@@ -63,12 +63,20 @@ class FtrfCall(C.Structure):
         ("ndc", C.c_int32), ("add_bg", C.c_int32), ("save_for_backward", C.c_int32),
         ("rays", _f32p), ("jitter", _f32p), ("rgb_map", _f32p), ("depth_map", _f32p), ("g_rgb_map", _f32p),
         ("cap_samples", C.c_int64), ("cap_app", C.c_int64),
+        ("lib_flags", C.c_uint64), ("lib_ctx", C.c_void_p),       # library-owned hand-off state (zero-initialised)
     ]
 
 
 class FtrfAdamSegment(C.Structure):
     _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
                 ("n", C.c_int64), ("lr", C.c_float), ("pad_", C.c_int32)]
+
+
+class FtrfRegion(C.Structure):
+    _fields_ = [("offset", C.c_int64), ("row_len", C.c_int64), ("row_stride", C.c_int64), ("n_rows", C.c_int64)]
+
+
+MAX_REGIONS = 24
 
 
 class FtrfCamera(C.Structure):
@@ -83,20 +91,24 @@ EXPORTS = [
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
     "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_event_record", "ftrf_stream_wait_event", "ftrf_zero_after", "ftrf_profile_enable", "ftrf_profile_read",
-    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_set_shade_path",
+    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce",
+    "ftrf_points_workspace_bytes", "ftrf_density_feature", "ftrf_app_feature", "ftrf_shade_points",
+    "ftrf_resample_factor", "ftrf_crop_factor", "ftrf_ortho_reg",
+    "ftrf_p2p_allreduce_regions", "ftrf_multimem_allreduce_regions",
 ]
+TEST_LIB_PATH = os.path.join(_HERE, "libfewtensorf_b200_test.so")    # superset build for tests / scripts only
 PROF_STAGES = 13
 
 
-def _load():
-    if not os.path.exists(LIB_PATH):
+def _load(path=LIB_PATH):
+    if not os.path.exists(path):
         raise ImportError(
-            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(or `make -C fewtensorf_b200/csrc`). fewtensorf_b200 has no CPU or PyTorch fallback.")
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(path)
     for name in EXPORTS:
         if not hasattr(lib, name):
-            raise ImportError(f"{LIB_PATH} does not export {name}")
+            raise ImportError(f"{path} does not export {name}")
     lib.ftrf_abi_version.restype = C.c_int
     lib.ftrf_last_error.restype = C.c_char_p
     lib.ftrf_workspace_layout.restype = C.c_size_t
@@ -150,6 +162,10 @@ def _load():
     lib.ftrf_multimem_allreduce.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
     lib.ftrf_p2p_allreduce.restype = C.c_int
     lib.ftrf_p2p_allreduce.argtypes = [C.POINTER(C.c_void_p), C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+    lib.ftrf_p2p_allreduce_regions.restype = C.c_int
+    lib.ftrf_p2p_allreduce_regions.argtypes = [C.POINTER(C.c_void_p), C.POINTER(FtrfRegion), C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.ftrf_multimem_allreduce_regions.restype = C.c_int
+    lib.ftrf_multimem_allreduce_regions.argtypes = [C.c_void_p, C.POINTER(FtrfRegion), C.c_int, C.c_int, C.c_int, C.c_void_p]
     lib.ftrf_reg_factors.restype = C.c_int
     lib.ftrf_reg_factors.argtypes = [C.POINTER(FtrfFactorSet), C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_void_p]
@@ -160,6 +176,31 @@ def _load():
     lib.ftrf_generate_rays.argtypes = [C.POINTER(FtrfCamera), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_launch_count.restype = C.c_ulonglong
     lib.ftrf_launch_count.argtypes = []
+    lib.ftrf_points_workspace_bytes.restype = C.c_size_t
+    lib.ftrf_points_workspace_bytes.argtypes = [C.POINTER(FtrfField), C.c_int64]
+    lib.ftrf_density_feature.restype = C.c_int
+    lib.ftrf_density_feature.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.ftrf_app_feature.restype = C.c_int
+    lib.ftrf_app_feature.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.ftrf_shade_points.restype = C.c_int
+    lib.ftrf_shade_points.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.ftrf_resample_factor.restype = C.c_int
+    lib.ftrf_resample_factor.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+    lib.ftrf_crop_factor.restype = C.c_int
+    lib.ftrf_crop_factor.argtypes = [C.c_void_p] + [C.c_int32] * 7 + [C.c_void_p, C.c_void_p]
+    lib.ftrf_ortho_reg.restype = C.c_int
+    lib.ftrf_ortho_reg.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                   C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    if lib.ftrf_abi_version() != 2:
+        raise ImportError(f"{path} ABI version mismatch")
+    return lib
+
+
+def load_test_lib():
+    """The superset test build (cross-check MLP back ends, unit-test entry points, debug switches).  For tests/ and
+    scripts/ only: the product never loads it."""
+    lib = _load(TEST_LIB_PATH)
     lib.ftrf_test_gemm3x.restype = C.c_int
     lib.ftrf_test_gemm3x.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int,
                                      C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
@@ -169,8 +210,6 @@ def _load():
                                       C.c_void_p, C.c_void_p]
     lib.ftrf_set_shade_path.restype = C.c_int
     lib.ftrf_set_shade_path.argtypes = [C.c_int]
-    if lib.ftrf_abi_version() != 1:
-        raise ImportError("libfewtensorf_b200.so ABI version mismatch")
     return lib
 
 

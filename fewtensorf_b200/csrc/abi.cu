@@ -1,5 +1,8 @@
 // abi.cu — the extern "C" boundary: argument checks, workspace carving, stage sequencing.
-// No torch types, no global mutable state besides the thread-local error string.
+// No torch types.  Mutable state: the thread-local error string, the thread-local profiling switch / events, each
+// host thread's cached side stream (k_shade_fused.cu) and one atomic launch counter; everything that belongs to a
+// CALL travels in the caller's FtrfCall (lib_flags / lib_ctx), so the entry points are re-entrant.
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -18,10 +21,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-static unsigned long long g_launches = 0;   // kernels this library has launched (every launch is followed by check_launch)
+static std::atomic<unsigned long long> g_launches{0};   // kernels this library has launched (every launch is followed by check_launch)
 
 int check_launch(const char* what) {
-  ++g_launches;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
@@ -34,9 +37,10 @@ int check_launch(const char* what) {
 static const char* kStageNames[FTRF_PROF_STAGES] = {
     "march", "density_fwd", "integrate_fwd", "app_fwd", "shade_fwd", "composite",
     "integrate_bwd", "shade_bwd_out", "shade_bwd_dgrad", "shade_wgrad", "shade_wgrad1_unfused", "app_bwd", "density_bwd"};
-static bool g_prof_on = false;
-static cudaEvent_t g_ev[FTRF_PROF_STAGES][2];
-static bool g_ev_made = false, g_ev_used[FTRF_PROF_STAGES];
+static thread_local bool g_prof_on = false;
+static thread_local cudaEvent_t g_ev[FTRF_PROF_STAGES][2];
+static thread_local bool g_ev_made = false, g_ev_used[FTRF_PROF_STAGES];
+bool prof_enabled() { return g_prof_on; }
 
 void prof_begin(int stage, cudaStream_t st) {
   if (g_prof_on) cudaEventRecord(g_ev[stage][0], st);
@@ -113,6 +117,8 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
     ws->a_gx = (float*)(b + offs[FTRF_WS_A_GX]);
     ws->wimg = mlp ? (float*)(b + offs[FTRF_WS_WIMG]) : nullptr;
     ws->ldx = (int)LDX;
+    ws->direct_xn = nullptr;
+    ws->direct_view = nullptr;
   }
   return cur;
 }
@@ -211,7 +217,7 @@ extern "C" const char* ftrf_profile_stage_name(int stage) {
   return (stage >= 0 && stage < FTRF_PROF_STAGES) ? kStageNames[stage] : "";
 }
 
-extern "C" unsigned long long ftrf_launch_count(void) { return ftrf::g_launches; }
+extern "C" unsigned long long ftrf_launch_count(void) { return ftrf::g_launches.load(std::memory_order_relaxed); }
 extern "C" int ftrf_abi_version(void) { return FTRF_ABI_VERSION; }
 extern "C" const char* ftrf_last_error(void) { return g_err; }
 
@@ -286,10 +292,10 @@ extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* w
     prof_begin(6, st);
     // MLP shading on the fused path: the MLP backward only needs dL/d rgb of the shaded samples (one small kernel);
     // the reverse scan, whose sigma gradients only the density backward reads, runs beside it on the side stream
-    cudaStream_t scan = (f->shading != FTRF_SHADE_SH && shade_path_is_fused() && !g_prof_on) ? side_scan_begin(st) : nullptr;
+    cudaStream_t scan = (f->shading != FTRF_SHADE_SH && shade_path_is_fused() && !g_prof_on) ? side_scan_begin(*c, st) : nullptr;
     if (scan) {
       if (int e = launch_integrate_bwd_sigma(*f, *c, ws, scan)) return e;
-      side_scan_end();
+      side_scan_end(*c);
       if (int e = launch_grgb(*f, *c, ws, st)) return e;
     } else {
       if (int e = launch_integrate_bwd(*f, *c, ws, st)) return e;
@@ -301,13 +307,13 @@ extern "C" int ftrf_backward_part(const FtrfField* f, const FtrfCall* c, void* w
     prof_end(11, st);
   }
   if (part != 1) {
-    if (int e = side_scan_join(st)) return e;
+    if (int e = side_scan_join(*c, st)) return e;
     prof_begin(12, st);
     int e = launch_density_bwd(*f, *c, ws, st);
     prof_end(12, st);
     if (e) return e;
   }
-  return side_tail_join(st);     // the un-permute of the first-layer weight gradient ran beside the kernels above
+  return side_tail_join(*c, st);     // the un-permute of the first-layer weight gradient ran beside the kernels above
 }
 
 extern "C" int ftrf_backward(const FtrfField* f, const FtrfCall* c, void* wsb, size_t ws_bytes, void* stream) {
@@ -351,4 +357,73 @@ extern "C" int ftrf_density_at(const FtrfField* f, const float* xyz, int64_t n, 
   if (int e = check_factor_set(f->den, f->model, "density", false)) return e;
   if (f->has_alpha_mask && !f->am_bits) { set_error("alpha mask bits missing"); return FTRF_E_ARG; }
   return launch_density_at(*f, xyz, n, sigma_out, (cudaStream_t)stream);
+}
+
+// ---- the module methods on points (compute_densityfeature / compute_appfeature / renderModule) ---------------
+namespace ftrf {
+__global__ void set_counters_kernel(int32_t* counters, int32_t n_app) {
+  if (threadIdx.x < 8) counters[threadIdx.x] = threadIdx.x == 1 ? n_app : 0;
+}
+static FtrfCall points_call(int64_t n) {
+  FtrfCall c;
+  memset(&c, 0, sizeof(c));
+  c.ray_cols = 6;
+  c.n_samples = 1;
+  c.cap_app = n;
+  return c;
+}
+static int points_setup(const FtrfField* f, int64_t n, void* wsb, size_t ws_bytes, FtrfCall* c, Ws* ws, cudaStream_t st) {
+  if (!f || !wsb || n < 0 || n > 0x7fffffff) { set_error("points call: bad argument (n %lld)", (long long)n); return FTRF_E_ARG; }
+  if (f->model != FTRF_MODEL_VM && f->model != FTRF_MODEL_CP) { set_error("unknown model kind %d", f->model); return FTRF_E_ARG; }
+  if (f->app_dim < 1 || f->app_dim > 64) { set_error("app_dim %d unsupported", f->app_dim); return FTRF_E_ARG; }
+  *c = points_call(n);
+  const size_t need = carve(*f, *c, nullptr, wsb, ws);
+  if (ws_bytes < need) { set_error("points workspace too small: %zu < %zu", ws_bytes, need); return FTRF_E_WORKSPACE; }
+  set_counters_kernel<<<1, 32, 0, st>>>(ws->counters, (int32_t)n);
+  return check_launch("set_counters");
+}
+}  // namespace ftrf
+
+extern "C" size_t ftrf_points_workspace_bytes(const FtrfField* f, int64_t n) {
+  if (!f || n < 0) { set_error("points_workspace_bytes: bad argument"); return 0; }
+  FtrfCall c = points_call(n);
+  return carve(*f, c, nullptr, nullptr, nullptr);
+}
+
+extern "C" int ftrf_density_feature(const FtrfField* f, const float* xn, int64_t n, float* out, void* stream) {
+  if (!f || !xn || !out || n < 0) { set_error("density_feature: bad argument"); return FTRF_E_ARG; }
+  if (int e = check_factor_set(f->den, f->model, "density", false)) return e;
+  return launch_density_feature(*f, xn, n, out, (cudaStream_t)stream);
+}
+
+extern "C" int ftrf_app_feature(const FtrfField* f, const float* xn, int64_t n, float* out, void* wsb, size_t ws_bytes,
+                                void* stream) {
+  if (!xn || !out) { set_error("app_feature: null argument"); return FTRF_E_ARG; }
+  if (n == 0) return FTRF_OK;
+  FtrfCall c;
+  Ws ws;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int e = points_setup(f, n, wsb, ws_bytes, &c, &ws, st)) return e;
+  if (int e = check_factor_set(f->app, f->model, "appearance", false)) return e;
+  if (!f->basis) { set_error("basis_mat missing"); return FTRF_E_ARG; }
+  ws.direct_xn = xn;
+  ws.a_feat = out;
+  return launch_appearance(*f, c, ws, st);
+}
+
+extern "C" int ftrf_shade_points(const FtrfField* f, const float* xn, const float* viewdirs, const float* features, int64_t n,
+                                 float* rgb_out, void* wsb, size_t ws_bytes, void* stream) {
+  if (!xn || !viewdirs || !features || !rgb_out) { set_error("shade_points: null argument"); return FTRF_E_ARG; }
+  if (n == 0) return FTRF_OK;
+  FtrfCall c;
+  Ws ws;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int e = points_setup(f, n, wsb, ws_bytes, &c, &ws, st)) return e;
+  if (f->shading < 0 || f->shading > FTRF_SHADE_SH) { set_error("unknown shading kind %d", f->shading); return FTRF_E_ARG; }
+  if (f->shading != FTRF_SHADE_SH && (!f->w1 || !f->b1 || !f->w2 || !f->b2 || !f->w3 || !f->b3)) { set_error("MLP weights missing"); return FTRF_E_ARG; }
+  ws.direct_xn = xn;
+  ws.direct_view = viewdirs;
+  ws.a_feat = const_cast<float*>(features);     // read-only here: the forward shading kernels never write it
+  ws.a_rgb = rgb_out;
+  return launch_shade(*f, c, ws, st);
 }

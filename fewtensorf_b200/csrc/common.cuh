@@ -8,6 +8,14 @@
 #include "../../include/fewtensorf.h"
 
 #define FTRF_SMS 148
+
+// Bring-up / cross-check switches exist only in the test build (libfewtensorf_b200_test.so, -DFTRF_TEST_BUILD);
+// the product library compiles them to constants and carries no process-global mutable state for them.
+#ifdef FTRF_TEST_BUILD
+#define FTRF_SWITCH(type, name, value) type name = value
+#else
+#define FTRF_SWITCH(type, name, value) static constexpr type name = value
+#endif
 #define FULL_MASK 0xffffffffu
 
 namespace ftrf {
@@ -40,7 +48,24 @@ struct Ws {
   float* a_gx;     // [cap_app][ldx]  dL/dX
   float* wimg;     // weight images of the fused MLP kernels (fused.cuh)
   int ldx;
+  // points-in calls (ftrf_app_feature / ftrf_shade_points): the shaded "list" is the caller's point array itself
+  const float* direct_xn;     // [n][3] normalised coordinates, or nullptr (per-ray path: slot -> ray -> position)
+  const float* direct_view;   // [n][3] view directions
 };
+
+// library-owned hand-off bits of FtrfCall::lib_flags
+enum : uint64_t {
+  CALL_IMG_FWD_PENDING = 1,   // forward weight image being built on the side stream, join before the fused forward
+  CALL_IMG_BWD_READY = 2,     // this call's forward built the dgrad weight image
+  CALL_SCRATCH_READY = 4,     // ... and zeroed the wgrad scratch
+  CALL_TAIL_PENDING = 8,      // un-permute of dW1 running on the side stream
+  CALL_SCAN_PENDING = 16,     // reverse scan of the integration backward running on the side stream
+  CALL_FORKED = 32,           // phase 0 of shade_prep_ahead recorded its fork event
+};
+struct CallState { uint64_t flags; void* ctx; };
+inline CallState& call_state(const FtrfCall& c) {
+  return *reinterpret_cast<CallState*>(const_cast<uint64_t*>(&c.lib_flags));
+}
 
 size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws* ws);
 void set_error(const char* fmt, ...);
@@ -62,6 +87,8 @@ int launch_shade_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t,
 int launch_appearance_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_density_at(const FtrfField&, const float* xyz, int64_t n, float* out, cudaStream_t);
+int launch_density_feature(const FtrfField&, const float* xn, int64_t n, float* out, cudaStream_t);
+bool prof_enabled();
 int launch_dense_alpha_bits(const FtrfField&, const float* lin, int X, int Y, int Z, float length, float thres,
                             uint32_t* raw, float* alpha_out, cudaStream_t);
 

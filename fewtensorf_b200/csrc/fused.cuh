@@ -89,14 +89,14 @@ inline size_t fused_wimg_bytes() { return (fused_bwd_offset_floats() + (size_t)4
 int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 int launch_shade_dgrad_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 bool shade_path_is_fused();
-bool prep_ahead_take_scratch(const float* scratch);   // true: this call's forward already zeroed the wgrad scratch
+bool prep_ahead_take_scratch(const FtrfCall&);        // true: this call's forward already zeroed the wgrad scratch
 size_t wgrad_fused_scratch_bytes();
-cudaStream_t side_tail_begin(cudaStream_t st);        // side stream ordered after `st`, or nullptr
-void side_tail_end();
-cudaStream_t side_scan_begin(cudaStream_t st);        // the same pair for the integration backward's reverse scan
-void side_scan_end();
-int side_scan_join(cudaStream_t st);
-int side_tail_join(cudaStream_t st);                  // `st` waits for the tail (no-op when none is pending)
+cudaStream_t side_tail_begin(const FtrfCall&, cudaStream_t st);   // side stream ordered after `st`, or nullptr
+void side_tail_end(const FtrfCall&);
+cudaStream_t side_scan_begin(const FtrfCall&, cudaStream_t st);   // the same pair for the integration backward's reverse scan
+void side_scan_end(const FtrfCall&);
+int side_scan_join(const FtrfCall&, cudaStream_t st);
+int side_tail_join(const FtrfCall&, cudaStream_t st);             // `st` waits for the tail (no-op when none is pending)
 int shade_prep_ahead(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int phase);   // weight images on a side stream
 
 // argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)
@@ -110,6 +110,7 @@ struct WgradFusedArgs {
   int dw2_vec;                                         // dw2 is 16-byte aligned
   int variant;                                         // bring-up switches
 };
-int launch_wgrad_fused(const WgradFusedArgs&, const FusedSpec&, float* g_w1, int ldw, float* g_b1, cudaStream_t);
+// `call`: the FtrfCall the hand-off flags live in (nullptr for the unit-test entry: everything in line)
+int launch_wgrad_fused(const WgradFusedArgs&, const FusedSpec&, float* g_w1, int ldw, float* g_b1, cudaStream_t, const FtrfCall* call);
 
 }  // namespace ftrf

@@ -65,7 +65,140 @@ p2p_allreduce_kernel(const PeerPtrs peers, size_t lo4, size_t hi4) {
   }
 }
 
+// ---- the same two exchanges restricted to the parts of the buffer that can hold a gradient -------------------
+// A plane's gradient is non-zero only inside the texel bounding box of the alphaMask (+ the interpolation ring):
+// samples outside it are culled before the density gather, so nothing is ever reduced into the other rows and
+// columns — exactly zero on every rank, nothing to exchange.  In the un-shrunk benchmark field that is 16 % of the
+// planes.  A region is a 2-D run of float4 units inside the flat buffer: n_rows rows of row_len4 units, row_stride4
+// apart, starting at off4 (lines and the dense basis / MLP tail are single rows).  The union of the regions is
+// numbered row-major, region after region, and split into `world` equal shares like the dense kernels' slices.
+struct RegionTable {
+  int n;
+  uint32_t first[FTRF_MAX_REGIONS + 1];        // virtual index of each region's first unit; first[n] = total
+  uint32_t off4[FTRF_MAX_REGIONS], row_len4[FTRF_MAX_REGIONS], row_stride4[FTRF_MAX_REGIONS];
+};
+
+__device__ __forceinline__ size_t region_unit(const RegionTable& t, uint32_t v) {
+  int r = 0;
+#pragma unroll 1
+  while (r + 1 < t.n && v >= t.first[r + 1]) ++r;
+  const uint32_t e = v - t.first[r];
+  const uint32_t row = e / t.row_len4[r], col = e - row * t.row_len4[r];
+  return (size_t)t.off4[r] + (size_t)row * t.row_stride4[r] + col;
+}
+
+template <int W>
+__global__ void __launch_bounds__(512)
+p2p_allreduce_regions_kernel(const PeerPtrs peers, const RegionTable tab, uint32_t lo, uint32_t hi) {
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t v = lo + blockIdx.x * blockDim.x + threadIdx.x; v < hi; v += stride) {
+    const size_t i = region_unit(tab, v);
+    float4 x[W];
+#pragma unroll
+    for (int r = 0; r < W; ++r)
+      asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(x[r].x), "=f"(x[r].y), "=f"(x[r].z), "=f"(x[r].w) : "l"(peers.p[r] + i * 4) : "memory");
+    float4 a = x[0];
+#pragma unroll
+    for (int r = 1; r < W; ++r) { a.x += x[r].x; a.y += x[r].y; a.z += x[r].z; a.w += x[r].w; }
+#pragma unroll
+    for (int r = 0; r < W; ++r)
+      asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                   ::"l"(peers.p[r] + i * 4), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+  }
+}
+
+__global__ void __launch_bounds__(512)
+multimem_allreduce_regions_kernel(float* __restrict__ mc, const RegionTable tab, uint32_t lo, uint32_t hi) {
+  const uint32_t stride = gridDim.x * blockDim.x;
+  constexpr int U = 4;
+  uint32_t v = lo + blockIdx.x * blockDim.x + threadIdx.x;
+  for (; v < hi; v += U * stride) {
+    float4 x[U];
+    float* p[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t vv = v + u * stride;
+      p[u] = vv < hi ? mc + region_unit(tab, vv) * 4 : nullptr;
+      if (p[u])
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x[u].x), "=f"(x[u].y), "=f"(x[u].z), "=f"(x[u].w) : "l"(p[u]) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (p[u])
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(p[u]), "f"(x[u].x), "f"(x[u].y), "f"(x[u].z), "f"(x[u].w) : "memory");
+  }
+}
+
+static int make_region_table(const FtrfRegion* regions, int n, RegionTable* t, const char* who) {
+  if (!regions || n < 1 || n > FTRF_MAX_REGIONS) { set_error("%s: 1..%d regions", who, FTRF_MAX_REGIONS); return FTRF_E_ARG; }
+  uint64_t total = 0;
+  t->n = n;
+  for (int r = 0; r < n; ++r) {
+    const FtrfRegion& g = regions[r];
+    if (g.offset < 0 || g.row_len < 4 || g.n_rows < 1 || (g.offset & 3) || (g.row_len & 3) || (g.row_stride & 3) ||
+        (g.n_rows > 1 && g.row_stride < g.row_len) || (uint64_t)g.offset + (uint64_t)(g.n_rows - 1) * (uint64_t)g.row_stride + (uint64_t)g.row_len > (1ull << 33)) {
+      set_error("%s: region %d is not a run of whole float4 units", who, r);
+      return FTRF_E_ARG;
+    }
+    t->first[r] = (uint32_t)total;
+    t->off4[r] = (uint32_t)(g.offset / 4);
+    t->row_len4[r] = (uint32_t)(g.row_len / 4);
+    t->row_stride4[r] = (uint32_t)(g.row_stride / 4);
+    total += (uint64_t)(g.row_len / 4) * (uint64_t)g.n_rows;
+    if (total >= (1ull << 32)) { set_error("%s: regions too large", who); return FTRF_E_ARG; }
+  }
+  t->first[n] = (uint32_t)total;
+  return FTRF_OK;
+}
+
 }  // namespace ftrf
+
+extern "C" int ftrf_p2p_allreduce_regions(void* const* peer_ptrs, const FtrfRegion* regions, int n_regions, int rank, int world,
+                                          void* stream) {
+  if (!peer_ptrs || (world != 2 && world != 4 && world != 8) || rank < 0 || rank >= world) {
+    ftrf::set_error("p2p_allreduce_regions: bad argument (world must be 2, 4 or 8)");
+    return FTRF_E_ARG;
+  }
+  ftrf::RegionTable tab;
+  if (int e = ftrf::make_region_table(regions, n_regions, &tab, "p2p_allreduce_regions")) return e;
+  ftrf::PeerPtrs pp{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_ptrs[r] || (((size_t)peer_ptrs[r]) & 15)) { ftrf::set_error("p2p_allreduce_regions: bad peer pointer %d", r); return FTRF_E_ARG; }
+    pp.p[r] = (float*)peer_ptrs[r];
+  }
+  const uint32_t n4 = tab.first[tab.n], per = (n4 + world - 1) / world;
+  const uint32_t lo = (uint64_t)per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+  if (hi > lo) {
+    const uint32_t want = (hi - lo + 511) / 512;
+    const int grid = (int)(want < (uint32_t)FTRF_SMS * 4 ? want : (uint32_t)FTRF_SMS * 4);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (world == 2) ftrf::p2p_allreduce_regions_kernel<2><<<grid, 512, 0, st>>>(pp, tab, lo, hi);
+    else if (world == 4) ftrf::p2p_allreduce_regions_kernel<4><<<grid, 512, 0, st>>>(pp, tab, lo, hi);
+    else ftrf::p2p_allreduce_regions_kernel<8><<<grid, 512, 0, st>>>(pp, tab, lo, hi);
+  }
+  return ftrf::check_launch("p2p_allreduce_regions");
+}
+
+extern "C" int ftrf_multimem_allreduce_regions(void* multicast_ptr, const FtrfRegion* regions, int n_regions, int rank, int world,
+                                               void* stream) {
+  if (!multicast_ptr || world < 1 || rank < 0 || rank >= world || (((size_t)multicast_ptr) & 15)) {
+    ftrf::set_error("multimem_allreduce_regions: bad argument");
+    return FTRF_E_ARG;
+  }
+  ftrf::RegionTable tab;
+  if (int e = ftrf::make_region_table(regions, n_regions, &tab, "multimem_allreduce_regions")) return e;
+  const uint32_t n4 = tab.first[tab.n], per = (n4 + world - 1) / world;
+  const uint32_t lo = (uint64_t)per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+  if (hi > lo) {
+    const uint32_t want = (hi - lo + 512 * 4 - 1) / (512 * 4);
+    const int grid = (int)(want < (uint32_t)FTRF_SMS * 4 ? want : (uint32_t)FTRF_SMS * 4);
+    ftrf::multimem_allreduce_regions_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>((float*)multicast_ptr, tab, lo, hi);
+  }
+  return ftrf::check_launch("multimem_allreduce_regions");
+}
 
 // peer_ptrs: `world` device pointers (host array) to the same symmetric buffer on every GPU, in rank order.
 extern "C" int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int world, void* stream) {

@@ -21,6 +21,11 @@ __host__ __device__ inline int app_np(const FtrfField& f) {
 }
 
 __device__ __forceinline__ void app_point(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t s, float xn[3]) {
+  if (ws.direct_xn) {          // points-in call (ftrf_app_feature)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) xn[k] = __ldg(ws.direct_xn + 3 * s + k);
+    return;
+  }
   int slot = ws.a_slot[s];
   Ray ray = load_ray_ws(f, c, ws, ws.s_ray[slot]);
   float p[3];
@@ -179,7 +184,7 @@ constexpr int TCT = 128;
 constexpr int TC_THREADS = 256 + 64;   // 256 workers + two warps computing the next tile's taps
 constexpr int TC_LBO_F = 36;      // operand tile: 144 B between K-adjacent core matrices (128 B + 16 B skew: the 12 lanes that
                                   // write the chunks of one sample row then hit different banks)
-int g_app_fwd_tc = 1;           // bring-up switch (ftrf_debug_set_app_tc)
+FTRF_SWITCH(int, g_app_fwd_tc, 1);           // bring-up switch (ftrf_debug_set_app_tc)
 
 __global__ void __launch_bounds__(TC_THREADS, 2)
 app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM) {
@@ -353,8 +358,8 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
 
 // Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
 constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thread
-int g_app_bwd_onegather = 1;    // VM: single-gather kernel (app_bwd_vm_kernel); 0 = two-gather kernel below
-int g_app_bwd_runs = -1;        // samples per run-merging segment of the VM scatter; 0 = one reduction set per sample, -1 = auto
+FTRF_SWITCH(int, g_app_bwd_onegather, 1);    // VM: single-gather kernel (app_bwd_vm_kernel); 0 = two-gather kernel below
+FTRF_SWITCH(int, g_app_bwd_runs, -1);        // samples per run-merging segment of the VM scatter; 0 = one reduction set per sample, -1 = auto
 
 __global__ void __launch_bounds__(256, 2)
 app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun) {
@@ -754,7 +759,7 @@ constexpr int BT_ISSUER = BT_WORK + 32;  // the thread that issues the MMA batch
                                          // dWb batch of a tile is issued while the 576 workers already stage the next one
 constexpr int BT_RUN = 4;              // samples per scatter segment = one 16-byte K unit of the product operand
 constexpr int BT_PT_SBO_F = 16 * 32 + 4;   // floats between 8-row groups of the product operand (2048 B + 16 B skew)
-int g_app_bwd_tc = 1;                  // ftrf_debug_set_app_bwd_tc
+FTRF_SWITCH(int, g_app_bwd_tc, 1);                  // ftrf_debug_set_app_bwd_tc
 
 struct AppBwdTcLayout { int np, rows_pt, qcols, tmem_cols; size_t wbi, g, gt, pt, q, tap, gf, bars, total; };
 static __host__ __device__ inline AppBwdTcLayout app_bwd_tc_layout(int NP) {
@@ -1063,6 +1068,7 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_set_app_tc(int on) {
   ftrf::g_app_fwd_tc = on;
   return 0;
@@ -1079,3 +1085,4 @@ extern "C" int ftrf_debug_set_app_runs(int runs) {
   ftrf::g_app_bwd_runs = runs;
   return 0;
 }
+#endif

@@ -14,7 +14,7 @@
 namespace ftrf {
 
 constexpr int GS = 4;   // lanes per sample
-int g_density_bwd_runs = 12;  // longest segment a lane group of the run-merging backward walks; 0 = one reduction set per sample (ftrf_debug_set_runs)
+FTRF_SWITCH(int, g_density_bwd_runs, 12);  // longest segment a lane group of the run-merging backward walks; 0 = one reduction set per sample (ftrf_debug_set_runs)
 
 __device__ __forceinline__ float group_sum(float v) {
   v += __shfl_xor_sync(FULL_MASK, v, 1);
@@ -163,6 +163,25 @@ density_at_kernel(const FtrfField f, const float* __restrict__ xyz, int64_t n, f
     }
     float feat = group_sum(part);
     if (s < n && sub == 0) out[s] = keep ? activate(f, feat) : 0.f;
+  }
+}
+
+// compute_densityfeature on points (models/tensoRF.py:207-227, :358-386): normalised coordinates in, the raw
+// sigma feature out (no alphaMask, no activation) — the module method, on the gather code of the hot path
+__global__ void __launch_bounds__(256)
+density_feature_kernel(const FtrfField f, const float* __restrict__ xn_in, int64_t n, float* __restrict__ out) {
+  const int sub = threadIdx.x & (GS - 1);
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  const int64_t n_pad = (n + 7) & ~(int64_t)7;
+  for (int64_t s = g0; s < n_pad; s += gstride) {
+    float part = 0.f;
+    if (s < n) {
+      const float xn[3] = {__ldg(xn_in + 3 * s), __ldg(xn_in + 3 * s + 1), __ldg(xn_in + 3 * s + 2)};
+      part = density_partial(f, xn, sub);
+    }
+    const float feat = group_sum(part);
+    if (s < n && sub == 0) out[s] = feat;
   }
 }
 
@@ -485,6 +504,12 @@ int launch_dense_alpha_bits(const FtrfField& f, const float* lin, int X, int Y, 
   return check_launch("dense_alpha_bits");
 }
 
+int launch_density_feature(const FtrfField& f, const float* xn, int64_t n, float* out, cudaStream_t st) {
+  if (n == 0) return FTRF_OK;
+  density_feature_kernel<<<sample_grid(n), 256, 0, st>>>(f, xn, n, out);
+  return check_launch("density_feature");
+}
+
 int launch_density_at(const FtrfField& f, const float* xyz, int64_t n, float* out, cudaStream_t st) {
   if (n == 0) return FTRF_OK;
   density_at_kernel<<<sample_grid(n), 256, 0, st>>>(f, xyz, n, out);
@@ -493,7 +518,9 @@ int launch_density_at(const FtrfField& f, const float* xyz, int64_t n, float* ou
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_set_runs(int density_runs) {
   ftrf::g_density_bwd_runs = density_runs;
   return 0;
 }
+#endif

@@ -217,6 +217,7 @@ int launch_gemm3x(const Gemm3xArgs& a, cudaStream_t st) {
 }  // namespace ftrf
 
 // test / bring-up entry (declared in include/fewtensorf.h)
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B, int64_t sn, int64_t sk, int N,
                                 int K, const float* bias, const float* mask, int ldm, int relu, float* out, int ldo,
                                 int variant, void* stream) {
@@ -226,3 +227,4 @@ extern "C" int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, cons
   a.bias = bias; a.mask = mask; a.ldm = ldm; a.relu = relu; a.out = out; a.ldo = ldo; a.variant = variant;
   return ftrf::launch_gemm3x(a, (cudaStream_t)stream);
 }
+#endif

@@ -1,6 +1,5 @@
-// k_shade.cu — stage 3 forward: positional encoding (+ FreeNeRF encoding mask) -> 3-layer MLP ->
-// sigmoid, or SH degree-2 shading.  Replaces MLPRender_Fea / MLPRender_PE / MLPRender
-// (models/mlp.py:27-155) and SHRender + eval_sh_bases(2,.) (models/mlp.py:15-19, models/sh.py:87-112).
+// k_shade.cu — TEST BUILD ONLY (libfewtensorf_b200_test.so): the first, fp32 CUDA-core forward of the shading MLP
+// (models/mlp.py:27-155), kept as an independent cross-check of the tcgen05 kernels the product runs.
 //
 // v1 data path (fp32 CUDA cores, exact fp32 products so the 1e-4 parity budget holds): persistent
 // CTAs, both weight matrices resident in shared memory (k-major), 64-sample tiles, 4x8 register
@@ -100,92 +99,30 @@ shade_mlp_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InS
   }
 }
 
-// ------------------------------------------------------------------------------------------ SH
-__device__ __forceinline__ void sh_basis2(const float v[3], float b[9]) {   // models/sh.py:98-112
-  const float x = v[0], y = v[1], z = v[2];
-  const float xx = x * x, yy = y * y, zz = z * z;
-  b[0] = 0.28209479177387814f;
-  b[1] = -0.4886025119029199f * y;
-  b[2] = 0.4886025119029199f * z;
-  b[3] = -0.4886025119029199f * x;
-  b[4] = 1.0925484305920792f * (x * y);
-  b[5] = -1.0925484305920792f * (y * z);
-  b[6] = 0.31539156525252005f * (2.0f * zz - xx - yy);
-  b[7] = -1.0925484305920792f * (x * z);
-  b[8] = 0.5462742152960396f * (xx - yy);
-}
-
-__global__ void __launch_bounds__(256)
-shade_sh_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
-  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
-  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
-    float view[3], pos[3], b[9];
-    shade_geometry(f, c, ws, s, view, pos);
-    sh_basis2(view, b);
-    const float* ft = ws.a_feat + s * f.app_dim;
-#pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-      float a = 0.f;
-#pragma unroll
-      for (int j = 0; j < 9; ++j) a = fmaf(b[j], ft[ch * 9 + j], a);
-      ws.a_rgb[s * 3 + ch] = fmaxf(a + 0.5f, 0.f);          // models/mlp.py:18
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256)
-shade_sh_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
-  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
-  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
-    float view[3], pos[3], b[9];
-    shade_geometry(f, c, ws, s, view, pos);
-    sh_basis2(view, b);
-#pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-      float g = ws.a_rgb[s * 3 + ch] > 0.f ? ws.a_grgb[s * 3 + ch] : 0.f;
-#pragma unroll
-      for (int j = 0; j < 9; ++j) ws.a_gfeat[s * f.app_dim + ch * 9 + j] = g * b[j];
-    }
-  }
-}
-
 size_t shade_fwd_smem(const InSpec& sp) {
   int ka = sp.kp + 4 > HS ? sp.kp + 4 : HS;
   size_t fl = (size_t)sp.kp * FC + FC * FC + 3 * FC + 2 * FC + 4 + (size_t)ST * ka + (size_t)ST * HS;
   return fl * sizeof(float);
 }
 
-// cuda_core: the fp32 CUDA-core kernels keep W1 and W2 whole in shared memory, which bounds the input width;
-// the tcgen05 back ends split a wide first layer instead (k_shade_tc.cu).
-int shade_check(const FtrfField& f, const InSpec& sp, bool cuda_core) {
-  if (f.feature_c != FC) { set_error("shade: featureC must be %d (got %d)", FC, f.feature_c); return FTRF_E_ARG; }
-  if (sp.in_dim != f.in_dim) { set_error("shade: in_dim %d does not match the shading mode (%d)", f.in_dim, sp.in_dim); return FTRF_E_ARG; }
-  if (sp.D + 6 > HS) { set_error("shade: unsupported input width %d", sp.in_dim); return FTRF_E_ARG; }
-  if (cuda_core && shade_fwd_smem(sp) > 227 * 1024) {
+int shade_check(const FtrfField& f, const InSpec& sp);
+// the CUDA-core kernels keep W1 and W2 whole in shared memory, which bounds the input width
+int shade_check_v1(const FtrfField& f, const InSpec& sp) {
+  if (int e = shade_check(f, sp)) return e;
+  if (shade_fwd_smem(sp) > 227 * 1024) {
     set_error("shade: input width %d needs too much shared memory on the CUDA-core back end (use the tensor-core one)", sp.in_dim);
     return FTRF_E_ARG;
   }
   return FTRF_OK;
 }
 
-int launch_shade_sh(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.app_dim != 27) { set_error("SH shading needs app_dim 27"); return FTRF_E_ARG; }
-  shade_sh_fwd_kernel<<<FTRF_SMS * 4, 256, 0, st>>>(f, c, ws);
-  return check_launch("shade_sh_fwd");
-}
-
 int launch_shade_v1(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp, true)) return e;
+  if (int e = shade_check_v1(f, sp)) return e;
   size_t smem = shade_fwd_smem(sp);
   cudaFuncSetAttribute(shade_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   shade_mlp_fwd_kernel<<<FTRF_SMS, 256, smem, st>>>(f, c, ws, sp);
   return check_launch("shade_mlp_fwd");
-}
-
-int launch_shade_sh_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  shade_sh_bwd_kernel<<<FTRF_SMS * 4, 256, 0, st>>>(f, c, ws);
-  return check_launch("shade_sh_bwd");
 }
 
 }  // namespace ftrf

@@ -271,12 +271,12 @@ shade_wgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const InSpe
   }
 }
 
-int shade_check(const FtrfField& f, const InSpec& sp, bool cuda_core);
+int shade_check_v1(const FtrfField& f, const InSpec& sp);
 int launch_shade_sh_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 
 int launch_shade_bwd_v1(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp, true)) return e;
+  if (int e = shade_check_v1(f, sp)) return e;
   if (sp.kp > 192) { set_error("shade backward: input width %d > 192 unsupported", sp.in_dim); return FTRF_E_ARG; }
   size_t sm_h = (size_t)(FC * FC + 3 * FC + 2 * ST * HS + ST * 4) * sizeof(float);
   size_t sm_i = (size_t)(FC * 192 + ST * HS + ST * 196) * sizeof(float);

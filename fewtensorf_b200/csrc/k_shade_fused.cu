@@ -15,7 +15,6 @@
 //              (TMA), completion on mbarriers.  Each weight chunk serves both sub-tiles.
 // Roles meet only through mbarriers: a_full / a_empty (operand ring), w_full / w_empty (weight
 // ring), acc1_full / acc2_full (tcgen05.commit).  TMEM: acc1[a,b] columns 0-255, acc2[a,b] 256-511.
-#include <atomic>
 #include "fused.cuh"
 #include "tc.cuh"
 
@@ -134,8 +133,8 @@ struct StaticSpec {
 struct DynamicSpec { static constexpr bool is_static = false; };
 
 // optional phase timeline of CTA 0 (debug aid, scripts/fused_timeline.py): dbg[role*512 + n]
-static long long* g_fused_dbg = nullptr;
-static long long* g_dgrad_dbg = nullptr;
+FTRF_SWITCH(long long*, g_fused_dbg, nullptr);
+FTRF_SWITCH(long long*, g_dgrad_dbg, nullptr);
 #define FZ_T(role, n) do { if (dbg && blockIdx.x == 0 && (n) < 512) dbg[(role) * 512 + (n)] = clock64(); } while (0)
 
 
@@ -259,9 +258,10 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
               float x0 = 0.f, x1 = 0.f;
               if (pi.kind == PK_TRIG) {
                 const SPair pr = s_pair[P];
-                // octave 0: sincosf; octave f: double-angle step from octave f-1 (the pairs of one
-                // channel are consecutive, frequency-minor) — 2 ulp-grade, far inside the 1e-4 budget
-                if (pi.fexp == 0) fast_sincos(src[pi.sa], &da_s, &da_c);
+                // octaves 0, 4, 8, ...: sincos of the scaled argument; the others: double-angle step from the octave
+                // below (the pairs of one channel are consecutive, frequency-minor).  Each step doubles the absolute
+                // error, so at most three are chained (pos_pe 8 of configs/free_tensorf_human.txt would chain seven).
+                if ((pi.fexp & 3) == 0) fast_sincos(src[pi.sa] * (float)(1 << pi.fexp), &da_s, &da_c);
                 else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
                 x0 = da_s * pr.ma;
                 x1 = da_c * pr.mb;
@@ -287,7 +287,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
             const int kind = pr.meta & 0xff, sa = (pr.meta >> 8) & 0xff, sb = (pr.meta >> 16) & 0xff;
             float x0 = 0.f, x1 = 0.f;
             if (kind == PK_TRIG) {
-              if (pr.scale == 1.f) fast_sincos(src[sa], &da_s, &da_c);
+              if (((__float_as_int(pr.scale) >> 23) & 3) == 3) fast_sincos(src[sa] * pr.scale, &da_s, &da_c);   // 2^f with f % 4 == 0
               else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
               x0 = da_s * pr.ma;
               x1 = da_c * pr.mb;
@@ -567,7 +567,7 @@ __device__ __forceinline__ void bz_epilogue(uint32_t t_acc2, const SPair* s_pair
         if (pi.kind == PK_COPY2 && bz_owned<SS>(pi.sb, H)) gf[pi.sb - C0] += gx[2 * pp + 1];
       } else if (pi.kind == PK_TRIG && bz_owned<SS>(pi.sa, H)) {
         const SPair pr = s_pair[P];
-        if (pi.fexp == 0) fast_sincos(ft[pi.sa - C0], &da_s, &da_c);
+        if ((pi.fexp & 3) == 0) fast_sincos(ft[pi.sa - C0] * (float)(1 << pi.fexp), &da_s, &da_c);
         else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
         // d/dfeat of (sin(a) ms, cos(a) mc), a = feat 2^f
         gf[pi.sa - C0] += (float)(1 << pi.fexp) * (da_c * pr.ma * gx[2 * pp] - da_s * pr.mb * gx[2 * pp + 1]);
@@ -785,155 +785,150 @@ size_t fused_bwd_wimg_floats() { return (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)8
 static int dgrad_variant(const FtrfField& f, const FusedSpec& fs) {
   using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
   using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
+  using SFew = StaticSpec<FTRF_SHADE_MLP, 18, 8, 2, 2>;      // configs/free_tensorf_human.txt:46-54: 153 inputs
   const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
   if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) return 0;
   if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) return 1;
-  return -1;                                     // (MLP: kp = 168 > 160 rows of the W1^T chunk; generic path)
+  if (f.shading == FTRF_SHADE_MLP && f.app_dim == 18 && f.pos_pe == 8 && f.view_pe == 2 && f.fea_pe == 2 && fs.kp == SFew::kp) return 2;
+  return -1;                                     // (MLP 27/2/2/2: kp = 168 > 160 rows of the W1^T chunk; generic path)
 }
 
 // The weight images only depend on the parameters, not on anything the step computes, so ftrf_forward_ex builds
 // them on a side stream at the very start of the call (beside march / density) instead of in front of the fused
 // forward and dgrad kernels, where the two ~7 us latency-bound launches sat on the step's serial chain.
-// Thread-local: entry points stay re-entrant; the hints are keyed by the image address inside the workspace.
-struct PrepAhead {
+// What a call has pending (images built ahead, side-stream work to join) is recorded in the caller's FtrfCall
+// (lib_flags / lib_ctx, see call_state()): the backward may run on another host thread than the forward (autograd
+// engine), and a split backward's two halves may run on different threads, without any process-wide state.
+// Each host thread only CACHES a side stream and its events here (created on first use, never freed: a context
+// recorded in a call must outlive the thread that made it).
+struct SideCtx {
   cudaStream_t side = nullptr;
-  cudaEvent_t fork = nullptr, done = nullptr;
-  const float* img_fwd = nullptr;      // forward image built ahead, join pending
-  bool forked = false;                 // phase 0 recorded the fork event of this call
-  int dev = -1;                        // device the side stream lives on
-};
-static thread_local PrepAhead g_prep;
-// The two hints the BACKWARD consumes are process-wide: an autograd engine runs it on another host thread than the
-// forward.  They are keyed by the address inside the workspace and taken with an exchange, so concurrent hosts can
-// at worst lose a hint (and prepare in line), never see a wrong one.
-static std::atomic<const float*> g_hint_img_bwd{nullptr}, g_hint_scratch{nullptr};
-static bool take_hint(std::atomic<const float*>& h, const float* want) {
-  const float* expect = want;
-  return h.compare_exchange_strong(expect, nullptr);
-}
-
-// The calling thread's side stream (created on first use; an autograd engine runs the backward on its own thread,
-// which gets its own).
-static bool ensure_side() {
+  cudaEvent_t fork = nullptr, done = nullptr;            // forward: weight images
+  cudaEvent_t tail_fork = nullptr, tail_done = nullptr;  // backward: un-permute of dW1
+  cudaEvent_t scan_fork = nullptr, scan_done = nullptr;  // backward: reverse scan of the integration stage
   int dev = -1;
-  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return false; }
-  if (g_prep.side) return g_prep.dev == dev;     // (one process per GPU; a thread that switches devices runs in line)
-  g_prep.dev = dev;
-  if (cudaStreamCreateWithFlags(&g_prep.side, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreateWithFlags(&g_prep.fork, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&g_prep.done, cudaEventDisableTiming) != cudaSuccess) {
-    g_prep.side = nullptr;
+};
+static thread_local SideCtx* t_side = nullptr;
+
+// The calling thread's side-stream context for the current device (nullptr: none, callers run in line).
+static SideCtx* ensure_side() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (t_side) return t_side->dev == dev ? t_side : nullptr;     // (one process per GPU; a thread that switches devices runs in line)
+  SideCtx* s = new SideCtx();
+  s->dev = dev;
+  bool ok = cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking) == cudaSuccess;
+  cudaEvent_t* evs[6] = {&s->fork, &s->done, &s->tail_fork, &s->tail_done, &s->scan_fork, &s->scan_done};
+  for (int i = 0; ok && i < 6; ++i) ok = cudaEventCreateWithFlags(evs[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
     cudaGetLastError();
-    return false;
+    delete s;
+    return nullptr;
   }
-  return true;
+  t_side = s;
+  return s;
 }
 
 // A tail that nothing later in the backward reads (the un-permute of the dW1 scratch into g_w1 / g_b1) runs on the
 // side stream beside the appearance and density backward kernels: side_tail_begin() orders the side stream after
 // everything enqueued on `st` so far and returns it (nullptr: no side stream, run in line); side_tail_end() records
-// its completion; side_tail_join() makes `st` wait for it (end of the backward call).
-static thread_local cudaEvent_t g_tail_fork = nullptr, g_tail_done = nullptr;
-static thread_local bool g_tail_pending = false;
-cudaStream_t side_tail_begin(cudaStream_t st) {
-  if (!ensure_side()) return nullptr;
-  if (!g_tail_fork) {
-    if (cudaEventCreateWithFlags(&g_tail_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&g_tail_done, cudaEventDisableTiming) != cudaSuccess) {
-      g_tail_fork = g_tail_done = nullptr;
-      cudaGetLastError();
-      return nullptr;
-    }
-  }
-  if (cudaEventRecord(g_tail_fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_tail_fork, 0) != cudaSuccess) {
+// its completion in the call; side_tail_join() makes `st` wait for it (end of the backward call).
+cudaStream_t side_tail_begin(const FtrfCall& c, cudaStream_t st) {
+  SideCtx* s = ensure_side();
+  if (!s) return nullptr;
+  CallState& cs = call_state(c);
+  if ((cs.flags & (CALL_TAIL_PENDING | CALL_SCAN_PENDING)) && cs.ctx != s) return nullptr;   // another thread's work pending: in line
+  if (cudaEventRecord(s->tail_fork, st) != cudaSuccess || cudaStreamWaitEvent(s->side, s->tail_fork, 0) != cudaSuccess) {
     cudaGetLastError();
     return nullptr;
   }
-  return g_prep.side;
+  return s->side;
 }
-void side_tail_end() {
-  if (cudaEventRecord(g_tail_done, g_prep.side) == cudaSuccess) g_tail_pending = true;
+void side_tail_end(const FtrfCall& c) {
+  SideCtx* s = t_side;
+  CallState& cs = call_state(c);
+  if (s && cudaEventRecord(s->tail_done, s->side) == cudaSuccess) { cs.flags |= CALL_TAIL_PENDING; cs.ctx = s; }
 }
-int side_tail_join(cudaStream_t st) {
-  if (!g_tail_pending) return FTRF_OK;
-  g_tail_pending = false;
-  if (cudaStreamWaitEvent(st, g_tail_done, 0) != cudaSuccess) return check_launch("side tail join");
+int side_tail_join(const FtrfCall& c, cudaStream_t st) {
+  CallState& cs = call_state(c);
+  if (!(cs.flags & CALL_TAIL_PENDING)) return FTRF_OK;
+  cs.flags &= ~(uint64_t)CALL_TAIL_PENDING;
+  if (cudaStreamWaitEvent(st, static_cast<SideCtx*>(cs.ctx)->tail_done, 0) != cudaSuccess) return check_launch("side tail join");
   return FTRF_OK;
 }
 
 // Same for the reverse scan of the integration backward (only the density backward reads its sigma gradients).
-static thread_local cudaEvent_t g_scan_fork = nullptr, g_scan_done = nullptr;
-static thread_local bool g_scan_pending = false;
-cudaStream_t side_scan_begin(cudaStream_t st) {
-  if (!ensure_side()) return nullptr;
-  if (!g_scan_fork) {
-    if (cudaEventCreateWithFlags(&g_scan_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&g_scan_done, cudaEventDisableTiming) != cudaSuccess) {
-      g_scan_fork = g_scan_done = nullptr;
-      cudaGetLastError();
-      return nullptr;
-    }
-  }
-  if (cudaEventRecord(g_scan_fork, st) != cudaSuccess || cudaStreamWaitEvent(g_prep.side, g_scan_fork, 0) != cudaSuccess) {
+cudaStream_t side_scan_begin(const FtrfCall& c, cudaStream_t st) {
+  SideCtx* s = ensure_side();
+  if (!s) return nullptr;
+  CallState& cs = call_state(c);
+  if ((cs.flags & (CALL_TAIL_PENDING | CALL_SCAN_PENDING)) && cs.ctx != s) return nullptr;
+  if (cudaEventRecord(s->scan_fork, st) != cudaSuccess || cudaStreamWaitEvent(s->side, s->scan_fork, 0) != cudaSuccess) {
     cudaGetLastError();
     return nullptr;
   }
-  return g_prep.side;
+  return s->side;
 }
-void side_scan_end() {
-  if (cudaEventRecord(g_scan_done, g_prep.side) == cudaSuccess) g_scan_pending = true;
+void side_scan_end(const FtrfCall& c) {
+  SideCtx* s = t_side;
+  CallState& cs = call_state(c);
+  if (s && cudaEventRecord(s->scan_done, s->side) == cudaSuccess) { cs.flags |= CALL_SCAN_PENDING; cs.ctx = s; }
 }
-int side_scan_join(cudaStream_t st) {
-  if (!g_scan_pending) return FTRF_OK;
-  g_scan_pending = false;
-  if (cudaStreamWaitEvent(st, g_scan_done, 0) != cudaSuccess) return check_launch("side scan join");
+int side_scan_join(const FtrfCall& c, cudaStream_t st) {
+  CallState& cs = call_state(c);
+  if (!(cs.flags & CALL_SCAN_PENDING)) return FTRF_OK;
+  cs.flags &= ~(uint64_t)CALL_SCAN_PENDING;
+  if (cudaStreamWaitEvent(st, static_cast<SideCtx*>(cs.ctx)->scan_done, 0) != cudaSuccess) return check_launch("side scan join");
   return FTRF_OK;
 }
 
-bool prep_ahead_take_scratch(const float* scratch) {
-  return take_hint(g_hint_scratch, scratch);
+bool prep_ahead_take_scratch(const FtrfCall& c) {
+  CallState& cs = call_state(c);
+  const bool had = (cs.flags & CALL_SCRATCH_READY) != 0;
+  cs.flags &= ~(uint64_t)CALL_SCRATCH_READY;
+  return had;
 }
 
 // phase 0 (before the call's first kernel is launched): mark the fork point on the caller's stream; phase 1 (after
 // that launch, so the host work below does not delay it): build the images on the side stream behind the mark.
 int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, int phase) {
+  CallState& cs = call_state(c);
   if (phase == 0) {
-    g_prep.img_fwd = nullptr;
-    g_hint_img_bwd.store(nullptr);
-    g_hint_scratch.store(nullptr);
-    g_prep.forked = false;
-  } else if (!g_prep.forked) {
+    cs.flags = 0;
+    cs.ctx = nullptr;
+  } else if (!(cs.flags & CALL_FORKED)) {
     return FTRF_OK;
   }
   if (f.shading == FTRF_SHADE_SH || c.cap_app == 0 || !ws.wimg) return FTRF_OK;
   InSpec sp = make_spec(f);
   FusedSpec fs;
   if (sp.in_dim != f.in_dim || !make_fused_spec(f, sp, fs) || fs.kp > ws.ldx) return FTRF_OK;
-  if (!ensure_side()) return FTRF_OK;            // no side stream: the launchers build the images in line
+  SideCtx* s = ensure_side();
+  if (!s) return FTRF_OK;                        // no side stream: the launchers build the images in line
   // after everything already on the caller's stream (the previous call's kernels still read the images)
   if (phase == 0) {
-    if (cudaEventRecord(g_prep.fork, st) != cudaSuccess) return check_launch("prep_ahead fork");
-    g_prep.forked = true;
+    if (cudaEventRecord(s->fork, st) != cudaSuccess) return check_launch("prep_ahead fork");
+    cs.flags |= CALL_FORKED;
+    cs.ctx = s;
     return FTRF_OK;
   }
-  g_prep.forked = false;
-  if (cudaStreamWaitEvent(g_prep.side, g_prep.fork, 0) != cudaSuccess) return check_launch("prep_ahead fork wait");
+  cs.flags &= ~(uint64_t)CALL_FORKED;
+  if (cudaStreamWaitEvent(s->side, s->fork, 0) != cudaSuccess) return check_launch("prep_ahead fork wait");
   float* img = ws.wimg;
   float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
-  prep_weights_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, img, w1p, sp.in_dim);
+  prep_weights_kernel<<<72, 128, 0, s->side>>>(f, fs, img, w1p, sp.in_dim);
   if (int e = check_launch("prep_weights")) return e;
-  g_prep.img_fwd = img;
+  cs.flags |= CALL_IMG_FWD_PENDING;
   if (c.save_for_backward && dgrad_variant(f, fs) >= 0) {
     float* bimg = ws.wimg + fused_bwd_offset_floats();
-    prep_weights_bwd_kernel<<<72, 128, 0, g_prep.side>>>(f, fs, bimg, sp.in_dim);
+    prep_weights_bwd_kernel<<<72, 128, 0, s->side>>>(f, fs, bimg, sp.in_dim);
     if (int e = check_launch("prep_weights_bwd")) return e;
-    g_hint_img_bwd.store(bimg);
     // the weight-gradient kernel's zeroed dW1 scratch (read by nothing before it): same side stream
     float* scratch = ws.wimg + fused_scratch_offset_floats();
-    if (cudaMemsetAsync(scratch, 0, wgrad_fused_scratch_bytes(), g_prep.side) != cudaSuccess) return check_launch("wgrad scratch memset");
-    g_hint_scratch.store(scratch);
+    if (cudaMemsetAsync(scratch, 0, wgrad_fused_scratch_bytes(), s->side) != cudaSuccess) return check_launch("wgrad scratch memset");
+    cs.flags |= CALL_IMG_BWD_READY | CALL_SCRATCH_READY;
   }
-  if (cudaEventRecord(g_prep.done, g_prep.side) != cudaSuccess) return check_launch("prep_ahead done");
+  if (cudaEventRecord(s->done, s->side) != cudaSuccess) return check_launch("prep_ahead done");
   return FTRF_OK;
 }
 
@@ -944,13 +939,15 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
   if (!make_fused_spec(f, sp, fs) || fs.kp > ws.ldx || !ws.wimg) return FTRF_OK;
   using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
   using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
+  using SFew = StaticSpec<FTRF_SHADE_MLP, 18, 8, 2, 2>;
   const int which = dgrad_variant(f, fs);
   if (which < 0) return FTRF_OK;
   *handled = true;
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg + fused_bwd_offset_floats();
-  if (take_hint(g_hint_img_bwd, img)) {
-    // built by this call's forward on the side stream, which the forward joined
+  CallState& cs = call_state(c);
+  if (cs.flags & CALL_IMG_BWD_READY) {
+    cs.flags &= ~(uint64_t)CALL_IMG_BWD_READY;      // built by this call's forward on the side stream, which the forward joined
   } else {
     prep_weights_bwd_kernel<<<72, 128, 0, st>>>(f, fs, img, sp.in_dim);
     if (int e = check_launch("prep_weights_bwd")) return e;
@@ -964,7 +961,8 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
     kern<<<grid, BZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_dgrad_dbg);
   };
   if (which == 0) go(shade_fused_dgrad_kernel<SFea>);
-  else go(shade_fused_dgrad_kernel<SPe>);
+  else if (which == 1) go(shade_fused_dgrad_kernel<SPe>);
+  else go(shade_fused_dgrad_kernel<SFew>);
   return check_launch("shade_fused_dgrad");
 }
 
@@ -983,12 +981,12 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg;
   float* w1p = c.save_for_backward ? img + fused_w1p_offset_floats() : nullptr;
-  if (g_prep.img_fwd == img) {
-    g_prep.img_fwd = nullptr;        // built at the start of this call on the side stream: join
-    if (cudaStreamWaitEvent(st, g_prep.done, 0) != cudaSuccess) return check_launch("prep_ahead join");
+  CallState& cs = call_state(c);
+  if (cs.flags & CALL_IMG_FWD_PENDING) {
+    cs.flags &= ~(uint64_t)CALL_IMG_FWD_PENDING;   // built at the start of this call on the side stream: join
+    if (cudaStreamWaitEvent(st, static_cast<SideCtx*>(cs.ctx)->done, 0) != cudaSuccess) return check_launch("prep_ahead join");
   } else {
-    g_hint_img_bwd.store(nullptr);               // (stage-level call: nothing was built ahead, stale hints must not survive)
-    g_hint_scratch.store(nullptr);
+    cs.flags &= ~(uint64_t)(CALL_IMG_BWD_READY | CALL_SCRATCH_READY);   // (stage-level call: nothing was built ahead)
     prep_weights_kernel<<<72, 128, 0, st>>>(f, fs, img, w1p, sp.in_dim);
     if (int e = check_launch("prep_weights")) return e;
   }
@@ -1003,16 +1001,19 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
   using SPe = StaticSpec<FTRF_SHADE_MLP_PE, 27, 2, 2, 2>;
   using SMlp = StaticSpec<FTRF_SHADE_MLP, 27, 2, 2, 2>;
+  using SFew = StaticSpec<FTRF_SHADE_MLP, 18, 8, 2, 2>;      // configs/free_tensorf_human.txt:46-54
   const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
   if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) go(shade_fused_fwd_kernel<SFea>);
   else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) go(shade_fused_fwd_kernel<SPe>);
   else if (f.shading == FTRF_SHADE_MLP && pe2 && f.pos_pe == 2 && f.fea_pe == 2 && fs.kp == SMlp::kp) go(shade_fused_fwd_kernel<SMlp>);
+  else if (f.shading == FTRF_SHADE_MLP && f.app_dim == 18 && f.pos_pe == 8 && f.view_pe == 2 && f.fea_pe == 2 && fs.kp == SFew::kp) go(shade_fused_fwd_kernel<SFew>);
   else go(shade_fused_fwd_kernel<DynamicSpec>);
   return check_launch("shade_fused_fwd");
 }
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_dgrad_timeline(void* device_buffer_3x512_i64) {
   ftrf::g_dgrad_dbg = (long long*)device_buffer_3x512_i64;
   return FTRF_OK;
@@ -1022,3 +1023,4 @@ extern "C" int ftrf_debug_fused_timeline(void* device_buffer_3x512_i64) {
   ftrf::g_fused_dbg = (long long*)device_buffer_3x512_i64;
   return FTRF_OK;
 }
+#endif

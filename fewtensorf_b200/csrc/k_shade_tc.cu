@@ -239,13 +239,15 @@ pe_bwd_internal_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const I
 }
 
 // ---------------------------------------------------------------------------------------- drivers
-int shade_check(const FtrfField& f, const InSpec& sp, bool cuda_core);
+int shade_check(const FtrfField& f, const InSpec& sp);
 int launch_shade_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_bwd_v1(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_sh(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 int launch_shade_sh_bwd(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t);
 
-static int g_shade_path = 2;     // 2 = fused tcgen05 kernels, 1 = tcgen05 GEMM per layer, 0 = fp32 CUDA cores (v1)
+// 2 = fused tcgen05 kernels (per-layer tcgen05 GEMMs for the shapes they do not cover); the test build can also
+// force 1 = one tcgen05 GEMM per layer, 0 = fp32 CUDA cores (k_shade.cu / k_shade_bwd.cu, cross-checks only)
+FTRF_SWITCH(int, g_shade_path, 2);
 
 static Gemm3xArgs gemm_args(const Ws& ws, const FtrfCall& c) {
   Gemm3xArgs g{};
@@ -297,9 +299,11 @@ bool shade_path_is_fused() { return g_shade_path == 2; }
 
 int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
   if (f.shading == FTRF_SHADE_SH) return launch_shade_sh(f, c, ws, st);
+#ifdef FTRF_TEST_BUILD
   if (!g_shade_path) return launch_shade_v1(f, c, ws, st);
+#endif
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp, false)) return e;
+  if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
   if (g_shade_path == 2) {
     bool handled = false;
@@ -325,9 +329,11 @@ int launch_shade(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream
 // all their work in part 1.
 int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, int part) {
   if (f.shading == FTRF_SHADE_SH) return part == 2 ? FTRF_OK : launch_shade_sh_bwd(f, c, ws, st);
+#ifdef FTRF_TEST_BUILD
   if (!g_shade_path) return part == 2 ? FTRF_OK : launch_shade_bwd_v1(f, c, ws, st);
+#endif
   InSpec sp = make_spec(f);
-  if (int e = shade_check(f, sp, false)) return e;
+  if (int e = shade_check(f, sp)) return e;
   if (c.cap_app == 0) return FTRF_OK;
   FusedSpec fs;
   const bool internal = g_shade_path == 2 && make_fused_spec(f, sp, fs) && fs.kp <= ws.ldx && ws.wimg;   // X saved by the fused forward
@@ -339,7 +345,7 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     wa.g2 = ws.a_gh2; wa.h1 = ws.a_h1; wa.g1 = ws.a_gh1; wa.x = ws.a_x; wa.ldx = ws.ldx; wa.kp = fs.kp;
     wa.count = ws.counters + 1; wa.cap = c.cap_app; wa.dw2 = f.g_w2;
     wa.dw1i = ws.wimg + fused_scratch_offset_floats();
-    int e = launch_wgrad_fused(wa, fs, f.g_w1, sp.in_dim, f.g_b1, st);
+    int e = launch_wgrad_fused(wa, fs, f.g_w1, sp.in_dim, f.g_b1, st, &c);
     prof_end(9, st);
     return e;
   }
@@ -388,7 +394,9 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_set_shade_path(int tensor_cores) {
   ftrf::g_shade_path = tensor_cores < 0 ? 0 : (tensor_cores > 2 ? 2 : tensor_cores);
   return FTRF_OK;
 }
+#endif

@@ -171,9 +171,11 @@ int launch_wgrad3x(const Wgrad3xArgs& a, cudaStream_t st) {
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_test_wgrad3x(const float* G, int ldg, const float* A, int lda, int K, int64_t M, float* dW, int ldw,
                                  float* dbias, void* stream) {
   ftrf::Wgrad3xArgs a{};
   a.G = G; a.ldg = ldg; a.A = A; a.lda = lda; a.K = K; a.count = nullptr; a.cap = M; a.dW = dW; a.ldw = ldw; a.dbias = dbias;
   return ftrf::launch_wgrad3x(a, (cudaStream_t)stream);
 }
+#endif

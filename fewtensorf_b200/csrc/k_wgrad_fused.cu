@@ -18,7 +18,7 @@
 
 namespace ftrf {
 
-static int g_wgrad_variant = 0;
+FTRF_SWITCH(int, g_wgrad_variant, 0);
 
 constexpr int WG_KS = 16;                 // samples per chunk (2 k-steps of 8)
 constexpr int WG_STAGES = 3;
@@ -230,14 +230,15 @@ __global__ void wgrad_unpermute_kernel(const float* __restrict__ dw1i, FusedSpec
 
 size_t wgrad_fused_scratch_bytes() { return (size_t)128 * WG_NGX_MAX * 4 * sizeof(float); }
 
-int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g_w1, int ldw, float* g_b1, cudaStream_t st) {
+int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g_w1, int ldw, float* g_b1, cudaStream_t st,
+                       const FtrfCall* call) {
   WgradFusedArgs a = a_in;
   a.ngt = (a.kp / 4 + 1 + 3) & ~3;
   a.dw2_vec = ((uintptr_t)a.dw2 & 15) == 0;
   a.variant = g_wgrad_variant;
   if (a.kp < 4 || a.ngt > WG_NGX_MAX || (a.kp & 3) || (a.ldx & 3) || a.cap < 0) { set_error("wgrad_fused: bad shape kp=%d ldx=%d", a.kp, a.ldx); return FTRF_E_ARG; }
   if (a.cap == 0) return FTRF_OK;
-  if (!prep_ahead_take_scratch(a.dw1i) &&
+  if (!(call && prep_ahead_take_scratch(*call)) &&
       cudaMemsetAsync(a.dw1i, 0, wgrad_fused_scratch_bytes(), st) != cudaSuccess) return check_launch("wgrad scratch memset");
   const size_t smem = (size_t)WG_STAGES * 2 * (3 * WG_G_FLOATS + WG_KS * a.ngt * 4) * 4 + 16 * 8;
   cudaFuncSetAttribute(wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -246,14 +247,15 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
   wgrad_fused_kernel<<<grid, WG_THREADS, smem, st>>>(a);
   if (int e = check_launch("wgrad_fused")) return e;
   // nothing later in the backward reads g_w1 / g_b1: off the serial chain, joined at the end of the call
-  cudaStream_t tail = side_tail_begin(st);
+  cudaStream_t tail = call ? side_tail_begin(*call, st) : nullptr;
   wgrad_unpermute_kernel<<<(128 * a.ngt * 4 + 255) / 256, 256, 0, tail ? tail : st>>>(a.dw1i, fs, a.ngt * 4, g_w1, ldw, g_b1);
-  if (tail) side_tail_end();
+  if (tail) side_tail_end(*call);
   return check_launch("wgrad_unpermute");
 }
 
 }  // namespace ftrf
 
+#ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_wgrad_variant(int v) { ftrf::g_wgrad_variant = v; return 0; }
 
 // unit-test entry: identity column order
@@ -265,5 +267,6 @@ extern "C" int ftrf_test_wgrad_fused(const float* g2, const float* h1, const flo
   ftrf::FusedSpec fs{};
   fs.kp = kp;
   for (int k = 0; k < kp; ++k) fs.orig[k] = (int16_t)(k < ldw ? k : -1);
-  return ftrf::launch_wgrad_fused(a, fs, dw1, ldw, db1, (cudaStream_t)stream);
+  return ftrf::launch_wgrad_fused(a, fs, dw1, ldw, db1, (cudaStream_t)stream, nullptr);
 }
+#endif

@@ -51,6 +51,11 @@ inline InSpec make_spec(const FtrfField& f) {
 // view direction fed to the shading module: raw d, or d/|d| for ndc rays (tensorBase.py:337-347)
 __device__ __forceinline__ void shade_geometry(const FtrfField& f, const FtrfCall& c, const Ws& ws, int64_t s,
                                                float view[3], float pos[3]) {
+  if (ws.direct_xn) {          // points-in call (ftrf_shade_points): the caller's arrays are the list
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { pos[k] = __ldg(ws.direct_xn + 3 * s + k); view[k] = __ldg(ws.direct_view + 3 * s + k); }
+    return;
+  }
   int slot = ws.a_slot[s];
   Ray ray = load_ray_ws(f, c, ws, ws.s_ray[slot]);
   float p[3];

@@ -47,9 +47,11 @@ def all_reduce_gradients(flat_grad: torch.Tensor, group=None) -> torch.Tensor:
 
 class SymmetricGradients:
     """Flat gradient buffer of `model` in symmetric memory + all-reduce by the library's own kernels over
-    NVLink: `ftrf_p2p_allreduce` (rank r sums slice r of every GPU's copy with peer loads and stores it into
-    every copy) or `ftrf_multimem_allreduce` (the same through the NVSwitch multicast address, reduction in
-    the switch), bracketed by two cross-GPU barriers on the signal pads.  The constructor times both and NCCL
+    NVLink: `ftrf_p2p_allreduce_regions` (rank r sums its share of every GPU's copy with peer loads and stores it
+    into every copy) or `ftrf_multimem_allreduce_regions` (the same through the NVSwitch multicast address,
+    reduction in the switch), bracketed by two cross-GPU barriers on the signal pads.  Only the regions of the
+    buffer that can hold a gradient travel (`TensorBase.grad_regions`: rows / columns of each factor inside the
+    alphaMask's texel bounding box; 16 % of the planes in the un-shrunk benchmark field).  The constructor times both and NCCL
     on the real buffer and keeps the fastest (2 x B200, 71 MB: p2p 129 us, NCCL 148-166 us, multimem 220 us).
     `SymmetricGradients.create` returns None where symmetric memory cannot be set up and callers use
     `all_reduce_gradients` (NCCL) instead.
@@ -87,9 +89,35 @@ class SymmetricGradients:
         import ctypes as C
         self.group = group
         self._peer_ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+        self.model = model
+        self._regions_key = None
+        self._refresh_regions()
         self.kind = self._autotune()          # "p2p", "multimem" or "nccl", whichever is fastest here
         model.set_grad_storage(self.storage)
-        self.model = model
+
+    def _refresh_regions(self) -> None:
+        """(Re)build the table of buffer regions that can hold a gradient (TensorBase.grad_regions): only those are
+        exchanged.  Keyed on the alphaMask / grid serials, so a mask rebuild or an upsample is picked up on the next
+        all_reduce; every rank derives the same table from the same (replicated) mask."""
+        import ctypes as C
+        from ._abi import MAX_REGIONS, FtrfRegion
+        m = self.model
+        key = (m._mask_serial(), m._host["serial"])
+        if key == self._regions_key:
+            return
+        regs = m.grad_regions(self.storage.numel())
+        ok = len(regs) <= MAX_REGIONS and all(r[0] % 4 == 0 and r[1] % 4 == 0 and r[2] % 4 == 0 for r in regs)
+        if not ok:                                          # (odd component counts: exchange the whole buffer)
+            n = self.storage.numel()
+            regs = [(0, n, n, 1)]
+        self._regions = (FtrfRegion * len(regs))(*[FtrfRegion(*[int(v) for v in r]) for r in regs])
+        self._n_regions = len(regs)
+        self.exchanged_floats = sum(int(r[1]) * int(r[3]) for r in regs)
+        self._regions_key = key
+
+    def describe(self) -> str:
+        return (f"{self.kind} over {self.exchanged_floats * 4 / 1e6:.1f} of {self.storage.numel() * 4 / 1e6:.1f} MB "
+                f"(rows/columns inside the alphaMask's texel box + basis/MLP; autotuned, ms: {self.timings_ms})")
 
     @classmethod
     def create(cls, model, group=None):
@@ -114,13 +142,14 @@ class SymmetricGradients:
         if kind == "nccl":
             dist.all_reduce(self.storage, op=dist.ReduceOp.SUM, group=self.group)
             return
+        self._refresh_regions()
         self.handle.barrier(channel=0)                       # every rank's backward has written its gradients
         if kind == "multimem":
-            check(self._lib.ftrf_multimem_allreduce(int(self.handle.multicast_ptr), self.storage.numel(), self.rank,
-                                                    self.world, st), "multimem_allreduce")
+            check(self._lib.ftrf_multimem_allreduce_regions(int(self.handle.multicast_ptr), self._regions, self._n_regions,
+                                                            self.rank, self.world, st), "multimem_allreduce_regions")
         else:
-            check(self._lib.ftrf_p2p_allreduce(self._peer_ptrs, self.storage.numel(), self.rank, self.world, st),
-                  "p2p_allreduce")
+            check(self._lib.ftrf_p2p_allreduce_regions(self._peer_ptrs, self._regions, self._n_regions, self.rank,
+                                                       self.world, st), "p2p_allreduce_regions")
         self.handle.barrier(channel=1)                       # every slice is back in every copy
 
     def _autotune(self) -> str:

@@ -67,6 +67,32 @@ def _channels_last_param(t: torch.Tensor, device) -> nn.Parameter:
     return nn.Parameter(buf.permute(0, 3, 1, 2))
 
 
+def _resample_param(p: torch.Tensor, h2: int, w2: int) -> nn.Parameter:
+    """F.interpolate(p, size=(h2, w2), mode='bilinear', align_corners=True) of a channels-last factor, written
+    channels-last by `ftrf_resample_factor` (tensoRF.py:273-277)."""
+    _, c, h, w = p.shape
+    src = p.detach()
+    if not _is_channels_last(src):
+        src = src.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+    buf = torch.empty((1, int(h2), int(w2), c), dtype=torch.float32, device=p.device)
+    with torch.cuda.device(p.device):
+        check(lib.ftrf_resample_factor(src.data_ptr(), c, h, w, buf.data_ptr(), int(h2), int(w2), _stream()), "resample_factor")
+    return nn.Parameter(buf.permute(0, 3, 1, 2))
+
+
+def _crop_param(p: torch.Tensor, y0: int, y1: int, x0: int, x1: int) -> nn.Parameter:
+    """p[..., y0:y1, x0:x1] of a channels-last factor as a new channels-last Parameter (`ftrf_crop_factor`)."""
+    _, c, h, w = p.shape
+    y0, y1, x0, x1 = max(int(y0), 0), min(int(y1), h), max(int(x0), 0), min(int(x1), w)
+    src = p.detach()
+    if not _is_channels_last(src):
+        src = src.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+    buf = torch.empty((1, y1 - y0, x1 - x0, c), dtype=torch.float32, device=p.device)
+    with torch.cuda.device(p.device):
+        check(lib.ftrf_crop_factor(src.data_ptr(), c, h, w, y0, y1, x0, x1, buf.data_ptr(), _stream()), "crop_factor")
+    return nn.Parameter(buf.permute(0, 3, 1, 2))
+
+
 def _is_channels_last(p: torch.Tensor) -> bool:
     _, c, h, w = p.shape
     return p.stride() == (h * w * c, 1, w * c, c) or (p.numel() == 0)
@@ -120,6 +146,7 @@ class AlphaGridMask(nn.Module):
         self.gridSize = torch.LongTensor([vol.shape[-1], vol.shape[-2], vol.shape[-3]]).to(self.device)
         self._bits = None
         self._host = None
+        self.__dict__.pop("_bbox", None)
 
     def _finish_packed(self, bits, dims):
         x, y, z = dims
@@ -147,6 +174,25 @@ class AlphaGridMask(nn.Module):
             self._finish_packed(bits, [x, y, z])
         return (self._bits,) + self._host
 
+    def texel_bbox(self):
+        """((x0, y0, z0), (x1, y1, z1)): inclusive index bounding box of the set texels, or None for an empty mask.
+        updateAlphaMask's dilation kernel reduces it on the device; masks built from a float volume derive it here."""
+        box = self.__dict__.get("_bbox")
+        if box is None:
+            occ = self.alpha_volume[0, 0] > 0                  # (Z, Y, X)
+            if not bool(occ.any()):
+                box = False
+            else:
+                lo, hi = [], []
+                for dims in ((0, 1), (0, 2), (1, 2)):          # reduce to the X, Y, Z profile in turn
+                    prof = occ.any(dim=dims[0]).any(dim=dims[1] - 1)
+                    idx = torch.nonzero(prof).flatten()
+                    lo.append(int(idx[0]))
+                    hi.append(int(idx[-1]))
+                box = (tuple(lo), tuple(hi))
+            self.__dict__["_bbox"] = box
+        return box or None
+
     def sample_alpha(self, xyz_sampled):
         c = self.normalize_coord(xyz_sampled).view(1, -1, 1, 1, 3)
         return F.grid_sample(self.alpha_volume, c, align_corners=True).view(-1)
@@ -167,9 +213,20 @@ class _ShadingMLP(nn.Module):
         self.mlp = nn.Sequential(l1, nn.ReLU(inplace=True), l2, nn.ReLU(inplace=True), l3)
         nn.init.constant_(self.mlp[-1].bias, 0)
 
-    def forward(self, pts, viewdirs, features, mask):
-        raise RuntimeError("the shading MLP runs fused inside TensorBase.forward (libfewtensorf_b200.so); "
-                           "it has no standalone PyTorch path")
+    def forward(self, pts, viewdirs, features, mask=None):
+        """models/mlp.py:41-69 / :88-107 / :127-155 — rgb [n,3] for n shaded points, on the same fused tcgen05
+        kernels `TensorBase.forward` runs (no autograd through this stand-alone call; training goes through the field)."""
+        owner = self.__dict__.get("_owner")
+        model = owner() if owner is not None else None
+        if model is None:
+            raise RuntimeError("this shading module is not attached to a TensorVMSplit / TensorCP (its kernels read "
+                               "the field's configuration); use model.renderModule")
+        return model._shade_points(pts, viewdirs, features, mask)
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d.pop("_owner", None)          # weak back-reference, re-bound by the owning field
+        return d
 
 
 class MLPRender_Fea(_ShadingMLP):
@@ -196,8 +253,35 @@ class MLPRender(_ShadingMLP):
         self.viewpe, self.pospe, self.feape = viewpe, pospe, feape
 
 
+def _points_workspace(field, n: int, device) -> torch.Tensor:
+    nbytes = lib.ftrf_points_workspace_bytes(C.byref(field), n)
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def _as_rows(t: torch.Tensor, cols: int, device) -> torch.Tensor:
+    return t.detach().reshape(-1, cols).to(device=device, dtype=torch.float32).contiguous()
+
+
+@torch.no_grad()
 def SHRender(xyz_sampled, viewdirs, features):
-    raise RuntimeError("SH shading runs fused inside TensorBase.forward (libfewtensorf_b200.so)")
+    """models/mlp.py:15-19 with eval_sh_bases(2, .) (models/sh.py:87-112): relu(sum_j B_j(view) fea[c, j] + 0.5) on the
+    SH shading kernel of the per-ray path.  CUDA tensors only (no CPU path)."""
+    if not features.is_cuda:
+        raise RuntimeError("fewtensorf_b200 needs CUDA tensors (no CPU path)")
+    dev = features.device
+    feat = _as_rows(features, 27, dev)
+    n = feat.shape[0]
+    view, pts = _as_rows(viewdirs, 3, dev), _as_rows(xyz_sampled, 3, dev)
+    if view.shape[0] != n or pts.shape[0] != n:
+        raise RuntimeError("SHRender: points, view directions and features differ in length")
+    f = FtrfField()
+    f.model, f.shading, f.app_dim, f.feature_c = _abi.MODEL_VM, _abi.SHADE_SH, 27, 128
+    rgb = torch.empty(n, 3, dtype=torch.float32, device=dev)
+    ws = _points_workspace(f, n, dev)
+    with torch.cuda.device(dev):
+        check(lib.ftrf_shade_points(C.byref(f), pts.data_ptr(), view.data_ptr(), feat.data_ptr(), n, rgb.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), _stream()), "shade_points")
+    return rgb
 
 
 class _Workspace:
@@ -276,6 +360,18 @@ class TensorBase(nn.Module):
             self.renderModule = SHRender
         else:
             raise ValueError(f"Unrecognized shading module {shadingMode!r}")
+        self._bind_render_module()
+
+    def _bind_render_module(self):
+        """The stand-alone `renderModule(pts, viewdirs, features, mask)` call runs this field's shading kernels."""
+        rm = self.__dict__.get("_modules", {}).get("renderModule")
+        if rm is not None:
+            import weakref
+            rm.__dict__["_owner"] = weakref.ref(self)
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        self._bind_render_module()
 
     def update_stepSize(self, gridSize):
         """models/tensorBase.py:104-111.  Derived constants are evaluated in fp32 on the CPU so they
@@ -399,6 +495,66 @@ class TensorBase(nn.Module):
             self._grad_cache = (key, buf, views)
             self._field_cache = {}
         return buf, views
+
+    def _grad_texel_box(self):
+        """Per axis (x, y, z): inclusive range of FACTOR texels a kept sample can touch, or None (no alphaMask: all).
+        A sample survives stage 1 only if one of the 8 mask texels around it is set with positive weight, i.e. its
+        mask-texel coordinate lies in (lo - 1, hi + 1) of the mask's set-texel bounding box on every axis; its
+        factor taps are floor(f) and floor(f) + 1 of the factor-texel coordinate f.  One more texel either side
+        absorbs fp32 rounding of the kernels' coordinate arithmetic."""
+        am = self.alphaMask
+        if am is None:
+            return None
+        box = am.texel_bbox()
+        g = self._host["grid"]
+        if box is None:
+            return [(0, 0)] * 3                                # empty mask: nothing is ever sampled
+        dims = [int(v) for v in am.gridSize.tolist()]
+        a_m = am.aabb.detach().double().cpu()
+        a_f = self.aabb.detach().double().cpu()
+        out = []
+        for ax in range(3):
+            if dims[ax] < 2 or g[ax] < 2:
+                out.append((0, g[ax] - 1))
+                continue
+            size_m, size_f = float(a_m[1, ax] - a_m[0, ax]), float(a_f[1, ax] - a_f[0, ax])
+            p_lo = float(a_m[0, ax]) + (box[0][ax] - 1) / (dims[ax] - 1) * size_m
+            p_hi = float(a_m[0, ax]) + (box[1][ax] + 1) / (dims[ax] - 1) * size_m
+            f_lo = (p_lo - float(a_f[0, ax])) / size_f * (g[ax] - 1)
+            f_hi = (p_hi - float(a_f[0, ax])) / size_f * (g[ax] - 1)
+            out.append((max(0, math.floor(f_lo) - 1), min(g[ax] - 1, math.floor(f_hi) + 2)))
+        return out
+
+    def grad_regions(self, total_floats=None):
+        """The parts of the flat gradient buffer that can be non-zero after a backward, as (offset, row_len, row_stride,
+        n_rows) in floats: per plane the rows x columns of `_grad_texel_box`, per line its texel range, then basis_mat
+        and the MLP as one dense run (up to `total_floats`, the padded buffer length).  Everything else is exactly
+        zero on every rank, so a multi-GPU step only exchanges these (dist.SymmetricGradients).  Regularisers that
+        touch whole planes (TV / L1) are identical on all ranks and are added AFTER the exchange."""
+        box = self._grad_texel_box()
+        g = self._host["grid"]
+        if box is None:
+            box = [(0, g[a] - 1) for a in range(3)]
+        params = self._all_params()
+        nf = len(self._factor_params())
+        kinds = (["plane"] * 3 + ["line"] * 3) * 2 if self._is_vm else ["line"] * 6
+        regions, off = [], 0
+        for i, p in enumerate(params[:nf]):
+            _, c, h, w = p.shape
+            k = i % 3
+            if kinds[i] == "plane":
+                (x0, x1), (y0, y1) = box[self.matMode[k][0]], box[self.matMode[k][1]]
+                if x1 >= x0 and y1 >= y0:
+                    regions.append((off + (y0 * w + x0) * c, (x1 - x0 + 1) * c, w * c, y1 - y0 + 1))
+            else:
+                l0, l1 = box[self.vecMode[k]]
+                if l1 >= l0:
+                    regions.append((off + l0 * c, (l1 - l0 + 1) * c, (l1 - l0 + 1) * c, 1))
+            off += p.numel()
+        total = sum(p.numel() for p in params) + GRAD_TAIL
+        end = int(total_floats) if total_floats is not None else (total + 3) // 4 * 4
+        regions.append((off, end - off, end - off, 1))
+        return regions
 
     def _zero_plumbing(self, device):
         """(side stream handle, fork event handle, done event handle) of the gradient-buffer memset."""
@@ -897,19 +1053,78 @@ class TensorBase(nn.Module):
         return _RegLossFn.apply(self, "density", 1, *self._reg_params("density"))
 
     def vectorDiffs(self, vector_comps):
-        """tensoRF.py:175-184: mean |off-diagonal| of each line's C x C Gram matrix (tiny; torch)."""
-        total = 0
-        for v in vector_comps:
-            n_comp, n_size = v.shape[1:-1]
-            m = v.reshape(n_comp, n_size)
-            dotp = m @ m.t()
-            non_diagonal = dotp.reshape(-1)[1:].view(n_comp - 1, n_comp + 1)[..., :-1]
-            total = total + torch.mean(torch.abs(non_diagonal))
-        return total
+        """tensoRF.py:175-184: sum over the lines of mean |off-diagonal| of the C x C Gram matrix, value and gradient
+        on `ftrf_ortho_reg` (an autograd scalar, like the other regularisers)."""
+        return _OrthoFn.apply(self, *list(vector_comps)).float()
 
     def vector_comp_diffs(self):
         """tensoRF.py:186-187."""
         return self.vectorDiffs(self.density_line) + self.vectorDiffs(self.app_line)
+
+    # ------------------------------------------------------------------ the module methods on points (SURVEY 8b)
+    def _decomp_mask(self, which: str, mask):
+        if mask is None:
+            return None
+        return {"encoding": {"pos": None, "view": None, "fea": None},
+                "decomp": {"den": mask if which == "den" else None, "app": mask if which == "app" else None}}
+
+    @_on_device
+    @torch.no_grad()
+    def compute_densityfeature(self, xyz_sampled, mask=None):
+        """models/tensoRF.py:207-227 (VM) / :358-386 (CP): sigma feature [n] of NORMALISED points, before
+        feature2density; `mask` is the decomposition mask of the reference (None, one tensor, or three).  Runs the
+        density gather of the per-ray path (`ftrf_density_feature`); no autograd through this stand-alone call."""
+        xn = _as_rows(xyz_sampled, 3, self.device)
+        field = self._fill_field(self._decomp_mask("den", mask))
+        out = torch.empty(xn.shape[0], dtype=torch.float32, device=xn.device)
+        check(lib.ftrf_density_feature(C.byref(field), xn.data_ptr(), xn.shape[0], out.data_ptr(), _stream()), "density_feature")
+        return out
+
+    @_on_device
+    @torch.no_grad()
+    def compute_appfeature(self, xyz_sampled, mask=None):
+        """models/tensoRF.py:230-263 (VM) / :388-415 (CP): appearance features [n, app_dim] of NORMALISED points
+        (plane x line gather + basis_mat) on the appearance kernel of the per-ray path (`ftrf_app_feature`)."""
+        xn = _as_rows(xyz_sampled, 3, self.device)
+        n = xn.shape[0]
+        field = self._fill_field(self._decomp_mask("app", mask))
+        out = torch.empty(n, int(self.app_dim), dtype=torch.float32, device=xn.device)
+        ws = _points_workspace(field, n, xn.device)
+        check(lib.ftrf_app_feature(C.byref(field), xn.data_ptr(), n, out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
+              "app_feature")
+        return out
+
+    @_on_device
+    @torch.no_grad()
+    def _shade_points(self, pts, viewdirs, features, mask=None):
+        """renderModule(pts, viewdirs, features, mask) for n points: mask = the encoding-mask dict of mlp.py
+        ({'pos','view','fea'} -> None | 0-dim | vector)."""
+        feat = _as_rows(features, int(self.app_dim), self.device)
+        n = feat.shape[0]
+        xn, view = _as_rows(pts, 3, self.device), _as_rows(viewdirs, 3, self.device)
+        if xn.shape[0] != n or view.shape[0] != n:
+            raise RuntimeError("renderModule: points, view directions and features differ in length")
+        enc = None
+        if mask is not None and any(mask.get(k) is not None for k in ("pos", "view", "fea")):
+            enc = {"encoding": {k: mask.get(k) for k in ("pos", "view", "fea")}, "decomp": {"den": None, "app": None}}
+        field = self._fill_field(enc)
+        rgb = torch.empty(n, 3, dtype=torch.float32, device=feat.device)
+        ws = _points_workspace(field, n, feat.device)
+        check(lib.ftrf_shade_points(C.byref(field), xn.data_ptr(), view.data_ptr(), feat.data_ptr(), n, rgb.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), _stream()), "shade_points")
+        return rgb
+
+    def sample_ray_ndc(self, rays_o, rays_d, is_train=True, N_samples=-1):
+        """models/tensorBase.py:178-187 (torch ops, the reference's own RNG draw; forward() runs the same sampling
+        inside the march kernel from the z table `_draw_rng` prepares)."""
+        S = N_samples if N_samples > 0 else self.nSamples
+        near, far = self.near_far
+        interpx = torch.linspace(near, far, S).unsqueeze(0).to(rays_o)
+        if is_train:
+            interpx = interpx + torch.rand_like(interpx).to(rays_o) * ((far - near) / S)
+        pts = rays_o[..., None, :] + rays_d[..., None, :] * interpx[..., None]
+        inside = ~((self.aabb[0] > pts) | (pts > self.aabb[1])).any(dim=-1)
+        return pts, interpx, inside
 
     def sample_ray(self, rays_o, rays_d, is_train=True, N_samples=-1):
         """models/tensorBase.py:189-208 (torch ops; used by filtering_rays, not by forward)."""
@@ -975,6 +1190,7 @@ class TensorBase(nn.Module):
         st = stats.cpu()                                                                # the call's one host sync
         total = int(st[6:8].view(torch.int64))
         self.alphaMask = AlphaGridMask.from_bits(self.device, self.aabb, bits, (X, Y, Z))
+        self.alphaMask.__dict__["_bbox"] = (tuple(int(v) for v in st[0:3]), tuple(int(v) for v in st[3:6])) if total else False
         self.last_alpha_rest = total / float(X * Y * Z)
         if total == 0:
             raise RuntimeError("updateAlphaMask: no lattice point reaches alphaMask_thres (the reference's "
@@ -1045,6 +1261,44 @@ class _RegLossFn(torch.autograd.Function):
                                    1.0 if kind == 0 else 0.0, 1.0 if kind == 1 else 0.0, scale.data_ptr(), None,
                                    1 if kind == 1 else 0, _stream()), "reg_factors")
         return (None, None, None) + tuple(grads[:ctx.n])
+
+
+class _OrthoFn(torch.autograd.Function):
+    """vector_comp_diffs (tensoRF.py:175-187) of a list of lines as an autograd scalar on `ftrf_ortho_reg`."""
+
+    @staticmethod
+    def _run(lines, grads, scale, out):
+        n = len(lines)
+        srcs = []
+        for v in lines:
+            s = v.detach()
+            if not _is_channels_last(s):
+                s = s.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+            srcs.append(s)
+        ptrs = (C.c_void_p * n)(*[s.data_ptr() for s in srcs])
+        gptrs = None if grads is None else (C.c_void_p * n)(*[g.data_ptr() for g in grads])
+        comps = (C.c_int32 * n)(*[int(v.shape[1]) for v in lines])
+        lens = (C.c_int32 * n)(*[int(v.shape[2]) for v in lines])
+        with torch.cuda.device(lines[0].device):
+            check(lib.ftrf_ortho_reg(ptrs, gptrs, comps, lens, n, 1.0, None if scale is None else scale.data_ptr(),
+                                     None if out is None else out.data_ptr(), _stream()), "ortho_reg")
+
+    @staticmethod
+    def forward(ctx, model, *lines):
+        ctx.lines = lines
+        out = torch.zeros(1, dtype=torch.float64, device=lines[0].device)
+        _OrthoFn._run(lines, None, None, out)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        lines = ctx.lines
+        # gradients laid out like the parameters (channels-last memory of the (1,C,L,1) shape)
+        grads = [torch.zeros((1, v.shape[2], 1, v.shape[1]), dtype=torch.float32, device=v.device).permute(0, 3, 1, 2)
+                 for v in lines]
+        scale = g.detach().to(torch.float32).reshape(1).contiguous()
+        _OrthoFn._run(lines, grads, scale, None)
+        return (None,) + tuple(grads)
 
 
 class _RenderFn(torch.autograd.Function):
@@ -1179,12 +1433,8 @@ class TensorVMSplit(TensorBase):
         for planes, lines in ((self.app_plane, self.app_line), (self.density_plane, self.density_line)):
             for i in range(3):
                 m0, m1 = self.matMode[i]
-                planes[i] = _channels_last_param(
-                    F.interpolate(planes[i].data, size=(res_target[m1], res_target[m0]), mode='bilinear', align_corners=True),
-                    planes[i].device)
-                lines[i] = _channels_last_param(
-                    F.interpolate(lines[i].data, size=(res_target[self.vecMode[i]], 1), mode='bilinear', align_corners=True),
-                    lines[i].device)
+                planes[i] = _resample_param(planes[i], res_target[m1], res_target[m0])
+                lines[i] = _resample_param(lines[i], res_target[self.vecMode[i]], 1)
         self.update_stepSize(res_target)
 
     @torch.no_grad()
@@ -1198,8 +1448,8 @@ class TensorVMSplit(TensorBase):
             v = self.vecMode[i]
             m0, m1 = self.matMode[i]
             for lines, planes in ((self.density_line, self.density_plane), (self.app_line, self.app_plane)):
-                lines[i] = _channels_last_param(lines[i].data[..., t_l[v]:b_r[v], :], lines[i].device)
-                planes[i] = _channels_last_param(planes[i].data[..., t_l[m1]:b_r[m1], t_l[m0]:b_r[m0]], planes[i].device)
+                lines[i] = _crop_param(lines[i], t_l[v], b_r[v], 0, 1)
+                planes[i] = _crop_param(planes[i], t_l[m1], b_r[m1], t_l[m0], b_r[m0])
         new_aabb = self._corrected_aabb(new_aabb, t_l, b_r)
         size = b_r - t_l
         self.aabb = new_aabb
@@ -1256,9 +1506,7 @@ class TensorCP(TensorBase):
         res_target = [int(v) for v in res_target]
         for lines in (self.density_line, self.app_line):
             for i in range(3):
-                lines[i] = _channels_last_param(
-                    F.interpolate(lines[i].data, size=(res_target[self.vecMode[i]], 1), mode='bilinear', align_corners=True),
-                    lines[i].device)
+                lines[i] = _resample_param(lines[i], res_target[self.vecMode[i]], 1)
         self.update_stepSize(res_target)
 
     @torch.no_grad()
@@ -1271,7 +1519,7 @@ class TensorCP(TensorBase):
         for i in range(3):
             v = self.vecMode[i]
             for lines in (self.density_line, self.app_line):
-                lines[i] = _channels_last_param(lines[i].data[..., t_l[v]:b_r[v], :], lines[i].device)
+                lines[i] = _crop_param(lines[i], t_l[v], b_r[v], 0, 1)
         new_aabb = TensorVMSplit._corrected_aabb(self, new_aabb, t_l, b_r)
         size = b_r - t_l
         self.aabb = new_aabb

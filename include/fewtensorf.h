@@ -23,6 +23,10 @@
  *                           models/tensorBase.py:215-256 getDenseAlpha / updateAlphaMask
  *   ftrf_filter_rays        models/tensorBase.py:259-288 filtering_rays
  *   ftrf_reg_factors        models/tensoRF.py:189-205 + loss.py:120-141   TV / L1 regularisers (value + gradient)
+ *   ftrf_ortho_reg          models/tensoRF.py:175-187   vector_comp_diffs (value + gradient)
+ *   ftrf_resample_factor, ftrf_crop_factor   models/tensoRF.py:267-327, :418-466   upsample_volume_grid / shrink
+ *   ftrf_density_feature, ftrf_app_feature, ftrf_shade_points
+ *                           models/tensoRF.py:207-263, :358-415; models/mlp.py:15-19, :41-155   the module methods on points
  *   ftrf_adam_step          train.py:272-273, :374-376   torch.optim.Adam over all parameter groups
  *   ftrf_generate_rays      dataLoader/ray_utils.py:24-85, dataLoader/blender.py:59   camera rays from a pose
  *   ftrf_zero_after (+ ftrf_event_record, ftrf_stream_wait_event)   train.py:374 optimizer.zero_grad()
@@ -40,7 +44,7 @@
 extern "C" {
 #endif
 
-#define FTRF_ABI_VERSION 1
+#define FTRF_ABI_VERSION 2
 
 enum { FTRF_MODEL_VM = 0, FTRF_MODEL_CP = 1 };
 enum { FTRF_SHADE_MLP_FEA = 0, FTRF_SHADE_MLP_PE = 1, FTRF_SHADE_MLP = 2, FTRF_SHADE_SH = 3 };
@@ -116,6 +120,12 @@ typedef struct FtrfCall {
   const float* g_rgb_map;   /* backward in: dL/d rgb_map [n_rays][3]                        */
   int64_t cap_samples;      /* capacity of the packed valid-sample list                     */
   int64_t cap_app;          /* capacity of the packed shaded-sample list                    */
+  /* Library-owned hand-off between the calls that share this struct (zero-initialise, then leave alone):
+   * which weight images the forward already prepared for the backward, and which side-stream work a split
+   * backward (ftrf_backward_part 1 then 2, possibly from different host threads) still has to join.  This is
+   * what keeps the entry points re-entrant: the library holds no process-wide state about a call. */
+  uint64_t lib_flags;
+  void* lib_ctx;
 } FtrfCall;
 
 /* Workspace sections (offsets in bytes from the workspace base, filled by ftrf_workspace_layout). */
@@ -155,6 +165,7 @@ const char* ftrf_last_error(void);          /* host string, thread-local */
 /* Returns total bytes; offsets_out (host, may be NULL) receives FTRF_WS_COUNT byte offsets. */
 size_t ftrf_workspace_layout(const FtrfField* field, const FtrfCall* call, int64_t* offsets_out);
 
+/* `call` is const for the caller's fields; lib_flags / lib_ctx are updated in place (see FtrfCall). */
 int ftrf_forward(const FtrfField* field, const FtrfCall* call, void* ws, size_t ws_bytes, void* stream);
 /* ftrf_forward that also hands the call's counters to the host as soon as they are final (after the
  * integration stage; the appearance / shading / compositing kernels follow on the stream): counters_host
@@ -217,25 +228,26 @@ int ftrf_unpack_alpha_mask(const uint32_t* bits, int32_t x, int32_t y, int32_t z
 int ftrf_filter_rays(const FtrfField* field, const float* rays, int32_t ray_cols, int64_t n, int32_t n_samples,
                      int32_t bbox_only, uint8_t* keep, void* stream);
 
-/* Bring-up / unit-test entry of the tensor-core contraction used by the shading MLP (tcgen05.mma
- * kind::tf32, 3xTF32 split): out[M][N] = epi(A[M][K] * B^T), B element (n,k) at B[n*sn + k*sk].
- * epi: + bias[n] (or NULL), ReLU if relu != 0, zero where mask[m*ldm+n] <= 0 (or NULL). */
-int ftrf_test_gemm3x(const float* A, int lda, int ka, int64_t M, const float* B, int64_t sn, int64_t sk, int N, int K,
-                     const float* bias, const float* mask, int ldm, int relu, float* out, int ldo, int variant,
+/* The module methods the reference exposes on POINTS instead of rays (models/tensoRF.py:207-263, :358-415
+ * compute_densityfeature / compute_appfeature; models/mlp.py:15-19, :41-69, :88-107, :127-155 renderModule), on
+ * the same kernels as the per-ray path.  xn / viewdirs / features are device arrays of n rows; xn holds
+ * NORMALISED coordinates (normalize_coord's output, tensorBase.py:130-131), as those methods take them.
+ *   ftrf_density_feature : sigma_feature[n]   (before feature2density; decomposition mask from field->den.mask)
+ *   ftrf_app_feature     : app_features[n][app_dim]   (gather + basis_mat; mask from field->app.mask)
+ *   ftrf_shade_points    : rgb[n][3] = renderModule(xn, viewdirs, features, field->enc_mask)
+ * The last two need a scratch buffer of ftrf_points_workspace_bytes(field, n) bytes (device memory). */
+size_t ftrf_points_workspace_bytes(const FtrfField* field, int64_t n);
+int ftrf_density_feature(const FtrfField* field, const float* xn, int64_t n, float* sigma_feature_out, void* stream);
+int ftrf_app_feature(const FtrfField* field, const float* xn, int64_t n, float* features_out, void* ws, size_t ws_bytes,
                      void* stream);
-
-/* dW[o][k] += sum_s G[s][o] A[s][k] (o < 128, k < K), dbias[o] += sum_s G[s][o] (or NULL) — the
- * tensor-core weight-gradient contraction, exposed for unit tests. */
-int ftrf_test_wgrad3x(const float* G, int ldg, const float* A, int lda, int K, int64_t M, float* dW, int ldw,
-                      float* dbias, void* stream);
-/* Shading-MLP back end (all CUDA): 2 (default) fused persistent tcgen05 kernels (3xTF32), 1 one tcgen05
- * GEMM launch per layer, 0 fp32 CUDA-core kernels. */
-int ftrf_set_shade_path(int path);
+int ftrf_shade_points(const FtrfField* field, const float* xn, const float* viewdirs, const float* features, int64_t n,
+                      float* rgb_out, void* ws, size_t ws_bytes, void* stream);
 
 /* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
  * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.
  * ftrf_profile_read must be called after the stream has been synchronised; ms_out receives
- * FTRF_PROF_STAGES durations in milliseconds (-1 for a stage that did not run since enabling). */
+ * FTRF_PROF_STAGES durations in milliseconds (-1 for a stage that did not run since enabling).
+ * The switch and the events belong to the CALLING HOST THREAD (thread-local), like ftrf_last_error. */
 #define FTRF_PROF_STAGES 13
 int ftrf_profile_enable(int on);
 int ftrf_profile_read(float* ms_out /* host */);
@@ -248,6 +260,22 @@ int ftrf_multimem_allreduce(void* multicast_ptr, size_t n_floats, int rank, int 
 /* The same exchange with plain peer loads / stores over NVLink: peer_ptrs[r] is rank r's copy of the symmetric
  * buffer (host array of `world` device pointers, world = 2, 4 or 8); same barrier contract. */
 int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int world, void* stream);
+/* The same two exchanges over the parts of the buffer that can hold a gradient: a region is n_rows runs of row_len
+ * floats, row_stride floats apart, starting at float `offset` of the buffer (all multiples of 4; lines and the dense
+ * basis / MLP tail are single rows).  Rows and columns of a plane outside the alphaMask's texel bounding box never
+ * receive a gradient (their samples are culled in stage 1), so they are exactly zero on every rank and need no
+ * exchange (fewtensorf_b200/module.py: TensorBase.grad_regions).  regions: HOST array, at most FTRF_MAX_REGIONS. */
+#define FTRF_MAX_REGIONS 24
+typedef struct FtrfRegion {
+  int64_t offset;
+  int64_t row_len;
+  int64_t row_stride;
+  int64_t n_rows;
+} FtrfRegion;
+int ftrf_p2p_allreduce_regions(void* const* peer_ptrs, const FtrfRegion* regions, int n_regions, int rank, int world,
+                               void* stream);
+int ftrf_multimem_allreduce_regions(void* multicast_ptr, const FtrfRegion* regions, int n_regions, int rank, int world,
+                                    void* stream);
 /* Regularisers of one factor set, value and gradient in one pass.
  *   TV : sum_k 1e-2 * TVLoss(plane_k)      models/tensoRF.py:195-205 with loss.py:120-141 (VM planes only; the
  *        reference's CP variant, tensoRF.py:474-484, is 0/0 = NaN and is refused with FTRF_E_ARG)
@@ -258,6 +286,20 @@ int ftrf_p2p_allreduce(void* const* peer_ptrs, size_t n_floats, int rank, int wo
  * both weights (autograd's upstream gradient).  `model` is FTRF_MODEL_*. */
 int ftrf_reg_factors(const FtrfFactorSet* fs, int model, float w_tv, float w_l1, const float* dev_scale,
                      double* loss_out, int with_lines, void* stream);
+/* Factor maintenance between training stages, on the channel-last factor layout.
+ *   ftrf_resample_factor : F.interpolate(mode='bilinear', align_corners=True) of one plane ([H][W][C] -> [H2][W2][C])
+ *                          or line (W = W2 = 1)      models/tensoRF.py:267-288, :418-435 upsample_volume_grid
+ *   ftrf_crop_factor     : rows [y0,y1) x columns [x0,x1) of a plane / line into a dense [y1-y0][x1-x0][C] buffer
+ *                          models/tensoRF.py:290-327, :437-466 shrink
+ *   ftrf_ortho_reg       : vector_comp_diffs, models/tensoRF.py:175-187 — for each of n_lines lines ([L][C]) the mean
+ *                          |off-diagonal| of its C x C Gram matrix is ADDED to loss_out (device double, may be NULL);
+ *                          where g_lines is non-NULL, weight * dev_scale * d(that mean)/d line is ADDED to g_lines[k].
+ *                          lines / g_lines / n_comp / line_len are HOST arrays of n_lines entries. */
+int ftrf_resample_factor(const float* src, int32_t C, int32_t H, int32_t W, float* dst, int32_t H2, int32_t W2, void* stream);
+int ftrf_crop_factor(const float* src, int32_t C, int32_t H, int32_t W, int32_t y0, int32_t y1, int32_t x0, int32_t x1,
+                     float* dst, void* stream);
+int ftrf_ortho_reg(const float* const* lines, float* const* g_lines, const int32_t* n_comp, const int32_t* line_len,
+                   int n_lines, float weight, const float* dev_scale, double* loss_out, void* stream);
 /* torch.optim.Adam(betas, eps; no weight decay / amsgrad) step `step` (1-based) over a host table of segments
  * in ONE launch (train.py:272-273 optimizer, :374-376 step; lr per segment = the param group's current lr,
  * which train.py:389-392 decays on the host).  All four arrays of a segment share one element order. */

@@ -1,6 +1,7 @@
 import sys, torch
 sys.path.insert(0, '.')
-from fewtensorf_b200._abi import lib, check
+from fewtensorf_b200._abi import check, load_test_lib
+lib = load_test_lib()
 M = 102186
 g = torch.Generator(device="cuda").manual_seed(1)
 X = torch.randn(M, 152, device="cuda", generator=g); X[:, 150:] = 0

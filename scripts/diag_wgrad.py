@@ -6,7 +6,8 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from fewtensorf_b200._abi import check, lib  # noqa: E402
+from fewtensorf_b200._abi import check, load_test_lib  # noqa: E402
+lib = load_test_lib()
 
 lib.ftrf_test_wgrad_fused.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64,
                                       C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]

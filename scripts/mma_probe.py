@@ -6,7 +6,8 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from fewtensorf_b200._abi import lib  # noqa: E402
+from fewtensorf_b200._abi import load_test_lib  # noqa: E402
+lib = load_test_lib()
 
 lib.ftrf_debug_mma_probe.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
 out = torch.zeros(2, dtype=torch.int64, device="cuda")

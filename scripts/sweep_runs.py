@@ -7,7 +7,8 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
-from fewtensorf_b200._abi import lib  # noqa: E402
+from fewtensorf_b200._abi import load_test_lib  # noqa: E402
+lib = load_test_lib()
 
 dev = torch.device("cuda", 0)
 m = bench.build_model(dev)

@@ -1,8 +1,48 @@
 """Helpers for the `-m gpu` parity tests: build the product model from a golden fixture / oracle field."""
+import contextlib
+
 import torch
 
 import fewtensorf_b200 as ft
 from oracle import field_oracle as O
+
+_TEST_LIB = None
+
+
+def test_lib():
+    """libfewtensorf_b200_test.so: the superset build with the cross-check back ends, unit-test entry points and
+    debug switches (the product library has none of them)."""
+    global _TEST_LIB
+    if _TEST_LIB is None:
+        from fewtensorf_b200 import _abi
+        _TEST_LIB = _abi.load_test_lib()
+    return _TEST_LIB
+
+
+test_lib.__test__ = False       # not a pytest test
+
+
+@contextlib.contextmanager
+def through_test_lib(setup=None, teardown=None):
+    """Route the module's C calls through the test build for the duration (same ABI, same structs), optionally
+    flipping one of its switches: `setup(lib)` on entry, `teardown(lib)` on exit."""
+    from fewtensorf_b200 import module
+    tl = test_lib()
+    old = module.lib
+    module.lib = tl
+    if setup is not None:
+        setup(tl)
+    try:
+        yield tl
+    finally:
+        if teardown is not None:
+            teardown(tl)
+        module.lib = old
+
+
+def shade_backend(path):
+    """0 = fp32 CUDA-core MLP kernels, 1 = one tcgen05 GEMM per layer, 2 = the fused tcgen05 kernels (product default)."""
+    return through_test_lib(lambda l: l.ftrf_set_shade_path(path), lambda l: l.ftrf_set_shade_path(2))
 
 
 def args_from_cfg(cfg: O.FieldConfig):

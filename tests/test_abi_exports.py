@@ -40,7 +40,20 @@ def test_struct_sizes_match_the_c_compiler():
 
 def test_error_convention_without_gpu():
     from fewtensorf_b200 import _abi
-    assert _abi.lib.ftrf_abi_version() == 1
+    assert _abi.lib.ftrf_abi_version() == 2
     rc = _abi.lib.ftrf_mse_loss(None, None, 0, None, None, None)
     assert rc == -1 and b"mse_loss" in _abi.lib.ftrf_last_error()
     assert _abi.lib.ftrf_workspace_layout(None, None, None) == 0
+
+
+def test_test_build_is_a_superset_and_the_product_has_no_debug_switches():
+    """libfewtensorf_b200_test.so (cross-check back ends, probes, unit-test entries) exports everything the product
+    does; the product exports none of the switches."""
+    from fewtensorf_b200 import _abi
+    tl = _abi.load_test_lib()
+    for n in _abi.EXPORTS:
+        assert hasattr(tl, n), n
+    for n in ("ftrf_set_shade_path", "ftrf_test_gemm3x", "ftrf_test_wgrad3x", "ftrf_test_wgrad_fused",
+              "ftrf_debug_mma_probe", "ftrf_debug_set_app_bwd_tc", "ftrf_debug_set_runs"):
+        assert hasattr(tl, n), n
+        assert not hasattr(_abi.lib, n), n

@@ -17,8 +17,7 @@ pytestmark = pytest.mark.gpu
                                                       ((32, 32, 32), (8, 8, 16), 333, False),
                                                       ((48, 48, 48), (64, 64, 64), 1500, False)])
 def test_app_backward_tensor_core_matches_cuda_core(grid, comps, n_rays, masked):
-    from fewtensorf_b200._abi import lib
-    from tests.gpu_util import model_from_field
+    from tests.gpu_util import model_from_field, through_test_lib
     cfg = O.FieldConfig(grid=grid, density_n_comp=(16, 16, 16), app_n_comp=comps)
     p = O.init_params(cfg, seed=31)
     O.plant_box(cfg, p)
@@ -33,13 +32,10 @@ def test_app_backward_tensor_core_matches_cuda_core(grid, comps, n_rays, masked)
                 "decomp": {"den": None, "app": [torch.rand(cc, generator=g).cuda() for cc in comps]}}
     grads = {}
     for tcore in (1, 0):
-        lib.ftrf_debug_set_app_bwd_tc(tcore)
-        try:
+        with through_test_lib(lambda l: l.ftrf_debug_set_app_bwd_tc(tcore), lambda l: l.ftrf_debug_set_app_bwd_tc(1)):
             torch.manual_seed(5)
             loss, nv = m.train_step(rays, target, mask, white_bg=True, N_samples=200)
             torch.cuda.synchronize()
-        finally:
-            lib.ftrf_debug_set_app_bwd_tc(1)
         grads[tcore] = {k: q.grad.detach().clone() for k, q in m.named_parameters()
                         if k.startswith(("app_plane", "app_line", "basis_mat"))}
         assert nv > 1000

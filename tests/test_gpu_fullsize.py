@@ -9,16 +9,13 @@ pytestmark = pytest.mark.gpu
 
 
 def _step(model, rays, target, path):
-    from fewtensorf_b200._abi import lib
-    lib.ftrf_set_shade_path(path)
-    try:
+    from tests.gpu_util import shade_backend
+    with shade_backend(path):
         torch.manual_seed(7)
         loss, nv = model.train_step(rays, target, None, white_bg=True, N_samples=1039)
         torch.cuda.synchronize()
         grads = {k: p.grad.detach().clone() for k, p in model.named_parameters()}
         return float(loss), int(nv), grads
-    finally:
-        lib.ftrf_set_shade_path(2)
 
 
 def _rel(a, b):

@@ -10,7 +10,9 @@ pytestmark = pytest.mark.gpu
 
 
 def run_gemm(A, B, bias=None, mask=None, relu=False, transposed_b=False, variant=0, ka=None):
-    from fewtensorf_b200._abi import check, lib
+    from fewtensorf_b200._abi import check
+    from tests.gpu_util import test_lib
+    lib = test_lib()
     M, lda = A.shape
     if transposed_b:          # B given as [K][N]; element (n,k) at B[k*N + n]
         K, N = B.shape
@@ -64,7 +66,9 @@ def test_gemm3x_epilogues_and_strided_b():
 
 @pytest.mark.parametrize("M,K,with_bias", [(32, 128, False), (1000, 150, True), (5000, 128, True), (100000, 150, True)])
 def test_wgrad3x_matches_fp64(M, K, with_bias):
-    from fewtensorf_b200._abi import check, lib
+    from fewtensorf_b200._abi import check
+    from tests.gpu_util import test_lib
+    lib = test_lib()
     g = torch.Generator(device="cuda").manual_seed(M + K)
     lda = (K + 7) // 8 * 8
     G = torch.randn(M, 128, device="cuda", generator=g) * (torch.rand(M, 128, device="cuda", generator=g) > 0.5)
@@ -85,7 +89,9 @@ def test_wgrad3x_matches_fp64(M, K, with_bias):
 @pytest.mark.parametrize("M,kp", [(16, 152), (17, 152), (1000, 152), (5000, 56), (100000, 152), (4097, 168)])
 def test_wgrad_fused_matches_fp64(M, kp):
     """Both MLP weight gradients + the bias gradient from one kernel (MN-major UMMA operands)."""
-    from fewtensorf_b200._abi import check, lib
+    from fewtensorf_b200._abi import check
+    from tests.gpu_util import test_lib
+    lib = test_lib()
     lib.ftrf_test_wgrad_fused.restype = C.c_int
     lib.ftrf_test_wgrad_fused.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -84,19 +84,18 @@ def test_gradients_autograd(case):
 @pytest.mark.parametrize("path", [0, 1])
 @pytest.mark.parametrize("case", [c for c in CASES if "sh" not in c])
 def test_other_shading_paths(case, path):
-    """The fp32 CUDA-core MLP kernels (ftrf_set_shade_path(0)) and the one-GEMM-per-layer tcgen05
-    path (1) must meet the same bars as the fused tcgen05 path (2) the other tests exercise by default."""
-    from fewtensorf_b200._abi import lib
-    lib.ftrf_set_shade_path(path)
-    try:
+    """The fp32 CUDA-core MLP kernels (test build, back end 0) and the one-GEMM-per-layer tcgen05 path (1; the
+    product's fall-back for shapes the fused kernels do not cover) must meet the same bars as the fused tcgen05
+    path (2) the other tests exercise by default."""
+    from tests.gpu_util import shade_backend
+    with shade_backend(path):
         g, f, m, rgb, depth, nv = _run(case, grad=True)
         loss = torch.mean((rgb - g.target.cuda()) ** 2)
         loss.backward()
+        torch.cuda.synchronize()
         assert rel_inf(rgb.detach().cpu(), g.t["rgb_map"]) < TOL
         for k, p in m.named_parameters():
             assert rel_inf(p.grad.cpu(), g.grads[k]) < TOL, k
-    finally:
-        lib.ftrf_set_shade_path(2)
 
 
 @pytest.mark.parametrize("case", [c for c in CASES if "train" in c and "ndc" not in c][:2])
