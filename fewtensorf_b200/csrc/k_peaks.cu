@@ -51,8 +51,11 @@ l1_read_kernel(const float4* __restrict__ buf, int iters, float* __restrict__ si
   float acc = 0.f;
   for (int it = 0; it < iters; ++it) {
     float4 v[4];
+    const int t = (threadIdx.x + it * 32) & 511;            // a different warp-sized run of the slice every pass
 #pragma unroll
-    for (int u = 0; u < 4; ++u) asm volatile("ld.global.ca.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(mine + threadIdx.x + u * 512));
+    for (int u = 0; u < 4; ++u)
+      asm volatile("ld.global.ca.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w)
+                   : "l"(mine + t + u * 512) : "memory");
 #pragma unroll
     for (int u = 0; u < 4; ++u) acc += (v[u].x + v[u].y) + (v[u].z + v[u].w);
   }

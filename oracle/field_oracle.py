@@ -297,8 +297,15 @@ def sh_basis_deg2(d):
     return out
 
 
-def shade(f: Field, xn, view, feat, enc_mask=None):
-    """MLP_Fea models/mlp.py:41-69; MLP_PE :88-107; MLP :127-155; SH :15-19."""
+def shade(f: Field, xn, view, feat, enc_mask=None, keep=None, relu_masks=None):
+    """MLP_Fea models/mlp.py:41-69; MLP_PE :88-107; MLP :127-155; SH :15-19.
+
+    Test aids for ReLU-kink analysis (not part of the reference): `keep`, if a dict, receives the two hidden
+    pre-activations (z1, z2); `relu_masks` = (m1, m2) boolean [n,128] replaces relu(z) by z * m, i.e. evaluates the
+    network with GIVEN unit on/off decisions.  Two implementations whose pre-activations agree to 1e-7 still
+    disagree on the sign of the handful that lie within 1e-7 of zero, and each such flip moves the gradients by
+    O(1/n) — comparing against the oracle evaluated with the other implementation's decisions separates that effect
+    from arithmetic error."""
     cfg = f.cfg
     if cfg.shading == "SH":
         basis = sh_basis_deg2(view)[:, None]
@@ -329,8 +336,12 @@ def shade(f: Field, xn, view, feat, enc_mask=None):
             cols.append(blk(feat, cfg.fea_pe, "fea"))
     x = torch.cat(cols, dim=-1)
     p = f.params
-    h = torch.relu(F.linear(x, p["renderModule.mlp.0.weight"], p["renderModule.mlp.0.bias"]))
-    h = torch.relu(F.linear(h, p["renderModule.mlp.2.weight"], p["renderModule.mlp.2.bias"]))
+    z1 = F.linear(x, p["renderModule.mlp.0.weight"], p["renderModule.mlp.0.bias"])
+    h = torch.relu(z1) if relu_masks is None else z1 * relu_masks[0]
+    z2 = F.linear(h, p["renderModule.mlp.2.weight"], p["renderModule.mlp.2.bias"])
+    h = torch.relu(z2) if relu_masks is None else z2 * relu_masks[1]
+    if keep is not None:
+        keep.update(z1=z1.detach(), z2=z2.detach())
     return torch.sigmoid(F.linear(h, p["renderModule.mlp.4.weight"], p["renderModule.mlp.4.bias"]))
 
 
@@ -344,7 +355,7 @@ def raw2alpha(sigma, dist):
 
 # --------------------------------------------------------------------------- the path
 def render_chunk(f: Field, rays, mask=None, white_bg=True, is_train=False, ndc_ray=False,
-                 n_samples=-1, jitter=None, bg_coin: Optional[bool] = None, keep=None):
+                 n_samples=-1, jitter=None, bg_coin: Optional[bool] = None, keep=None, relu_masks=None):
     """One call of the field on a ray chunk — models/tensorBase.py:321-395 (TensorBase.forward).
 
     RNG inputs are explicit so the CUDA path can be fed the same draws:
@@ -387,7 +398,7 @@ def render_chunk(f: Field, rays, mask=None, white_bg=True, is_train=False, ndc_r
     app = weight > f.cfg.weight_thres
     if app.any():
         feat = app_feature(f, xn[app], amask)
-        rgb[app] = shade(f, xn[app], viewdirs[app], feat, enc)
+        rgb[app] = shade(f, xn[app], viewdirs[app], feat, enc, keep=keep, relu_masks=relu_masks)
 
     acc = torch.sum(weight, -1)
     rgb_map = torch.sum(weight[..., None] * rgb, -2)

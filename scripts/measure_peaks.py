@@ -45,10 +45,10 @@ def measure(dev=None, quick=False):
     sink = torch.zeros(4, device=dev)
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     out = {"gpu": torch.cuda.get_device_name(dev), "sms": sms, "l2_read": {}, "l2_red": {}}
-    iters = 4 if quick else 20
-    for mb in ((16, 32) if quick else (8, 16, 24, 32, 40, 64)):
+    for mb in ((32,) if quick else (8, 16, 24, 32, 40, 64)):
         buf = torch.zeros(mb << 18, device=dev)                    # mb MiB of fp32
         n = buf.numel() * 4
+        iters = max(4, ((1024 if quick else 4096) << 20) // n)      # same bytes per launch whatever the set: the launch ramp is amortised alike
         for ctas in (sms * 2, sms * 4):
             t = _time(lambda: lib.ftrf_peak_l2_read(buf.data_ptr(), n, iters, ctas, sink.data_ptr(), st()))
             out["l2_read"][f"{mb}MB_x{ctas}"] = round(n * iters / t / 1e9, 1)

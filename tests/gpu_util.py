@@ -101,3 +101,36 @@ def dense_from_packed(model, st, n_rays, S):
     out["tmin"] = model.workspace_section(st, "TMIN", torch.float32, n_rays).cpu()
     out["ray"], out["idx"] = ray, idx
     return out
+
+
+def relu_decisions_in_oracle_order(model, st, app_mask):
+    """The shading MLP's unit on/off decisions of a finished (saving) call, reordered to the oracle's sample order
+    (row-major over the [N,S] shaded mask): (m1, m2) boolean [n,128] CPU tensors for `oracle.shade(relu_masks=...)`.
+    The kernels' shaded list is compacted ray by ray in launch order, not sorted; each entry knows its (ray, index)."""
+    n = st.n_valid
+    V = st.n_samples
+    slot = model.workspace_section(st, "A_SLOT", torch.int32, n).long()
+    ray = model.workspace_section(st, "S_RAY", torch.int32, V).long()[slot].cpu()
+    idx = model.workspace_section(st, "S_IDX", torch.int32, V).long()[slot].cpu()
+    pos = (torch.cumsum(app_mask.reshape(-1).long(), 0) - 1).reshape(app_mask.shape)[ray, idx]
+    assert bool(app_mask[ray, idx].all()) and int(app_mask.sum()) == n, "shaded sets differ: decisions cannot be aligned"
+    out = []
+    for name in ("A_H1", "A_H2"):
+        h = model.workspace_section(st, name, torch.float32, n * 128).view(n, 128).cpu()
+        m = torch.zeros(n, 128, dtype=torch.bool)
+        m[pos] = h > 0
+        out.append(m)
+    return out[0], out[1]
+
+
+def flip_aware_reference(f, loss_and_grads_kw, keep, masks):
+    """(n_flips, worst |z| at a flip, grads) — if the GPU's ReLU decisions `masks` differ from the oracle's anywhere,
+    the oracle is re-evaluated WITH those decisions (every differing pre-activation must be roundoff-sized) and its
+    gradients are returned; otherwise (0, 0.0, None)."""
+    d1, d2 = (keep["z1"] > 0) != masks[0], (keep["z2"] > 0) != masks[1]
+    n_flips = int(d1.sum()) + int(d2.sum())
+    if n_flips == 0:
+        return 0, 0.0, None
+    worst = max(float(keep["z1"][d1].abs().max()) if d1.any() else 0.0, float(keep["z2"][d2].abs().max()) if d2.any() else 0.0)
+    res = O.loss_and_grads(f, relu_masks=(masks[0].float(), masks[1].float()), **loss_and_grads_kw)
+    return n_flips, worst, res

@@ -82,12 +82,12 @@ def _build(case):
 
 @pytest.mark.parametrize("case", list(CASES))
 def test_full_size_matches_oracle(case):
-    from tests.gpu_util import dense_from_packed, pin_rng
+    from tests.gpu_util import dense_from_packed, flip_aware_reference, pin_rng, relu_decisions_in_oracle_order
     m, f, rays, target, jitter, S, train = _build(case)
     assert S == (m.nSamples if CASES[case][4] < 0 else CASES[case][4])
     keep = {}
-    loss_o, rgb_o, depth_o, nv_o, grads_o = O.loss_and_grads(f, rays, target, is_train=train, white_bg=True, n_samples=S,
-                                                             jitter=jitter, keep=keep)
+    kw = dict(rays=rays, target=target, is_train=train, white_bg=True, n_samples=S, jitter=jitter)
+    loss_o, rgb_o, depth_o, nv_o, grads_o = O.loss_and_grads(f, keep=keep, **kw)
     if train:
         pin_rng(m, jitter, False, True)
     rgb, depth, nv = m(rays.cuda(), None, white_bg=True, is_train=train, N_samples=CASES[case][4])
@@ -110,7 +110,19 @@ def test_full_size_matches_oracle(case):
     assert int(nv_o) > 5 * N_RAYS
     assert rel_inf(rgb.detach().cpu(), rgb_o) < TOL
     assert rel_inf(depth.cpu(), depth_o) < TOL
-    assert float(loss.detach()) == pytest.approx(float(loss_o), rel=1e-5)
+    assert float(loss.detach()) == pytest.approx(float(loss_o), rel=5e-5)
+    # ReLU kinks: a hidden pre-activation within ~1e-6 of zero may round to the other side on the tensor cores (3xTF32
+    # keeps ~22 mantissa bits per operand); each such flip moves the gradients by O(1 / shaded samples), far above 1e-4
+    # at 512 rays.  The decisions are read back, every differing pre-activation must be roundoff-sized, and the
+    # gradients are then held to 1e-4 against the oracle evaluated with the kernels' decisions.
+    if m.shadingMode != "SH" and not diff.any():
+        n_flips, worst_z, res = flip_aware_reference(f, kw, keep, relu_decisions_in_oracle_order(m, st, keep["app"]))
+        if n_flips:
+            assert n_flips <= 64 and worst_z < 2e-5, (n_flips, worst_z)
+            assert rel_inf(rgb.detach().cpu(), res[1]) < TOL
+            grads_o = res[4]
+            print(f"{case}: {n_flips} ReLU decisions differ from the oracle (largest |z| there {worst_z:.1e}); gradients "
+                  "compared against the oracle evaluated with the kernels' decisions")
     worst = {}
     for k, p in m.named_parameters():
         assert p.grad is not None and p.grad.shape == grads_o[k].shape, k
