@@ -89,6 +89,7 @@ inline size_t fused_wimg_bytes() { return (fused_bwd_offset_floats() + (size_t)4
 int launch_shade_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 int launch_shade_dgrad_fused(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, bool* handled);
 bool shade_path_is_fused();
+bool shade_dgrad_is_fused(const FtrfField&, const FtrfCall&, const Ws&);   // launch_shade_dgrad_fused will handle this call
 bool prep_ahead_take_scratch(const FtrfCall&);        // true: this call's forward already zeroed the wgrad scratch
 size_t wgrad_fused_scratch_bytes();
 cudaStream_t side_tail_begin(const FtrfCall&, cudaStream_t st);   // side stream ordered after `st`, or nullptr
@@ -109,6 +110,12 @@ struct WgradFusedArgs {
   int ngt;                                             // X operand groups (N of the dW1 product = 4 ngt)
   int dw2_vec;                                         // dw2 is 16-byte aligned
   int variant;                                         // bring-up switches
+  // fold3 != 0: `g2` holds h2 (the layer-2 activations) and `go4` [M] = (dL/d pre-sigmoid output, 0) per sample as the
+  // fused dgrad kernel left it; g_h2 = relu'(h2) * (go W3) is rebuilt by the producers, which also accumulate the
+  // output layer's gradients dW3 = go^T h2, db3 = sum go and db2 = sum g_h2 (flushed with atomics at the end)
+  int fold3;
+  const float4* go4; const float* w3;
+  float* dw3; float* db3; float* db2;
 };
 // `call`: the FtrfCall the hand-off flags live in (nullptr for the unit-test entry: everything in line)
 int launch_wgrad_fused(const WgradFusedArgs&, const FusedSpec&, float* g_w1, int ldw, float* g_b1, cudaStream_t, const FtrfCall* call);

@@ -361,7 +361,7 @@ constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thre
 FTRF_SWITCH(int, g_app_bwd_onegather, 1);    // VM: single-gather kernel (app_bwd_vm_kernel); 0 = two-gather kernel below
 FTRF_SWITCH(int, g_app_bwd_runs, -1);        // samples per run-merging segment of the VM scatter; 0 = one reduction set per sample, -1 = auto
 
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(512, 1)
 app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun) {
   extern __shared__ __align__(16) float smem[];
   const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, Dp = (D + 3) & ~3;
@@ -483,6 +483,45 @@ app_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int arun)
         }
         flush_plane(pr, a.g_plane[k], W, C, ch);
         flush_line(lr, a.g_line[k], C, ch);
+      }
+    } else if (arun > 0) {
+      // TensorCP, run merging over the three lines: every sample of a step lands in the same few hundred rows of each
+      // line, so per-sample reductions are bound by same-address contention; a thread owns one 4-channel chunk and
+      // walks `arun` consecutive samples, reducing a line's running gradient only when its cell changes
+      const int C = a.n_comp[0], nq = C / 4, nsegs = (ATILE + arun - 1) / arun;
+      const int tile_n = (int)min((int64_t)ATILE, n - t0);
+      for (int item = threadIdx.x; item < nsegs * nq; item += blockDim.x) {
+        const int seg = item / nq, q = item - seg * nq, ch = 4 * q;
+        float4 m1 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (a.mask[0]) m1 = mask4(a.mask[0], a.mask_stride[0], ch);          // tensoRF.py:415 (once)
+        LineRun lr[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) lr[k].kl = -1;
+        const int i1 = min(tile_n, (seg + 1) * arun);
+        for (int i = seg * arun; i < i1; ++i) {
+          Tap t[3];
+          float4 lv[3];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            t[k] = make_tap(XN[i * 3 + vecm(k)], a.line_len[k]);
+            lv[k] = line4(a.line[k], C, t[k], ch);
+          }
+          const float4 gq = mul4(*reinterpret_cast<const float4*>(P + (size_t)i * NPs + ch), m1);
+          const float4 gk[3] = {mul4(gq, mul4(lv[1], lv[2])), mul4(gq, mul4(lv[0], lv[2])), mul4(gq, mul4(lv[0], lv[1]))};
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            const int kl = t[k].i0 | (t[k].i1 << 16);
+            if (kl != lr[k].kl) {
+              flush_line(lr[k], a.g_line[k], C, ch);
+              lr[k].kl = kl;
+              lr[k].a0 = z4(); lr[k].a1 = z4();
+            }
+            lr[k].a0 = fma4(t[k].w0, gk[k], lr[k].a0);
+            lr[k].a1 = fma4(t[k].w1, gk[k], lr[k].a1);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) flush_line(lr[k], a.g_line[k], C, ch);
       }
     } else if (sl < ATILE && s < n) {
       const float* gqrow = P + (size_t)sl * NPs;
@@ -1042,10 +1081,12 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
   cudaFuncSetAttribute(app_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   // run-merging scatter: (ATILE / run) * NP / 4 work items per tile; auto = the shortest run whose items fit
   // one pass of the CTA (48x3 components: run 10, 252 items)
-  int arun = f.model == FTRF_MODEL_VM ? g_app_bwd_runs : 0;
+  // TensorCP (288 components): 512 threads, so that the scatter's (segment, chunk) items still fit one pass
+  const int threads = f.model == FTRF_MODEL_CP ? 512 : 256;
+  int arun = g_app_bwd_runs;
   if (arun < 0) {
     arun = 4;
-    while (arun < ATILE && ((ATILE + arun - 1) / arun) * (app_np(f) / 4) > 256) ++arun;
+    while (arun < ATILE && ((ATILE + arun - 1) / arun) * (app_np(f) / 4) > threads) ++arun;
   }
   if (f.model == FTRF_MODEL_VM && g_app_bwd_tc && arun != 0) {
     const int NP = app_np(f);
@@ -1056,13 +1097,13 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
       return check_launch("app_bwd_vm_tc");
     }
   }
-  if (arun > 0 && g_app_bwd_onegather) {
+  if (f.model == FTRF_MODEL_VM && arun > 0 && g_app_bwd_onegather) {
     const size_t sm2 = smem + ((size_t)ATILE * NPs + (size_t)ATILE * 3 * 4) * sizeof(float);
     cudaFuncSetAttribute(app_bwd_vm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     app_bwd_vm_kernel<<<FTRF_SMS * 2, 256, sm2, st>>>(f, c, ws, arun);
     return check_launch("app_bwd_vm");
   }
-  app_bwd_kernel<<<FTRF_SMS * 2, 256, smem, st>>>(f, c, ws, arun);
+  app_bwd_kernel<<<FTRF_SMS * 2, threads, smem, st>>>(f, c, ws, arun);
   return check_launch("app_bwd");
 }
 

@@ -382,13 +382,20 @@ density_bwd_vm_runs_kernel(const FtrfField f, const FtrfCall c, const Ws ws, con
 // segment's samples (three samples each) into shared memory, then walk the segment once per factor pair
 // with only that pair's accumulators live.  ~70 registers instead of 128: three CTAs per SM instead of two,
 // and no lane recomputes what its neighbours compute.
-constexpr int DSEG = 12;            // longest segment (samples) a lane group walks
-constexpr int DBW_CTAS = 3;         // resident CTAs per SM the grid is sized for
+#ifndef FTRF_DSEG
+#define FTRF_DSEG 12
+#endif
+#ifndef FTRF_DBW_CTAS
+#define FTRF_DBW_CTAS 2      // two CTAs of <= 128 registers (no spills) beat three of 85: 94 -> 85 us (scripts/variant_sweep.sh)
+#endif
+constexpr int DSEG = FTRF_DSEG;          // longest segment (samples) a lane group walks
+constexpr int DBW_CTAS = FTRF_DBW_CTAS;  // resident CTAs per SM the grid is sized for
 
 __global__ void __launch_bounds__(256, DBW_CTAS)
 density_bwd_vm_staged_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
-  __shared__ float4 s_tap[256 / GS][DSEG][3];
-  __shared__ float s_g[256 / GS][DSEG];
+  extern __shared__ __align__(16) uint8_t dbw_smem[];
+  float4 (*s_tap)[DSEG][3] = reinterpret_cast<float4 (*)[DSEG][3]>(dbw_smem);
+  float (*s_g)[DSEG] = reinterpret_cast<float (*)[DSEG]>(dbw_smem + sizeof(float4) * (256 / GS) * DSEG * 3);
   if (ws.counters[2] & 1) return;
   const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
   const int sub = threadIdx.x & (GS - 1), grp = threadIdx.x / GS;
@@ -475,6 +482,84 @@ density_bwd_vm_staged_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   }
 }
 
+// TensorCP: the same staged walk over the three lines (models/tensoRF.py:358-386: feature = sum_c prod_k line_k).  Every
+// sample of a step lands in the same few hundred line rows, so one reduction set per sample (density_bwd_kernel) is
+// bound by same-address contention in L2; consecutive samples of a ray share their line cells on all three axes, and
+// a lane group that keeps the running gradient of its current cell per line in registers issues a third of them.
+__global__ void __launch_bounds__(256, DBW_CTAS)
+density_bwd_cp_staged_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+  extern __shared__ __align__(16) uint8_t dbw_smem[];
+  float4 (*s_tap)[DSEG][3] = reinterpret_cast<float4 (*)[DSEG][3]>(dbw_smem);
+  float (*s_g)[DSEG] = reinterpret_cast<float (*)[DSEG]>(dbw_smem + sizeof(float4) * (256 / GS) * DSEG * 3);
+  if (ws.counters[2] & 1) return;
+  const int64_t n = min((int64_t)ws.counters[0], c.cap_samples);
+  const int sub = threadIdx.x & (GS - 1), grp = threadIdx.x / GS;
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const int64_t gstride = (int64_t)gridDim.x * blockDim.x / GS;
+  const int64_t per = (n + gstride - 1) / gstride;
+  const int64_t rounds = max((int64_t)1, (per + DSEG - 1) / DSEG);
+  const int DRUN = (int)max((int64_t)1, (per + rounds - 1) / rounds);
+  const int64_t nseg = (n + DRUN - 1) / DRUN;
+  const FtrfFactorSet& d = f.den;
+  const int C = d.n_comp[0];
+  const int64_t seg_pad = (nseg + 7) & ~(int64_t)7;        // whole warps take the same trips (__syncwarp below)
+  for (int64_t seg = g0; seg < seg_pad; seg += gstride) {
+    const int64_t s0 = seg * DRUN;
+    const int len = seg < nseg ? (int)min((int64_t)DRUN, n - s0) : 0;
+    __syncwarp();
+    for (int j = sub; j < len; j += GS) {
+      const int64_t s = s0 + j;
+      const float g = ws.s_gsig[s];
+      s_g[grp][j] = g;
+      if (g != 0.f) {
+        const Ray ray = load_ray_ws(f, c, ws, ws.s_ray[s]);
+        float p[3], xn[3];
+        sample_pt(ray, sample_z(f, c, ray, ws.s_idx[s]), p);
+        normalize_pt(f, p, xn);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {                      // tap of line k (axis vecMode[k])
+          const Tap t = make_tap(xn[vecm(k)], d.line_len[k]);
+          s_tap[grp][j][k] = make_float4(__int_as_float(t.i0), __int_as_float(t.i1), t.w0, t.w1);
+        }
+      }
+    }
+    __syncwarp();
+    for (int ch = sub * 4; ch < C; ch += GS * 4) {
+      float4 m1 = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (d.mask[0]) m1 = mask4(d.mask[0], d.mask_stride[0], ch);          // tensoRF.py:384 (once, not squared)
+      LineRun lr[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) lr[k].kl = -1;
+      for (int j = 0; j < len; ++j) {
+        const float g = s_g[grp][j];
+        if (g == 0.f) continue;
+        float4 t[3], lv[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          t[k] = s_tap[grp][j][k];
+          const float* ln = d.line[k] + ch;
+          lv[k] = fma4(t[k].w, ld4(ln + (size_t)__float_as_int(t[k].y) * C), scale4(t[k].z, ld4(ln + (size_t)__float_as_int(t[k].x) * C)));
+        }
+        const float4 gm = scale4(g, m1);
+        const float4 gk[3] = {mul4(gm, mul4(lv[1], lv[2])), mul4(gm, mul4(lv[0], lv[2])), mul4(gm, mul4(lv[0], lv[1]))};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int kl = __float_as_int(t[k].x) | (__float_as_int(t[k].y) << 16);
+          if (kl != lr[k].kl) {
+            flush_line(lr[k], d.g_line[k], C, ch);
+            lr[k].kl = kl;
+            lr[k].a0 = z4(); lr[k].a1 = z4();
+          }
+          lr[k].a0 = fma4(t[k].z, gk[k], lr[k].a0);
+          lr[k].a1 = fma4(t[k].w, gk[k], lr[k].a1);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) flush_line(lr[k], d.g_line[k], C, ch);
+    }
+  }
+}
+
 static int sample_grid(int64_t n_hint) {
   int64_t blocks = (n_hint * GS + 255) / 256;
   int64_t cap = (int64_t)FTRF_SMS * 8;
@@ -489,8 +574,17 @@ int launch_density(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStre
 }
 
 int launch_density_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st) {
-  if (f.model == FTRF_MODEL_VM && g_density_bwd_runs == 12) density_bwd_vm_staged_kernel<<<FTRF_SMS * DBW_CTAS, 256, 0, st>>>(f, c, ws);
+  if (f.model == FTRF_MODEL_VM && g_density_bwd_runs == 12) {
+    constexpr size_t smem = (sizeof(float4) * 3 + sizeof(float)) * (256 / GS) * DSEG;
+    cudaFuncSetAttribute(density_bwd_vm_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    density_bwd_vm_staged_kernel<<<FTRF_SMS * DBW_CTAS, 256, smem, st>>>(f, c, ws);
+  }
   else if (f.model == FTRF_MODEL_VM && g_density_bwd_runs) density_bwd_vm_runs_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws, g_density_bwd_runs);
+  else if (f.model == FTRF_MODEL_CP && g_density_bwd_runs) {
+    constexpr size_t smem = (sizeof(float4) * 3 + sizeof(float)) * (256 / GS) * DSEG;
+    cudaFuncSetAttribute(density_bwd_cp_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    density_bwd_cp_staged_kernel<<<FTRF_SMS * DBW_CTAS, 256, smem, st>>>(f, c, ws);
+  }
   else density_bwd_kernel<<<FTRF_SMS * 8, 256, 0, st>>>(f, c, ws);
   return check_launch("density_bwd");
 }

@@ -473,9 +473,11 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
 
 // ================================================================================================
 // Backward input-gradient chain as ONE persistent kernel:
-//   g_h1 = relu'(h1) * (g_h2 W2)  ->  g_X = g_h1 W1  ->  g_feat (chain rule through the encoding)
-// per 128-sample tile.  g_h2 arrives from layer3_bwd_kernel; g_h1 is written out for the weight-gradient
-// kernel; g_X never leaves the SM.
+//   go = g_rgb * sigmoid'  ->  g_h2 = relu'(h2) * (go W3)  ->  g_h1 = relu'(h1) * (g_h2 W2)  ->  g_X = g_h1 W1  ->  g_feat
+// (chain rule through the encoding) per 128-sample tile.  g_h2 is formed in registers from the saved h2 (it is never
+// written: the output-layer backward used to be a kernel of its own that wrote it and this one read it back, 105 MB
+// per step); go (3 floats per sample) is left in the workspace for the weight-gradient kernel, which rebuilds g_h2
+// the same way and also owns dW3 / db3 / db2; g_h1 is written out for that kernel; g_X never leaves the SM.
 // Roles: two groups of 8 compute warps work on alternate tiles (one group's loads / epilogue overlap
 // the other group's products), thread = (sample row, half of the columns); warp 16 issues the MMAs tile
 // by tile; warp 17 streams the weights by TMA: per tile 8 sub-chunks (K = 16) of W2^T [128 x 16] then 8
@@ -590,7 +592,8 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
   float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [group][A_STAGES][hi, lo][4096]
   float* w_ring = a_ring + (size_t)BZ_GROUPS * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS;   // [W_STAGES][BZ_WSTAGE_FLOATS]
   SPair* s_pair = reinterpret_cast<SPair*>(w_ring + (size_t)BZ_W_STAGES * BZ_WSTAGE_FLOATS);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_pair + FZ_MAX_K / 2);
+  float* s_w3 = reinterpret_cast<float*>(s_pair + FZ_MAX_K / 2);                    // [3][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_w3 + 3 * FC);
   uint64_t* a_full = bars;                                   // [group][A_STAGES]  4 warp arrivals (the column half that owns the chunk)
   uint64_t* a_empty = a_full + BZ_GROUPS * BZ_A_STAGES;
   uint64_t* w_full = a_empty + BZ_GROUPS * BZ_A_STAGES;      // [W_STAGES]
@@ -611,6 +614,7 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
     tc::fence_barrier_init();
   }
   if (warp == 16) tc::tmem_alloc(tmem_slot, 512);
+  for (int e = tid; e < 3 * FC; e += BZ_THREADS) s_w3[e] = __ldg(f.w3 + e);
   for (int e = tid; e < fs.kp / 2; e += BZ_THREADS) {
     const PairRec r = fs.pair[e];
     SPair p;
@@ -657,14 +661,31 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
       const bool live = row < n;
       const uint32_t ac0 = (uint32_t)li * 8;
       if (tl) FZ_T(g, li * 8 + 0);
-      // ---- g_h2 chunks (half, half + 2) -> operand ring (A of g_h2 W2); all loads in flight at once
+      // ---- g_h2 chunks (half, half + 2) -> operand ring (A of g_h2 W2); all loads in flight at once.
+      // g_h2 = relu'(h2) * (go W3) with go = dL/d rgb * rgb (1 - rgb) (sigmoid backward, models/mlp.py:66-67)
       {
         float v[64];
         if (live) {
 #pragma unroll
           for (int jj = 0; jj < 2; ++jj)
 #pragma unroll
-            for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_gh2 + row * FC + (jj * 2 + half) * 32 + u * 8, v + jj * 32 + 8 * u);
+            for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_h2 + row * FC + (jj * 2 + half) * 32 + u * 8, v + jj * 32 + 8 * u);
+          float go[3];
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) {
+            const float r = ws.a_rgb[row * 3 + ch];
+            go[ch] = ws.a_grgb[row * 3 + ch] * r * (1.f - r);
+          }
+          if (half == 0) *reinterpret_cast<float4*>(ws.a_gh2 + row * 4) = make_float4(go[0], go[1], go[2], 0.f);   // go4, for the wgrad kernel
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            const float* w3 = s_w3 + (jj * 2 + half) * 32;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float g = go[0] * w3[i] + go[1] * w3[FC + i] + go[2] * w3[2 * FC + i];
+              v[jj * 32 + i] = v[jj * 32 + i] > 0.f ? g : 0.f;
+            }
+          }
         } else {
 #pragma unroll
           for (int i = 0; i < 64; ++i) v[i] = 0.f;
@@ -932,6 +953,12 @@ int shade_prep_ahead(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
   return FTRF_OK;
 }
 
+bool shade_dgrad_is_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws) {
+  InSpec sp = make_spec(f);
+  FusedSpec fs;
+  return make_fused_spec(f, sp, fs) && fs.kp <= ws.ldx && ws.wimg && dgrad_variant(f, fs) >= 0;
+}
+
 int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaStream_t st, bool* handled) {
   *handled = false;
   InSpec sp = make_spec(f);
@@ -953,7 +980,7 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
     if (int e = check_launch("prep_weights_bwd")) return e;
   }
   const size_t smem = ((size_t)BZ_GROUPS * BZ_A_STAGES * 2 * FZ_CHUNK_FLOATS + (size_t)BZ_W_STAGES * BZ_WSTAGE_FLOATS) * 4 +
-                      (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 24 * 8 + 16;
+                      (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + (size_t)3 * FC * 4 + 24 * 8 + 16;
   int64_t tiles = (c.cap_app + 127) / 128;
   int grid = (int)(tiles < FTRF_SMS ? tiles : FTRF_SMS);
   auto go = [&](auto kern) {

@@ -344,15 +344,27 @@ int launch_shade_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
     WgradFusedArgs wa{};
     wa.g2 = ws.a_gh2; wa.h1 = ws.a_h1; wa.g1 = ws.a_gh1; wa.x = ws.a_x; wa.ldx = ws.ldx; wa.kp = fs.kp;
     wa.count = ws.counters + 1; wa.cap = c.cap_app; wa.dw2 = f.g_w2;
+    if (shade_dgrad_is_fused(f, c, ws)) {     // that kernel formed g_h2 itself and left go4 where g_h2 used to go
+      wa.fold3 = 1;
+      wa.g2 = ws.a_h2;
+      wa.go4 = reinterpret_cast<const float4*>(ws.a_gh2);
+      wa.w3 = f.w3; wa.dw3 = f.g_w3; wa.db3 = f.g_b3; wa.db2 = f.g_b2;
+    }
     wa.dw1i = ws.wimg + fused_scratch_offset_floats();
     int e = launch_wgrad_fused(wa, fs, f.g_w1, sp.in_dim, f.g_b1, st, &c);
     prof_end(9, st);
     return e;
   }
-  prof_begin(7, st);
-  layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
-  if (int e = check_launch("layer3_bwd")) return e;
-  prof_end(7, st); prof_begin(8, st);      // stage 7: output layer; stage 8: dgrad chain down to g_feat
+  // stage 7: output-layer backward as a kernel of its own — only where the fused dgrad kernel does not run (it forms
+  // g_h2 in its prologue and the fused wgrad kernel takes dW3 / db3 / db2); stage 8: dgrad chain down to g_feat
+  const bool fold3 = internal && shade_dgrad_is_fused(f, c, ws);
+  if (!fold3) {
+    prof_begin(7, st);
+    layer3_bwd_kernel<<<FTRF_SMS * 2, 256, 0, st>>>(f, c, ws);
+    if (int e = check_launch("layer3_bwd")) return e;
+    prof_end(7, st);
+  }
+  prof_begin(8, st);
   bool fused_dgrad = false;
   if (internal) {
     if (int e = launch_shade_dgrad_fused(f, c, ws, st, &fused_dgrad)) return e;

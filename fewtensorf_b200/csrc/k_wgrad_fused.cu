@@ -62,6 +62,7 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float fold_dw3[3] = {0.f, 0.f, 0.f}, fold_db2 = 0.f, fold_db3[3] = {0.f, 0.f, 0.f};     // output-layer gradients (fold3)
   const int64_t M = a.count ? min((int64_t)*a.count, a.cap) : a.cap;
   const int64_t nchunks = (M + WG_KS - 1) / WG_KS;
   if ((int64_t)blockIdx.x >= nchunks) return;
@@ -91,10 +92,17 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   if (warp < WG_PROD_WARPS) {
     // ============================================================ producers
     // unit (col, ku) = samples 4ku..4ku+3 of one column; lanes run over col (coalesced 4-byte loads).
-    // Three register sets rotate, so the loads of chunk j+3 are in flight while chunks j..j+2 are written.
-    float v[3][20];
+    // Two register sets rotate, so the loads of chunk j+2 are in flight while chunks j, j+1 are written (17 warps
+    // leave 96 registers per thread: a third set spills once the output-layer gradients live here too).
+    float v[2][20];
     const int xu = a.kp * 4;                              // X units per chunk
     const int gcol = tid & 127, gku = tid >> 7;           // this thread's unit of every 128-wide tile
+    float w3c[3] = {0.f, 0.f, 0.f};
+    float (&dw3)[3] = fold_dw3, &db2 = fold_db2, (&db3)[3] = fold_db3;
+    if (a.fold3) {
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) w3c[ch] = __ldg(a.w3 + ch * 128 + gcol);
+    }
     auto load = [&](int j, float (&r)[20]) {
       const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS;
 #pragma unroll
@@ -125,6 +133,24 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     };
     auto store = [&](int j, float (&r)[20]) {
       const int stg = j % WG_STAGES;
+      if (a.fold3) {
+        // r[0..3] holds h2 of this thread's column for four samples: rebuild g_h2 and collect the output layer's gradients
+        const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS + gku * 4;
+        if (j + 1 < my_chunks) {                        // the next chunk's go values: into L1 while this chunk is written
+          const float4* nx = a.go4 + ((int64_t)blockIdx.x + (int64_t)(j + 1) * gridDim.x) * WG_KS + gku * 4;
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 g = s0 + i < M ? __ldg(a.go4 + s0 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float h = r[i];
+          dw3[0] = fmaf(g.x, h, dw3[0]); dw3[1] = fmaf(g.y, h, dw3[1]); dw3[2] = fmaf(g.z, h, dw3[2]);
+          const float gh = h > 0.f ? g.x * w3c[0] + g.y * w3c[1] + g.z * w3c[2] : 0.f;
+          db2 += gh;
+          if (gcol == 0) { db3[0] += g.x; db3[1] += g.y; db3[2] += g.z; }
+          r[i] = gh;
+        }
+      }
       tc::mbar_wait(empty + stg, ((j / WG_STAGES) & 1) ^ 1);
       float* S = ring + (size_t)stg * WG_STAGE_FLOATS;
       const int off = tc::canon_off(gcol, gku, 4);
@@ -143,17 +169,12 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     };
     load(0, v[0]);
     if (1 < my_chunks) load(1, v[1]);
-    if (2 < my_chunks) load(2, v[2]);
-    for (int j = 0; j < my_chunks; j += 3) {
+    for (int j = 0; j < my_chunks; j += 2) {
       store(j, v[0]);
-      if (j + 3 < my_chunks) load(j + 3, v[0]);
+      if (j + 2 < my_chunks) load(j + 2, v[0]);
       if (j + 1 < my_chunks) {
         store(j + 1, v[1]);
-        if (j + 4 < my_chunks) load(j + 4, v[1]);
-      }
-      if (j + 2 < my_chunks) {
-        store(j + 2, v[2]);
-        if (j + 5 < my_chunks) load(j + 5, v[2]);
+        if (j + 3 < my_chunks) load(j + 3, v[1]);
       }
     }
   } else if (lane == 0) {
@@ -186,9 +207,19 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     tc::mma_commit(done);
   }
   // ============================================================ epilogue: TMEM -> red.global.add.v4
+  float* part = ring;                                   // [4 gku][128 col][4]: free once `done` has fired
   if (warp < WG_PROD_WARPS) {
     tc::mbar_wait(done, 0);
     tc::fence_after_sync();
+    if (a.fold3) {
+      const int gcol = tid & 127, gku = tid >> 7;
+      *reinterpret_cast<float4*>(part + (gku * 128 + gcol) * 4) = make_float4(fold_dw3[0], fold_dw3[1], fold_dw3[2], fold_db2);
+      if (gcol == 0) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch)
+          if (fold_db3[ch] != 0.f) atomicAdd(a.db3 + ch, fold_db3[ch]);
+      }
+    }
     const int q = warp & 3, o = q * 32 + lane;
     const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
     const int ncb = 4 + (WG_NGX * 4 + 31) / 32;
@@ -210,6 +241,18 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   }
   tc::fence_before_sync();
   __syncthreads();
+  if (a.fold3 && tid < 128) {                           // sum the four sample-quarter partials of every hidden unit
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 p = *reinterpret_cast<const float4*>(part + (q * 128 + tid) * 4);
+      s.x += p.x; s.y += p.y; s.z += p.z; s.w += p.w;
+    }
+    if (s.x != 0.f) atomicAdd(a.dw3 + tid, s.x);
+    if (s.y != 0.f) atomicAdd(a.dw3 + 128 + tid, s.y);
+    if (s.z != 0.f) atomicAdd(a.dw3 + 256 + tid, s.z);
+    if (s.w != 0.f) atomicAdd(a.db2 + tid, s.w);
+  }
   if (warp == WG_PROD_WARPS) tc::tmem_dealloc(tmem, 512);
 }
 

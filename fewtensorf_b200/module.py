@@ -626,13 +626,14 @@ class TensorBase(nn.Module):
                 keep.append(mk)
                 fs.mask[k] = mk.data_ptr()
 
-    def _fill_field(self, mask, grad_views=None) -> FtrfField:
+    def _fill_field(self, mask, grad_views=None, params=None) -> FtrfField:
         """FtrfField for this call.  Without FreeNeRF masks the struct only depends on the parameter
-        pointers, the alphaMask and the derived constants, so it is cached on exactly those."""
+        pointers, the alphaMask and the derived constants, so it is cached on exactly those.
+        `params`: the caller's `_all_params()` list (saves fetching it again on the hot path)."""
         if mask is None:
             # every input of _build_field: parameter pointers, mask / derived-constant serials and the plain
             # attributes a caller may change between calls
-            key = (tuple(p.data_ptr() for p in self._all_params()), self._mask_serial(), self._host["serial"],
+            key = (tuple(p.data_ptr() for p in (params if params is not None else self._all_params())), self._mask_serial(), self._host["serial"],
                    self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr(),
                    bool(self.use_coarse_mask), float(self.near_far[0]), float(self.near_far[1]),
                    float(self.distance_scale), float(self.density_shift), self.fea2denseAct, self.shadingMode)
@@ -738,12 +739,12 @@ class TensorBase(nn.Module):
             ev.synchronize()
         return int(c[0]), int(c[1]), int(c[2])
 
-    def _launch_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, caps=None) -> _CallState:
+    def _launch_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, caps=None, params=None) -> _CallState:
         """Enqueue march -> density -> integrate -> appearance -> shade -> composite (one C call, no sync)."""
         if not rays.is_cuda:
             raise RuntimeError("fewtensorf_b200 needs CUDA tensors (no CPU path)")
         N = rays.shape[0]
-        field = self._fill_field(mask)
+        field = self._fill_field(mask, None, params)
         call = FtrfCall()
         call.n_rays, call.ray_cols, call.n_samples = N, rays.shape[1], S
         call.is_train, call.ndc, call.add_bg, call.save_for_backward = int(is_train), int(ndc), int(add_bg), int(save)
@@ -800,11 +801,11 @@ class TensorBase(nn.Module):
         self._last_call = st
         return True
 
-    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, before_sync=None) -> _CallState:
+    def _run_forward(self, rays, jitter, mask, S, is_train, ndc, add_bg, save, before_sync=None, params=None) -> _CallState:
         """Forward with overflow handling: launch, sync once, repeat with larger lists if needed.
         `before_sync(st)` runs after the kernels are enqueued and before the host waits for them."""
         while True:
-            st = self._launch_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save)
+            st = self._launch_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save, params=params)
             if before_sync is not None:
                 before_sync(st)
             if self._finish_forward(st):
@@ -875,8 +876,11 @@ class TensorBase(nn.Module):
         step = max(1, MAX_CANDIDATES // S)
         outs = []
         for lo in range(0, max(N, 1), step):
-            r = rays[lo:lo + step]
-            j = jitter[lo:lo + step] if (jitter is not None and not ndc_ray) else jitter
+            if N <= step:                       # the usual case: one launch sequence, no slicing
+                r, j = rays, jitter
+            else:
+                r = rays[lo:lo + step]
+                j = jitter[lo:lo + step] if (jitter is not None and not ndc_ray) else jitter
             if need_grad:
                 outs.append(_RenderFn.apply(self, r, j, mask, S, is_train, ndc_ray, add_bg, *params))
             else:
@@ -1324,11 +1328,12 @@ class _RenderFn(torch.autograd.Function):
             buf, views = st.gradbuf = model.grad_buffer()
             model._zero_grad_buffer_async(buf)
             st.zeroing = True
-            st.bfield = model._fill_field(mask, views)
+            st.bfield = model._fill_field(mask, views, list(params))
             st.pre_gen = model.__dict__.get("_grad_gen", 0)
 
         model._zero_fork(rays.device)       # the memset may start here, beside the forward kernels
-        st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True, before_sync=prepare_backward)
+        st = model._run_forward(rays, jitter, mask, S, is_train, ndc, add_bg, save=True, before_sync=prepare_backward,
+                                params=list(params))
         st.wsobj.busy = True
         ctx.model, ctx.st = model, st
         ctx.token = _GraphToken()

@@ -15,7 +15,7 @@ frames = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 dev = torch.device("cuda", 0)
 model = bench.build_model(dev, shading=shading)
 rays = bench.camera_rays(dev)
-n = 16
+n = 13
 names = [lib.ftrf_profile_stage_name(i).decode() for i in range(n)]
 buf = (C.c_float * n)()
 acc = [0.0] * n
