@@ -38,7 +38,8 @@ GRID = 300
 MASK_GRID = 256
 RAYS_PER_GPU = 4096
 N_SAMPLES = 1039          # int(norm([300]*3) / 0.5), utils.py:124-125 / train.py:208
-SPIN_CYCLES = 500_000     # ~0.25 ms at 1.9 GHz: spin kernel in front of every device-timed step (see timed())
+SPIN_CYCLES = 1_000_000   # ~0.5 ms at 1.9 GHz: spin kernel in front of every device-timed step (see timed()); longer than the
+                          # host needs to enqueue a step even with eight ranks sharing the box's cores
 CPU_SAMPLE_RAYS = 2048    # bounded CPU sample (same workload, first rays of the batch); also the parity sample
 CPU_1T_RAYS = 256         # single-thread figure (script.sh:8-17 runs the reference with OMP_NUM_THREADS=1)
 CPU_FRAME_CHUNKS = 12     # of the 157 chunks of 4096 rays a frame is rendered in (renderer.py:149-183)
@@ -477,7 +478,7 @@ def workload_config(n_gpus):
                         + (" + all-reduce of the gradient buffer" if n_gpus > 1 else ""),
             "rays_per_gpu": RAYS_PER_GPU, "n_samples": N_SAMPLES, "grid": GRID, "mask_grid": MASK_GRID,
             "l2": "flushed between timed steps (512 MiB write)",
-            "queue": "a 0.25 ms spin kernel precedes every device-timed step so its launches are queued ahead of it "
+            "queue": "a 0.5 ms spin kernel precedes every device-timed step so its launches are queued ahead of it "
                      "(device time without host launch bubbles; e2e includes them)",
             "parallelism": f"ray-sharded x{n_gpus}"}
 
@@ -632,6 +633,8 @@ def run_gpu(args):
             dist.all_reduce(model._gradbuf)
 
     def step(r=rays, t=target):
+        if sg is not None:          # the exchange is enqueued inside the step, right behind the backward kernels
+            return model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world, allreduce=sg)
         loss, nv = model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
         if world > 1:
             reduce_grads()
@@ -702,9 +705,7 @@ def run_gpu(args):
     def e2e_fused():
         r = rays_p.to(dev, non_blocking=True)
         tg = target_p.to(dev, non_blocking=True)
-        loss, nv = model.train_step(r, tg, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
-        if world > 1:
-            reduce_grads()
+        loss, nv = step(r, tg)
         return loss.item()
 
     def wall(fn):

@@ -64,6 +64,7 @@ class FtrfCall(C.Structure):
         ("rays", _f32p), ("jitter", _f32p), ("rgb_map", _f32p), ("depth_map", _f32p), ("g_rgb_map", _f32p),
         ("cap_samples", C.c_int64), ("cap_app", C.c_int64),
         ("lib_flags", C.c_uint64), ("lib_ctx", C.c_void_p),       # library-owned hand-off state (zero-initialised)
+        ("overflow_out", C.c_void_p),
     ]
 
 
@@ -94,7 +95,7 @@ EXPORTS = [
     "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce",
     "ftrf_points_workspace_bytes", "ftrf_density_feature", "ftrf_app_feature", "ftrf_shade_points",
     "ftrf_resample_factor", "ftrf_crop_factor", "ftrf_ortho_reg",
-    "ftrf_p2p_allreduce_regions", "ftrf_multimem_allreduce_regions",
+    "ftrf_p2p_allreduce_regions", "ftrf_multimem_allreduce_regions", "ftrf_allreduce_regions_fused",
 ]
 TEST_LIB_PATH = os.path.join(_HERE, "libfewtensorf_b200_test.so")    # superset build for tests / scripts only
 PROF_STAGES = 13
@@ -166,6 +167,9 @@ def _load(path=LIB_PATH):
     lib.ftrf_p2p_allreduce_regions.argtypes = [C.POINTER(C.c_void_p), C.POINTER(FtrfRegion), C.c_int, C.c_int, C.c_int, C.c_void_p]
     lib.ftrf_multimem_allreduce_regions.restype = C.c_int
     lib.ftrf_multimem_allreduce_regions.argtypes = [C.c_void_p, C.POINTER(FtrfRegion), C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.ftrf_allreduce_regions_fused.restype = C.c_int
+    lib.ftrf_allreduce_regions_fused.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(FtrfRegion),
+                                                 C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p]
     lib.ftrf_reg_factors.restype = C.c_int
     lib.ftrf_reg_factors.argtypes = [C.POINTER(FtrfFactorSet), C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_void_p]

@@ -132,6 +132,87 @@ multimem_allreduce_regions_kernel(float* __restrict__ mc, const RegionTable tab,
   }
 }
 
+// ---- the same exchange with the two cross-GPU barriers INSIDE the kernel ------------------------------------
+// flags[r] is rank r's copy of a small symmetric int32 array: [0, 16) arrival flags of barrier A (one slot per sender),
+// [16, 32) of barrier B, [64] "go" word CTA 0 releases this GPU's other CTAs with, [65] finished-CTA counter.
+// `epoch` grows by one per call on every rank.  CTA 0 (always the first scheduled) signals and awaits barrier A — every
+// rank's backward has written its gradients — then lets the grid run; the last CTA to finish its share signals and
+// awaits barrier B — every share is back in every copy — so the kernel's end is the collective's end.  Two launches
+// and their gaps fewer than bracketing the exchange with separate barrier kernels.
+struct FlagPtrs { uint32_t* p[16]; };
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <int W, bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+allreduce_regions_fused_kernel(const PeerPtrs peers, float* __restrict__ mc, const FlagPtrs flags, const RegionTable tab,
+                               uint32_t lo, uint32_t hi, int rank, uint32_t epoch) {
+  uint32_t* mine = flags.p[rank];
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < W) {
+      __threadfence_system();
+      st_release_sys(flags.p[threadIdx.x] + rank, epoch);                 // barrier A: tell peer `tid` we are here
+      while (ld_acquire_sys(mine + threadIdx.x) < epoch) {}               //            and wait for peer `tid`
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine + 64), "r"(epoch) : "memory");
+  } else {
+    if (threadIdx.x == 0) while (ld_acquire_gpu(mine + 64) < epoch) {}
+    __syncthreads();
+  }
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t v = lo + blockIdx.x * blockDim.x + threadIdx.x; v < hi; v += stride) {
+    const size_t i = region_unit(tab, v);
+    if (MULTIMEM) {
+      float4 x;
+      float* p = mc + i * 4;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "l"(p) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                   ::"l"(p), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w) : "memory");
+    } else {
+      float4 x[W];
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x[r].x), "=f"(x[r].y), "=f"(x[r].z), "=f"(x[r].w) : "l"(peers.p[r] + i * 4) : "memory");
+      float4 a = x[0];
+#pragma unroll
+      for (int r = 1; r < W; ++r) { a.x += x[r].x; a.y += x[r].y; a.z += x[r].z; a.w += x[r].w; }
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(peers.p[r] + i * 4), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool last;
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(mine + 65, 1u);
+    last = done == gridDim.x - 1;
+    if (last) mine[65] = 0;                                               // (next launch starts after this kernel ends)
+  }
+  __syncthreads();
+  if (last && threadIdx.x < W) {
+    __threadfence_system();
+    st_release_sys(flags.p[threadIdx.x] + 16 + rank, epoch);              // barrier B
+    while (ld_acquire_sys(mine + 16 + threadIdx.x) < epoch) {}
+  }
+}
+
 static int make_region_table(const FtrfRegion* regions, int n, RegionTable* t, const char* who) {
   if (!regions || n < 1 || n > FTRF_MAX_REGIONS) { set_error("%s: 1..%d regions", who, FTRF_MAX_REGIONS); return FTRF_E_ARG; }
   uint64_t total = 0;
@@ -180,6 +261,40 @@ extern "C" int ftrf_p2p_allreduce_regions(void* const* peer_ptrs, const FtrfRegi
     else ftrf::p2p_allreduce_regions_kernel<8><<<grid, 512, 0, st>>>(pp, tab, lo, hi);
   }
   return ftrf::check_launch("p2p_allreduce_regions");
+}
+
+extern "C" int ftrf_allreduce_regions_fused(void* const* peer_ptrs, void* multicast_ptr, void* const* flag_ptrs,
+                                            const FtrfRegion* regions, int n_regions, int rank, int world, uint32_t epoch,
+                                            void* stream) {
+  if (!peer_ptrs || !flag_ptrs || (world != 2 && world != 4 && world != 8) || rank < 0 || rank >= world || epoch == 0) {
+    ftrf::set_error("allreduce_regions_fused: bad argument (world must be 2, 4 or 8)");
+    return FTRF_E_ARG;
+  }
+  ftrf::RegionTable tab;
+  if (int e = ftrf::make_region_table(regions, n_regions, &tab, "allreduce_regions_fused")) return e;
+  ftrf::PeerPtrs pp{};
+  ftrf::FlagPtrs fp{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_ptrs[r] || (((size_t)peer_ptrs[r]) & 15) || !flag_ptrs[r]) { ftrf::set_error("allreduce_regions_fused: bad peer pointer %d", r); return FTRF_E_ARG; }
+    pp.p[r] = (float*)peer_ptrs[r];
+    fp.p[r] = (uint32_t*)flag_ptrs[r];
+  }
+  const uint32_t n4 = tab.first[tab.n], per = (n4 + world - 1) / world;
+  const uint32_t lo = (uint64_t)per * rank < n4 ? per * rank : n4, hi = lo + per < n4 ? lo + per : n4;
+  const uint32_t want = hi > lo ? (hi - lo + 511) / 512 : 1;
+  const int grid = (int)(want < (uint32_t)FTRF_SMS * 2 ? want : (uint32_t)FTRF_SMS * 2);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* mc = (float*)multicast_ptr;
+  if (mc) {
+    if (world == 2) ftrf::allreduce_regions_fused_kernel<2, true><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+    else if (world == 4) ftrf::allreduce_regions_fused_kernel<4, true><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+    else ftrf::allreduce_regions_fused_kernel<8, true><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+  } else {
+    if (world == 2) ftrf::allreduce_regions_fused_kernel<2, false><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+    else if (world == 4) ftrf::allreduce_regions_fused_kernel<4, false><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+    else ftrf::allreduce_regions_fused_kernel<8, false><<<grid, 512, 0, st>>>(pp, mc, fp, tab, lo, hi, rank, epoch);
+  }
+  return ftrf::check_launch("allreduce_regions_fused");
 }
 
 extern "C" int ftrf_multimem_allreduce_regions(void* multicast_ptr, const FtrfRegion* regions, int n_regions, int rank, int world,

@@ -167,6 +167,7 @@ composite_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 __global__ void __launch_bounds__(INT_WARPS * 32)
 integrate_bwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const bool write_grgb) {
   const int warp = threadIdx.x >> 5, lane = lane_id();
+  if (write_grgb && c.overflow_out && blockIdx.x == 0 && threadIdx.x == 0) *c.overflow_out = ws.counters[2] ? 1.f : 0.f;
   const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
   for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
     const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
@@ -270,6 +271,7 @@ int launch_composite(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaSt
 __global__ void __launch_bounds__(256)
 grgb_kernel(const FtrfCall c, const Ws ws) {
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  if (c.overflow_out && blockIdx.x == 0 && threadIdx.x == 0) *c.overflow_out = ws.counters[2] ? 1.f : 0.f;
   for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < n; a += (int64_t)gridDim.x * blockDim.x) {
     const int slot = ws.a_slot[a];
     const int r = ws.s_ray[slot];

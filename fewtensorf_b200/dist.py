@@ -89,6 +89,14 @@ class SymmetricGradients:
         import ctypes as C
         self.group = group
         self._peer_ptrs = (C.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+        # flags of the barriers the fused kernels run inside themselves (ftrf_allreduce_regions_fused)
+        self._flags = symm_mem.empty(128, dtype=torch.int32, device=dev)
+        self._flags.zero_()
+        self._flag_handle = symm_mem.rendezvous(self._flags, pg.group_name)
+        self._flag_ptrs = (C.c_void_p * self.world)(*[int(p) for p in self._flag_handle.buffer_ptrs])
+        self._epoch = 0
+        torch.cuda.synchronize()
+        dist.barrier(group=group)                        # every rank's flags are zero before anybody signals
         self.model = model
         self._regions_key = None
         self._refresh_regions()
@@ -137,12 +145,18 @@ class SymmetricGradients:
         return sg
 
     def _launch(self, kind: str) -> None:
-        from ._abi import check
-        st = torch.cuda.current_stream().cuda_stream
+        from ._abi import check, current_stream_handle
+        st = current_stream_handle()
         if kind == "nccl":
             dist.all_reduce(self.storage, op=dist.ReduceOp.SUM, group=self.group)
             return
         self._refresh_regions()
+        if kind in ("p2p_fused", "multimem_fused"):
+            self._epoch += 1
+            mc = int(self.handle.multicast_ptr) if kind == "multimem_fused" else None
+            check(self._lib.ftrf_allreduce_regions_fused(self._peer_ptrs, mc, self._flag_ptrs, self._regions, self._n_regions,
+                                                         self.rank, self.world, self._epoch, st), "allreduce_regions_fused")
+            return
         self.handle.barrier(channel=0)                       # every rank's backward has written its gradients
         if kind == "multimem":
             check(self._lib.ftrf_multimem_allreduce_regions(int(self.handle.multicast_ptr), self._regions, self._n_regions,
@@ -160,6 +174,9 @@ class SymmetricGradients:
             kinds.append("multimem")
         if self.world in (2, 4, 8):
             kinds.append("p2p")
+            kinds.append("p2p_fused")
+            if int(self.handle.multicast_ptr):
+                kinds.append("multimem_fused")
         times = []
         for kind in kinds:
             for _ in range(3):

@@ -897,8 +897,10 @@ class TensorBase(nn.Module):
         backward into the flat gradient buffer.  Sets `.grad` of every parameter to its view of that
         buffer and returns (loss 0-dim device tensor, num_valid_samples int).
 
+        allreduce=<dist.SymmetricGradients>: the gradients are summed over the group by the library's own NVLink
+        kernels, enqueued right behind the backward (before the step's one host wait).
         allreduce=True (one process per GPU, torch.distributed initialised): the gradients are summed over
-        `group` inside the step, overlapped with the backward — the appearance planes / lines / basis
+        `group` inside the step with NCCL, overlapped with the backward — the appearance planes / lines / basis
         and the MLP (3/4 of the bytes) are final before the density backward and travel while it runs; the
         density gradients follow.  Pass grad_scale = n_local / n_global
         (dist.grad_scale).  A rank whose packed lists overflowed raises a flag that rides in the buffer's
@@ -915,7 +917,8 @@ class TensorBase(nn.Module):
         loss = torch.empty(1, dtype=torch.float32, device=rays.device)
         g_rgb = torch.empty(N, 3, dtype=torch.float32, device=rays.device)
         reduce_on = bool(allreduce) and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
-        lo, hi = self._early_grad_span() if reduce_on else (0, 0)
+        reducer = allreduce if (reduce_on and hasattr(allreduce, "all_reduce")) else None     # dist.SymmetricGradients
+        lo, hi = self._early_grad_span() if (reduce_on and reducer is None) else (0, 0)
         while True:
             # everything is enqueued back to back (the kernels read the sample counts from device memory);
             # the single host sync comes at the end and only decides whether a list overflowed
@@ -933,9 +936,19 @@ class TensorBase(nn.Module):
                 if self._finish_forward(st, whole_stream=True):
                     break
                 continue
-            # this rank's overflow flag (final after the forward) rides in the tail slot
-            counters = self.workspace_section(st, "COUNTERS", torch.int32, 8)
-            buf[-GRAD_TAIL:-GRAD_TAIL + 1].copy_(counters[2:3].ne(0))
+            # this rank's overflow flag (final after the forward) rides in the tail slot: the backward's first kernel
+            # writes it there (FtrfCall.overflow_out)
+            st.call.overflow_out = buf.data_ptr() + (buf.numel() - GRAD_TAIL) * 4
+            if reducer is not None:
+                # the library's own exchange (NVLink peer loads / multimem over the regions that can hold a gradient),
+                # enqueued right behind the backward: the host's one wait of the step comes after it
+                self._run_backward(st, g_rgb, views)
+                reducer.all_reduce()
+                flag = self._tail_flag(buf)
+                ok = self._finish_forward(st, whole_stream=True)
+                if float(flag[0]) == 0.0 and ok:
+                    break
+                continue
             self._run_backward(st, g_rgb, views, part=1)
             works = [dist.all_reduce(buf[lo:], group=group, async_op=True)]
             self._run_backward(st, g_rgb, views, part=2)

@@ -126,6 +126,10 @@ typedef struct FtrfCall {
    * what keeps the entry points re-entrant: the library holds no process-wide state about a call. */
   uint64_t lib_flags;
   void* lib_ctx;
+  /* backward, optional (NULL = off): device float that receives 1.0 if this call's packed lists overflowed, else 0.0.
+   * A multi-GPU step points it at the tail slot of the gradient buffer, so the flag travels with the all-reduce and
+   * every rank learns that some rank has to repeat the step (fewtensorf_b200/module.py: train_step). */
+  float* overflow_out;
 } FtrfCall;
 
 /* Workspace sections (offsets in bytes from the workspace base, filled by ftrf_workspace_layout). */
@@ -276,6 +280,11 @@ int ftrf_p2p_allreduce_regions(void* const* peer_ptrs, const FtrfRegion* regions
                                void* stream);
 int ftrf_multimem_allreduce_regions(void* multicast_ptr, const FtrfRegion* regions, int n_regions, int rank, int world,
                                     void* stream);
+/* The region exchange with both cross-GPU barriers inside the kernel (no bracketing barrier launches): flag_ptrs[r] is
+ * rank r's copy of a zero-initialised symmetric int32[128] array, epoch = 1, 2, 3, ... per call (the same on every
+ * rank).  multicast_ptr != NULL selects the NVSwitch multimem path, NULL the peer-load path. */
+int ftrf_allreduce_regions_fused(void* const* peer_ptrs, void* multicast_ptr, void* const* flag_ptrs, const FtrfRegion* regions,
+                                 int n_regions, int rank, int world, uint32_t epoch, void* stream);
 /* Regularisers of one factor set, value and gradient in one pass.
  *   TV : sum_k 1e-2 * TVLoss(plane_k)      models/tensoRF.py:195-205 with loss.py:120-141 (VM planes only; the
  *        reference's CP variant, tensoRF.py:474-484, is 0/0 = NaN and is refused with FTRF_E_ARG)

@@ -51,8 +51,8 @@ def _worker(rank, world, port, out):
     frac = None
     if sg is not None:
         frac = sg.exchanged_floats / sg.storage.numel()
-        for kind in ("p2p", "multimem"):
-            if kind == "multimem" and not int(sg.handle.multicast_ptr):
+        for kind in ("p2p", "multimem", "p2p_fused", "multimem_fused"):      # *_fused: barriers inside the exchange kernel
+            if kind.startswith("multimem") and not int(sg.handle.multicast_ptr):
                 continue
             sg.kind = kind
             for _ in range(2):
@@ -60,6 +60,10 @@ def _worker(rank, world, port, out):
                 sg.all_reduce()
             assert model._gradbuf.untyped_storage().data_ptr() == sg.storage.untyped_storage().data_ptr()
             res[kind] = grads()
+        # the exchange enqueued inside train_step, behind the backward and before the step's host wait
+        for _ in range(2):
+            run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg)
+        res["in_step"] = grads()
     dist.barrier()
     if rank == 0:
         # one GPU, the concatenated batch (mean over 2n rays = sum of the two pre-scaled rank means)
@@ -90,4 +94,4 @@ def test_two_rank_gradients_equal_one_gpu_on_the_concatenated_batch():
     assert "nccl" in errs and "overlapped" in errs
     assert max(errs.values()) < 1e-5, errs
     if frac is not None:
-        assert "p2p" in errs and frac < 0.6
+        assert "p2p" in errs and "p2p_fused" in errs and frac < 0.6
