@@ -761,6 +761,9 @@ def run_gpu(args):
     for n_, ms in zip(names, stage_ms):
         row = stage_roofline(n_, ms, units, peaks)
         if row:
+            t_ = traffic.get(n_, {})
+            if "l1tex_pct" in t_:       # ncu's own unit utilisation of the stage's kernel, from the tracked capture of this build
+                row["ncu_pct"] = {k[:-4]: t_[k] for k in ("l1tex_pct", "lts_pct", "dram_pct", "tensor_pct", "sm_pct") if k in t_}
             stages[n_] = row
     top = max(stages, key=lambda k: stages[k]["ms"])
     tr = stages[top]
@@ -768,6 +771,7 @@ def run_gpu(args):
             "achieved": tr["achieved"], "peak": tr["peak"], "unit": "TFLOP/s" if tr["bound"] == "tensor" else "GB/s", "frac": tr["frac"],
             "traffic": traffic.get(top, {}).get("dram_bytes_per_launch"), "traffic_source": traffic.get(top, {}).get("source"),
             "ms_per_launch": tr["ms"], "algorithmic_per_launch": tr.get("bytes", tr.get("flops")),
+            "onchip_traffic_ncu": {k: traffic.get(top, {}).get(k) for k in ("l1_load_bytes", "l2_read_bytes", "l2_red_bytes", "l1tex_pct", "lts_pct", "tensor_pct")},
             "note": "bound_detail l2 / l1: the kernel's bytes are served on chip; peak = measured L2 read (+ reduction) or L1 "
                     "bandwidth, not HBM (\"bound\" keeps the contract's two-value vocabulary)",
             "peaks": {k: peaks[k] for k in ("hbm", "l2_read", "l2_red", "l1_read", "tf32", "bf16", "hbm_src", "onchip_src")}}

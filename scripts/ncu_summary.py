@@ -60,13 +60,27 @@ def _bytes(val, unit):
     return float(val.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}.get(unit, 1)
 
 
+SECTORS = {'l1_load_bytes': 'l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum',      # sectors looked up in L1 by global loads
+           'l2_read_bytes': 'lts__t_sectors_srcunit_tex_op_read.sum',                # sectors L2 served to the SMs
+           'l2_red_bytes': 'lts__t_sectors_srcunit_tex_op_red.sum',                  # sectors reduced in L2 (red.global)
+           'l2_write_bytes': 'lts__t_sectors_srcunit_tex_op_write.sum'}
+PCTS = {'l1tex_pct': 'l1tex__throughput.avg.pct_of_peak_sustained_elapsed',
+        'lts_pct': 'lts__throughput.avg.pct_of_peak_sustained_elapsed',
+        'dram_pct': 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+        'tensor_pct': 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm_pct': 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
+        'warps_active_pct': 'sm__warps_active.avg.pct_of_peak_sustained_active'}
+
+
 def traffic(path, out, source=None):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch, summed over the kernels of each bench stage
-    (one training step captured with `ncu --set full`)."""
+    """Per bench stage, from one training step captured with `ncu --set full`: dram__bytes_read + write per launch
+    (bench.py's roofline.traffic), the on-chip traffic of the stage's dominant kernel (L1 load sectors, L2 read /
+    reduction / write sectors, 32 B each), ncu's unit percentages and the duration under the profiler."""
     import json
     rows = list(csv.reader(open(path)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     idx = {h: i for i, h in enumerate(hdr)}
+    num = lambda d, m: float(d[idx[m]].replace(',', '')) if m in idx and d[idx[m]] not in ('', 'n/a') else 0.0
     res = {}
     for d in data:
         name = d[idx['Kernel Name']].split('(')[0].split('<')[0].split('::')[-1].replace('void ', '').strip()
@@ -74,14 +88,29 @@ def traffic(path, out, source=None):
         if st is None:
             continue
         b = sum(_bytes(d[idx[m]], units[idx[m]]) for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+        rec = {'dram': b, 'us': num(d, 'gpu__time_duration.sum')}
+        rec.update({k: num(d, m) * 32 for k, m in SECTORS.items()})
+        rec.update({k: num(d, m) for k, m in PCTS.items()})
+        rec['red_instructions'] = num(d, 'smsp__inst_executed_op_global_red.sum')
         e = res.setdefault(st, {'per_kernel': {}, 'source': source or path})
-        e['per_kernel'].setdefault(name, []).append(b)
+        e['per_kernel'].setdefault(name, []).append(rec)
     for e in res.values():       # a kernel captured twice (window straddles two steps) counts once: mean per launch
-        e['kernels'] = sorted(e['per_kernel'])
-        e['dram_bytes_per_launch'] = int(sum(sum(v) / len(v) for v in e.pop('per_kernel').values()))
+        pk = e.pop('per_kernel')
+        mean = lambda v, key: sum(r[key] for r in v) / len(v)
+        e['kernels'] = sorted(pk)
+        e['dram_bytes_per_launch'] = int(sum(mean(v, 'dram') for v in pk.values()))
+        top = max(pk, key=lambda k: mean(pk[k], 'us'))            # the stage's dominant kernel
+        e['dominant_kernel'] = top
+        e['us_under_ncu'] = round(mean(pk[top], 'us'), 2)
+        for k in list(SECTORS) + ['red_instructions']:
+            e[k] = int(mean(pk[top], k))
+        for k in PCTS:
+            e[k] = round(mean(pk[top], k), 1)
     json.dump(res, open(out, 'w'), indent=1, sort_keys=True)
     for k, e in sorted(res.items()):
-        print(f"{k:20s} {e['dram_bytes_per_launch'] / 1e6:10.2f} MB  {','.join(e['kernels'])}")
+        print(f"{k:18s} dram {e['dram_bytes_per_launch'] / 1e6:8.2f} MB  l1 {e['l1_load_bytes'] / 1e6:8.1f}  l2rd {e['l2_read_bytes'] / 1e6:8.1f}  "
+              f"l2red {e['l2_red_bytes'] / 1e6:7.1f} MB | l1tex {e['l1tex_pct']:5.1f}% lts {e['lts_pct']:5.1f}% dram {e['dram_pct']:5.1f}% "
+              f"tensor {e['tensor_pct']:5.1f}% | {e['us_under_ncu']:7.1f} us  {e['dominant_kernel']}")
 
 
 if __name__ == "__main__":
