@@ -9,6 +9,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from fewtensorf_b200._abi import load_test_lib  # noqa: E402
 lib = load_test_lib()
+import fewtensorf_b200.module as _M  # noqa: E402
+_M.lib = lib          # the timeline hooks only exist in the test build: route the module's calls through it
 
 dev = torch.device("cuda", 0)
 m = bench.build_model(dev)
