@@ -78,6 +78,8 @@ class FtrfRegion(C.Structure):
 
 
 MAX_REGIONS = 24
+STATIC_SCRATCH_BYTES = 16 << 20    # FTRF_STATIC_SCRATCH_BYTES / FTRF_STATIC_MAX_POINTS (ftrf_shade_points_static)
+STATIC_MAX_POINTS = 8192
 
 
 class FtrfCamera(C.Structure):
@@ -93,7 +95,7 @@ EXPORTS = [
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
     "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_event_record", "ftrf_stream_wait_event", "ftrf_zero_after", "ftrf_profile_enable", "ftrf_profile_read",
     "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce",
-    "ftrf_points_workspace_bytes", "ftrf_density_feature", "ftrf_app_feature", "ftrf_shade_points",
+    "ftrf_points_workspace_bytes", "ftrf_density_feature", "ftrf_app_feature", "ftrf_shade_points", "ftrf_shade_points_static",
     "ftrf_resample_factor", "ftrf_crop_factor", "ftrf_ortho_reg",
     "ftrf_p2p_allreduce_regions", "ftrf_multimem_allreduce_regions", "ftrf_allreduce_regions_fused",
 ]
@@ -189,6 +191,9 @@ def _load(path=LIB_PATH):
     lib.ftrf_shade_points.restype = C.c_int
     lib.ftrf_shade_points.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.ftrf_shade_points_static.restype = C.c_int
+    lib.ftrf_shade_points_static.argtypes = [C.POINTER(FtrfField), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                             C.c_void_p]
     lib.ftrf_resample_factor.restype = C.c_int
     lib.ftrf_resample_factor.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     lib.ftrf_crop_factor.restype = C.c_int

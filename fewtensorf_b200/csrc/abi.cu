@@ -427,3 +427,59 @@ extern "C" int ftrf_shade_points(const FtrfField* f, const float* xn, const floa
   ws.a_rgb = rgb_out;
   return launch_shade(*f, c, ws, st);
 }
+
+// ---- ftrf_shade_points without a caller-provided (or any) allocation ---------------------------------------------
+// Added; the reference has no counterpart.  Callers that must not call
+// cudaMalloc (CUDA graph capture, tight serving loops) get the scratch of ftrf_shade_points — the counters, the tf32
+// hi / lo weight images prep_weights_kernel writes and the fused forward reads, the carved row buffers — out of ONE
+// file-scope device array that every GPU loading this library holds until exit.  In host code `g_static_scratch` is only
+// the host-side stand-in of the symbol: its device address is looked up once per device (that device current) with
+// cudaGetSymbolAddress and that pointer is what the kernels get.  All calls share the array and it keeps the last
+// call's contents: what must start at a known value (the counters) is rewritten by set_counters_kernel at the top of
+// every call, the weight images are rebuilt by every call; two calls that overlap on the GPU (different streams,
+// no ordering) race on it.
+namespace ftrf {
+static __device__ __align__(256) unsigned char g_static_scratch[FTRF_STATIC_SCRATCH_BYTES];
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::atomic<void*> g_static_scratch_addr[STATIC_MAX_DEVICES];
+
+static int static_scratch(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= STATIC_MAX_DEVICES) {
+    cudaGetLastError();
+    set_error("static scratch: no current device (%d)", dev);
+    return FTRF_E_CUDA;
+  }
+  void* p = g_static_scratch_addr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      set_error("static scratch: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return FTRF_E_CUDA;
+    }
+    g_static_scratch_addr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return FTRF_OK;
+}
+}  // namespace ftrf
+
+extern "C" int ftrf_shade_points_static(const FtrfField* f, const float* xn, const float* viewdirs, const float* features,
+                                        int64_t n, float* rgb_out, void* stream) {
+  if (!f) { set_error("shade_points_static: null field"); return FTRF_E_ARG; }
+  if (n < 0 || n > FTRF_STATIC_MAX_POINTS) {
+    set_error("shade_points_static: %lld points exceed the static scratch's limit of %d (use ftrf_shade_points with your own buffer)",
+              (long long)n, (int)FTRF_STATIC_MAX_POINTS);
+    return FTRF_E_ARG;
+  }
+  const size_t need = ftrf_points_workspace_bytes(f, n);
+  if (need == 0 || need > (size_t)FTRF_STATIC_SCRATCH_BYTES) {
+    set_error("shade_points_static: this field needs %zu scratch bytes for %lld points, the static array holds %zu",
+              need, (long long)n, (size_t)FTRF_STATIC_SCRATCH_BYTES);
+    return FTRF_E_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  if (int e = static_scratch(&scratch)) return e;
+  return ftrf_shade_points(f, xn, viewdirs, features, n, rgb_out, scratch, (size_t)FTRF_STATIC_SCRATCH_BYTES, stream);
+}

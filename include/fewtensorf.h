@@ -246,6 +246,21 @@ int ftrf_app_feature(const FtrfField* field, const float* xn, int64_t n, float* 
                      void* stream);
 int ftrf_shade_points(const FtrfField* field, const float* xn, const float* viewdirs, const float* features, int64_t n,
                       float* rgb_out, void* ws, size_t ws_bytes, void* stream);
+/* ftrf_shade_points for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs, outputs and
+ * kernels as ftrf_shade_points, but the scratch (counters, the MLP's tf32 weight images, row buffers) is a file-scope
+ * `static __device__` array of FTRF_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library
+ * holds until exit; the call performs no cudaMalloc / cudaFree and calls no allocating routine.
+ *   limits : n <= FTRF_STATIC_MAX_POINTS (8192) and ftrf_points_workspace_bytes(field, n) <= FTRF_STATIC_SCRATCH_BYTES
+ *            (16 MiB; the shipped MLP shapes need 0.8 MB of weight images + ~1.8 KB per point: 15.2 MB at the limit);
+ *            beyond either the call returns FTRF_E_ARG / FTRF_E_WORKSPACE with text and launches nothing.
+ *   sharing: all calls (all streams, all host threads) use the ONE array of the current device, and it keeps the last
+ *            call's contents; each call rewrites what it needs (counters, weight images), so calls ordered on one stream
+ *            are independent — calls that overlap on the GPU race and are not supported. */
+#define FTRF_STATIC_SCRATCH_BYTES (16u << 20)
+#define FTRF_STATIC_MAX_POINTS 8192
+int ftrf_shade_points_static(const FtrfField* field, const float* xn, const float* viewdirs, const float* features, int64_t n,
+                             float* rgb_out, void* stream);
 
 /* Per-stage device timing (bench / profiling aid; new, no reference counterpart).  When enabled,
  * ftrf_forward / ftrf_backward record CUDA events on the caller's stream around every stage.
