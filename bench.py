@@ -649,7 +649,7 @@ def run_gpu(args):
         step()
     barrier()
 
-    def timed(k, profile, fn=step):
+    def timed(k, profile, fn=step, prequeue=True):
         lib.ftrf_profile_enable(1 if profile else 0)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
         stage = [0.0] * PROF_STAGES
@@ -658,7 +658,8 @@ def run_gpu(args):
         barrier()
         for i in range(k):
             flush.zero_()                       # evict L2 between timed steps (untimed)
-            torch.cuda._sleep(SPIN_CYCLES)      # hold the GPU ~0.25 ms (untimed) so the step's launches are queued
+            if prequeue:
+                torch.cuda._sleep(SPIN_CYCLES)  # hold the GPU ~0.5 ms (untimed) so the step's launches are queued
             ev[i][0].record()                   # ahead of it: the device time of a step excludes host launch bubbles
             last = fn()
             ev[i][1].record()
@@ -678,6 +679,12 @@ def run_gpu(args):
     launches = int(lib.ftrf_launch_count() - launches0)
     clocks = sampler.summary()
     _, stage_ms, _ = timed(min(args.steps, 20), True)
+    k_plain = min(args.steps, 20)
+    plain_ms, _, _ = timed(k_plain, False, prequeue=False)   # the same steps WITHOUT the spin kernel: host launch bubbles included
+    tp = torch.tensor([plain_ms], device=dev)
+    if world > 1:
+        dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+    plain_ms = float(tp) / k_plain
     t = torch.tensor([total_ms], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -799,6 +806,8 @@ def run_gpu(args):
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": dict(workload_config(world), **({"allreduce": (sg.describe() if sg is not None else "nccl")} if world > 1 else {})),
            "clocks": clocks,
+           "without_prequeue": {"ms_per_step": plain_ms, "value": RAYS_PER_GPU * world / (plain_ms * 1e-3), "unit": "rays/s",
+                                "note": "the same device-timed steps without the spin kernel in front: host launch bubbles included"},
            "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32,
                    "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing)",
                    "train_step_api_value": e2e_fused_rps},

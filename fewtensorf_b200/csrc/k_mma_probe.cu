@@ -114,7 +114,189 @@ __global__ void __launch_bounds__(128, 1) layout_probe_kernel(int a_mn, uint32_t
   if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 512);
 }
 
+// Issue-side cost of what a fused kernel's MMA thread does around its dispatches: groups of 12 TS-form MMAs (one operand
+// chunk of the 3xTF32 scheme) with, per group, `commits` tcgen05.commit, `waits` waits on an mbarrier whose phase has
+// already completed, and optionally a tcgen05.fence::after_thread_sync.  out[0] = clocks for `groups` groups (issue),
+// out[1] = until the last MMA has completed.
+__global__ void __launch_bounds__(640, 1) issue_probe_kernel(int groups, int commits, int waits, int fence, int per_group, long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ uint64_t bar, done_bar, sink_bar[4];
+  __shared__ uint32_t slot[2];
+  float* sm = reinterpret_cast<float*>(smem_raw);
+  for (int i = threadIdx.x; i < 40960; i += blockDim.x) sm[i] = 0.f;
+  if (threadIdx.x == 0) {
+    slot[1] = 7u;
+    tc::mbar_init(&bar, 1);
+    tc::mbar_init(&done_bar, 1);
+    for (int i = 0; i < 4; ++i) tc::mbar_init(sink_bar + i, 1);
+    tc::fence_barrier_init();
+  }
+  if (threadIdx.x < 32) tc::tmem_alloc(slot, 512);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = slot[0];
+  if (threadIdx.x >= 128) {                      // noise warps beside the issuer: what slows its dispatches?
+    const int noise = fence >> 4, w = threadIdx.x >> 5;
+    const uint32_t t_lane = ((uint32_t)((w & 3) * 32)) << 16;
+    float x = (float)threadIdx.x, y = 1.0001f;
+    volatile uint32_t* stop = slot + 1;
+    while (*stop == 7u) {
+      if (noise == 1) {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) { x = fmaf(x, y, 0.5f); y = fmaf(y, 1.0001f, x * 1e-9f); }
+      } else if (noise == 2) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          tc::tmem_st4(tmem + t_lane + 448 + (uint32_t)(i * 4), x, y, x, y);
+          tc::tmem_st4(tmem + t_lane + 480 + (uint32_t)(i * 4), x, y, x, y);
+        }
+        tc::tmem_wait_st();
+        float v[8];
+        tc::tmem_ld8(tmem + t_lane + 448, v);
+        tc::tmem_wait_ld();
+        x += v[0];
+      } else if (noise == 3) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float q;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(q) : "r"(tc::smem_u32(sm + 36864 + ((threadIdx.x * 4 + i * 64) & 1023))) : "memory");
+          x += q;
+        }
+      } else {
+        __nanosleep(200);
+      }
+    }
+    if (x == 1234.5f) out[2] = (long long)x;
+  }
+  if (threadIdx.x == 32 && commits >= 8) {       // a second issuing thread (own warp) on its own accumulator / barriers
+    commits -= 8;
+    while (!tc::mbar_try_wait(&bar, 0)) {}
+    const uint32_t idesc = tc::idesc_tf32(128, 128);
+    const uint32_t b_lo = tc::desc_lo(tc::smem_u32(sm) + 65536, 128), d_hi = tc::desc_hi(1024);
+    for (int g = 0; g < groups; ++g) {
+      for (int w = 0; w < waits; ++w) tc::mbar_wait(&bar, 0);
+      if (fence) tc::fence_after_sync();
+      const uint32_t a = tmem + 384 + (uint32_t)(g & 1) * 64, d = tmem + 128;
+      for (int s = 0; s < per_group / 3; ++s) {
+        tc::mma_tf32_ts_lo(d, a + 32 + (s & 3) * 8, b_lo + (s & 3) * 16, d_hi, idesc, 1u);
+        tc::mma_tf32_ts_lo(d, a + (s & 3) * 8, b_lo + 1024 + (s & 3) * 16, d_hi, idesc, 1u);
+        tc::mma_tf32_ts_lo(d, a + (s & 3) * 8, b_lo + (s & 3) * 16, d_hi, idesc, 1u);
+      }
+      for (int k = 0; k < commits; ++k) tc::mma_commit(sink_bar + 2 + k);
+    }
+    tc::mma_commit(&done_bar);
+  }
+  if (threadIdx.x == 0) {
+    const bool two = commits >= 8;
+    if (two) commits -= 8;
+    tc::mbar_arrive(&bar);                       // phase 0 of `bar` is complete: waits on parity 0 return at once
+    const uint32_t idesc = tc::idesc_tf32(128, 128);
+    const uint32_t b_lo = tc::desc_lo(tc::smem_u32(sm) + 32768, 128), d_hi = tc::desc_hi(1024);
+    long long t0 = clock64();
+    for (int g = 0; g < groups; ++g) {
+      for (int w = 0; w < waits; ++w) {
+        if (((fence >> 1) & 3) == 0) tc::mbar_wait(&bar, 0);
+        else if (((fence >> 1) & 3) == 1) {
+          uint32_t ok;
+          do {
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(ok) : "r"(tc::smem_u32(&bar)), "r"(0) : "memory");
+          } while (!ok);
+        } else {
+          uint32_t v;
+          do {
+            asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(tc::smem_u32(slot) + 4) : "memory");
+          } while (v == 0xffffffffu);
+        }
+      }
+      if (fence & 1) tc::fence_after_sync();
+      const uint32_t a = tmem + 256 + (uint32_t)(g & 1) * 64, d = tmem;
+      for (int s = 0; s < per_group / 3; ++s) {
+        tc::mma_tf32_ts_lo(d, a + 32 + (s & 3) * 8, b_lo + (s & 3) * 16, d_hi, idesc, 1u);
+        tc::mma_tf32_ts_lo(d, a + (s & 3) * 8, b_lo + 1024 + (s & 3) * 16, d_hi, idesc, 1u);
+        tc::mma_tf32_ts_lo(d, a + (s & 3) * 8, b_lo + (s & 3) * 16, d_hi, idesc, 1u);
+      }
+      for (int k = 0; k < commits; ++k) tc::mma_commit(sink_bar + k);
+    }
+    long long t1 = clock64();
+    tc::mma_commit(&done_bar);
+    tc::mbar_wait(&done_bar, 0);
+    if (two) tc::mbar_wait(&done_bar, 1);
+    long long t2 = clock64();
+    if (blockIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
+    *reinterpret_cast<volatile uint32_t*>(slot + 1) = 0u;      // stops the noise warps
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 512);
+}
+
+// TS-form check: C[128 x 128] = A[128 x 32] B[128 x 32]^T with A written to TMEM by tcgen05.st (thread = row, one
+// 32-bit column per k) and B in shared memory (K-major no-swizzle).  Inputs are expected to be tf32-representable.
+__global__ void __launch_bounds__(128, 1) ts_gemm_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ Cout) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  float* sB = reinterpret_cast<float*>(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int e = tid; e < 128 * 8; e += 128) {
+    const int n = e >> 3, ku = e & 7;
+    *reinterpret_cast<float4*>(sB + tc::canon_off(n, ku, 8)) = *reinterpret_cast<const float4*>(B + n * 32 + ku * 4);
+  }
+  if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  if (warp == 0) tc::tmem_alloc(&slot, 256);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = slot;
+  const uint32_t t_lane = ((uint32_t)(warp * 32)) << 16;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const float4 v = *reinterpret_cast<const float4*>(A + tid * 32 + u * 4);
+    tc::tmem_st4(tmem + t_lane + 128 + u * 4, v.x, v.y, v.z, v.w);
+  }
+  tc::tmem_wait_st();
+  tc::fence_before_sync();
+  __syncthreads();
+  if (tid == 0) {
+    tc::fence_after_sync();
+    const uint32_t idesc = tc::idesc_tf32(128, 128);
+    const uint32_t b_lo = tc::desc_lo(tc::smem_u32(sB), 128), d_hi = tc::desc_hi(1024);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) tc::mma_tf32_ts_lo(tmem, tmem + 128 + s * 8, b_lo + s * 16, d_hi, idesc, s ? 1u : 0u);
+    tc::mma_commit(&bar);
+  }
+  tc::mbar_wait(&bar, 0);
+  tc::fence_after_sync();
+  for (int j = 0; j < 4; ++j) {
+    float acc[32];
+    tc::tmem_ld32(tmem + t_lane + j * 32, acc);
+    tc::tmem_wait_ld();
+    for (int i = 0; i < 32; ++i) Cout[tid * 128 + j * 32 + i] = acc[i];
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+}
+
 }  // namespace ftrf
+
+extern "C" int ftrf_debug_issue_probe(int groups, int commits, int waits, int fence, int per_group, int ctas, long long* out_device,
+                                      void* stream) {
+  if (commits < 0 || (commits & 7) > 2 || per_group % 3) return -1;
+  cudaFuncSetAttribute(ftrf::issue_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 163840);
+  ftrf::issue_probe_kernel<<<ctas, (fence >> 4) ? 128 + 512 : 128, 163840, (cudaStream_t)stream>>>(groups, commits, waits, fence, per_group, out_device);
+  return ftrf::check_launch("issue_probe");
+}
+
+extern "C" int ftrf_test_ts_gemm(const float* A, const float* B, float* C, void* stream) {
+  cudaFuncSetAttribute(ftrf::ts_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768);
+  ftrf::ts_gemm_kernel<<<1, 128, 32768, (cudaStream_t)stream>>>(A, B, C);
+  return ftrf::check_launch("ts_gemm");
+}
 
 extern "C" int ftrf_debug_layout_probe(int a_mn, unsigned lbo, unsigned sbo, int within, float* out_device, void* stream) {
   cudaFuncSetAttribute(ftrf::layout_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304);

@@ -471,6 +471,405 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
   if (warp == 8) tc::tmem_dealloc(tmem, 512);
 }
 
+#ifdef FTRF_TEST_BUILD
+// ================================================================================================
+// TEST BUILD ONLY — an experiment that did NOT beat the kernel above and is kept for the measurements it carries
+// (scripts/issue_probe.py, scripts/fused_timeline.py): 104 us per training step against 89 us,
+// 11.4 ms against 10.6 ms per MLP_Fea frame.  What it taught: (i) tcgen05.st / tcgen05.ld traffic of the compute warps
+// slows concurrent MMAs by ~40 % (issue probe with noise warps), so moving the operand from shared memory to tensor
+// memory only trades one contention for another; (ii) with 256 TMEM columns left beside the two accumulators the operand
+// ring is two stages deep, and every producer step pays a commit -> wait -> tcgen05.wait::st -> arrive round trip of
+// ~1 k clocks that such a shallow ring cannot hide.
+// Forward, second generation ("TS"): the activation operand of both layers lives in TENSOR MEMORY, written there by
+// the compute warps with tcgen05.st (thread = sample row, one 32-bit column per k, tf32 hi | lo), and the MMAs take
+// it from there (tcgen05.mma with A in TMEM); shared memory only carries the streamed weight chunks.
+// What shapes it (scripts/issue_probe.py, measured): whatever the MMA-issuing thread does between dispatches is NOT
+// hidden behind them — a successful barrier wait costs it ~225 clk (any shared-memory round trip does), the first
+// commit of a batch ~125, further ones ~50 — so 12-MMA operand chunks with two waits and three commits each ran at
+// 113 clk per MMA (the first-generation kernel above).  Here an operand GROUP is 64 k-columns (24 MMAs), the issuer
+// waits ONCE per group (the weight streamer forwards the weights' arrival to the operand barrier) and commits twice.
+//   warps 0-15  thread = (sample row, slice t): warp % 4 = TMEM lane quadrant (32 rows of the 128-row tile), warp / 4 = t.
+//               All sixteen warps build every operand group together (slice t = its columns 16 t .. 16 t + 15): X groups
+//               for layer 1, bias + ReLU + split of the layer-1 accumulator for layer 2.  The layer-2 epilogue (bias +
+//               ReLU, partial 128 -> 3 product) goes by 32-column slice; partials meet in shared memory.
+//   warp 16     issues every MMA (3xTF32), in ring order X groups, h1 groups per tile
+//   warp 17     streams the weight chunks (cp.async.bulk, 3 stages x 64 KB) and arrives on a group's barrier for them
+// TMEM: acc1 columns 0-127, acc2 128-255, operand ring 2 stages x (64 hi + 64 lo) columns at 256.
+// A warp runs  epi1(i) -> X(i+1) -> epi2(i)  per tile; with the in-order issue that is also what protects the
+// accumulators (L1 of tile i+1 follows every warp's reads of acc1(i), L2 of tile i+1 every warp's epi2(i)).
+constexpr int FT_CWARPS = 16;
+constexpr int FT_THREADS = (FT_CWARPS + 2) * 32;
+constexpr int FT_R_STAGES = 2;                     // operand ring (TMEM), 128 columns per stage
+constexpr int FT_W_STAGES = 3;                     // weight ring (shared memory), 64 KB per stage
+constexpr int FT_GK = 64;                          // k-columns of an operand group
+constexpr int FT_TILE = 128;
+constexpr uint32_t FT_ACC1 = 0, FT_ACC2 = 128, FT_RING = 256;
+int g_fwd_ts = 0;                                  // ftrf_debug_set_fwd_ts: 1 = this kernel instead of the SS kernel above
+
+template <int V> struct IC { static constexpr int value = V; };
+
+template <class SS>
+__global__ void __launch_bounds__(FT_THREADS, 1)
+shade_fwd_ts_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  float* w_ring = reinterpret_cast<float*>(smem_raw);                               // [W_STAGES][2 chunks][hi, lo][4096]
+  float* s_b1 = w_ring + (size_t)FT_W_STAGES * 4 * FZ_CHUNK_FLOATS;                 // [128]
+  float* s_b2 = s_b1 + FC;                                                          // [128]
+  float* s_w3 = s_b2 + FC;                                                          // [3][128]
+  float4* s_part = reinterpret_cast<float4*>(s_w3 + 3 * FC);                        // [2][4 slices][128] partial layer-3 sums
+  SPair* s_pair = reinterpret_cast<SPair*>(s_part + 2 * 4 * FT_TILE);               // [kp/2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_pair + FZ_MAX_K / 2);
+  uint64_t* o_full = bars;                       // [R_STAGES]  16 warp arrivals + the weight streamer's
+  uint64_t* o_empty = o_full + FT_R_STAGES;      // [R_STAGES]  tcgen05.commit
+  uint64_t* w_full = o_empty + FT_R_STAGES;      // [W_STAGES]  expect_tx + bulk copies
+  uint64_t* w_empty = w_full + FT_W_STAGES;      // [W_STAGES]  tcgen05.commit
+  uint64_t* acc_full = w_empty + FT_W_STAGES;    // [2]         layer 1, layer 2
+  uint64_t* part_full = acc_full + 2;            // [1]         16 warp arrivals: the partial layer-3 sums of a tile are in s_part
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(part_full + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int64_t ntiles = (n + FT_TILE - 1) / FT_TILE;
+  if ((int64_t)blockIdx.x >= ntiles) return;
+  const int my_tiles = (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int n1 = fs.n1, nxg = (fs.kp + FT_GK - 1) / FT_GK, ng = nxg + 2;        // W1 chunks; X groups, groups per tile
+
+  if (tid == 0) {
+    for (int i = 0; i < FT_R_STAGES; ++i) { tc::mbar_init(o_full + i, FT_CWARPS + 1); tc::mbar_init(o_empty + i, 1); }
+    for (int i = 0; i < FT_W_STAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
+    tc::mbar_init(acc_full + 0, 1);
+    tc::mbar_init(acc_full + 1, 1);
+    tc::mbar_init(part_full, FT_CWARPS);
+    tc::fence_barrier_init();
+  }
+  if (warp == FT_CWARPS) tc::tmem_alloc(tmem_slot, 512);
+  for (int e = tid; e < FC; e += FT_THREADS) { s_b1[e] = __ldg(f.b1 + e); s_b2[e] = __ldg(f.b2 + e); }
+  for (int e = tid; e < 3 * FC; e += FT_THREADS) s_w3[e] = __ldg(f.w3 + e);
+  for (int e = tid; e < fs.kp / 2; e += FT_THREADS) {
+    const PairRec r = fs.pair[e];
+    SPair p;
+    p.meta = (int)r.kind | ((int)r.sa << 8) | ((int)r.sb << 16);
+    p.scale = (float)(1 << r.fexp);
+    p.ma = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.ma) : 1.f;
+    p.mb = r.kind == PK_TRIG ? enc_mask_at(f, r.msrc, r.mb) : 1.f;
+    s_pair[e] = p;
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < FT_CWARPS) {
+    // =============================================================== compute warps: thread = (sample row, slice t)
+    const int team = warp >> 2, q = warp & 3, r_in = q * 32 + lane;
+    const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
+    const uint32_t t_acc1 = tmem + t_lane + FT_ACC1 + (uint32_t)(team * 16);    // + 64 G: this thread's columns of h1 group G
+    const uint32_t t_acc2 = tmem + t_lane + FT_ACC2 + (uint32_t)(team * 32);
+    const uint32_t t_ring = tmem + t_lane + FT_RING;
+    const float b3[3] = {__ldg(f.b3), __ldg(f.b3 + 1), __ldg(f.b3 + 2)};
+    const bool save = c.save_for_backward != 0;
+    const int D = fs.D;
+    const bool tl = warp == 0 && lane == 0;
+    auto tile_row = [&](int it) { return ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * FT_TILE + r_in; };
+    // sources of one row: [feat(D) | view(3) | pos(3)]
+    auto load_src = [&](int64_t row, float* dst) {
+      const bool live = row < n;
+      if constexpr (SS::is_static) {
+#pragma unroll
+        for (int k = 0; k < SS::D + 6; ++k) dst[k] = 0.f;
+        if (live) {
+          const float* fp = ws.a_feat + row * SS::D;
+#pragma unroll
+          for (int k = 0; k < SS::D; ++k) dst[k] = fp[k];
+          float v[3], p[3];
+          shade_geometry(f, c, ws, row, v, p);
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { dst[SS::D + k] = v[k]; dst[SS::D + 3 + k] = p[k]; }
+        }
+      } else {
+        if (live) {
+          const float* fp = ws.a_feat + row * D;
+          for (int k = 0; k < D; ++k) dst[k] = fp[k];
+          float v[3], p[3];
+          shade_geometry(f, c, ws, row, v, p);
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { dst[D + k] = v[k]; dst[D + 3 + k] = p[k]; }
+        } else {
+          for (int k = 0; k < D + 6; ++k) dst[k] = 0.f;
+        }
+      }
+    };
+    float src[FZ_MAX_SRC];
+    float da_s = 0.f, da_c = 1.f;                      // running (sin, cos) of the current source at the current octave
+
+    // stage of ring use `g`: wait until the MMAs that read its previous content have completed
+    auto ring_acquire = [&](uint32_t g) -> uint32_t {
+      const uint32_t stg = g % FT_R_STAGES;
+      tc::mbar_wait(o_empty + stg, ((g / FT_R_STAGES) & 1) ^ 1);
+      tc::fence_after_sync();
+      return t_ring + stg * (2 * FT_GK);
+    };
+    auto ring_publish = [&](uint32_t g) {
+      tc::tmem_wait_st();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(o_full + (g % FT_R_STAGES));
+    };
+    auto put4 = [&](uint32_t base, int u, const float v[4]) {      // unit u (4 columns) of a group: hi | lo
+      float4 h, l;
+      split4(v, h, l);
+      tc::tmem_st4(base + (uint32_t)(u * 4), h.x, h.y, h.z, h.w);
+      tc::tmem_st4(base + FT_GK + (uint32_t)(u * 4), l.x, l.y, l.z, l.w);
+    };
+
+    // this thread's 16 columns (units 4 t .. 4 t + 3) of X group G -> operand ring (+ X saved for backward).  The first trig
+    // pair of the part takes a fresh sincos: the octave below it is another thread's.
+    auto x_part = [&](auto gc, auto tmc, int gd, int64_t row, uint32_t g) {
+      constexpr int G = decltype(gc)::value, TM = decltype(tmc)::value;
+      const int grp = SS::is_static ? G : gd, tm = SS::is_static ? TM : team;
+      const bool live = row < n;
+      const uint32_t base = ring_acquire(g);
+      auto emit = [&](int u, int col, const float v[4]) {
+        put4(base, u, v);
+        if (save && live) *reinterpret_cast<float4*>(ws.a_x + row * ws.ldx + col) = make_float4(v[0], v[1], v[2], v[3]);
+      };
+      if constexpr (SS::is_static) {
+#pragma unroll
+        for (int uu = 0; uu < 4; ++uu) {
+          constexpr int C0 = G * FT_GK + TM * 16;        // first column of the part
+          if (C0 + uu * 4 < SS::kp) {
+            float v[4];
+#pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {
+              const int P = (C0 + uu * 4) / 2 + p2;
+              const PairInfo pi = SS::pair(P);
+              float x0 = 0.f, x1 = 0.f;
+              if (pi.kind == PK_TRIG) {
+                const SPair pr = s_pair[P];
+                if ((pi.fexp & 3) == 0 || P == C0 / 2) fast_sincos(src[pi.sa] * (float)(1 << pi.fexp), &da_s, &da_c);
+                else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
+                x0 = da_s * pr.ma;
+                x1 = da_c * pr.mb;
+              } else if (pi.kind == PK_COPY2) {
+                x0 = src[pi.sa];
+                x1 = src[pi.sb];
+              } else if (pi.kind == PK_COPY1) {
+                x0 = src[pi.sa];
+              }
+              v[2 * p2] = x0;
+              v[2 * p2 + 1] = x1;
+            }
+            emit(4 * TM + uu, C0 + uu * 4, v);
+          }
+        }
+      } else {
+        for (int uu = 0; uu < 4; ++uu) {
+          const int col = grp * FT_GK + tm * 16 + uu * 4;
+          if (col < fs.kp) {                             // warp-uniform
+            float v[4];
+#pragma unroll
+            for (int p2 = 0; p2 < 2; ++p2) {
+              const SPair pr = s_pair[col / 2 + p2];
+              const int kind = pr.meta & 0xff, sa = (pr.meta >> 8) & 0xff, sb = (pr.meta >> 16) & 0xff;
+              float x0 = 0.f, x1 = 0.f;
+              if (kind == PK_TRIG) {
+                if (((__float_as_int(pr.scale) >> 23) & 3) == 3 || (uu == 0 && p2 == 0)) fast_sincos(src[sa] * pr.scale, &da_s, &da_c);
+                else { const float s2 = 2.f * da_s * da_c; da_c = fmaf(-2.f * da_s, da_s, 1.f); da_s = s2; }
+                x0 = da_s * pr.ma;
+                x1 = da_c * pr.mb;
+              } else if (kind == PK_COPY2) {
+                x0 = src[sa];
+                x1 = src[sb];
+              } else if (kind == PK_COPY1) {
+                x0 = src[sa];
+              }
+              v[2 * p2] = x0;
+              v[2 * p2 + 1] = x1;
+            }
+            emit(4 * tm + uu, col, v);
+          }
+        }
+      }
+      ring_publish(g);
+    };
+    // every X group of one tile (this thread's slice of each); g0 = ring use of group 0
+    auto build_team = [&](auto tmc, int64_t row, uint32_t g0) {
+      if constexpr (SS::is_static) {
+        constexpr int NXG = (SS::kp + FT_GK - 1) / FT_GK;
+        if constexpr (0 < NXG) x_part(IC<0>{}, tmc, 0, row, g0 + 0);
+        if constexpr (1 < NXG) x_part(IC<1>{}, tmc, 1, row, g0 + 1);
+        if constexpr (2 < NXG) x_part(IC<2>{}, tmc, 2, row, g0 + 2);
+      }
+    };
+    auto build_x = [&](int64_t row, uint32_t g0) {
+      if constexpr (SS::is_static) {
+        switch (team) {
+          case 0: build_team(IC<0>{}, row, g0); break;
+          case 1: build_team(IC<1>{}, row, g0); break;
+          case 2: build_team(IC<2>{}, row, g0); break;
+          default: build_team(IC<3>{}, row, g0); break;
+        }
+      } else {
+        for (int k = 0; k < nxg; ++k) x_part(IC<0>{}, IC<0>{}, k, row, g0 + (uint32_t)k);
+      }
+    };
+
+    load_src(tile_row(0), src);
+    build_x(tile_row(0), 0u);
+    for (int it = 0; it < my_tiles; ++it) {
+      const int64_t row = tile_row(it), row_next = tile_row(it + 1);
+      const bool live = row < n, more = it + 1 < my_tiles;
+      const uint32_t g0 = (uint32_t)it * (uint32_t)ng;
+      if (tl) FZ_T(0, it * 8 + 0);
+      if (more) load_src(row_next, src);               // in flight during the layer-1 epilogue below
+      // ---- layer-1 accumulator -> the two layer-2 operand groups (bias + ReLU + split), this thread's 16 columns of each
+      tc::mbar_wait(acc_full + 0, it & 1);
+      tc::fence_after_sync();
+      if (tl) FZ_T(0, it * 8 + 1);
+      {
+        float acc[32];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tc::tmem_ld8(t_acc1 + (uint32_t)((j >> 1) * FT_GK + (j & 1) * 8), acc + 8 * j);
+        tc::tmem_wait_ld();                            // every read of acc1 precedes this warp's first X publish below
+#pragma unroll
+        for (int G = 0; G < 2; ++G) {
+          const int c0 = G * FT_GK + team * 16;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc[16 * G + i] = fmaxf(acc[16 * G + i] + s_b1[c0 + i], 0.f);
+          if (save && live) {
+            st_global_v8(ws.a_h1 + row * FC + c0, acc + 16 * G);
+            st_global_v8(ws.a_h1 + row * FC + c0 + 8, acc + 16 * G + 8);
+          }
+          const uint32_t g = g0 + (uint32_t)(nxg + G);
+          const uint32_t base = ring_acquire(g);
+#pragma unroll
+          for (int uu = 0; uu < 4; ++uu) put4(base, 4 * team + uu, acc + 16 * G + 4 * uu);
+          ring_publish(g);
+        }
+      }
+      if (tl) FZ_T(0, it * 8 + 2);
+      // ---- the next tile's input rows
+      if (more) build_x(row_next, g0 + (uint32_t)ng);
+      if (tl) FZ_T(0, it * 8 + 3);
+      // ---- layer-2 accumulator slice: bias + ReLU, partial 128 -> 3 product
+      tc::mbar_wait(acc_full + 1, it & 1);
+      tc::fence_after_sync();
+      if (tl) FZ_T(0, it * 8 + 4);
+      float o3[3] = {0.f, 0.f, 0.f};
+      {
+        float acc[32];
+        tc::tmem_ld32(t_acc2, acc);
+        tc::tmem_wait_ld();
+        tc::fence_before_sync();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b2[team * 32 + i], 0.f);
+        if (save && live) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h2 + row * FC + team * 32 + u * 8, acc + 8 * u);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float4* wr = reinterpret_cast<const float4*>(s_w3 + k * FC + team * 32);
+          float sacc = 0.f;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            float4 w4 = wr[u];
+            sacc = fmaf(acc[4 * u], w4.x, sacc); sacc = fmaf(acc[4 * u + 1], w4.y, sacc);
+            sacc = fmaf(acc[4 * u + 2], w4.z, sacc); sacc = fmaf(acc[4 * u + 3], w4.w, sacc);
+          }
+          o3[k] = sacc;
+        }
+      }
+      float4* part = s_part + (size_t)(it & 1) * 4 * FT_TILE;
+      part[team * FT_TILE + r_in] = make_float4(o3[0], o3[1], o3[2], 0.f);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(part_full);       // (release: the partial sums above are visible to the waiter)
+      if (team == (it & 3)) tc::mbar_wait(part_full, it & 1);
+      if (team == (it & 3) && live) {                  // the finishing slice rotates; nobody else waits
+        const float4 p0 = part[r_in], p1 = part[FT_TILE + r_in], p2 = part[2 * FT_TILE + r_in], p3 = part[3 * FT_TILE + r_in];
+        const float o0 = b3[0] + ((p0.x + p1.x) + (p2.x + p3.x));
+        const float o1 = b3[1] + ((p0.y + p1.y) + (p2.y + p3.y));
+        const float o2 = b3[2] + ((p0.z + p1.z) + (p2.z + p3.z));
+        ws.a_rgb[row * 3 + 0] = 1.f / (1.f + expf(-o0));
+        ws.a_rgb[row * 3 + 1] = 1.f / (1.f + expf(-o1));
+        ws.a_rgb[row * 3 + 2] = 1.f / (1.f + expf(-o2));
+      }
+      if (tl) FZ_T(0, it * 8 + 5);
+    }
+  } else if (warp == FT_CWARPS) {
+    // =============================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_tf32(128, 128);
+      const uint32_t w_lo0 = tc::desc_lo(tc::smem_u32(w_ring), 128);
+      const uint32_t d_hi = tc::desc_hi(1024);
+      uint32_t g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        for (int k = 0; k < ng; ++k, ++g) {
+          const uint32_t as = g % FT_R_STAGES, wsg = g % FT_W_STAGES;
+          const bool l1 = k < nxg;
+          const int ksteps = l1 ? min(FT_GK, fs.kp - k * FT_GK) / 8 : FT_GK / 8;
+          FZ_T(1, g * 2 + 0);
+          tc::mbar_wait(o_full + as, (g / FT_R_STAGES) & 1);       // operands AND weights (the streamer arrives for them)
+          FZ_T(1, g * 2 + 1);
+          tc::fence_after_sync();
+          const uint32_t w_lo = w_lo0 + wsg * (uint32_t)(4 * FZ_CHUNK_FLOATS * 4 / 16);
+          const uint32_t a_hi = tmem + FT_RING + as * (2 * FT_GK), a_lo = a_hi + FT_GK;
+          const uint32_t d = tmem + (l1 ? FT_ACC1 : FT_ACC2);
+          const uint32_t fresh = (k == 0 || k == nxg) ? 0u : 1u;
+          constexpr uint32_t LO = FZ_CHUNK_FLOATS * 4 / 16;      // hi -> lo half of a weight chunk, in 16-byte units
+#pragma unroll
+          for (int s = 0; s < FT_GK / 8; ++s) {
+            if (s < ksteps) {
+              const uint32_t wb = w_lo + (uint32_t)(s >> 2) * (2 * LO) + (uint32_t)(s & 3) * 16;   // chunk s / 4 of the stage
+              tc::mma_tf32_ts_lo(d, a_lo + s * 8, wb, d_hi, idesc, s == 0 ? fresh : 1u);
+              tc::mma_tf32_ts_lo(d, a_hi + s * 8, wb + LO, d_hi, idesc, 1u);
+              tc::mma_tf32_ts_lo(d, a_hi + s * 8, wb, d_hi, idesc, 1u);
+            }
+          }
+          tc::mma_commit(o_empty + as);
+          tc::mma_commit(w_empty + wsg);
+          if (k == nxg - 1) tc::mma_commit(acc_full + 0);
+          if (k == ng - 1) tc::mma_commit(acc_full + 1);
+        }
+      }
+    }
+  } else {
+    // =============================================================== weight streamer (TMA): group g's chunks into stage g % 3,
+    // up to three groups ahead; arrives on the group's operand barrier once its weights have landed
+    if (lane == 0) {
+      const uint32_t total = (uint32_t)my_tiles * (uint32_t)ng;
+      uint32_t issued = 0;
+      for (uint32_t g = 0; g < total; ++g) {
+        while (issued < total && issued < g + FT_W_STAGES) {
+          const uint32_t wsg = issued % FT_W_STAGES;
+          const int k = (int)(issued % (uint32_t)ng);
+          const int c0 = k < nxg ? 2 * k : n1 + 2 * (k - nxg);                   // first weight chunk of the group
+          const int nc = k < nxg ? min(2, n1 - 2 * k) : 2;
+          tc::mbar_wait(w_empty + wsg, ((issued / FT_W_STAGES) & 1) ^ 1);
+          mbar_expect_tx(w_full + wsg, (uint32_t)(nc * FZ_CHUNK_BYTES));
+          for (int j = 0; j < nc; ++j)
+            bulk_g2s(w_ring + ((size_t)wsg * 2 + j) * 2 * FZ_CHUNK_FLOATS, wimg + (size_t)(c0 + j) * 2 * FZ_CHUNK_FLOATS,
+                     (uint32_t)FZ_CHUNK_BYTES, w_full + wsg);
+          ++issued;
+        }
+        tc::mbar_wait(w_full + (g % FT_W_STAGES), (g / FT_W_STAGES) & 1);
+        if (g >= FT_R_STAGES) tc::mbar_wait(o_full + (g % FT_R_STAGES), ((g - FT_R_STAGES) / FT_R_STAGES) & 1);   // its previous phase is over
+        tc::mbar_arrive(o_full + (g % FT_R_STAGES));
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == FT_CWARPS) tc::tmem_dealloc(tmem, 512);
+}
+
+static size_t fwd_ts_smem() {
+  return (size_t)FT_W_STAGES * 4 * FZ_CHUNK_FLOATS * 4 + (size_t)(2 * FC + 3 * FC) * 4 + (size_t)2 * 4 * FT_TILE * sizeof(float4) +
+         (size_t)(FZ_MAX_K / 2) * sizeof(SPair) + 32 * 8 + 16;
+}
+
+#endif  // FTRF_TEST_BUILD
+
 // ================================================================================================
 // Backward input-gradient chain as ONE persistent kernel:
 //   go = g_rgb * sigmoid'  ->  g_h2 = relu'(h2) * (go W3)  ->  g_h1 = relu'(h1) * (g_h2 W2)  ->  g_X = g_h1 W1  ->  g_feat
@@ -1030,6 +1429,22 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
   using SMlp = StaticSpec<FTRF_SHADE_MLP, 27, 2, 2, 2>;
   using SFew = StaticSpec<FTRF_SHADE_MLP, 18, 8, 2, 2>;      // configs/free_tensorf_human.txt:46-54
   const bool pe2 = f.app_dim == 27 && f.view_pe == 2;
+#ifdef FTRF_TEST_BUILD
+  if (g_fwd_ts) {                                  // the TMEM-operand experiment (see shade_fwd_ts_kernel)
+    const int64_t tiles = (c.cap_app + FT_TILE - 1) / FT_TILE;
+    const int grid_ts = (int)(tiles < FTRF_SMS ? tiles : FTRF_SMS);
+    auto go_ts = [&](auto kern) {
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_ts_smem());
+      kern<<<grid_ts, FT_THREADS, fwd_ts_smem(), st>>>(f, c, ws, fs, img, g_fused_dbg);
+    };
+    if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) go_ts(shade_fwd_ts_kernel<SFea>);
+    else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) go_ts(shade_fwd_ts_kernel<SPe>);
+    else if (f.shading == FTRF_SHADE_MLP && pe2 && f.pos_pe == 2 && f.fea_pe == 2 && fs.kp == SMlp::kp) go_ts(shade_fwd_ts_kernel<SMlp>);
+    else if (f.shading == FTRF_SHADE_MLP && f.app_dim == 18 && f.pos_pe == 8 && f.view_pe == 2 && f.fea_pe == 2 && fs.kp == SFew::kp) go_ts(shade_fwd_ts_kernel<SFew>);
+    else go_ts(shade_fwd_ts_kernel<DynamicSpec>);
+    return check_launch("shade_fwd_ts");
+  }
+#endif
   if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) go(shade_fused_fwd_kernel<SFea>);
   else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) go(shade_fused_fwd_kernel<SPe>);
   else if (f.shading == FTRF_SHADE_MLP && pe2 && f.pos_pe == 2 && f.fea_pe == 2 && fs.kp == SMlp::kp) go(shade_fused_fwd_kernel<SMlp>);
@@ -1041,6 +1456,11 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
 }  // namespace ftrf
 
 #ifdef FTRF_TEST_BUILD
+extern "C" int ftrf_debug_set_fwd_ts(int on) {
+  ftrf::g_fwd_ts = on;
+  return FTRF_OK;
+}
+
 extern "C" int ftrf_debug_dgrad_timeline(void* device_buffer_3x512_i64) {
   ftrf::g_dgrad_dbg = (long long*)device_buffer_3x512_i64;
   return FTRF_OK;

@@ -31,15 +31,16 @@ for it in range(3):
 lib.ftrf_debug_fused_timeline(None)
 b = buf.cpu().view(3, 512)
 t0 = int(b[0, 0])
-print("compute warp 0 (pair: src_start x_start x_done acc1_ready epi1_done acc2_ready epi2_done), clocks since start")
-for it in range(4):
-    row = [int(v) - t0 for v in b[0, it * 8: it * 8 + 7]]
-    if row[0] < 0:
+print("compute warp 0 (tile: start acc1_ready epi1_done x_done acc2_ready end), clocks since start")
+for it in range(6):
+    row = [int(v) - t0 for v in b[0, it * 8: it * 8 + 6]]
+    if row[0] < 0 and it:
         break
-    print(it, row, "deltas", [row[i + 1] - row[i] for i in range(6)])
-print("mma thread (chunk: t_begin, wait_w, wait_a) and tma issue time")
-for wc in range(30):
-    r = [int(v) - t0 for v in b[1, wc * 3: wc * 3 + 3]]
-    if r[0] < -10**9:
-        break
-    print(wc, "mma begin", r[0], "w_wait", r[1] - r[0], "a_wait", r[2] - r[1], "| tma issue", int(b[2, wc]) - t0)
+    print(it, row)
+for role, name in ((1, "MMA issuer"),):
+    print(name, "(chunk: begin, operands ready -> waited)")
+    for g in range(30):
+        r = [int(v) - t0 for v in b[role, g * 2: g * 2 + 2]]
+        if r[0] < -10**9:
+            break
+        print(" ", g, "begin", r[0], "waited", r[1] - r[0])
