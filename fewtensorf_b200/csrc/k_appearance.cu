@@ -356,6 +356,226 @@ app_fwd_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
   if (warp == 0) tc::tmem_dealloc(tmem, 32);
 }
 
+
+// Warp-specialised build of the same forward (one CTA per SM).  In the kernel above a CTA alternates gather ->
+// __syncthreads -> products -> wait (the operand tile is single-buffered) three times per tile and then drains the
+// accumulator behind two more block-wide barriers; two CTAs per SM overlap that only coarsely (ncu: L1 at 45 %,
+// warps active 28 %).  Here the roles never wait for each other inside a tile:
+//   warps 0-11   gather workers: plane x line products of pair k -> operand buffer p % 2 (tf32 hi | lo, K-major)
+//   warps 12-13  taps of the NEXT tile (slot -> ray -> position, three dependent global round trips)
+//   warp 14      one lane issues the 3xTF32 products of a filled buffer into accumulator tile % 2 (32 TMEM columns each)
+//   warps 15-18  epilogue: accumulator rows -> shared staging -> one contiguous block of app_dim * 128 floats
+// all meeting through mbarriers only (operand full / empty, taps full / empty, accumulator full / empty).
+constexpr int AW_WORKERS = 384, AW_TAP0 = 384, AW_MMA_WARP = 14, AW_EPI_WARP0 = 15;
+constexpr int AW_THREADS = (12 + 2 + 1 + 4) * 32;
+FTRF_SWITCH(int, g_app_fwd_ws, 1);           // ftrf_debug_set_app_ws (test build): 0 = app_fwd_tc_kernel above
+
+__global__ void __launch_bounds__(AW_THREADS, 1)
+app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM) {
+  extern __shared__ __align__(1024) uint8_t app_raw[];
+  const FtrfFactorSet& a = f.app;
+  const int NP = a.n_comp[0] + a.n_comp[1] + a.n_comp[2], D = f.app_dim;
+  const size_t PSZ = (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F;      // floats of one hi (or lo) operand tile [128 x CM]
+  float* Bimg = reinterpret_cast<float*>(app_raw);                 // per pair k: hi [32 x C_k] then lo [32 x C_k]
+  float* P = Bimg + (size_t)2 * 32 * NP;                           // [2 buffers][hi, lo][PSZ]
+  float4* TAP0 = reinterpret_cast<float4*>(P + 4 * PSZ);           // 2 x [128][3] (i0, i1, w0, w1) per axis
+  float* stage = reinterpret_cast<float*>(TAP0 + 2 * TCT * 3);     // [128][D]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage + TCT * 32);
+  uint64_t* p_full = bars;            // [2] 12 warp arrivals
+  uint64_t* p_empty = bars + 2;       // [2] tcgen05.commit
+  uint64_t* tap_full = bars + 4;      // [2] 2 warp arrivals
+  uint64_t* tap_empty = bars + 6;     // [2] 12 warp arrivals
+  uint64_t* acc_full = bars + 8;      // [2] tcgen05.commit
+  uint64_t* acc_empty = bars + 10;    // [2] 4 warp arrivals
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 12);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  const int64_t ntiles = (n + TCT - 1) / TCT;
+  if ((int64_t)blockIdx.x >= ntiles) return;
+  const int my_tiles = (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  auto tile_base = [&](int i) { return ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * TCT; };
+
+  {   // basis matrix image (outputs padded to 32 rows of zeros)
+    int base = 0, kb = 0;
+    for (int k = 0; k < 3; ++k) {
+      const int Ck = a.n_comp[k], nq = Ck >> 2;
+      for (int e = tid; e < 32 * nq; e += AW_THREADS) {
+        const int o = e / nq, ku = e - o * nq;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f), h, l;
+        if (o < D) w = ld4(f.basis + (size_t)o * NP + kb + ku * 4);
+        const float v[4] = {w.x, w.y, w.z, w.w};
+        tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y); tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+        const int off = tc::canon_off(o, ku, nq);
+        *reinterpret_cast<float4*>(Bimg + base + off) = h;
+        *reinterpret_cast<float4*>(Bimg + base + 32 * Ck + off) = l;
+      }
+      base += 2 * 32 * Ck;
+      kb += Ck;
+    }
+  }
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(p_full + i, 12); tc::mbar_init(p_empty + i, 1);
+      tc::mbar_init(tap_full + i, 2); tc::mbar_init(tap_empty + i, 12);
+      tc::mbar_init(acc_full + i, 1); tc::mbar_init(acc_empty + i, 4);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == AW_MMA_WARP) tc::tmem_alloc(tslot, 64);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tslot;
+
+  if (tid < AW_WORKERS) {
+    // =============================================================== gather workers
+    for (int i = 0; i < my_tiles; ++i) {
+      const float4* TAP = TAP0 + (size_t)(i & 1) * (TCT * 3);
+      tc::mbar_wait(tap_full + (i & 1), (i >> 1) & 1);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int Ck = a.n_comp[k], nq = Ck >> 2, W = a.plane_w[k];
+        const uint32_t p = (uint32_t)i * 3u + (uint32_t)k, b = p & 1u;
+        float* Phi = P + (size_t)b * 2 * PSZ;
+        float* Plo = Phi + PSZ;
+        tc::mbar_wait(p_empty + b, ((p >> 1) & 1u) ^ 1u);
+        // two items per iteration, all twelve gathers issued before the first use
+        for (int item = tid; item < TCT * nq; item += 2 * AW_WORKERS) {
+          float4 pv[2], lv[2];
+          int off[2];
+          bool on[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int it2 = item + u * AW_WORKERS;
+            on[u] = it2 < TCT * nq;
+            const int sl = on[u] ? it2 / nq : 0, cq = on[u] ? it2 - sl * nq : 0, ch = cq * 4;
+            const float4 ax = TAP[sl * 3 + mat0(k)], ay = TAP[sl * 3 + mat1(k)], al = TAP[sl * 3 + vecm(k)];
+            const Tap tx = {__float_as_int(ax.x), __float_as_int(ax.y), ax.z, ax.w};
+            const Tap ty = {__float_as_int(ay.x), __float_as_int(ay.y), ay.z, ay.w};
+            const Tap tl = {__float_as_int(al.x), __float_as_int(al.y), al.z, al.w};
+            pv[u] = plane4(a.plane[k], W, Ck, tx, ty, ch);
+            lv[u] = line4(a.line[k], Ck, tl, ch);
+            if (a.mask[k]) {                                   // (plane m)(line m), tensoRF.py:250, :257
+              const float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+              pv[u] = mul4(pv[u], m);
+              lv[u] = mul4(lv[u], m);
+            }
+            off[u] = ((sl >> 3) * nq + cq) * TC_LBO_F + (sl & 7) * 4;
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            if (!on[u]) continue;
+            const float4 v4 = mul4(pv[u], lv[u]);
+            float4 h, l;
+            const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+            tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y); tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
+            *reinterpret_cast<float4*>(Phi + off[u]) = h;
+            *reinterpret_cast<float4*>(Plo + off[u]) = l;
+          }
+        }
+        tc::fence_async_smem();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(p_full + b);
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tap_empty + (i & 1));
+    }
+  } else if (warp < AW_MMA_WARP) {
+    // =============================================================== taps, one tile ahead of the workers
+    for (int i = 0; i < my_tiles; ++i) {
+      float4* dst = TAP0 + (size_t)(i & 1) * (TCT * 3);
+      const int64_t tbase = tile_base(i);
+      tc::mbar_wait(tap_empty + (i & 1), ((i >> 1) & 1) ^ 1);
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int r = (tid - AW_TAP0) * 2 + u;
+        const int64_t s = tbase + r;
+        float4 tp[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) tp[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // index 0, weight 0
+        if (s < n) {
+          float xn[3];
+          app_point(f, c, ws, s, xn);
+          const Taps3 T = make_taps3(a, xn);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
+        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j) dst[r * 3 + j] = tp[j];
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tap_full + (i & 1));
+    }
+  } else if (warp == AW_MMA_WARP) {
+    // =============================================================== products
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_tf32(128, 32);
+      for (int i = 0; i < my_tiles; ++i) {
+        const uint32_t ab = (uint32_t)i & 1u, d = tmem + ab * 32u;
+        tc::mbar_wait(acc_empty + ab, (((uint32_t)i >> 1) & 1u) ^ 1u);
+        int bbase = 0;
+        for (int k = 0; k < 3; ++k) {
+          const int Ck = a.n_comp[k], nq = Ck >> 2;
+          const uint32_t p = (uint32_t)i * 3u + (uint32_t)k, b = p & 1u;
+          const float* Phi = P + (size_t)b * 2 * PSZ;
+          tc::mbar_wait(p_full + b, (p >> 1) & 1u);
+          tc::fence_after_sync();
+          const uint32_t hi_w = tc::desc_hi((uint32_t)nq * 128u), hi_a = tc::desc_hi((uint32_t)nq * TC_LBO_F * 4u);
+          const uint32_t ah = tc::desc_lo(tc::smem_u32(Phi), TC_LBO_F * 4), al_ = tc::desc_lo(tc::smem_u32(Phi + PSZ), TC_LBO_F * 4);
+          const uint32_t bh = tc::desc_lo(tc::smem_u32(Bimg + bbase), 128), bl = tc::desc_lo(tc::smem_u32(Bimg + bbase + 32 * Ck), 128);
+          for (int ks = 0; ks < (Ck >> 3); ++ks) {
+            const uint32_t o = (uint32_t)ks * 16u;          // two core-matrix columns per k-step
+            const uint32_t oa = (uint32_t)ks * (2u * TC_LBO_F * 4u / 16u);
+            tc::mma_tf32_ss_lo2(d, al_ + oa, hi_a, bh + o, hi_w, idesc, (k == 0 && ks == 0) ? 0u : 1u);
+            tc::mma_tf32_ss_lo2(d, ah + oa, hi_a, bl + o, hi_w, idesc, 1u);
+            tc::mma_tf32_ss_lo2(d, ah + oa, hi_a, bh + o, hi_w, idesc, 1u);
+          }
+          tc::mma_commit(p_empty + b);
+          if (k == 2) tc::mma_commit(acc_full + ab);
+          bbase += 2 * 32 * Ck;
+        }
+      }
+    }
+  } else {
+    // =============================================================== epilogue: accumulator rows -> staging -> global
+    const int q = warp & 3, row = q * 32 + lane, et = tid - AW_EPI_WARP0 * 32;
+    for (int i = 0; i < my_tiles; ++i) {
+      const uint32_t ab = (uint32_t)i & 1u;
+      const int64_t t0 = tile_base(i);
+      tc::mbar_wait(acc_full + ab, ((uint32_t)i >> 1) & 1u);
+      tc::fence_after_sync();
+      float acc[32];
+      tc::tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + ab * 32u, acc);
+      tc::tmem_wait_ld();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(acc_empty + ab);
+#pragma unroll
+      for (int o = 0; o < 32; ++o)
+        if (o < D) stage[row * D + o] = acc[o];
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      {
+        const int rows = (int)min((int64_t)TCT, n - t0);
+        const int total = rows * D;                       // floats; the block starts 16-byte aligned (t0 % 128 == 0)
+        float* dst = ws.a_feat + t0 * D;
+        if ((((size_t)dst) & 15) == 0) {
+          for (int e = et * 4; e < total; e += 128 * 4) {
+            if (e + 4 <= total) *reinterpret_cast<float4*>(dst + e) = *reinterpret_cast<const float4*>(stage + e);
+            else for (int j = e; j < total; ++j) dst[j] = stage[j];
+          }
+        } else {
+          for (int e = et; e < total; e += 128) dst[e] = stage[e];
+        }
+      }
+      asm volatile("bar.sync 2, 128;" ::: "memory");      // the staging block is free for the next tile
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == AW_MMA_WARP) tc::tmem_dealloc(tmem, 64);
+}
+
 // Backward: dWb += G^T P (register tiles, flushed once per CTA), g_prod = Wb^T g_feat, scatter.
 constexpr int BW_TT = 2;        // (4 outputs x 4 comps) register tiles per thread
 FTRF_SWITCH(int, g_app_bwd_onegather, 1);    // VM: single-gather kernel (app_bwd_vm_kernel); 0 = two-gather kernel below
@@ -768,6 +988,15 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
   const FtrfFactorSet& a = f.app;
   const int cm = f.model == FTRF_MODEL_VM ? (a.n_comp[0] > a.n_comp[1] ? (a.n_comp[0] > a.n_comp[2] ? a.n_comp[0] : a.n_comp[2]) : (a.n_comp[1] > a.n_comp[2] ? a.n_comp[1] : a.n_comp[2])) : 0;
   if (g_app_fwd_tc && f.model == FTRF_MODEL_VM && a.n_comp[0] % 8 == 0 && a.n_comp[1] % 8 == 0 && a.n_comp[2] % 8 == 0 && cm <= 64) {
+    if (g_app_fwd_ws) {
+      const size_t smw = ((size_t)2 * 32 * app_np(f) + (size_t)4 * (TCT / 8) * (cm / 4) * TC_LBO_F + (size_t)TCT * 32) * sizeof(float) +
+                         (size_t)2 * TCT * 3 * sizeof(float4) + 16 * 8;
+      if (smw <= 227 * 1024) {
+        cudaFuncSetAttribute(app_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smw);
+        app_fwd_ws_kernel<<<FTRF_SMS, AW_THREADS, smw, st>>>(f, c, ws, cm);
+        return check_launch("app_fwd_ws");
+      }
+    }
     const size_t sm = ((size_t)2 * 32 * app_np(f) + (size_t)2 * (TCT / 8) * (cm / 4) * TC_LBO_F) * sizeof(float) + (size_t)2 * TCT * 3 * sizeof(float4) + 32;
     cudaFuncSetAttribute(app_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     app_fwd_tc_kernel<<<FTRF_SMS * 2, TC_THREADS, sm, st>>>(f, c, ws, cm);
@@ -1112,6 +1341,11 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
 #ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_set_app_tc(int on) {
   ftrf::g_app_fwd_tc = on;
+  return 0;
+}
+
+extern "C" int ftrf_debug_set_app_ws(int on) {
+  ftrf::g_app_fwd_ws = on;
   return 0;
 }
 
