@@ -370,11 +370,15 @@ constexpr int AW_WORKERS = 384, AW_TAP0 = 384, AW_MMA_WARP = 14, AW_EPI_WARP0 = 
 constexpr int AW_THREADS = (12 + 2 + 1 + 4) * 32;
 FTRF_SWITCH(int, g_app_fwd_ws, 1);           // ftrf_debug_set_app_ws (test build): 0 = app_fwd_tc_kernel above
 
+// CP = true: TensorCP (models/tensoRF.py:388-415): one product of three line samples per component, the C components
+// cut into chunks of CM (<= 64) that play the role of VM's three factor pairs.
+template <bool CP>
 __global__ void __launch_bounds__(AW_THREADS, 1)
 app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM) {
   extern __shared__ __align__(1024) uint8_t app_raw[];
   const FtrfFactorSet& a = f.app;
-  const int NP = a.n_comp[0] + a.n_comp[1] + a.n_comp[2], D = f.app_dim;
+  const int NP = CP ? a.n_comp[0] : a.n_comp[0] + a.n_comp[1] + a.n_comp[2], D = f.app_dim;
+  const int nch = CP ? a.n_comp[0] / CM : 3;                        // operand chunks per tile
   const size_t PSZ = (size_t)(TCT / 8) * (CM / 4) * TC_LBO_F;      // floats of one hi (or lo) operand tile [128 x CM]
   float* Bimg = reinterpret_cast<float*>(app_raw);                 // per pair k: hi [32 x C_k] then lo [32 x C_k]
   float* P = Bimg + (size_t)2 * 32 * NP;                           // [2 buffers][hi, lo][PSZ]
@@ -397,8 +401,8 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
 
   {   // basis matrix image (outputs padded to 32 rows of zeros)
     int base = 0, kb = 0;
-    for (int k = 0; k < 3; ++k) {
-      const int Ck = a.n_comp[k], nq = Ck >> 2;
+    for (int k = 0; k < nch; ++k) {
+      const int Ck = CP ? CM : a.n_comp[k], nq = Ck >> 2;
       for (int e = tid; e < 32 * nq; e += AW_THREADS) {
         const int o = e / nq, ku = e - o * nq;
         float4 w = make_float4(0.f, 0.f, 0.f, 0.f), h, l;
@@ -433,16 +437,15 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
     for (int i = 0; i < my_tiles; ++i) {
       const float4* TAP = TAP0 + (size_t)(i & 1) * (TCT * 3);
       tc::mbar_wait(tap_full + (i & 1), (i >> 1) & 1);
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        const int Ck = a.n_comp[k], nq = Ck >> 2, W = a.plane_w[k];
-        const uint32_t p = (uint32_t)i * 3u + (uint32_t)k, b = p & 1u;
+      for (int k = 0; k < nch; ++k) {
+        const int Ck = CP ? CM : a.n_comp[k], nq = Ck >> 2, W = CP ? 0 : a.plane_w[k];
+        const uint32_t p = (uint32_t)i * (uint32_t)nch + (uint32_t)k, b = p & 1u;
         float* Phi = P + (size_t)b * 2 * PSZ;
         float* Plo = Phi + PSZ;
         tc::mbar_wait(p_empty + b, ((p >> 1) & 1u) ^ 1u);
         // two items per iteration, all twelve gathers issued before the first use
         for (int item = tid; item < TCT * nq; item += 2 * AW_WORKERS) {
-          float4 pv[2], lv[2];
+          float4 pv[2], lv[2], mv[2];
           int off[2];
           bool on[2];
 #pragma unroll
@@ -450,23 +453,32 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
             const int it2 = item + u * AW_WORKERS;
             on[u] = it2 < TCT * nq;
             const int sl = on[u] ? it2 / nq : 0, cq = on[u] ? it2 - sl * nq : 0, ch = cq * 4;
-            const float4 ax = TAP[sl * 3 + mat0(k)], ay = TAP[sl * 3 + mat1(k)], al = TAP[sl * 3 + vecm(k)];
+            const float4 ax = TAP[sl * 3 + (CP ? 0 : mat0(k))], ay = TAP[sl * 3 + (CP ? 1 : mat1(k))], al = TAP[sl * 3 + (CP ? 2 : vecm(k))];
             const Tap tx = {__float_as_int(ax.x), __float_as_int(ax.y), ax.z, ax.w};
             const Tap ty = {__float_as_int(ay.x), __float_as_int(ay.y), ay.z, ay.w};
             const Tap tl = {__float_as_int(al.x), __float_as_int(al.y), al.z, al.w};
-            pv[u] = plane4(a.plane[k], W, Ck, tx, ty, ch);
-            lv[u] = line4(a.line[k], Ck, tl, ch);
-            if (a.mask[k]) {                                   // (plane m)(line m), tensoRF.py:250, :257
-              const float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
-              pv[u] = mul4(pv[u], m);
-              lv[u] = mul4(lv[u], m);
+            mv[u] = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (CP) {                                            // TAP[sl][j] is line j's tap: (l0 l1) l2, then the mask
+              const int cg = k * CM + ch;                        // component index in the lines
+              pv[u] = mul4(line4(a.line[0], NP, tx, cg), line4(a.line[1], NP, ty, cg));
+              lv[u] = line4(a.line[2], NP, tl, cg);
+              if (a.mask[0]) mv[u] = mask4(a.mask[0], a.mask_stride[0], cg);      // tensoRF.py:415
+            } else {
+              pv[u] = plane4(a.plane[k], W, Ck, tx, ty, ch);
+              lv[u] = line4(a.line[k], Ck, tl, ch);
+              if (a.mask[k]) {                                   // (plane m)(line m), tensoRF.py:250, :257
+                const float4 m = mask4(a.mask[k], a.mask_stride[k], ch);
+                pv[u] = mul4(pv[u], m);
+                lv[u] = mul4(lv[u], m);
+              }
             }
             off[u] = ((sl >> 3) * nq + cq) * TC_LBO_F + (sl & 7) * 4;
           }
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
             if (!on[u]) continue;
-            const float4 v4 = mul4(pv[u], lv[u]);
+            float4 v4 = mul4(pv[u], lv[u]);
+            if (CP) v4 = mul4(v4, mv[u]);
             float4 h, l;
             const float v[4] = {v4.x, v4.y, v4.z, v4.w};
             tc::split_tf32(v[0], h.x, l.x); tc::split_tf32(v[1], h.y, l.y); tc::split_tf32(v[2], h.z, l.z); tc::split_tf32(v[3], h.w, l.w);
@@ -497,7 +509,13 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
         if (s < n) {
           float xn[3];
           app_point(f, c, ws, s, xn);
-          const Taps3 T = make_taps3(a, xn);
+          Taps3 T;
+          if (CP) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) T.a[j] = make_tap(xn[vecm(j)], a.line_len[j]);
+          } else {
+            T = make_taps3(a, xn);
+          }
 #pragma unroll
           for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
         }
@@ -515,9 +533,9 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
         const uint32_t ab = (uint32_t)i & 1u, d = tmem + ab * 32u;
         tc::mbar_wait(acc_empty + ab, (((uint32_t)i >> 1) & 1u) ^ 1u);
         int bbase = 0;
-        for (int k = 0; k < 3; ++k) {
-          const int Ck = a.n_comp[k], nq = Ck >> 2;
-          const uint32_t p = (uint32_t)i * 3u + (uint32_t)k, b = p & 1u;
+        for (int k = 0; k < nch; ++k) {
+          const int Ck = CP ? CM : a.n_comp[k], nq = Ck >> 2;
+          const uint32_t p = (uint32_t)i * (uint32_t)nch + (uint32_t)k, b = p & 1u;
           const float* Phi = P + (size_t)b * 2 * PSZ;
           tc::mbar_wait(p_full + b, (p >> 1) & 1u);
           tc::fence_after_sync();
@@ -532,7 +550,7 @@ app_fwd_ws_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int CM
             tc::mma_tf32_ss_lo2(d, ah + oa, hi_a, bh + o, hi_w, idesc, 1u);
           }
           tc::mma_commit(p_empty + b);
-          if (k == 2) tc::mma_commit(acc_full + ab);
+          if (k == nch - 1) tc::mma_commit(acc_full + ab);
           bbase += 2 * 32 * Ck;
         }
       }
@@ -992,8 +1010,8 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
       const size_t smw = ((size_t)2 * 32 * app_np(f) + (size_t)4 * (TCT / 8) * (cm / 4) * TC_LBO_F + (size_t)TCT * 32) * sizeof(float) +
                          (size_t)2 * TCT * 3 * sizeof(float4) + 16 * 8;
       if (smw <= 227 * 1024) {
-        cudaFuncSetAttribute(app_fwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smw);
-        app_fwd_ws_kernel<<<FTRF_SMS, AW_THREADS, smw, st>>>(f, c, ws, cm);
+        cudaFuncSetAttribute(app_fwd_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smw);
+        app_fwd_ws_kernel<false><<<FTRF_SMS, AW_THREADS, smw, st>>>(f, c, ws, cm);
         return check_launch("app_fwd_ws");
       }
     }
@@ -1001,6 +1019,19 @@ int launch_appearance(const FtrfField& f, const FtrfCall& c, const Ws& ws, cudaS
     cudaFuncSetAttribute(app_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     app_fwd_tc_kernel<<<FTRF_SMS * 2, TC_THREADS, sm, st>>>(f, c, ws, cm);
     return check_launch("app_fwd_tc");
+  }
+  if (g_app_fwd_ws && f.model == FTRF_MODEL_CP && a.n_comp[0] % 8 == 0) {
+    // TensorCP on the tensor cores: components in chunks of the largest multiple of 8 that divides them (288 -> 6 x 48)
+    const int C = a.n_comp[0];
+    int ck = 0;
+    for (int d = 64; d >= 8 && !ck; d -= 8) if (C % d == 0) ck = d;
+    const size_t smw = ((size_t)2 * 32 * C + (size_t)4 * (TCT / 8) * (ck / 4) * TC_LBO_F + (size_t)TCT * 32) * sizeof(float) +
+                       (size_t)2 * TCT * 3 * sizeof(float4) + 16 * 8;
+    if (ck && smw <= 227 * 1024) {
+      cudaFuncSetAttribute(app_fwd_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smw);
+      app_fwd_ws_kernel<true><<<FTRF_SMS, AW_THREADS, smw, st>>>(f, c, ws, ck);
+      return check_launch("app_fwd_ws_cp");
+    }
   }
   size_t smem = ((size_t)app_np(f) * 32 + (size_t)app_np(f) * LDP) * sizeof(float);
   if (int e = app_check(f, smem)) return e;

@@ -44,19 +44,21 @@ def test_app_backward_tensor_core_matches_cuda_core(grid, comps, n_rays, masked)
         assert rel_inf(grads[1][k], grads[0][k]) < 2e-5, k
 
 
-@pytest.mark.parametrize("comps,n,masked", [((48, 48, 48), 128 * 300 + 77, False), ((16, 32, 48), 5000, True), ((8, 8, 16), 129, False),
-                                            ((64, 64, 64), 128 * 149, False)])
-def test_app_forward_builds_agree(comps, n, masked):
+@pytest.mark.parametrize("model,comps,n,masked", [("VM", (48, 48, 48), 128 * 300 + 77, False), ("VM", (16, 32, 48), 5000, True),
+                                                  ("VM", (8, 8, 16), 129, False), ("VM", (64, 64, 64), 128 * 149, False),
+                                                  ("CP", (288, 288, 288), 128 * 150 + 5, True), ("CP", (96, 96, 96), 4000, False),
+                                                  ("CP", (72, 72, 72), 700, False), ("CP", (40, 40, 40), 128, True)])
+def test_app_forward_builds_agree(model, comps, n, masked):
     """The three forward builds of the VM appearance stage — warp-specialised tcgen05 (shipped), two-CTA tcgen05, CUDA
     cores — on the same points, against each other and the oracle; tile counts above and below one wave of CTAs."""
     from tests.gpu_util import model_from_field, through_test_lib
-    cfg = O.FieldConfig(grid=(40, 48, 56), density_n_comp=(16, 16, 16), app_n_comp=comps)
+    cfg = O.FieldConfig(model=model, grid=(40, 48, 56), density_n_comp=(16, 16, 16), app_n_comp=comps)
     p = O.init_params(cfg, seed=41)
     f = O.Field(cfg, p)
     m = model_from_field(f, "cuda")
     g = torch.Generator().manual_seed(42)
     xn = torch.rand(n, 3, generator=g) * 2.1 - 1.05
-    mask = [torch.rand(c, generator=g) for c in comps] if masked else None
+    mask = [torch.rand(c, generator=g) for c in (comps if model == "VM" else comps[:1])] if masked else None
     want = O.app_feature(f, xn, mask)
     mk = None if mask is None else [t.cuda() for t in mask]
     got = {}
@@ -67,5 +69,6 @@ def test_app_forward_builds_agree(comps, n, masked):
         got["cuda_cores"] = m.compute_appfeature(xn.cuda(), mk)
     for k, v in got.items():
         assert rel_inf(v.cpu(), want) < 1e-4, k
-    assert torch.equal(got["ws"], got["tc"])                      # same products in the same order
+    if model == "VM":
+        assert torch.equal(got["ws"], got["tc"])                  # same products in the same order
     assert rel_inf(got["ws"], got["cuda_cores"]) < 2e-5
