@@ -1082,11 +1082,18 @@ static __host__ __device__ inline AppBwdTcLayout app_bwd_tc_layout(int NP) {
   return L;
 }
 
+// CP = true: TensorCP (models/tensoRF.py:388-415).  The C components are cut into NB blocks of NP = C / NB (<= 144, what
+// the operand tiles of one CTA hold); CTA j works on block j % NB for the tiles j / NB, j / NB + grid / NB, ... — its basis
+// image, its product operand and its dWb accumulator only ever see that block, so nothing is reloaded per tile.  The gather /
+// scatter pass multiplies three line samples instead of a plane and a line sample and merges runs on three lines.
+template <bool CP>
 __global__ void __launch_bounds__(BT_THREADS, 1)
-app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
+app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const int NB) {
   extern __shared__ __align__(1024) float bsm[];
   const FtrfFactorSet& a = f.app;
-  const int NP = app_np(f), NPs = NP + 4, D = f.app_dim, n_kg = NP / 4;
+  const int NPT = app_np(f), NP = NPT / NB, cb0 = CP ? ((int)blockIdx.x % NB) * NP : 0;     // all components; this CTA's block
+  const int NPs = NP + 4, D = f.app_dim, n_kg = NP / 4;
+  const int64_t tile0 = (int64_t)(blockIdx.x / NB) * BT, tile_step = (int64_t)(gridDim.x / NB) * BT;
   const AppBwdTcLayout L = app_bwd_tc_layout(NP);
   float* WbH = bsm + L.wbi; float* WbL = WbH + (size_t)NP * 32;
   float* GH = bsm + L.g;    float* GL = GH + 128 * 32;
@@ -1100,7 +1107,7 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
-  if ((int64_t)blockIdx.x * BT >= n) return;
+  if (tile0 >= n) return;
 
   // resident operands: Wb image (row = component, k = output o, zero for o >= D); zero G rows 64..127 and P^T
   for (int e = tid; e < NP * 8; e += BT_THREADS) {
@@ -1109,7 +1116,7 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int o = ku * 4 + j;
-      tc::split_tf32(o < D ? __ldg(f.basis + (size_t)o * NP + nrow) : 0.f, h[j], l[j]);
+      tc::split_tf32(o < D ? __ldg(f.basis + (size_t)o * NPT + cb0 + nrow) : 0.f, h[j], l[j]);
     }
     const int off = tc::canon_off(nrow, ku, 8);
     *reinterpret_cast<float4*>(WbH + off) = make_float4(h[0], h[1], h[2], h[3]);
@@ -1140,7 +1147,13 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     if (st < n) {
       float xn[3];
       app_point(f, c, ws, st, xn);
-      const Taps3 T = make_taps3(a, xn);
+      Taps3 T;
+      if (CP) {                                           // line j samples axis vecm(j)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) T.a[j] = make_tap(xn[vecm(j)], a.line_len[j]);
+      } else {
+        T = make_taps3(a, xn);
+      }
 #pragma unroll
       for (int j = 0; j < 3; ++j) tp[j] = make_float4(__int_as_float(T.a[j].i0), __int_as_float(T.a[j].i1), T.a[j].w0, T.a[j].w1);
     }
@@ -1150,10 +1163,10 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     const int64_t lim = min((int64_t)BT, n - tbase) * D;
     for (int e = r; e < BT * D; e += 64) GF[e] = e < lim ? __ldg(ws.a_gfeat + tbase * D + e) : 0.f;
   };
-  if (tid >= BT_WORK) make_taps((int64_t)blockIdx.x * BT, TAP0, tid - BT_WORK);
+  if (tid >= BT_WORK) make_taps(tile0, TAP0, tid - BT_WORK);
   __syncthreads();                        // the first tile's staging reads the g_feat block
 
-  for (int64_t t0 = (int64_t)blockIdx.x * BT; t0 < n; t0 += (int64_t)gridDim.x * BT) {
+  for (int64_t t0 = tile0; t0 < n; t0 += tile_step) {
     const int tile_n = (int)min((int64_t)BT, n - t0);
     // ---- stage g_feat as both operands, and the taps.  The previous tile's dWb products may still be running:
     // they read the other G^T buffer and P^T, which is not written before the wait below.
@@ -1217,63 +1230,109 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
     // ---- gather once: products into the dWb operand, plane / line gradients with run merging
     const float4* TAP = TAP0 + (size_t)gtb * (BT * 3);
     if (tid >= BT_WORK) {
-      const int64_t tn = t0 + (int64_t)gridDim.x * BT;
+      const int64_t tn = t0 + tile_step;
       if (tn < n) make_taps(tn, TAP0 + (size_t)(gtb ^ 1) * (BT * 3), tid - BT_WORK);
     }
     for (int item = tid; item < (BT / BT_RUN) * n_kg && tid < BT_WORK; item += BT_WORK) {
       const int seg = item / n_kg, q = item - seg * n_kg;
-      int k = 0, base = 0;
-      while (k < 2 && 4 * q >= base + a.n_comp[k]) { base += a.n_comp[k]; ++k; }
-      const int ch = 4 * q - base, C = a.n_comp[k], W = a.plane_w[k];
-      const int m0 = mat0(k), m1 = mat1(k), mv = vecm(k);
-      float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
-      if (a.mask[k]) { const float4 m = mask4(a.mask[k], a.mask_stride[k], ch); m2 = mul4(m, m); }
-      const float* pl = a.plane[k] + ch;
-      const float* ln = a.line[k] + ch;
-      PlaneRun pr; LineRun lr;
-      pr.kx = -1; pr.ky = -1; lr.kl = -1;
       float pq[BT_RUN][4];
+      if (CP) {
+        const int ch = cb0 + 4 * q, C = NPT;              // component index in the lines
+        float4 m1 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (a.mask[0]) m1 = mask4(a.mask[0], a.mask_stride[0], ch);          // tensoRF.py:415 (once)
+        const float* ln0 = a.line[0] + ch;
+        const float* ln1 = a.line[1] + ch;
+        const float* ln2 = a.line[2] + ch;
+        LineRun lr[3];
 #pragma unroll
-      for (int u = 0; u < BT_RUN; ++u) {
-        const int i = seg * BT_RUN + u;
-        pq[u][0] = pq[u][1] = pq[u][2] = pq[u][3] = 0.f;
-        if (i >= tile_n) continue;
-        const float4 ax = TAP[i * 3 + m0], ay = TAP[i * 3 + m1], al = TAP[i * 3 + mv];
-        const int x0 = __float_as_int(ax.x), x1 = __float_as_int(ax.y), y0 = __float_as_int(ay.x), y1 = __float_as_int(ay.y);
-        const int l0 = __float_as_int(al.x), l1 = __float_as_int(al.y);
-        const float* r0 = pl + ((size_t)y0 * W) * C;
-        const float* r1 = pl + ((size_t)y1 * W) * C;
-        const float4 c00 = ld4(r0 + (size_t)x0 * C), c10 = ld4(r0 + (size_t)x1 * C);
-        const float4 c01 = ld4(r1 + (size_t)x0 * C), c11 = ld4(r1 + (size_t)x1 * C);
-        const float4 e0 = ld4(ln + (size_t)l0 * C), e1 = ld4(ln + (size_t)l1 * C);
-        const float w00 = ax.z * ay.z, w10 = ax.w * ay.z, w01 = ax.z * ay.w, w11 = ax.w * ay.w;
-        float4 pv = z4(), lv = z4();
-        pv = fma4(w00, c00, pv); pv = fma4(w10, c10, pv); pv = fma4(w01, c01, pv); pv = fma4(w11, c11, pv);
-        lv = fma4(al.z, e0, lv); lv = fma4(al.w, e1, lv);
-        const float4 prod = mul4(mul4(pv, lv), m2);
-        pq[u][0] = prod.x; pq[u][1] = prod.y; pq[u][2] = prod.z; pq[u][3] = prod.w;
-        const float4 gq = mul4(*reinterpret_cast<const float4*>(Q + (size_t)i * NPs + 4 * q), m2);
-        const float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
-        const int kx = x0 | (x1 << 16), ky = y0 | (y1 << 16), kl = l0 | (l1 << 16);
-        if (kx != pr.kx || ky != pr.ky) {
-          flush_plane(pr, a.g_plane[k], W, C, ch);
-          pr.kx = kx; pr.ky = ky;
-          pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+        for (int j = 0; j < 3; ++j) lr[j].kl = -1;
+#pragma unroll
+        for (int u = 0; u < BT_RUN; ++u) {
+          const int i = seg * BT_RUN + u;
+          pq[u][0] = pq[u][1] = pq[u][2] = pq[u][3] = 0.f;
+          if (i >= tile_n) continue;
+          const float4 t0 = TAP[i * 3 + 0], t1 = TAP[i * 3 + 1], t2 = TAP[i * 3 + 2];
+          const int a0 = __float_as_int(t0.x), a1 = __float_as_int(t0.y), b0 = __float_as_int(t1.x), b1 = __float_as_int(t1.y);
+          const int c0 = __float_as_int(t2.x), c1 = __float_as_int(t2.y);
+          const float4 e00 = ld4(ln0 + (size_t)a0 * C), e01 = ld4(ln0 + (size_t)a1 * C);
+          const float4 e10 = ld4(ln1 + (size_t)b0 * C), e11 = ld4(ln1 + (size_t)b1 * C);
+          const float4 e20 = ld4(ln2 + (size_t)c0 * C), e21 = ld4(ln2 + (size_t)c1 * C);
+          float4 l0 = z4(), l1 = z4(), l2 = z4();
+          l0 = fma4(t0.z, e00, l0); l0 = fma4(t0.w, e01, l0);
+          l1 = fma4(t1.z, e10, l1); l1 = fma4(t1.w, e11, l1);
+          l2 = fma4(t2.z, e20, l2); l2 = fma4(t2.w, e21, l2);
+          const float4 prod = mul4(mul4(mul4(l0, l1), l2), m1);
+          pq[u][0] = prod.x; pq[u][1] = prod.y; pq[u][2] = prod.z; pq[u][3] = prod.w;
+          const float4 gq = mul4(*reinterpret_cast<const float4*>(Q + (size_t)i * NPs + 4 * q), m1);
+          const float4 gk[3] = {mul4(gq, mul4(l1, l2)), mul4(gq, mul4(l0, l2)), mul4(gq, mul4(l0, l1))};
+          const int key[3] = {a0 | (a1 << 16), b0 | (b1 << 16), c0 | (c1 << 16)};
+          const float w0[3] = {t0.z, t1.z, t2.z}, w1[3] = {t0.w, t1.w, t2.w};
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            if (key[j] != lr[j].kl) {
+              flush_line(lr[j], a.g_line[j], C, ch);
+              lr[j].kl = key[j];
+              lr[j].a0 = z4(); lr[j].a1 = z4();
+            }
+            lr[j].a0 = fma4(w0[j], gk[j], lr[j].a0);
+            lr[j].a1 = fma4(w1[j], gk[j], lr[j].a1);
+          }
         }
-        pr.a00 = fma4(w00, gp, pr.a00);
-        pr.a10 = fma4(w10, gp, pr.a10);
-        pr.a01 = fma4(w01, gp, pr.a01);
-        pr.a11 = fma4(w11, gp, pr.a11);
-        if (kl != lr.kl) {
-          flush_line(lr, a.g_line[k], C, ch);
-          lr.kl = kl;
-          lr.a0 = z4(); lr.a1 = z4();
+#pragma unroll
+        for (int j = 0; j < 3; ++j) flush_line(lr[j], a.g_line[j], C, ch);
+      } else {
+        int k = 0, base = 0;
+        while (k < 2 && 4 * q >= base + a.n_comp[k]) { base += a.n_comp[k]; ++k; }
+        const int ch = 4 * q - base, C = a.n_comp[k], W = a.plane_w[k];
+        const int m0 = mat0(k), m1 = mat1(k), mv = vecm(k);
+        float4 m2 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (a.mask[k]) { const float4 m = mask4(a.mask[k], a.mask_stride[k], ch); m2 = mul4(m, m); }
+        const float* pl = a.plane[k] + ch;
+        const float* ln = a.line[k] + ch;
+        PlaneRun pr; LineRun lr;
+        pr.kx = -1; pr.ky = -1; lr.kl = -1;
+  #pragma unroll
+        for (int u = 0; u < BT_RUN; ++u) {
+          const int i = seg * BT_RUN + u;
+          pq[u][0] = pq[u][1] = pq[u][2] = pq[u][3] = 0.f;
+          if (i >= tile_n) continue;
+          const float4 ax = TAP[i * 3 + m0], ay = TAP[i * 3 + m1], al = TAP[i * 3 + mv];
+          const int x0 = __float_as_int(ax.x), x1 = __float_as_int(ax.y), y0 = __float_as_int(ay.x), y1 = __float_as_int(ay.y);
+          const int l0 = __float_as_int(al.x), l1 = __float_as_int(al.y);
+          const float* r0 = pl + ((size_t)y0 * W) * C;
+          const float* r1 = pl + ((size_t)y1 * W) * C;
+          const float4 c00 = ld4(r0 + (size_t)x0 * C), c10 = ld4(r0 + (size_t)x1 * C);
+          const float4 c01 = ld4(r1 + (size_t)x0 * C), c11 = ld4(r1 + (size_t)x1 * C);
+          const float4 e0 = ld4(ln + (size_t)l0 * C), e1 = ld4(ln + (size_t)l1 * C);
+          const float w00 = ax.z * ay.z, w10 = ax.w * ay.z, w01 = ax.z * ay.w, w11 = ax.w * ay.w;
+          float4 pv = z4(), lv = z4();
+          pv = fma4(w00, c00, pv); pv = fma4(w10, c10, pv); pv = fma4(w01, c01, pv); pv = fma4(w11, c11, pv);
+          lv = fma4(al.z, e0, lv); lv = fma4(al.w, e1, lv);
+          const float4 prod = mul4(mul4(pv, lv), m2);
+          pq[u][0] = prod.x; pq[u][1] = prod.y; pq[u][2] = prod.z; pq[u][3] = prod.w;
+          const float4 gq = mul4(*reinterpret_cast<const float4*>(Q + (size_t)i * NPs + 4 * q), m2);
+          const float4 gp = mul4(gq, lv), gl = mul4(gq, pv);
+          const int kx = x0 | (x1 << 16), ky = y0 | (y1 << 16), kl = l0 | (l1 << 16);
+          if (kx != pr.kx || ky != pr.ky) {
+            flush_plane(pr, a.g_plane[k], W, C, ch);
+            pr.kx = kx; pr.ky = ky;
+            pr.a00 = z4(); pr.a10 = z4(); pr.a01 = z4(); pr.a11 = z4();
+          }
+          pr.a00 = fma4(w00, gp, pr.a00);
+          pr.a10 = fma4(w10, gp, pr.a10);
+          pr.a01 = fma4(w01, gp, pr.a01);
+          pr.a11 = fma4(w11, gp, pr.a11);
+          if (kl != lr.kl) {
+            flush_line(lr, a.g_line[k], C, ch);
+            lr.kl = kl;
+            lr.a0 = z4(); lr.a1 = z4();
+          }
+          lr.a0 = fma4(al.z, gl, lr.a0);
+          lr.a1 = fma4(al.w, gl, lr.a1);
         }
-        lr.a0 = fma4(al.z, gl, lr.a0);
-        lr.a1 = fma4(al.w, gl, lr.a1);
+        flush_plane(pr, a.g_plane[k], W, C, ch);
+        flush_line(lr, a.g_line[k], C, ch);
       }
-      flush_plane(pr, a.g_plane[k], W, C, ch);
-      flush_line(lr, a.g_line[k], C, ch);
       // rows 4q..4q+3 (components), K unit `seg` (samples 4 seg .. 4 seg + 3)
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -1326,7 +1385,7 @@ app_bwd_vm_tc_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
       if (mine)
 #pragma unroll
         for (int o = 0; o < 32; ++o)
-          if (o < D && acc[o] != 0.f) atomicAdd(f.g_basis + (size_t)o * NP + comp, acc[o]);
+          if (o < D && acc[o] != 0.f) atomicAdd(f.g_basis + (size_t)o * NPT + cb0 + comp, acc[o]);
     }
   }
   tc::fence_before_sync();
@@ -1352,9 +1411,25 @@ int launch_appearance_bwd(const FtrfField& f, const FtrfCall& c, const Ws& ws, c
     const int NP = app_np(f);
     const AppBwdTcLayout L = app_bwd_tc_layout(NP);
     if (NP % 16 == 0 && NP >= 16 && NP <= 256 && f.app_dim <= 32 && L.total + 1024 <= 227 * 1024 && L.tmem_cols <= 512) {
-      cudaFuncSetAttribute(app_bwd_vm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
-      app_bwd_vm_tc_kernel<<<FTRF_SMS, BT_THREADS, L.total, st>>>(f, c, ws);
+      cudaFuncSetAttribute(app_bwd_vm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+      app_bwd_vm_tc_kernel<false><<<FTRF_SMS, BT_THREADS, L.total, st>>>(f, c, ws, 1);
       return check_launch("app_bwd_vm_tc");
+    }
+  }
+  if (f.model == FTRF_MODEL_CP && g_app_bwd_tc && arun != 0) {
+    // component blocks of at most 144 (the operand tiles of one CTA), as few as divide C into multiples of 16; the grid is
+    // rounded down to a multiple of the block count (288 components: 2 blocks x 74 CTAs)
+    const int C = app_np(f);
+    int nb = 0;
+    for (int t = 1; t <= 8 && !nb; ++t)
+      if (C % t == 0 && (C / t) % 16 == 0 && C / t <= 144 && C / t >= 16) nb = t;
+    if (nb && f.app_dim <= 32) {
+      const AppBwdTcLayout L = app_bwd_tc_layout(C / nb);
+      if (L.total + 1024 <= 227 * 1024 && L.tmem_cols <= 512) {
+        cudaFuncSetAttribute(app_bwd_vm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+        app_bwd_vm_tc_kernel<true><<<(FTRF_SMS / nb) * nb, BT_THREADS, L.total, st>>>(f, c, ws, nb);
+        return check_launch("app_bwd_cp_tc");
+      }
     }
   }
   if (f.model == FTRF_MODEL_VM && arun > 0 && g_app_bwd_onegather) {

@@ -12,13 +12,18 @@ from tests.util import rel_inf
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("grid,comps,n_rays,masked", [((64, 64, 64), (48, 48, 48), 2048, False),
-                                                      ((40, 48, 56), (16, 32, 48), 700, True),
-                                                      ((32, 32, 32), (8, 8, 16), 333, False),
-                                                      ((48, 48, 48), (64, 64, 64), 1500, False)])
-def test_app_backward_tensor_core_matches_cuda_core(grid, comps, n_rays, masked):
+@pytest.mark.parametrize("model,grid,comps,n_rays,masked", [("VM", (64, 64, 64), (48, 48, 48), 2048, False),
+                                                            ("VM", (40, 48, 56), (16, 32, 48), 700, True),
+                                                            ("VM", (32, 32, 32), (8, 8, 16), 333, False),
+                                                            ("VM", (48, 48, 48), (64, 64, 64), 1500, False),
+                                                            ("CP", (64, 64, 64), (288, 288, 288), 2048, True),
+                                                            ("CP", (40, 48, 56), (96, 96, 96), 700, False),
+                                                            ("CP", (32, 32, 32), (48, 48, 48), 333, False),
+                                                            ("CP", (48, 48, 48), (160, 160, 160), 1500, True)])
+def test_app_backward_tensor_core_matches_cuda_core(model, grid, comps, n_rays, masked):
+    """(TensorCP: the same kernel over component blocks of <= 144, three line samples per product.)"""
     from tests.gpu_util import model_from_field, through_test_lib
-    cfg = O.FieldConfig(grid=grid, density_n_comp=(16, 16, 16), app_n_comp=comps)
+    cfg = O.FieldConfig(model=model, grid=grid, density_n_comp=(16, 16, 16), app_n_comp=comps)
     p = O.init_params(cfg, seed=31)
     O.plant_box(cfg, p)
     m = model_from_field(O.Field(cfg, p), "cuda")
@@ -29,7 +34,7 @@ def test_app_backward_tensor_core_matches_cuda_core(grid, comps, n_rays, masked)
     if masked:
         g = torch.Generator().manual_seed(34)
         mask = {"encoding": {"pos": None, "view": None, "fea": None},
-                "decomp": {"den": None, "app": [torch.rand(cc, generator=g).cuda() for cc in comps]}}
+                "decomp": {"den": None, "app": [torch.rand(cc, generator=g).cuda() for cc in (comps if model == "VM" else comps[:1])]}}
     grads = {}
     for tcore in (1, 0):
         with through_test_lib(lambda l: l.ftrf_debug_set_app_bwd_tc(tcore), lambda l: l.ftrf_debug_set_app_bwd_tc(1)):
