@@ -26,7 +26,10 @@ constexpr int WG_NGX_MAX = 48;            // 16-byte column groups of the X oper
 constexpr int WG_G_FLOATS = WG_KS * 128;  // one hi (or lo) tile of a 128-wide operand
 constexpr int WG_PROD_WARPS = 16;
 constexpr int WG_PROD = WG_PROD_WARPS * 32;
-constexpr int WG_THREADS = WG_PROD + 32;
+constexpr int WG_RAW_OPS = 2, WG_RAW_STAGES = 2;   // RAW build: operand stages (69.6 KB each) and raw stages (34.6 KB each); 1 + 4 measured slower
+constexpr int WG_L2_AHEAD = 0;                     // chunks the bulk-copy warp prefetches into L2 ahead of its copies
+constexpr int WG_THREADS = WG_PROD + 64;   // + the MMA-issuing warp and the bulk-copy warp
+FTRF_SWITCH(int, g_wgrad_raw, 1);          // ftrf_debug_set_wgrad_raw (test build): 0 = producers load from global memory themselves
 
 
 // Predicated read-only 4-byte load that stays where it is written: `volatile` keeps it ordered with the
@@ -48,18 +51,29 @@ __device__ __forceinline__ void red4g(float* p, float a, float b, float c, float
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// RAW = true (shipped): the activation rows of a chunk — 16 consecutive samples, i.e. one contiguous block of each array —
+// are brought into a two-stage shared-memory ring by cp.async.bulk (warp 17), and the producers transpose from THERE.
+// With RAW = false the producers load from global memory themselves (four 4-byte loads per K-major unit, two register sets
+// in flight): ncu showed them stalled on those loads 45 % of the time (L1 hit rate 4 %: every byte is used once) with DRAM at
+// 29 % — memory-level parallelism bounded by registers.  Bulk copies need none: two stages keep 69 KB per SM in flight.
+template <bool RAW>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_fused_kernel(const WgradFusedArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  float* ring = reinterpret_cast<float*>(smem_raw);                    // [STAGES][G2h,G2l,H1h,H1l,G1h,G1l,Xh,Xl]
+  constexpr int NSTG = RAW ? WG_RAW_OPS : WG_STAGES, RS = WG_RAW_STAGES;
+  float* ring = reinterpret_cast<float*>(smem_raw);                    // [NSTG][G2h,G2l,H1h,H1l,G1h,G1l,Xh,Xl]
   const int WG_NGX = a.ngt;
   const int WG_X_FLOATS = WG_KS * WG_NGX * 4;
   const int WG_STAGE_FLOATS = 2 * (3 * WG_G_FLOATS + WG_X_FLOATS);      // G2, H1, G1, X, each hi + lo
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)WG_STAGES * WG_STAGE_FLOATS);
-  uint64_t* full = bars;                      // [STAGES]  8 producer warps
-  uint64_t* empty = bars + WG_STAGES;         // [STAGES]  tcgen05.commit
-  uint64_t* done = bars + 2 * WG_STAGES;      // accumulators final
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int RAW_X = 3 * WG_G_FLOATS, RAW_GO = RAW_X + WG_KS * a.ldx, RAW_FLOATS = RAW_GO + WG_KS * 4;   // raw stage: h2 | h1 | g_h1 | X | go4
+  float* raw = ring + (size_t)NSTG * WG_STAGE_FLOATS;                  // [RS][RAW_FLOATS] (RAW only)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(raw + (RAW ? RS * (size_t)RAW_FLOATS : 0));
+  uint64_t* full = bars;                      // [NSTG]  16 producer warps
+  uint64_t* empty = bars + NSTG;              // [NSTG]  tcgen05.commit
+  uint64_t* done = bars + 2 * NSTG;           // accumulators final
+  uint64_t* raw_full = done + 1;              // [RS]  expect_tx + bulk copies
+  uint64_t* raw_empty = raw_full + RS;        // [RS]  16 producer warps have read the stage
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(raw_empty + RS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float fold_dw3[3] = {0.f, 0.f, 0.f}, fold_db2 = 0.f, fold_db3[3] = {0.f, 0.f, 0.f};     // output-layer gradients (fold3)
@@ -69,13 +83,14 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   const int my_chunks = (int)((nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x);
 
   if (tid == 0) {
-    for (int i = 0; i < WG_STAGES; ++i) { tc::mbar_init(full + i, WG_PROD_WARPS); tc::mbar_init(empty + i, 1); }
+    for (int i = 0; i < NSTG; ++i) { tc::mbar_init(full + i, WG_PROD_WARPS); tc::mbar_init(empty + i, 1); }
     tc::mbar_init(done, 1);
+    for (int i = 0; i < RS; ++i) { tc::mbar_init(raw_full + i, 1); tc::mbar_init(raw_empty + i, WG_PROD_WARPS); }
     tc::fence_barrier_init();
   }
   if (warp == WG_PROD_WARPS) tc::tmem_alloc(tmem_slot, 512);
   // constant part of every X stage: the ones column (bias gradient) and the zero padding columns
-  for (int e = tid; e < WG_STAGES * 2 * (WG_NGX * 4 - a.kp) * 4; e += WG_THREADS) {
+  for (int e = tid; e < NSTG * 2 * (WG_NGX * 4 - a.kp) * 4; e += WG_THREADS) {
     int ku = e & 3, r = e >> 2;
     int col = a.kp + r % (WG_NGX * 4 - a.kp); r /= (WG_NGX * 4 - a.kp);
     int hl = r & 1, stg = r >> 1;
@@ -97,6 +112,13 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     float v[2][20];
     const int xu = a.kp * 4;                              // X units per chunk
     const int gcol = tid & 127, gku = tid >> 7;           // this thread's unit of every 128-wide tile
+    int xdst[2];                                          // operand offsets of this thread's X units (-1: none)
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int id = tid + WG_PROD * q;
+      const int ku = id / a.kp, col = id - ku * a.kp;
+      xdst[q] = id < xu ? tc::canon_off(col, ku, 4) : -1;
+    }
     float w3c[3] = {0.f, 0.f, 0.f};
     float (&dw3)[3] = fold_dw3, &db2 = fold_db2, (&db3)[3] = fold_db3;
     if (a.fold3) {
@@ -131,18 +153,18 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
       *reinterpret_cast<float4*>(hi + off) = h;
       *reinterpret_cast<float4*>(lo + off) = l;
     };
-    auto store = [&](int j, float (&r)[20]) {
-      const int stg = j % WG_STAGES;
+    auto store = [&](int j, float (&r)[20], const float4* gor) {      // gor: this thread's four go4 records (RAW), else nullptr
+      const int stg = j % NSTG;
       if (a.fold3) {
         // r[0..3] holds h2 of this thread's column for four samples: rebuild g_h2 and collect the output layer's gradients
         const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS + gku * 4;
-        if (j + 1 < my_chunks) {                        // the next chunk's go values: into L1 while this chunk is written
+        if (!RAW && j + 1 < my_chunks) {                // the next chunk's go values: into L1 while this chunk is written
           const float4* nx = a.go4 + ((int64_t)blockIdx.x + (int64_t)(j + 1) * gridDim.x) * WG_KS + gku * 4;
           asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float4 g = s0 + i < M ? __ldg(a.go4 + s0 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4 g = RAW ? gor[i] : (s0 + i < M ? __ldg(a.go4 + s0 + i) : make_float4(0.f, 0.f, 0.f, 0.f));
           const float h = r[i];
           dw3[0] = fmaf(g.x, h, dw3[0]); dw3[1] = fmaf(g.y, h, dw3[1]); dw3[2] = fmaf(g.z, h, dw3[2]);
           const float gh = h > 0.f ? g.x * w3c[0] + g.y * w3c[1] + g.z * w3c[2] : 0.f;
@@ -151,30 +173,100 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
           r[i] = gh;
         }
       }
-      tc::mbar_wait(empty + stg, ((j / WG_STAGES) & 1) ^ 1);
+      tc::mbar_wait(empty + stg, ((j / NSTG) & 1) ^ 1);
       float* S = ring + (size_t)stg * WG_STAGE_FLOATS;
       const int off = tc::canon_off(gcol, gku, 4);
       put(S, S + WG_G_FLOATS, off, r);
       put(S + 2 * WG_G_FLOATS, S + 3 * WG_G_FLOATS, off, r + 4);
       put(S + 4 * WG_G_FLOATS, S + 5 * WG_G_FLOATS, off, r + 8);
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const int id = tid + WG_PROD * q;
-        const int ku = id / a.kp, col = id - ku * a.kp;
-        if (id < xu) put(S + 6 * WG_G_FLOATS, S + 6 * WG_G_FLOATS + WG_X_FLOATS, tc::canon_off(col, ku, 4), r + 12 + q * 4);
-      }
+      for (int q = 0; q < 2; ++q)
+        if (xdst[q] >= 0) put(S + 6 * WG_G_FLOATS, S + 6 * WG_G_FLOATS + WG_X_FLOATS, xdst[q], r + 12 + q * 4);
       tc::fence_async_smem();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(full + stg);
     };
-    load(0, v[0]);
-    if (1 < my_chunks) load(1, v[1]);
-    for (int j = 0; j < my_chunks; j += 2) {
-      store(j, v[0]);
-      if (j + 2 < my_chunks) load(j + 2, v[0]);
-      if (j + 1 < my_chunks) {
-        store(j + 1, v[1]);
-        if (j + 3 < my_chunks) load(j + 3, v[1]);
+    if constexpr (RAW) {
+      // per-thread constants of the X part (a division by kp per chunk showed up as the hottest integer work)
+      int xsrc[2], xrow[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int id = tid + WG_PROD * q;
+        const int ku = id / a.kp, col = id - ku * a.kp;
+        xrow[q] = id < xu ? ku * 4 : WG_KS;             // first sample row of the unit (WG_KS: no unit)
+        xsrc[q] = RAW_X + ku * 4 * a.ldx + col;
+      }
+      const int gsrc = gku * 4 * 128 + gcol;
+      for (int j = 0; j < my_chunks; ++j) {
+        const int rs = j % RS;
+        const float* R = raw + (size_t)rs * RAW_FLOATS;
+        const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS;
+        const int nrow = (int)min((int64_t)WG_KS, M - s0);         // rows past the end were not copied: stale shared memory
+        float (&r)[20] = v[0];
+        float4 gor[4];
+        tc::mbar_wait(raw_full + rs, (j / RS) & 1);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int sl = gku * 4 + i;
+          const bool ok = sl < nrow;
+          r[i] = ok ? R[gsrc + i * 128] : 0.f;
+          r[4 + i] = ok ? R[WG_G_FLOATS + gsrc + i * 128] : 0.f;
+          r[8 + i] = ok ? R[2 * WG_G_FLOATS + gsrc + i * 128] : 0.f;
+          gor[i] = (ok && a.fold3) ? *reinterpret_cast<const float4*>(R + RAW_GO + sl * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {                     // X: kp columns x 4 units
+#pragma unroll
+          for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] + i < nrow ? R[xsrc[q] + i * a.ldx] : 0.f;
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(raw_empty + rs);   // (release: this warp's reads of the stage are done)
+        store(j, r, gor);
+      }
+    } else {
+      load(0, v[0]);
+      if (1 < my_chunks) load(1, v[1]);
+      for (int j = 0; j < my_chunks; j += 2) {
+        store(j, v[0], nullptr);
+        if (j + 2 < my_chunks) load(j + 2, v[0]);
+        if (j + 1 < my_chunks) {
+          store(j + 1, v[1], nullptr);
+          if (j + 3 < my_chunks) load(j + 3, v[1]);
+        }
+      }
+    }
+  } else if (warp == WG_PROD_WARPS + 1) {
+    // ============================================================ bulk-copy warp: the raw rows of chunk j -> raw stage j % 2
+    if (RAW && lane == 0) {
+      // the shared-memory ring holds two chunks, i.e. one copy in flight while the other stage is read: far too little
+      // for DRAM latency.  cp.async.bulk.prefetch.L2 needs no destination: chunks up to WG_L2_AHEAD ahead are pulled
+      // into L2, and the copies into shared memory then pay L2 latency only.
+      auto prefetch = [&](int jj) {
+        if (jj >= my_chunks) return;
+        const int64_t p0 = ((int64_t)blockIdx.x + (int64_t)jj * gridDim.x) * WG_KS;
+        const uint32_t prow = (uint32_t)min((int64_t)WG_KS, M - p0);
+        auto pf = [](const void* ptr, uint32_t bytes) {
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+        };
+        pf(a.g2 + p0 * 128, prow * 512u);
+        pf(a.h1 + p0 * 128, prow * 512u);
+        pf(a.g1 + p0 * 128, prow * 512u);
+        pf(a.x + p0 * a.ldx, prow * (uint32_t)(a.ldx * 4));
+      };
+      for (int jj = RS; jj < RS + WG_L2_AHEAD; ++jj) prefetch(jj);
+      for (int j = 0; j < my_chunks; ++j) {
+        prefetch(j + RS + WG_L2_AHEAD);
+        const int rs = j % RS;
+        float* R = raw + (size_t)rs * RAW_FLOATS;
+        const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS;
+        const uint32_t rows = (uint32_t)min((int64_t)WG_KS, M - s0);
+        tc::mbar_wait(raw_empty + rs, ((j / RS) & 1) ^ 1);
+        tc::mbar_expect_tx(raw_full + rs, rows * (uint32_t)(3 * 512 + a.ldx * 4 + (a.fold3 ? 16 : 0)));
+        tc::bulk_g2s(R, a.g2 + s0 * 128, rows * 512u, raw_full + rs);
+        tc::bulk_g2s(R + WG_G_FLOATS, a.h1 + s0 * 128, rows * 512u, raw_full + rs);
+        tc::bulk_g2s(R + 2 * WG_G_FLOATS, a.g1 + s0 * 128, rows * 512u, raw_full + rs);
+        tc::bulk_g2s(R + RAW_X, a.x + s0 * a.ldx, rows * (uint32_t)(a.ldx * 4), raw_full + rs);
+        if (a.fold3) tc::bulk_g2s(R + RAW_GO, a.go4 + s0, rows * 16u, raw_full + rs);
       }
     }
   } else if (lane == 0) {
@@ -185,8 +277,8 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
     const uint32_t lo_x = tc::desc_lo(tc::smem_u32(ring + 6 * WG_G_FLOATS), 128);
     const uint32_t GU = WG_G_FLOATS * 4 / 16, XU = WG_X_FLOATS * 4 / 16, SU = WG_STAGE_FLOATS * 4 / 16;
     for (int j = 0; j < my_chunks; ++j) {
-      const int stg = j % WG_STAGES;
-      tc::mbar_wait(full + stg, (j / WG_STAGES) & 1);
+      const int stg = j % NSTG;
+      tc::mbar_wait(full + stg, (j / NSTG) & 1);
       tc::fence_after_sync();
       const uint32_t g = lo_g + (uint32_t)stg * SU, x = lo_x + (uint32_t)stg * SU;
 #pragma unroll
@@ -283,11 +375,20 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
   if (a.cap == 0) return FTRF_OK;
   if (!(call && prep_ahead_take_scratch(*call)) &&
       cudaMemsetAsync(a.dw1i, 0, wgrad_fused_scratch_bytes(), st) != cudaSuccess) return check_launch("wgrad scratch memset");
-  const size_t smem = (size_t)WG_STAGES * 2 * (3 * WG_G_FLOATS + WG_KS * a.ngt * 4) * 4 + 16 * 8;
-  cudaFuncSetAttribute(wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const size_t stage_b = (size_t)2 * (3 * WG_G_FLOATS + WG_KS * a.ngt * 4) * 4;
+  const size_t raw_b = (size_t)(3 * WG_G_FLOATS + WG_KS * a.ldx + WG_KS * 4) * 4;
+  const bool use_raw = g_wgrad_raw && WG_RAW_OPS * stage_b + WG_RAW_STAGES * raw_b + 256 <= 227 * 1024 &&
+                       (((uintptr_t)a.g2 | (uintptr_t)a.h1 | (uintptr_t)a.g1 | (uintptr_t)a.x | (uintptr_t)a.go4) & 15) == 0;
+  const size_t smem = use_raw ? WG_RAW_OPS * stage_b + WG_RAW_STAGES * raw_b + 24 * 8 : (size_t)WG_STAGES * stage_b + 24 * 8;
   int64_t chunks = (a.cap + WG_KS - 1) / WG_KS;
   int grid = (int)(chunks < FTRF_SMS ? chunks : FTRF_SMS);
-  wgrad_fused_kernel<<<grid, WG_THREADS, smem, st>>>(a);
+  if (use_raw) {
+    cudaFuncSetAttribute(wgrad_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    wgrad_fused_kernel<true><<<grid, WG_THREADS, smem, st>>>(a);
+  } else {
+    cudaFuncSetAttribute(wgrad_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    wgrad_fused_kernel<false><<<grid, WG_THREADS, smem, st>>>(a);
+  }
   if (int e = check_launch("wgrad_fused")) return e;
   // nothing later in the backward reads g_w1 / g_b1: off the serial chain, joined at the end of the call
   cudaStream_t tail = call ? side_tail_begin(*call, st) : nullptr;
@@ -300,6 +401,7 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
 
 #ifdef FTRF_TEST_BUILD
 extern "C" int ftrf_debug_wgrad_variant(int v) { ftrf::g_wgrad_variant = v; return 0; }
+extern "C" int ftrf_debug_set_wgrad_raw(int on) { ftrf::g_wgrad_raw = on; return 0; }
 
 // unit-test entry: identity column order
 extern "C" int ftrf_test_wgrad_fused(const float* g2, const float* h1, const float* g1, const float* x, int ldx, int kp,

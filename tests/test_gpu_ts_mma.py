@@ -51,3 +51,38 @@ def test_tmem_operand_forward_matches_the_product_kernel_and_the_oracle(shading,
     assert rel_inf(ref.cpu(), want) < 1e-4
     assert rel_inf(got.cpu(), want) < 1e-4
     assert rel_inf(got.cpu(), ref.cpu()) < 2e-5
+
+
+def test_wgrad_bulk_copy_ring_matches_direct_loads():
+    """wgrad_fused_kernel<RAW> (activation rows brought in by cp.async.bulk, transposed from shared memory) against the
+    build whose producers load from global memory: same sums in the same order, on a sample count with a ragged tail."""
+    from tests.gpu_util import test_lib
+    lib = test_lib()
+    M, kp, ldx = 16 * 300 + 11, 152, 152
+    g = torch.Generator().manual_seed(3)
+    g2 = torch.randn(M, 128, generator=g).cuda()
+    h1 = torch.randn(M, 128, generator=g).relu().cuda()
+    g1 = torch.randn(M, 128, generator=g).cuda()
+    x = torch.randn(M, ldx, generator=g).cuda()
+    lib.ftrf_test_wgrad_fused.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_int64] + [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 3
+    out = {}
+    for raw in (1, 0):
+        lib.ftrf_debug_set_wgrad_raw(raw)
+        dw2 = torch.zeros(128, 128, device="cuda")
+        dw1 = torch.zeros(128, kp, device="cuda")
+        db1 = torch.zeros(128, device="cuda")
+        scratch = torch.zeros(128 * 48 * 4, device="cuda")
+        rc = lib.ftrf_test_wgrad_fused(g2.data_ptr(), h1.data_ptr(), g1.data_ptr(), x.data_ptr(), ldx, kp, M, dw2.data_ptr(),
+                                       dw1.data_ptr(), kp, db1.data_ptr(), scratch.data_ptr(), None)
+        assert rc == 0
+        torch.cuda.synchronize()
+        out[raw] = (dw2, dw1, db1)
+    lib.ftrf_debug_set_wgrad_raw(1)
+    want2 = g2.double().T @ h1.double()
+    want1 = g1.double().T @ x[:, :kp].double()
+    for raw in (1, 0):
+        assert float((out[raw][0].double() - want2).abs().max()) < 2e-5 * float(want2.abs().max())
+        assert float((out[raw][1].double() - want1).abs().max()) < 2e-5 * float(want1.abs().max())
+        assert float((out[raw][2].double() - g1.double().sum(0)).abs().max()) < 2e-5 * float(g1.double().sum(0).abs().max())
+    for a, b in zip(out[1], out[0]):
+        assert float((a - b).abs().max()) < 1e-5 * float(b.abs().max())
