@@ -61,6 +61,7 @@ enum : uint64_t {
   CALL_TAIL_PENDING = 8,      // un-permute of dW1 running on the side stream
   CALL_SCAN_PENDING = 16,     // reverse scan of the integration backward running on the side stream
   CALL_FORKED = 32,           // phase 0 of shade_prep_ahead recorded its fork event
+  CALL_MASKS_READY = 64,      // the fused forward left the ReLU sign masks of h1 / h2 (32 B per shaded sample) in ws.a_gx
 };
 struct CallState { uint64_t flags; void* ctx; };
 inline CallState& call_state(const FtrfCall& c) {

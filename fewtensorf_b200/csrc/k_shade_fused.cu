@@ -91,6 +91,22 @@ __device__ __forceinline__ void st_global_v8(float* p, const float* v) {
                "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
 }
 
+// Bit i = (v[i] > 0) for 32 values that are >= +0 (outputs of a ReLU): as unsigned integers they are non-zero exactly when
+// positive, so `v + 0xffffffff` carries out exactly then, and `m = m + m + carry` shifts the bit in — two integer
+// instructions per value (the dgrad kernel reads these 4 bytes instead of 128 bytes of activations).
+__device__ __forceinline__ uint32_t relu_sign_bits(const float v[32]) {
+  uint32_t p[4] = {0u, 0u, 0u, 0u};          // four independent carry chains of eight values each
+#pragma unroll
+  for (int i = 7; i >= 0; --i) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t junk;
+      asm("{\n\tadd.cc.u32 %1, %2, 0xffffffff;\n\taddc.u32 %0, %0, %0;\n\t}" : "+r"(p[q]), "=r"(junk) : "r"(__float_as_uint(v[q * 8 + i])));
+    }
+  }
+  return p[0] | (p[1] << 8) | (p[2] << 16) | (p[3] << 24);
+}
+
 struct SPair { int meta; float scale, ma, mb; };     // meta = kind | sa << 8 | sb << 16
 
 // Compile-time copy of make_fused_spec()'s column recipe for the shipped configurations: with every
@@ -135,6 +151,7 @@ struct DynamicSpec { static constexpr bool is_static = false; };
 // optional phase timeline of CTA 0 (debug aid, scripts/fused_timeline.py): dbg[role*512 + n]
 FTRF_SWITCH(long long*, g_fused_dbg, nullptr);
 FTRF_SWITCH(long long*, g_dgrad_dbg, nullptr);
+FTRF_SWITCH(int, g_dgrad_masks, 1);        // ftrf_debug_set_dgrad_masks (test build): 0 = the dgrad kernel reads h1 / h2 back
 #define FZ_T(role, n) do { if (dbg && blockIdx.x == 0 && (n) < 512) dbg[(role) * 512 + (n)] = clock64(); } while (0)
 
 
@@ -336,6 +353,9 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
       tc::mbar_wait(acc_full + 0, it & 1);
       tc::fence_after_sync();
       if (tl) FZ_T(0, it * 8 + 3);
+      // ReLU sign bits of h1 (words 0..3) / h2 (4..7) for the dgrad kernel, word-major [8][cap_app]: a warp's store of one
+      // word is 128 contiguous bytes
+      uint32_t* const sgn = reinterpret_cast<uint32_t*>(ws.a_gx) + row;
       for (int j = 0; j < 4; ++j, ++ac) {
         const int stg = ac % FZ_A_STAGES;
         float acc[32];
@@ -346,6 +366,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         if (save && live) {
 #pragma unroll
           for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h1 + row * FC + j * 32 + u * 8, acc + 8 * u);
+          sgn[(size_t)j * c.cap_app] = relu_sign_bits(acc);
         }
         tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
         float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
@@ -387,6 +408,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         if (save && live) {
 #pragma unroll
           for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h2 + row * FC + j * 32 + u * 8, acc + 8 * u);
+          sgn[(size_t)(4 + j) * c.cap_app] = relu_sign_bits(acc);
         }
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -985,7 +1007,8 @@ __device__ __forceinline__ void bz_epilogue(uint32_t t_acc2, const SPair* s_pair
 
 template <class SS>
 __global__ void __launch_bounds__(BZ_THREADS, 1)
-shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg) {
+shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg,
+                         const int masks) {     // masks: the forward left the ReLU sign bits of h1 / h2 in ws.a_gx (32 B per sample)
   static_assert(SS::is_static && SS::kp <= BZ_W1_ROWS, "dgrad kernel is built for the static specs only");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [group][A_STAGES][hi, lo][4096]
@@ -1062,13 +1085,23 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
       if (tl) FZ_T(g, li * 8 + 0);
       // ---- g_h2 chunks (half, half + 2) -> operand ring (A of g_h2 W2); all loads in flight at once.
       // g_h2 = relu'(h2) * (go W3) with go = dL/d rgb * rgb (1 - rgb) (sigmoid backward, models/mlp.py:66-67)
+      uint32_t hm[2] = {0u, 0u};                            // relu'(h1) of my two chunks as bit masks
       {
         float v[64];
         if (live) {
+          if (masks) {                                      // sign bits instead of the values: v > 0 <=> bit set
+            const uint32_t* mk = reinterpret_cast<const uint32_t*>(ws.a_gx) + row;      // word-major [8][cap_app]
+            hm[0] = __ldg(mk + (size_t)half * c.cap_app);
+            hm[1] = __ldg(mk + (size_t)(half + 2) * c.cap_app);
+            const uint32_t b0 = __ldg(mk + (size_t)(4 + half) * c.cap_app), b1 = __ldg(mk + (size_t)(6 + half) * c.cap_app);
 #pragma unroll
-          for (int jj = 0; jj < 2; ++jj)
+            for (int i = 0; i < 32; ++i) { v[i] = (float)((b0 >> i) & 1u); v[32 + i] = (float)((b1 >> i) & 1u); }
+          } else {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_h2 + row * FC + (jj * 2 + half) * 32 + u * 8, v + jj * 32 + 8 * u);
+            for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+              for (int u = 0; u < 4; ++u) ld_global_v8(ws.a_h2 + row * FC + (jj * 2 + half) * 32 + u * 8, v + jj * 32 + 8 * u);
+          }
           float go[3];
 #pragma unroll
           for (int ch = 0; ch < 3; ++ch) {
@@ -1093,9 +1126,8 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
         put_chunk(ac0 + 2 + half, v + 32);
       }
       if (tl) FZ_T(g, li * 8 + 1);
-      // ---- relu'(h1) of my two chunks as bit masks, fetched while the first product runs
-      uint32_t hm[2] = {0u, 0u};
-      if (live) {
+      // ---- relu'(h1) of my two chunks as bit masks, fetched while the first product runs (unless the forward left them)
+      if (live && !masks) {
         float h1[64];
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj)
@@ -1372,6 +1404,8 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
   if (c.cap_app == 0) return FTRF_OK;
   float* img = ws.wimg + fused_bwd_offset_floats();
   CallState& cs = call_state(c);
+  const int masks = (cs.flags & CALL_MASKS_READY) && g_dgrad_masks ? 1 : 0;     // this call's fused forward wrote the sign masks
+  cs.flags &= ~(uint64_t)CALL_MASKS_READY;
   if (cs.flags & CALL_IMG_BWD_READY) {
     cs.flags &= ~(uint64_t)CALL_IMG_BWD_READY;      // built by this call's forward on the side stream, which the forward joined
   } else {
@@ -1384,7 +1418,7 @@ int launch_shade_dgrad_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws
   int grid = (int)(tiles < FTRF_SMS ? tiles : FTRF_SMS);
   auto go = [&](auto kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, BZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_dgrad_dbg);
+    kern<<<grid, BZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_dgrad_dbg, masks);
   };
   if (which == 0) go(shade_fused_dgrad_kernel<SFea>);
   else if (which == 1) go(shade_fused_dgrad_kernel<SPe>);
@@ -1445,6 +1479,7 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
     return check_launch("shade_fwd_ts");
   }
 #endif
+  if (c.save_for_backward && ws.a_gx) cs.flags |= CALL_MASKS_READY;      // the kernels below leave the ReLU sign masks in ws.a_gx
   if (f.shading == FTRF_SHADE_MLP_FEA && pe2 && f.fea_pe == 2 && fs.kp == SFea::kp) go(shade_fused_fwd_kernel<SFea>);
   else if (f.shading == FTRF_SHADE_MLP_PE && pe2 && f.pos_pe == 2 && fs.kp == SPe::kp) go(shade_fused_fwd_kernel<SPe>);
   else if (f.shading == FTRF_SHADE_MLP && pe2 && f.pos_pe == 2 && f.fea_pe == 2 && fs.kp == SMlp::kp) go(shade_fused_fwd_kernel<SMlp>);
@@ -1456,6 +1491,11 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
 }  // namespace ftrf
 
 #ifdef FTRF_TEST_BUILD
+extern "C" int ftrf_debug_set_dgrad_masks(int on) {
+  ftrf::g_dgrad_masks = on;
+  return FTRF_OK;
+}
+
 extern "C" int ftrf_debug_set_fwd_ts(int on) {
   ftrf::g_fwd_ts = on;
   return FTRF_OK;
