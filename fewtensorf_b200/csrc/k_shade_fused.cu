@@ -905,12 +905,14 @@ static size_t fwd_ts_smem() {
 // of W1^T [160 x 16] (internal column order).  Each group owns a 2-stage operand ring, so a group never
 // runs more than one barrier phase ahead of the MMA warp.  TMEM: acc1 columns 0-127 (shared: a tile's
 // acc1 is drained before its second product ends), acc2 of group g at 128 + 160 g.
-constexpr int BZ_GROUPS = 2, BZ_A_STAGES = 2, BZ_W_STAGES = 4;
+constexpr int BZ_GROUPS = 2, BZ_A_STAGES = 2, BZ_W_STAGES = 2;
 constexpr int BZ_W1_ROWS = 160;                                  // kp (152) padded to a multiple of 16
 constexpr int BZ_SUB_K = 16;                                     // k extent of a streamed weight sub-chunk
 constexpr int BZ_W2_SUB_FLOATS = 2 * 128 * BZ_SUB_K;             // hi + lo
 constexpr int BZ_W1_SUB_FLOATS = 2 * BZ_W1_ROWS * BZ_SUB_K;
-constexpr int BZ_WSTAGE_FLOATS = BZ_W1_SUB_FLOATS;
+constexpr int BZ_WSTAGE_FLOATS = 2 * BZ_W1_SUB_FLOATS;            // a stage = the two sub-chunks (K = 32) one operand chunk needs:
+                                                                 // one barrier wait and one commit of the issuing thread per chunk
+                                                                 // instead of two (each wait costs it ~225 clk, scripts/issue_probe.py)
 constexpr int BZ_THREADS = (BZ_GROUPS * 8 + 2) * 32;
 
 __global__ void __launch_bounds__(256)
@@ -1186,12 +1188,12 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
           FZ_T(2, (it * 8 + ch) * 2 + 0);
           tc::mbar_wait(a_full + g * BZ_A_STAGES + as, (ac / BZ_A_STAGES) & 1);
           FZ_T(2, (it * 8 + ch) * 2 + 1);
+          const int wsg = wc % BZ_W_STAGES;
+          tc::mbar_wait(w_full + wsg, (wc / BZ_W_STAGES) & 1);
+          tc::fence_after_sync();
 #pragma unroll
-          for (int sub = 0; sub < 2; ++sub, ++wc) {
-            const int wsg = wc % BZ_W_STAGES;
-            tc::mbar_wait(w_full + wsg, (wc / BZ_W_STAGES) & 1);
-            tc::fence_after_sync();
-            const uint32_t wh = w_lo0 + (uint32_t)wsg * (BZ_WSTAGE_FLOATS * 4 / 16);
+          for (int sub = 0; sub < 2; ++sub) {
+            const uint32_t wh = w_lo0 + (uint32_t)wsg * (BZ_WSTAGE_FLOATS * 4 / 16) + (uint32_t)sub * (2 * wlo);
 #pragma unroll
             for (int s = 0; s < 2; ++s) {
               const uint32_t ao = (uint32_t)(sub * 2 + s) * 16, wo = (uint32_t)s * 16;
@@ -1200,8 +1202,9 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
               tc::mma_tf32_ss_lo2(d, ah + ao, a_hi, wh + wlo + wo, w_hi, idesc, 1u);
               tc::mma_tf32_ss_lo2(d, ah + ao, a_hi, wh + wo, w_hi, idesc, 1u);
             }
-            tc::mma_commit(w_empty + wsg);
           }
+          tc::mma_commit(w_empty + wsg);
+          ++wc;
           tc::mma_commit(a_empty + g * BZ_A_STAGES + as);
           if (ch == 3) tc::mma_commit(acc_full + g * 2 + 0);
           if (ch == 7) tc::mma_commit(acc_full + g * 2 + 1);
@@ -1213,10 +1216,10 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
     if (lane == 0) {
       uint32_t wc = 0;
       for (int it = 0; it < my_tiles; ++it)
-        for (int sc = 0; sc < 16; ++sc, ++wc) {
+        for (int sc = 0; sc < 16; sc += 2, ++wc) {          // sub-chunks sc, sc + 1 are adjacent in the image: one copy
           const int wsg = wc % BZ_W_STAGES;
           const bool first = sc < 8;
-          const uint32_t bytes = (uint32_t)(first ? BZ_W2_SUB_FLOATS : BZ_W1_SUB_FLOATS) * 4;
+          const uint32_t bytes = (uint32_t)(first ? BZ_W2_SUB_FLOATS : BZ_W1_SUB_FLOATS) * 4 * 2;
           const float* src = first ? wimg + (size_t)sc * BZ_W2_SUB_FLOATS
                                    : wimg + (size_t)8 * BZ_W2_SUB_FLOATS + (size_t)(sc - 8) * BZ_W1_SUB_FLOATS;
           tc::mbar_wait(w_empty + wsg, ((wc / BZ_W_STAGES) & 1) ^ 1);
