@@ -255,13 +255,23 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
       tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
       float* Ahi = a_ring + ((size_t)stg * 2 + sub) * (2 * FZ_CHUNK_FLOATS);
       float* Alo = Ahi + FZ_CHUNK_FLOATS;
+      float xs[4];                                        // the even unit of a pair, until its odd neighbour is ready
       auto emit = [&](int u, const float v[4]) {
         float4 h, l;
         split4(v, h, l);
         const int off = tc::canon_off(r_in, u, 8);
         *reinterpret_cast<float4*>(Ahi + off) = h;
         *reinterpret_cast<float4*>(Alo + off) = l;
-        if (save && live) *reinterpret_cast<float4*>(ws.a_x + row * ws.ldx + ch * 32 + u * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        // X saved for the weight-gradient kernel: two units per store = one full 32-byte sector (kp is a multiple of 8;
+        // 16-byte stores left half-written sectors behind: 15 us of the kernel went into them)
+        if (u & 1) {
+          if (save && live) {
+            const float w[8] = {xs[0], xs[1], xs[2], xs[3], v[0], v[1], v[2], v[3]};
+            st_global_v8(ws.a_x + row * ws.ldx + ch * 32 + (u - 1) * 4, w);
+          }
+        } else {
+          xs[0] = v[0]; xs[1] = v[1]; xs[2] = v[2]; xs[3] = v[3];
+        }
       };
       if constexpr (SS::is_static) {
 #pragma unroll
