@@ -23,7 +23,7 @@ namespace ftrf {
 constexpr int FZ_A_STAGES = 2;
 constexpr int FZ_W_STAGES = 2;
 constexpr int FZ_CHUNK_FLOATS = 128 * 32;              // one hi (or lo) [128 x 32] chunk
-constexpr int FZ_THREADS = 320;
+constexpr int FZ_THREADS = 352;                        // 8 compute warps, two MMA-issuing warps (one per sub-tile), the weight streamer
 constexpr int FZ_PAIR_ROWS = 256;
 
 // ------------------------------------------------------------------------------------------ prep
@@ -182,10 +182,10 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
   const int n1 = fs.n1, nck = n1 + 4;
 
   if (tid == 0) {
-    for (int i = 0; i < FZ_A_STAGES; ++i) { tc::mbar_init(a_full + i, 8); tc::mbar_init(a_empty + i, 1); }
-    for (int i = 0; i < FZ_W_STAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 1); }
-    tc::mbar_init(acc_full + 0, 1);
-    tc::mbar_init(acc_full + 1, 1);
+    for (int i = 0; i < FZ_A_STAGES; ++i) { tc::mbar_init(a_full + i, 8); tc::mbar_init(a_empty + i, 2); }
+    for (int i = 0; i < FZ_W_STAGES; ++i) { tc::mbar_init(w_full + i, 1); tc::mbar_init(w_empty + i, 2); }
+    tc::mbar_init(acc_full + 0, 2);                // one commit per issuing thread
+    tc::mbar_init(acc_full + 1, 2);
     tc::fence_barrier_init();
   }
   if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
@@ -440,9 +440,13 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         for (int k = 0; k < 3; ++k) ws.a_rgb[row * 3 + k] = 1.f / (1.f + expf(-o3[k]));
       }
     }
-  } else if (warp == 8) {
-    // =============================================================== MMA issuer
+  } else if (warp == 8 || warp == 9) {
+    // =============================================================== MMA issuers: warp 8 sub-tile a, warp 9 sub-tile b.
+    // What an issuing thread does between dispatches is not hidden behind them (two waits + three commits per chunk cost
+    // as much as 10 of its 12 MMAs, scripts/issue_probe.py), but two threads interleave on the tensor pipe: each one's
+    // overhead runs behind the other's products.  A stage is free when both have committed (barrier counts 2).
     if (lane == 0) {
+      const int sub = warp - 8;
       const uint32_t idesc = tc::idesc_tf32(128, 128);
       const uint32_t a_lo0 = tc::desc_lo(tc::smem_u32(a_ring), 128), w_lo0 = tc::desc_lo(tc::smem_u32(w_ring), 128);
       const uint32_t d_hi = tc::desc_hi(1024);
@@ -452,11 +456,11 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
           const int as = ac % FZ_A_STAGES, wsg = wc % FZ_W_STAGES;
           const bool l1 = ch < n1;
           const int ksteps = l1 ? min(32, fs.kp - ch * 32) / 8 : 4;
-          FZ_T(1, wc * 3 + 0);
+          if (sub == 0) FZ_T(1, wc * 3 + 0);
           tc::mbar_wait(w_full + wsg, (wc / FZ_W_STAGES) & 1);
-          FZ_T(1, wc * 3 + 1);
+          if (sub == 0) FZ_T(1, wc * 3 + 1);
           tc::mbar_wait(a_full + as, (ac / FZ_A_STAGES) & 1);
-          FZ_T(1, wc * 3 + 2);
+          if (sub == 0) FZ_T(1, wc * 3 + 2);
           tc::fence_after_sync();
           // descriptor low words: address >> 4 (+ LBO field); a k-step advances by 256 B = 16 units
           const uint32_t w_lo = w_lo0 + (uint32_t)wsg * (2 * FZ_CHUNK_FLOATS * 4 / 16);
@@ -464,8 +468,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
           const uint32_t d0 = tmem + (uint32_t)(l1 ? 0 : 256);
           const uint32_t fresh = (l1 ? ch == 0 : ch == n1) ? 0u : 1u;
           constexpr uint32_t LO = FZ_CHUNK_FLOATS * 4 / 16;      // hi -> lo half of a chunk, in 16-byte units
-#pragma unroll
-          for (int sub = 0; sub < 2; ++sub) {
+          {
             const uint32_t ah = a_lo + (uint32_t)sub * (2 * LO), d = d0 + (uint32_t)(sub * 128);
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
