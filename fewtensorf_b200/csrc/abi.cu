@@ -74,12 +74,14 @@ size_t carve(const FtrfField& f, const FtrfCall& c, int64_t* off, void* base, Ws
   sz[FTRF_WS_A_FEAT] = A * D * 4;
   sz[FTRF_WS_A_RGB] = A * 12;
   const size_t LDX = (size_t)((f.in_dim + 1 + 7) & ~7);
-  sz[FTRF_WS_A_H1] = mlp ? A * H * 4 : 0;
-  sz[FTRF_WS_A_H2] = mlp ? A * H * 4 : 0;
-  sz[FTRF_WS_A_X] = mlp ? A * LDX * 4 : 0;
+  // the fused MLP kernels may save activations in padded blocks of 16 rows (fused.cuh: act16_off): 17/16 of the row-major size
+  const size_t A16 = (A + 15) / 16;
+  sz[FTRF_WS_A_H1] = mlp ? A16 * act16_block_floats((int)H) * 4 : 0;
+  sz[FTRF_WS_A_H2] = mlp ? A16 * act16_block_floats((int)H) * 4 : 0;
+  sz[FTRF_WS_A_X] = mlp ? A16 * act16_block_floats((int)LDX) * 4 : 0;
   sz[FTRF_WS_A_GX] = (train && mlp) ? A * LDX * 4 : 0;
   sz[FTRF_WS_A_GRGB] = train ? A * 12 : 0;
-  sz[FTRF_WS_A_GH1] = (train && mlp) ? A * H * 4 : 0;
+  sz[FTRF_WS_A_GH1] = (train && mlp) ? A16 * act16_block_floats((int)H) * 4 : 0;
   sz[FTRF_WS_A_GH2] = (train && mlp) ? A * H * 4 : 0;
   sz[FTRF_WS_A_GFEAT] = train ? A * D * 4 : 0;
   sz[FTRF_WS_WIMG] = mlp ? fused_wimg_bytes() : 0;

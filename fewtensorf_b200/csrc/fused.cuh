@@ -101,6 +101,22 @@ int side_tail_join(const FtrfCall&, cudaStream_t st);             // `st` waits 
 int shade_prep_ahead(const FtrfField&, const FtrfCall&, const Ws&, cudaStream_t, int phase);   // weight images on a side stream
 
 // argument block of the fused weight-gradient kernel (k_wgrad_fused.cu)
+// Layout of the activations the fused forward / dgrad kernels save for the weight-gradient kernel (X, h1, h2, g_h1) when
+// ws.counters[WS_ACT_LAYOUT] == 1: blocks of 16 rows; inside a block the 8-column groups are outermost and every group
+// (16 rows x 8 floats = 512 bytes) is followed by 32 bytes of padding —
+//     (row, col) of a W-column array  ->  (row / 16) (W / 8) 136  +  (col / 8) 136  +  (row % 16) 8  +  col % 8
+// A thread of those kernels owns a sample row, so with plain row-major arrays a warp's 32-byte store touched 32 different
+// lines; here the 16 rows of a block are contiguous per 8-column group: 4x fewer store wavefronts (10 us of the forward, 5
+// of the dgrad kernel).  The weight-gradient kernel consumes whole blocks with ONE bulk copy per array and chunk, and the
+// padding — which travels with the copy — puts the four groups a warp reads from shared memory into different banks.
+// 0 = row-major (the per-layer GEMM path, and every array when the fused dgrad kernel does not cover the field).
+constexpr int WS_ACT_LAYOUT = 6;          // index in ws.counters
+constexpr int ACT16_G8 = 16 * 8 + 8;      // floats of one 8-column group of a block
+__host__ __device__ __forceinline__ size_t act16_block_floats(int W) { return (size_t)(W / 8) * ACT16_G8; }
+__host__ __device__ __forceinline__ size_t act16_off(int64_t row, int col, int W) {
+  return (size_t)(row >> 4) * act16_block_floats(W) + (size_t)(col >> 3) * ACT16_G8 + (size_t)(((int)(row & 15) << 3) + (col & 7));
+}
+
 struct WgradFusedArgs {
   const float* g2; const float* h1; const float* g1;   // [M][128] row-major
   const float* x; int ldx; int kp;                     // [M][ldx], kp <= 152 data columns (multiple of 4)

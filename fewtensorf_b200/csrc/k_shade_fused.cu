@@ -151,6 +151,7 @@ struct DynamicSpec { static constexpr bool is_static = false; };
 // optional phase timeline of CTA 0 (debug aid, scripts/fused_timeline.py): dbg[role*512 + n]
 FTRF_SWITCH(long long*, g_fused_dbg, nullptr);
 FTRF_SWITCH(long long*, g_dgrad_dbg, nullptr);
+FTRF_SWITCH(int, g_act_perm, 1);           // ftrf_debug_set_act_perm (test build): 0 = saved activations stay row-major
 FTRF_SWITCH(int, g_dgrad_masks, 1);        // ftrf_debug_set_dgrad_masks (test build): 0 = the dgrad kernel reads h1 / h2 back
 #define FZ_T(role, n) do { if (dbg && blockIdx.x == 0 && (n) < 512) dbg[(role) * 512 + (n)] = clock64(); } while (0)
 
@@ -158,7 +159,8 @@ FTRF_SWITCH(int, g_dgrad_masks, 1);        // ftrf_debug_set_dgrad_masks (test b
 // ------------------------------------------------------------------------------------------ kernel
 template <class SS>
 __global__ void __launch_bounds__(FZ_THREADS, 1)
-shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg) {
+shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const FusedSpec fs, const float* __restrict__ wimg, long long* dbg,
+                       const int perm) {       // perm: save X / h1 / h2 in the 16-row block layout (act16_off), else row-major
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   float* a_ring = reinterpret_cast<float*>(smem_raw);                               // [A_STAGES][2 subs][hi, lo][4096]
   float* w_ring = a_ring + (size_t)FZ_A_STAGES * 4 * FZ_CHUNK_FLOATS;               // [W_STAGES][hi, lo][4096]
@@ -176,6 +178,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t n = min((int64_t)ws.counters[1], c.cap_app);
+  if (blockIdx.x == 0 && tid == 0 && c.save_for_backward) ws.counters[WS_ACT_LAYOUT] = perm;     // the layout travels with the data
   const int64_t npairs = (n + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
   if ((int64_t)blockIdx.x >= npairs) return;
   const int my_pairs = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);
@@ -267,7 +270,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         if (u & 1) {
           if (save && live) {
             const float w[8] = {xs[0], xs[1], xs[2], xs[3], v[0], v[1], v[2], v[3]};
-            st_global_v8(ws.a_x + row * ws.ldx + ch * 32 + (u - 1) * 4, w);
+            st_global_v8(ws.a_x + (perm ? act16_off(row, ch * 32 + (u - 1) * 4, ws.ldx) : (size_t)row * ws.ldx + ch * 32 + (u - 1) * 4), w);
           }
         } else {
           xs[0] = v[0]; xs[1] = v[1]; xs[2] = v[2]; xs[3] = v[3];
@@ -375,7 +378,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b1[j * 32 + i], 0.f);
         if (save && live) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h1 + row * FC + j * 32 + u * 8, acc + 8 * u);
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h1 + (perm ? act16_off(row, j * 32 + u * 8, FC) : (size_t)row * FC + j * 32 + u * 8), acc + 8 * u);
           sgn[(size_t)j * c.cap_app] = relu_sign_bits(acc);
         }
         tc::mbar_wait(a_empty + stg, ((ac / FZ_A_STAGES) & 1) ^ 1);
@@ -417,7 +420,7 @@ shade_fused_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const F
         for (int i = 0; i < 32; ++i) acc[i] = fmaxf(acc[i] + s_b2[j * 32 + i], 0.f);
         if (save && live) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h2 + row * FC + j * 32 + u * 8, acc + 8 * u);
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_h2 + (perm ? act16_off(row, j * 32 + u * 8, FC) : (size_t)row * FC + j * 32 + u * 8), acc + 8 * u);
           sgn[(size_t)(4 + j) * c.cap_app] = relu_sign_bits(acc);
         }
 #pragma unroll
@@ -1043,6 +1046,7 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
   const int64_t ntiles = (n + 127) / 128;
   if ((int64_t)blockIdx.x >= ntiles) return;
   const int my_tiles = (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const int perm = ws.counters[WS_ACT_LAYOUT];          // layout the forward saved in: g_h1 goes out the same way
 
   if (tid == 0) {
     for (int i = 0; i < BZ_GROUPS * BZ_A_STAGES; ++i) { tc::mbar_init(a_full + i, 4); tc::mbar_init(a_empty + i, 1); }
@@ -1167,7 +1171,7 @@ shade_fused_dgrad_kernel(const FtrfField f, const FtrfCall c, const Ws ws, const
         for (int i = 0; i < 32; ++i) acc[i] = ((hm[jj] >> i) & 1u) ? acc[i] : 0.f;
         if (live) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_gh1 + row * FC + j * 32 + u * 8, acc + 8 * u);
+          for (int u = 0; u < 4; ++u) st_global_v8(ws.a_gh1 + (perm ? act16_off(row, j * 32 + u * 8, FC) : (size_t)row * FC + j * 32 + u * 8), acc + 8 * u);
         }
         put_chunk(ac0 + 4 + j, acc);
       }
@@ -1467,11 +1471,13 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
     if (int e = check_launch("prep_weights")) return e;
   }
   const size_t smem = fused_fwd_smem();
+  // the block layout of the saved activations is only understood by the fused backward kernels: both must cover this field
+  const int perm = (g_act_perm && c.save_for_backward && shade_dgrad_is_fused(f, c, ws)) ? 1 : 0;
   int64_t pairs = (c.cap_app + FZ_PAIR_ROWS - 1) / FZ_PAIR_ROWS;
   int grid = (int)(pairs < FTRF_SMS ? pairs : FTRF_SMS);
   auto go = [&](auto kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, FZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_fused_dbg);
+    kern<<<grid, FZ_THREADS, smem, st>>>(f, c, ws, fs, img, g_fused_dbg, perm);
   };
   // shipped configurations (app_dim 27, pe 2/2/2 — configs/*.txt, config.yaml) get the unrolled build
   using SFea = StaticSpec<FTRF_SHADE_MLP_FEA, 27, 2, 2, 2>;
@@ -1507,6 +1513,11 @@ int launch_shade_fused(const FtrfField& f, const FtrfCall& c, const Ws& ws, cuda
 }  // namespace ftrf
 
 #ifdef FTRF_TEST_BUILD
+extern "C" int ftrf_debug_set_act_perm(int on) {
+  ftrf::g_act_perm = on;
+  return FTRF_OK;
+}
+
 extern "C" int ftrf_debug_set_dgrad_masks(int on) {
   ftrf::g_dgrad_masks = on;
   return FTRF_OK;

@@ -26,6 +26,7 @@ constexpr int WG_NGX_MAX = 48;            // 16-byte column groups of the X oper
 constexpr int WG_G_FLOATS = WG_KS * 128;  // one hi (or lo) tile of a 128-wide operand
 constexpr int WG_PROD_WARPS = 16;
 constexpr int WG_PROD = WG_PROD_WARPS * 32;
+constexpr int WG_G8 = ACT16_G8;                     // floats of one 8-column group of a raw stage (16 rows x 8 + padding)
 constexpr int WG_RAW_OPS = 2, WG_RAW_STAGES = 2;   // RAW build: operand stages (69.6 KB each) and raw stages (34.6 KB each); 1 + 4 measured slower
 constexpr int WG_L2_AHEAD = 0;                     // chunks the bulk-copy warp prefetches into L2 ahead of its copies
 constexpr int WG_THREADS = WG_PROD + 64;   // + the MMA-issuing warp and the bulk-copy warp
@@ -65,7 +66,10 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
   const int WG_NGX = a.ngt;
   const int WG_X_FLOATS = WG_KS * WG_NGX * 4;
   const int WG_STAGE_FLOATS = 2 * (3 * WG_G_FLOATS + WG_X_FLOATS);      // G2, H1, G1, X, each hi + lo
-  const int RAW_X = 3 * WG_G_FLOATS, RAW_GO = RAW_X + WG_KS * a.ldx, RAW_FLOATS = RAW_GO + WG_KS * 4;   // raw stage: h2 | h1 | g_h1 | X | go4
+  // raw stage: h2 | h1 | g_h1 | X | go4.  Block layout of the saved activations (perm): every 8-column group of the 16 rows is
+  // 512 contiguous bytes, copied to a 544-byte slot (WG_G8 floats) so that the four groups a warp reads sit in different banks
+  const int RAW_A = 16 * WG_G8, RAW_X = 3 * RAW_A, RAW_GO = RAW_X + ((a.ldx + 7) / 8) * WG_G8, RAW_FLOATS = RAW_GO + WG_KS * 4;
+  const bool perm = a.count != nullptr && a.count[WS_ACT_LAYOUT - 1] != 0;        // (count = ws.counters + 1)
   float* raw = ring + (size_t)NSTG * WG_STAGE_FLOATS;                  // [RS][RAW_FLOATS] (RAW only)
   uint64_t* bars = reinterpret_cast<uint64_t*>(raw + (RAW ? RS * (size_t)RAW_FLOATS : 0));
   uint64_t* full = bars;                      // [NSTG]  16 producer warps
@@ -131,9 +135,10 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
       for (int i = 0; i < 4; ++i) {
         const int64_t s = s0 + gku * 4 + i;
         const bool ok = s < M;
-        r[i] = ldg_early(a.g2 + s * 128 + gcol, ok);
-        r[4 + i] = ldg_early(a.h1 + s * 128 + gcol, ok);
-        r[8 + i] = ldg_early(a.g1 + s * 128 + gcol, ok);
+        const size_t o = perm ? act16_off(s, gcol, 128) : (size_t)s * 128 + gcol;
+        r[i] = ldg_early(a.g2 + o, ok);
+        r[4 + i] = ldg_early(a.h1 + o, ok);
+        r[8 + i] = ldg_early(a.g1 + o, ok);
       }
 #pragma unroll
       for (int q = 0; q < 2; ++q) {                       // X: kp columns x 4 units
@@ -142,7 +147,7 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int64_t s = s0 + ku * 4 + i;
-          r[12 + q * 4 + i] = ldg_early(a.x + s * a.ldx + col, id < xu && s < M);
+          r[12 + q * 4 + i] = ldg_early(a.x + (perm ? act16_off(s, col, a.ldx) : (size_t)s * a.ldx + col), id < xu && s < M);
         }
       }
     };
@@ -194,9 +199,10 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
         const int id = tid + WG_PROD * q;
         const int ku = id / a.kp, col = id - ku * a.kp;
         xrow[q] = id < xu ? ku * 4 : WG_KS;             // first sample row of the unit (WG_KS: no unit)
-        xsrc[q] = RAW_X + ku * 4 * a.ldx + col;
+        xsrc[q] = RAW_X + (perm ? (col >> 3) * WG_G8 + ku * 4 * 8 + (col & 7) : ku * 4 * a.ldx + col);
       }
-      const int gsrc = gku * 4 * 128 + gcol;
+      const int gsrc = perm ? (gcol >> 3) * WG_G8 + gku * 4 * 8 + (gcol & 7) : gku * 4 * 128 + gcol;
+      const int rstep = perm ? 8 : 128, xstep = perm ? 8 : a.ldx;      // floats between consecutive rows
       for (int j = 0; j < my_chunks; ++j) {
         const int rs = j % RS;
         const float* R = raw + (size_t)rs * RAW_FLOATS;
@@ -209,15 +215,15 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
         for (int i = 0; i < 4; ++i) {
           const int sl = gku * 4 + i;
           const bool ok = sl < nrow;
-          r[i] = ok ? R[gsrc + i * 128] : 0.f;
-          r[4 + i] = ok ? R[WG_G_FLOATS + gsrc + i * 128] : 0.f;
-          r[8 + i] = ok ? R[2 * WG_G_FLOATS + gsrc + i * 128] : 0.f;
+          r[i] = ok ? R[gsrc + i * rstep] : 0.f;
+          r[4 + i] = ok ? R[RAW_A + gsrc + i * rstep] : 0.f;
+          r[8 + i] = ok ? R[2 * RAW_A + gsrc + i * rstep] : 0.f;
           gor[i] = (ok && a.fold3) ? *reinterpret_cast<const float4*>(R + RAW_GO + sl * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int q = 0; q < 2; ++q) {                     // X: kp columns x 4 units
 #pragma unroll
-          for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] + i < nrow ? R[xsrc[q] + i * a.ldx] : 0.f;
+          for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] + i < nrow ? R[xsrc[q] + i * xstep] : 0.f;
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(raw_empty + rs);   // (release: this warp's reads of the stage are done)
@@ -261,11 +267,22 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
         const int64_t s0 = ((int64_t)blockIdx.x + (int64_t)j * gridDim.x) * WG_KS;
         const uint32_t rows = (uint32_t)min((int64_t)WG_KS, M - s0);
         tc::mbar_wait(raw_empty + rs, ((j / RS) & 1) ^ 1);
-        tc::mbar_expect_tx(raw_full + rs, rows * (uint32_t)(3 * 512 + a.ldx * 4 + (a.fold3 ? 16 : 0)));
-        tc::bulk_g2s(R, a.g2 + s0 * 128, rows * 512u, raw_full + rs);
-        tc::bulk_g2s(R + WG_G_FLOATS, a.h1 + s0 * 128, rows * 512u, raw_full + rs);
-        tc::bulk_g2s(R + 2 * WG_G_FLOATS, a.g1 + s0 * 128, rows * 512u, raw_full + rs);
-        tc::bulk_g2s(R + RAW_X, a.x + s0 * a.ldx, rows * (uint32_t)(a.ldx * 4), raw_full + rs);
+        if (perm) {
+          // whole 16-row blocks (the arrays are padded to them), padding included: the stage has the global layout
+          const uint32_t hb = (uint32_t)act16_block_floats(128) * 4, xb = (uint32_t)act16_block_floats(a.ldx) * 4;
+          const int64_t blk = s0 >> 4;
+          tc::mbar_expect_tx(raw_full + rs, 3 * hb + xb + (a.fold3 ? rows * 16u : 0u));
+          tc::bulk_g2s(R, a.g2 + blk * (hb / 4), hb, raw_full + rs);
+          tc::bulk_g2s(R + RAW_A, a.h1 + blk * (hb / 4), hb, raw_full + rs);
+          tc::bulk_g2s(R + 2 * RAW_A, a.g1 + blk * (hb / 4), hb, raw_full + rs);
+          tc::bulk_g2s(R + RAW_X, a.x + blk * (xb / 4), xb, raw_full + rs);
+        } else {
+          tc::mbar_expect_tx(raw_full + rs, rows * (uint32_t)(3 * 512 + a.ldx * 4 + (a.fold3 ? 16 : 0)));
+          tc::bulk_g2s(R, a.g2 + s0 * 128, rows * 512u, raw_full + rs);
+          tc::bulk_g2s(R + RAW_A, a.h1 + s0 * 128, rows * 512u, raw_full + rs);
+          tc::bulk_g2s(R + 2 * RAW_A, a.g1 + s0 * 128, rows * 512u, raw_full + rs);
+          tc::bulk_g2s(R + RAW_X, a.x + s0 * a.ldx, rows * (uint32_t)(a.ldx * 4), raw_full + rs);
+        }
         if (a.fold3) tc::bulk_g2s(R + RAW_GO, a.go4 + s0, rows * 16u, raw_full + rs);
       }
     }
@@ -376,7 +393,7 @@ int launch_wgrad_fused(const WgradFusedArgs& a_in, const FusedSpec& fs, float* g
   if (!(call && prep_ahead_take_scratch(*call)) &&
       cudaMemsetAsync(a.dw1i, 0, wgrad_fused_scratch_bytes(), st) != cudaSuccess) return check_launch("wgrad scratch memset");
   const size_t stage_b = (size_t)2 * (3 * WG_G_FLOATS + WG_KS * a.ngt * 4) * 4;
-  const size_t raw_b = (size_t)(3 * WG_G_FLOATS + WG_KS * a.ldx + WG_KS * 4) * 4;
+  const size_t raw_b = (size_t)(3 * 16 * WG_G8 + ((a.ldx + 7) / 8) * WG_G8 + WG_KS * 4) * 4;
   const bool use_raw = g_wgrad_raw && WG_RAW_OPS * stage_b + WG_RAW_STAGES * raw_b + 256 <= 227 * 1024 &&
                        (((uintptr_t)a.g2 | (uintptr_t)a.h1 | (uintptr_t)a.g1 | (uintptr_t)a.x | (uintptr_t)a.go4) & 15) == 0;
   const size_t smem = use_raw ? WG_RAW_OPS * stage_b + WG_RAW_STAGES * raw_b + 24 * 8 : (size_t)WG_STAGES * stage_b + 24 * 8;

@@ -819,6 +819,18 @@ class TensorBase(nn.Module):
         nbytes = count * torch.empty((), dtype=dtype).element_size()
         return st.ws[o:o + nbytes].view(dtype)
 
+    def saved_activation(self, st: _CallState, name: str, cols: int) -> torch.Tensor:
+        """[n_valid, cols] row-major copy of an activation array the MLP kernels saved (A_X, A_H1, A_H2, A_GH1), whatever
+        layout they chose: counters[6] == 1 means padded blocks of 16 rows with the 8-column groups outermost inside a block
+        (csrc/fused.cuh: act16_off).  Test / diagnostics aid."""
+        n = st.n_valid
+        layout = int(self.workspace_section(st, "COUNTERS", torch.int32, 8)[6])
+        if layout == 0:
+            return self.workspace_section(st, name, torch.float32, n * cols).view(n, cols).clone()
+        nb = (n + 15) // 16                      # blocks of 16 rows, every 8-column group padded from 16 to 17 rows of 8 floats
+        blk = self.workspace_section(st, name, torch.float32, nb * (cols // 8) * 17 * 8).view(nb, cols // 8, 17, 8)
+        return blk[:, :, :16, :].permute(0, 2, 1, 3).reshape(nb * 16, cols)[:n].clone()
+
     def _run_backward(self, st: _CallState, g_rgb: torch.Tensor, grad_views, part: int = 0, prepared: bool = False) -> None:
         """part 0: the whole backward; 1 / 2: its two halves (ftrf_backward_part), 2 reuses 1's arguments.
         prepared: st.bfield was already marshalled for these gradient views (during the forward)."""

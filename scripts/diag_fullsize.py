@@ -43,7 +43,7 @@ for path in (2, 1, 0):
         import ctypes as C
         ldx = (st.field.in_dim + 1 + 7) // 8 * 8
         sec = lambda name, cols: m.workspace_section(st, name, torch.float32, n * cols).view(n, cols).double()
-        X, h1, h2 = sec("A_X", ldx), sec("A_H1", 128), sec("A_H2", 128)
+        X, h1, h2 = (m.saved_activation(st, nm, cc).double() for nm, cc in (("A_X", ldx), ("A_H1", 128), ("A_H2", 128)))
         # W1 in the kernels' internal column order is not needed: compare h2 from h1, and h1 sign statistics
         W2, b2 = m.renderModule.mlp[2].weight.double(), m.renderModule.mlp[2].bias.double()
         z2 = h1 @ W2.t() + b2

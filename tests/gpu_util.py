@@ -116,7 +116,7 @@ def relu_decisions_in_oracle_order(model, st, app_mask):
     assert bool(app_mask[ray, idx].all()) and int(app_mask.sum()) == n, "shaded sets differ: decisions cannot be aligned"
     out = []
     for name in ("A_H1", "A_H2"):
-        h = model.workspace_section(st, name, torch.float32, n * 128).view(n, 128).cpu()
+        h = model.saved_activation(st, name, 128).cpu()
         m = torch.zeros(n, 128, dtype=torch.bool)
         m[pos] = h > 0
         out.append(m)

@@ -40,7 +40,7 @@ def _mlp_grads_fp64(model, st, internal):
     offs = (C.c_int64 * _abi.WS_COUNT)()
     _abi.lib.ftrf_workspace_layout(C.byref(st.field), C.byref(st.call), offs)
     ldx = (st.field.in_dim + 1 + 7) // 8 * 8
-    X, h1, h2 = sec("A_X", ldx), sec("A_H1", 128), sec("A_H2", 128)
+    X, h1, h2 = (model.saved_activation(st, nm, cc).double() for nm, cc in (("A_X", ldx), ("A_H1", 128), ("A_H2", 128)))
     rgb, grgb = sec("A_RGB", 3), sec("A_GRGB", 3)
     m = model.renderModule.mlp
     W2, W3 = m[2].weight.double(), m[4].weight.double()
@@ -74,7 +74,7 @@ def _mlp_grads_fp64(model, st, internal):
     h2_ref = torch.relu(h1_ref @ W2.t() + m[2].bias.double())
     rgb_ref = torch.sigmoid(h2_ref @ W3.t() + m[4].bias.double())
     gx_ref = g_h1 @ W1i
-    chain = {"h1": (h1, h1_ref), "h2": (h2, h2_ref), "rgb": (rgb, rgb_ref), "g_h1": (sec("A_GH1", 128), g_h1)}
+    chain = {"h1": (h1, h1_ref), "h2": (h2, h2_ref), "rgb": (rgb, rgb_ref), "g_h1": (model.saved_activation(st, "A_GH1", 128).double(), g_h1)}
     if internal is None:
         chain["g_x"] = (sec("A_GX", ldx)[:, :gx_ref.shape[1]], gx_ref)
     else:
