@@ -38,7 +38,7 @@ GRID = 300
 MASK_GRID = 256
 RAYS_PER_GPU = 4096
 N_SAMPLES = 1039          # int(norm([300]*3) / 0.5), utils.py:124-125 / train.py:208
-SPIN_CYCLES = 1_000_000   # ~0.5 ms at 1.9 GHz: spin kernel in front of every device-timed step (see timed()); longer than the
+SPIN_CYCLES = int(os.environ.get("FTRF_BENCH_SPIN", 1_000_000))   # ~0.5 ms at 1.9 GHz: spin kernel in front of every device-timed step (see timed()); longer than the
                           # host needs to enqueue a step even with eight ranks sharing the box's cores
 CPU_SAMPLE_RAYS = 2048    # bounded CPU sample (same workload, first rays of the batch); also the parity sample
 CPU_1T_RAYS = 256         # single-thread figure (script.sh:8-17 runs the reference with OMP_NUM_THREADS=1)
@@ -478,8 +478,8 @@ def workload_config(n_gpus):
                         + (" + all-reduce of the gradient buffer" if n_gpus > 1 else ""),
             "rays_per_gpu": RAYS_PER_GPU, "n_samples": N_SAMPLES, "grid": GRID, "mask_grid": MASK_GRID,
             "l2": "flushed between timed steps (512 MiB write)",
-            "queue": "a 0.5 ms spin kernel precedes every device-timed step so its launches are queued ahead of it "
-                     "(device time without host launch bubbles; e2e includes them)",
+            "queue": "steps are enqueued as the host gets to them (no pre-queue spin kernel in front of the timed steps: host "
+                     "launch bubbles, if any, are inside the headline; `with_prequeue` is the same measurement behind one)",
             "parallelism": f"ray-sharded x{n_gpus}"}
 
 
@@ -649,6 +649,8 @@ def run_gpu(args):
         step()
     barrier()
 
+    align = torch.zeros(1, device=dev)
+
     def timed(k, profile, fn=step, prequeue=True):
         lib.ftrf_profile_enable(1 if profile else 0)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
@@ -660,6 +662,10 @@ def run_gpu(args):
             flush.zero_()                       # evict L2 between timed steps (untimed)
             if prequeue:
                 torch.cuda._sleep(SPIN_CYCLES)  # hold the GPU ~0.5 ms (untimed) so the step's launches are queued
+                if world > 1:                   # ... and line the ranks up behind it on the DEVICE (a tiny all-reduce): every
+                    dist.all_reduce(align)      # rank's step then starts at the same instant, as it does behind the previous
+                                                # step's exchange in a training loop (without it the ranks start one host-launch
+                                                # skew apart and the early ones wait that long inside their exchange kernel)
             ev[i][0].record()                   # ahead of it: the device time of a step excludes host launch bubbles
             last = fn()
             ev[i][1].record()
@@ -675,12 +681,12 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = lib.ftrf_launch_count()
-    total_ms, _, last = timed(args.steps, False)
+    total_ms, _, last = timed(args.steps, False, prequeue=False)     # the headline: no spin kernel in front of the steps
     launches = int(lib.ftrf_launch_count() - launches0)
     clocks = sampler.summary()
     _, stage_ms, _ = timed(min(args.steps, 20), True)
     k_plain = min(args.steps, 20)
-    plain_ms, _, _ = timed(k_plain, False, prequeue=False)   # the same steps WITHOUT the spin kernel: host launch bubbles included
+    plain_ms, _, _ = timed(k_plain, False, prequeue=True)    # the same steps BEHIND a spin kernel: their launches are queued ahead, no host bubbles
     tp = torch.tensor([plain_ms], device=dev)
     if world > 1:
         dist.all_reduce(tp, op=dist.ReduceOp.MAX)
@@ -739,7 +745,7 @@ def run_gpu(args):
         big, bigt = big_h.to(dev), bigt_h.to(dev)
         for _ in range(3):
             step(big, bigt)
-        ms5, _, _ = timed(10, False, lambda: step(big, bigt))
+        ms5, _, _ = timed(10, False, lambda: step(big, bigt), prequeue=False)
         t5 = torch.tensor([ms5 / 10], device=dev)
         dist.all_reduce(t5, op=dist.ReduceOp.MAX)
         multi["config5_8192_rays_per_gpu"] = {"ms_per_step": round(float(t5), 4), "global_batch": 8192 * world,
@@ -806,8 +812,10 @@ def run_gpu(args):
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": dict(workload_config(world), **({"allreduce": (sg.describe() if sg is not None else "nccl")} if world > 1 else {})),
            "clocks": clocks,
-           "without_prequeue": {"ms_per_step": plain_ms, "value": RAYS_PER_GPU * world / (plain_ms * 1e-3), "unit": "rays/s",
-                                "note": "the same device-timed steps without the spin kernel in front: host launch bubbles included"},
+           "with_prequeue": {"ms_per_step": plain_ms, "value": RAYS_PER_GPU * world / (plain_ms * 1e-3), "unit": "rays/s",
+                             "note": "the same device-timed steps, each behind an untimed 0.5 ms spin kernel (+ a device-side rank alignment at N > 1) "
+                                     "so that its launches are queued ahead of it; at 8 GPUs this is SLOWER than the headline (0.78 vs 0.74 ms), "
+                                     "at 1 GPU the two agree within 1-2 %"},
            "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32,
                    "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing)",
                    "train_step_api_value": e2e_fused_rps},
