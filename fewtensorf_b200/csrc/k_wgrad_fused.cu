@@ -211,19 +211,34 @@ wgrad_fused_kernel(const WgradFusedArgs a) {
         float (&r)[20] = v[0];
         float4 gor[4];
         tc::mbar_wait(raw_full + rs, (j / RS) & 1);
+        if (nrow == WG_KS) {                              // every chunk but the last: no per-row masking
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int sl = gku * 4 + i;
-          const bool ok = sl < nrow;
-          r[i] = ok ? R[gsrc + i * rstep] : 0.f;
-          r[4 + i] = ok ? R[RAW_A + gsrc + i * rstep] : 0.f;
-          r[8 + i] = ok ? R[2 * RAW_A + gsrc + i * rstep] : 0.f;
-          gor[i] = (ok && a.fold3) ? *reinterpret_cast<const float4*>(R + RAW_GO + sl * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+          for (int i = 0; i < 4; ++i) {
+            r[i] = R[gsrc + i * rstep];
+            r[4 + i] = R[RAW_A + gsrc + i * rstep];
+            r[8 + i] = R[2 * RAW_A + gsrc + i * rstep];
+            gor[i] = a.fold3 ? *reinterpret_cast<const float4*>(R + RAW_GO + (gku * 4 + i) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {                     // X: kp columns x 4 units
+          for (int q = 0; q < 2; ++q) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] + i < nrow ? R[xsrc[q] + i * xstep] : 0.f;
+            for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] < WG_KS ? R[xsrc[q] + i * xstep] : 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int sl = gku * 4 + i;
+            const bool ok = sl < nrow;
+            r[i] = ok ? R[gsrc + i * rstep] : 0.f;
+            r[4 + i] = ok ? R[RAW_A + gsrc + i * rstep] : 0.f;
+            r[8 + i] = ok ? R[2 * RAW_A + gsrc + i * rstep] : 0.f;
+            gor[i] = (ok && a.fold3) ? *reinterpret_cast<const float4*>(R + RAW_GO + sl * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {                     // X: kp columns x 4 units
+#pragma unroll
+            for (int i = 0; i < 4; ++i) r[12 + q * 4 + i] = xrow[q] + i < nrow ? R[xsrc[q] + i * xstep] : 0.f;
+          }
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(raw_empty + rs);   // (release: this warp's reads of the stage are done)
