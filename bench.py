@@ -522,12 +522,13 @@ STAGE_MODEL = {
     "density_fwd":     ("l2", {"vd": 1152.0}, {}),
     "integrate_fwd":   ("hbm", {"vd": 12.0, "va": 4.0}, {}),
     "app_fwd":         ("l2", {"va": 3456.0}, {}),
-    "shade_fwd":       ("tensor", {"va": 3 * 2.0 * (IN_DIM * 128 + 128 * 128)}, {"va": 108.0 + 608 + 512 + 512 + 12}),
+    # DRAM side of the MLP stages: activations are saved in padded 16-row blocks (17/16 of their size) + 32 B of sign masks
+    "shade_fwd":       ("tensor", {"va": 3 * 2.0 * (IN_DIM * 128 + 128 * 128)}, {"va": 108.0 + 646 + 544 + 544 + 32 + 12}),
     "composite":       ("hbm", {"vd": 8.0, "va": 12.0, "ray": 16.0}, {}),
     "integrate_bwd":   ("hbm", {"vd": 24.0, "va": 24.0}, {}),
     "shade_bwd_out":   ("hbm", {"va": 512.0 + 512 + 24}, {}),
-    "shade_bwd_dgrad": ("tensor", {"va": 3 * 2.0 * (128 * 128 + 128 * IN_DIM)}, {"va": 512.0 * 3 + 108 + 108}),
-    "shade_wgrad":     ("tensor", {"va": 3 * 2.0 * (128 * 128 + 128 * (IN_DIM + 1))}, {"va": 512.0 * 3 + 608}),
+    "shade_bwd_dgrad": ("tensor", {"va": 3 * 2.0 * (128 * 128 + 128 * IN_DIM)}, {"va": 32.0 + 24 + 108 + 544 + 108 + 16}),
+    "shade_wgrad":     ("tensor", {"va": 3 * 2.0 * (128 * 128 + 128 * (IN_DIM + 1))}, {"va": 544.0 * 3 + 646 + 16}),
     "shade_wgrad1_unfused": ("tensor", {"va": 0.0}, {}),
     "app_bwd":         ("l2rw", {"va": 3456.0}, {}),        # taps re-read + as many bytes of gradient reduced
     "density_bwd":     ("l2rw", {"vd": 1152.0}, {}),

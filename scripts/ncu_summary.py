@@ -48,7 +48,7 @@ def raw(path):
 
 
 STAGE_OF = {'march_kernel': 'march', 'density_fwd_kernel': 'density_fwd', 'integrate_fwd_kernel': 'integrate_fwd',
-            'app_fwd_tc_kernel': 'app_fwd', 'app_fwd_kernel': 'app_fwd', 'prep_weights_kernel': 'shade_fwd',
+            'app_fwd_ws_kernel': 'app_fwd', 'app_fwd_tc_kernel': 'app_fwd', 'app_fwd_kernel': 'app_fwd', 'prep_weights_kernel': 'shade_fwd',
             'shade_fused_fwd_kernel': 'shade_fwd', 'composite_kernel': 'composite', 'integrate_bwd_kernel': 'integrate_bwd',
             'layer3_bwd_kernel': 'shade_bwd_out', 'prep_weights_bwd_kernel': 'shade_bwd_dgrad',
             'shade_fused_dgrad_kernel': 'shade_bwd_dgrad', 'wgrad_fused_kernel': 'shade_wgrad',
