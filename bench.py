@@ -177,24 +177,28 @@ class ClockSampler(threading.Thread):
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
+    def __init__(self, index, enabled=True):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.proc, self.enabled = index, [], None, enabled
 
     def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
+        # ONE long-lived nvidia-smi in loop mode (the recipe's form): a process per sample, on every rank, measurably disturbed
+        # the first timed loop of an 8-rank run
+        if not self.enabled:
+            return
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                parts = [p.strip() for p in line.strip().split(",")]
                 if len(parts) >= 6:
                     self.rows.append(parts)
-            except Exception:
-                pass
-            time.sleep(0.05)
+        except Exception:
+            pass
 
     def summary(self):
-        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.terminate()
         self.join(timeout=6)
         sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -679,8 +683,9 @@ def run_gpu(args):
         lib.ftrf_profile_enable(0)
         return sum(a.elapsed_time(b) for a, b in ev), stage, last
 
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, enabled=(rank == 0))      # rank 0's GPU speaks for the box (same clocks policy on all)
     sampler.start()
+    time.sleep(0.3)                                         # nvidia-smi is up before the timed region starts
     launches0 = lib.ftrf_launch_count()
     total_ms, _, last = timed(args.steps, False, prequeue=False)     # the headline: no spin kernel in front of the steps
     launches = int(lib.ftrf_launch_count() - launches0)

@@ -36,10 +36,16 @@ integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
   const int warp = threadIdx.x >> 5, lane = lane_id();
   const int chunks = (c.n_samples + 31) >> 5;
   uint32_t* bal = s_shade + warp * chunks;
+  __shared__ int s_cnt[INT_WARPS], s_base[INT_WARPS];
   const int64_t stride = (int64_t)gridDim.x * INT_WARPS;
-  for (int64_t r = (int64_t)blockIdx.x * INT_WARPS + warp; r < c.n_rays; r += stride) {
-    const int off = ws.ray_off[r], cnt = ws.ray_cnt[r];
-    Ray ray = load_ray_ws(f, c, ws, r);
+  // (the trip count is the same for every warp of the CTA: the shaded-list space of its rays is allocated with ONE atomic
+  // per CTA and pass — an atomicAdd per ray on the one cursor serialises in L2 at ~3.7 ns each, which for the 4096 rays
+  // of a training batch was the whole 15 us of this kernel)
+  for (int64_t r0 = (int64_t)blockIdx.x * INT_WARPS; r0 < c.n_rays; r0 += stride) {
+    const int64_t r = r0 + warp;
+    const bool have = r < c.n_rays;
+    const int off = have ? ws.ray_off[r] : 0, cnt = have ? ws.ray_cnt[r] : 0;
+    Ray ray = load_ray_ws(f, c, ws, have ? r : r0);
     const float dnorm = ray_dnorm(c, ray);
     float carry = 1.f, acc = 0.f, depth = 0.f;
     int n_shade = 0;
@@ -81,10 +87,18 @@ integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
         depth = fmaf(w, z, depth);
       }
     }
-    int base = 0;
-    if (lane == 0 && n_shade) base = atomicAdd(ws.counters + 1, n_shade);
-    base = __shfl_sync(FULL_MASK, base, 0);
-    __syncwarp();
+    if (lane == 0) s_cnt[warp] = n_shade;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+#pragma unroll
+      for (int w = 0; w < INT_WARPS; ++w) { s_base[w] = tot; tot += s_cnt[w]; }
+      const int b0 = tot ? atomicAdd(ws.counters + 1, tot) : 0;
+#pragma unroll
+      for (int w = 0; w < INT_WARPS; ++w) s_base[w] += b0;
+    }
+    __syncthreads();
+    int base = s_base[warp];
     for (int j0 = 0; j0 < cnt; j0 += 32) {
       const int j = j0 + lane;
       const uint32_t b = bal[j0 >> 5];
@@ -105,7 +119,7 @@ integrate_fwd_kernel(const FtrfField f, const FtrfCall c, const Ws ws) {
       acc += __shfl_xor_sync(FULL_MASK, acc, d);
       depth += __shfl_xor_sync(FULL_MASK, depth, d);
     }
-    if (lane == 0) {
+    if (lane == 0 && have) {
       ws.acc[r] = acc;
       float last = __ldg(c.rays + r * c.ray_cols + (c.ray_cols - 1));     // rays_chunk[..., -1], :388
       c.depth_map[r] = depth + (1.f - acc) * last;
