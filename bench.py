@@ -681,6 +681,8 @@ def run_gpu(args):
                     stage[s] += max(buf[s], 0.0) / k
         barrier()
         lib.ftrf_profile_enable(0)
+        if os.environ.get("FTRF_BENCH_TRACE") and rank == 0:          # per-step times of this loop (diagnostics)
+            print("trace", "prequeue" if prequeue else "plain", [round(a.elapsed_time(b), 3) for a, b in ev], file=sys.stderr, flush=True)
         return sum(a.elapsed_time(b) for a, b in ev), stage, last
 
     sampler = ClockSampler(local, enabled=(rank == 0))      # rank 0's GPU speaks for the box (same clocks policy on all)
