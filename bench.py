@@ -637,10 +637,19 @@ def run_gpu(args):
         else:
             dist.all_reduce(model._gradbuf)
 
-    def step(r=rays, t=target):
+    # The device-timed loops use train_step(wait="counters"): the call returns once the sample counts are final (behind the
+    # integration stage) and the host enqueues the next step while this one runs; `with_host_wait_per_step` in the JSON
+    # line is the same loop with the host waiting for the end of every step.  The end-to-end train_step figure replays the
+    # step's captured CUDA graph (one launch from the host) unless --no-graph.
+    wait_mode = "step" if args.wait_step else "counters"
+    use_graph = not args.no_graph and (world == 1 or sg is not None)
+
+    def step(r=rays, t=target, graph=False, wait=None):
+        wait = wait_mode if wait is None else wait
         if sg is not None:          # the exchange is enqueued inside the step, right behind the backward kernels
-            return model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world, allreduce=sg)
-        loss, nv = model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world)
+            return model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world, allreduce=sg, graph=graph, wait=wait)
+        loss, nv = model.train_step(r, t, None, white_bg=True, N_samples=N_SAMPLES, grad_scale=inv_world, graph=graph,
+                                    wait=(wait if world == 1 else "step"))
         if world > 1:
             reduce_grads()
         return loss, nv
@@ -691,8 +700,20 @@ def run_gpu(args):
     launches0 = lib.ftrf_launch_count()
     total_ms, _, last = timed(args.steps, False, prequeue=False)     # the headline: no spin kernel in front of the steps
     launches = int(lib.ftrf_launch_count() - launches0)
+    overflowed = model.check_steps()                        # N > 1, wait="counters": steps that ran with an overflowed list anywhere
+    if overflowed:                                          # (capacities have grown since) — measure again, once
+        launches0 = lib.ftrf_launch_count()
+        total_ms, _, last = timed(args.steps, False, prequeue=False)
+        launches = int(lib.ftrf_launch_count() - launches0)
+        overflowed = model.check_steps() - overflowed
     clocks = sampler.summary()
     _, stage_ms, _ = timed(min(args.steps, 20), True)
+    k_wait = min(args.steps, 20)                          # the same steps with the host waiting for the end of each
+    waited_ms, _, _ = timed(k_wait, False, fn=lambda: step(wait="step"), prequeue=False)
+    tw = torch.tensor([waited_ms], device=dev)
+    if world > 1:
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+    waited_ms = float(tw) / k_wait
     k_plain = min(args.steps, 20)
     plain_ms, _, _ = timed(k_plain, False, prequeue=True)    # the same steps BEHIND a spin kernel: their launches are queued ahead, no host bubbles
     tp = torch.tensor([plain_ms], device=dev)
@@ -724,9 +745,12 @@ def run_gpu(args):
         return loss.item()
 
     def e2e_fused():
+        if use_graph:                      # host tensors go straight into the captured step's input buffers
+            loss, nv = step(rays_p, target_p, graph=True)
+            return loss.item()
         r = rays_p.to(dev, non_blocking=True)
         tg = target_p.to(dev, non_blocking=True)
-        loss, nv = step(r, tg)
+        loss, nv = step(r, tg, wait="step")
         return loss.item()
 
     def wall(fn):
@@ -824,11 +848,22 @@ def run_gpu(args):
                              "note": "the same device-timed steps, each behind an untimed 0.5 ms spin kernel (+ a device-side rank alignment at N > 1) "
                                      "so that its launches are queued ahead of it; at 8 GPUs this is SLOWER than the headline (0.78 vs 0.74 ms), "
                                      "at 1 GPU the two agree within 1-2 %"},
-           "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 9 * 4, "d2h_bytes_per_step": 4 + 32,
-                   "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing)",
-                   "train_step_api_value": e2e_fused_rps},
+           "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 10 * 4, "d2h_bytes_per_step": 4 + 32,
+                   "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing); h2d = rays, targets "
+                          "and the step's jitter (drawn on the host like the reference's)",
+                   "train_step_api_value": e2e_fused_rps,
+                   "train_step_api": "model.train_step(pinned host rays, targets" + (", graph=True)" if use_graph else ")") + " + loss.item()"},
            "gpu_launches": launches, "roofline": roof, "stages": stages,
            "samples": {"valid_per_step": vd, "shaded_per_step": va, "loss": float(last[0])}}
+    out["host_wait"] = {"mode": wait_mode, "overflowed_steps": overflowed,
+                        "note": "train_step(wait='counters'): the call returns once the step's sample counts and overflow flags are "
+                                "final (behind the integration stage); the next step is enqueued while this one runs"}
+    out["with_host_wait_per_step"] = {"ms_per_step": waited_ms, "value": RAYS_PER_GPU * world / (waited_ms * 1e-3), "unit": "rays/s",
+                                      "note": "the same steps with the host waiting for the end of every step (train_step(wait='step')): the end "
+                                              "event then sits behind the host's wake-up, ~45 us after the last kernel"}
+    if use_graph:
+        out["step_graph"] = dict(model.step_graph_info(), note="e2e.train_step_api_value replays the step's captured launch sequence "
+                                 "(same kernels and arguments as call by call; jitter drawn per step)")
     if cpu:
         out["cpu_baseline"] = cpu
         out["cpu_baseline_1thread"] = cpu1
@@ -892,6 +927,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity legs")
+    ap.add_argument("--no-graph", action="store_true", help="end-to-end train_step figure: enqueue the step call by call instead of replaying its captured CUDA graph")
+    ap.add_argument("--wait-step", action="store_true", help="device-timed loops: the host waits for the end of every step (train_step(wait='step'))")
     ap.add_argument("--no-render", action="store_true", help="skip the 800x800 render leg and the side legs")
     args = ap.parse_args()
     if args.impl == "reference":

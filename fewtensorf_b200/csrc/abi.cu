@@ -220,6 +220,7 @@ extern "C" const char* ftrf_profile_stage_name(int stage) {
 }
 
 extern "C" unsigned long long ftrf_launch_count(void) { return ftrf::g_launches.load(std::memory_order_relaxed); }
+extern "C" void ftrf_launch_count_add(long long delta) { ftrf::g_launches.fetch_add((unsigned long long)delta, std::memory_order_relaxed); }
 extern "C" int ftrf_abi_version(void) { return FTRF_ABI_VERSION; }
 extern "C" const char* ftrf_last_error(void) { return g_err; }
 

@@ -297,6 +297,12 @@ class _Workspace:
         return self.buf
 
 
+class _StepGraph:
+    """One captured training step (train_step(graph=True)): the graph, the call state it was captured with and the
+    buffers its nodes point at."""
+    __slots__ = ("graph", "st", "loss", "loss_pin", "g_rgb", "jitter", "launches", "keep")
+
+
 class _CallState:
     """Everything backward needs from one forward call."""
     __slots__ = ("field", "call", "ws", "ws_bytes", "keep", "n_valid", "n_samples", "offsets", "wsobj", "mask", "bfield", "pre_gen", "zeroing", "gradbuf")
@@ -631,12 +637,7 @@ class TensorBase(nn.Module):
         pointers, the alphaMask and the derived constants, so it is cached on exactly those.
         `params`: the caller's `_all_params()` list (saves fetching it again on the hot path)."""
         if mask is None:
-            # every input of _build_field: parameter pointers, mask / derived-constant serials and the plain
-            # attributes a caller may change between calls
-            key = (tuple(p.data_ptr() for p in (params if params is not None else self._all_params())), self._mask_serial(), self._host["serial"],
-                   self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr(),
-                   bool(self.use_coarse_mask), float(self.near_far[0]), float(self.near_far[1]),
-                   float(self.distance_scale), float(self.density_shift), self.fea2denseAct, self.shadingMode)
+            key = self._field_key(grad_views, params)
             cache = self.__dict__.setdefault("_field_cache", {})
             f = cache.get(key)
             if f is None:
@@ -645,6 +646,14 @@ class TensorBase(nn.Module):
                 f = cache[key] = self._build_field(None, grad_views)
             return f
         return self._build_field(mask, grad_views)
+
+    def _field_key(self, grad_views=None, params=None):
+        """Every input of _build_field without FreeNeRF masks: parameter pointers, mask / derived-constant serials and
+        the plain attributes a caller may change between calls."""
+        return (tuple(p.data_ptr() for p in (params if params is not None else self._all_params())), self._mask_serial(), self._host["serial"],
+                self.rayMarch_weight_thres, 0 if grad_views is None else grad_views[0].data_ptr(),
+                bool(self.use_coarse_mask), float(self.near_far[0]), float(self.near_far[1]),
+                float(self.distance_scale), float(self.density_shift), self.fea2denseAct, self.shadingMode)
 
     def _mask_serial(self) -> int:
         if self.alphaMask is None:
@@ -845,36 +854,35 @@ class TensorBase(nn.Module):
               "backward")
 
     # ------------------------------------------------------------------ the hot path
-    def _draw_rng(self, n_rays, S, is_train, ndc_ray, white_bg, device):
-        """Host RNG draws in the reference's order and from the same (CPU) generator:
-        jitter (tensorBase.py:183 / :201) first, then the background coin (:380)."""
-        jitter = None
+    def _draw_rng_host(self, n_rays, S, is_train, ndc_ray, white_bg):
+        """Host RNG draws in the reference's order and from the same (CPU) generator: jitter (tensorBase.py:183 / :201)
+        first, then the background coin (:380).  Returns (jitter in the persistent pinned staging buffer or None,
+        add_bg); every call ends with a stream sync before the next draw can overwrite the buffer."""
+        def staging(n):
+            pin = getattr(self, "_jitter_pin", None)
+            if pin is None or pin.numel() < n:
+                pin = self._jitter_pin = torch.empty(max(n, 1 << 16), dtype=torch.float32).pin_memory()
+            return pin[:n]
         if ndc_ray:
             near, far = self.near_far
             z = torch.linspace(near, far, S).unsqueeze(0)
             if is_train:
                 z = z + torch.rand_like(z) * ((far - near) / S)
-            jitter = z.reshape(-1)
-        elif is_train:
+            add_bg = bool(white_bg or (is_train and bool(torch.rand((1,)) < 0.5)))
+            pin = staging(z.numel())
+            pin.copy_(z.reshape(-1))
+            return pin, add_bg
+        if is_train:
             # tensorBase.py:201 draws torch.rand(n_rays, 1): the same n_rays values of the CPU generator, written
             # straight into the pinned staging buffer
-            pin = getattr(self, "_jitter_pin", None)
-            if pin is None or pin.numel() < n_rays:
-                pin = self._jitter_pin = torch.empty(max(n_rays, 1 << 16), dtype=torch.float32).pin_memory()
-            torch.rand(n_rays, out=pin[:n_rays])
-            add_bg = bool(white_bg or bool(torch.rand((1,)) < 0.5))
-            return pin[:n_rays].to(device, non_blocking=True), add_bg
-        add_bg = bool(white_bg or (is_train and bool(torch.rand((1,)) < 0.5)))
-        if jitter is not None:
-            # staged through a persistent pinned buffer; every call ends with a stream sync before the
-            # next draw can overwrite it
-            n = jitter.numel()
-            pin = getattr(self, "_jitter_pin", None)
-            if pin is None or pin.numel() < n:
-                pin = self._jitter_pin = torch.empty(max(n, 1 << 16), dtype=torch.float32).pin_memory()
-            pin[:n].copy_(jitter)
-            jitter = pin[:n].to(device, non_blocking=True)
-        return jitter, add_bg
+            pin = staging(n_rays)
+            torch.rand(n_rays, out=pin)
+            return pin, bool(white_bg or bool(torch.rand((1,)) < 0.5))
+        return None, bool(white_bg)
+
+    def _draw_rng(self, n_rays, S, is_train, ndc_ray, white_bg, device):
+        pin, add_bg = self._draw_rng_host(n_rays, S, is_train, ndc_ray, white_bg)
+        return (None if pin is None else pin.to(device, non_blocking=True)), add_bg
 
     @_on_device
     def forward(self, rays_chunk, mask, white_bg=True, is_train=False, ndc_ray=False, N_samples=-1):
@@ -904,7 +912,7 @@ class TensorBase(nn.Module):
 
     @_on_device
     def train_step(self, rays, rgb_target, mask=None, white_bg=True, ndc_ray=False, N_samples=-1, grad_scale=1.0,
-                   allreduce=False, group=None):
+                   allreduce=False, group=None, graph=False, wait="step"):
         """Fused training step without the autograd engine: forward, MSE loss (train.py:338) and
         backward into the flat gradient buffer.  Sets `.grad` of every parameter to its view of that
         buffer and returns (loss 0-dim device tensor, num_valid_samples int).
@@ -916,9 +924,32 @@ class TensorBase(nn.Module):
         and the MLP (3/4 of the bytes) are final before the density backward and travel while it runs; the
         density gradients follow.  Pass grad_scale = n_local / n_global
         (dist.grad_scale).  A rank whose packed lists overflowed raises a flag that rides in the buffer's
-        tail slot, so every rank repeats the step together."""
+        tail slot, so every rank repeats the step together.
+
+        graph=True (no FreeNeRF masks, not the NCCL variant): the step's launch sequence is captured once in a CUDA
+        graph and replayed — same kernels, same arguments, one launch from the host instead of sixteen
+        (`_train_step_graphed`); the loss then comes back as a 0-dim CPU tensor (copied out inside the graph).
+
+        wait="counters" (not with graph=True or the NCCL variant): return as soon as the sample counts are final —
+        after the integration stage, about a sixth into the step — instead of after the last kernel.  The lists'
+        overflow flags are final at that point too, so on one GPU nothing changes but the moment the call returns: an
+        overflowed step is repeated inside the call as before, the loss and the gradients are ordinary stream-ordered
+        tensors, and the host enqueues the next step while this one runs (the wait at the end of a step otherwise
+        costs ~45 us of idle GPU per step: host wake-up and the launch latency of the next step).  With a gradient
+        exchange (`allreduce=<SymmetricGradients>`) a rank cannot repeat a step alone: the call never repeats, an
+        overflow anywhere raises the exchanged tail flag, and that is noticed one step late — `step_overflows`
+        counts such steps (their gradients are not to be used; the capacities have grown, the next step is clean) and
+        `check_steps()` waits for the stream and returns the count."""
         import torch.distributed as dist
+        if wait not in ("step", "counters"):
+            raise ValueError("train_step: wait is 'step' or 'counters'")
         S = int(N_samples) if N_samples > 0 else int(self.nSamples)
+        reduce_on = bool(allreduce) and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        reducer = allreduce if (reduce_on and hasattr(allreduce, "all_reduce")) else None     # dist.SymmetricGradients
+        if graph and mask is None and (reducer is not None or not reduce_on):
+            if rays.shape[0] * S > MAX_CANDIDATES:
+                raise RuntimeError("train_step: batch too large for one launch sequence; split the batch")
+            return self._train_step_graphed(rays, rgb_target, S, white_bg, ndc_ray, float(grad_scale), reducer)
         rays = rays.detach().to(device=self.device, dtype=torch.float32).contiguous()
         target = rgb_target.detach().to(device=self.device, dtype=torch.float32).contiguous()
         N = rays.shape[0]
@@ -928,61 +959,204 @@ class TensorBase(nn.Module):
         buf, views = self.grad_buffer()
         loss = torch.empty(1, dtype=torch.float32, device=rays.device)
         g_rgb = torch.empty(N, 3, dtype=torch.float32, device=rays.device)
-        reduce_on = bool(allreduce) and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
-        reducer = allreduce if (reduce_on and hasattr(allreduce, "all_reduce")) else None     # dist.SymmetricGradients
-        lo, hi = self._early_grad_span() if (reduce_on and reducer is None) else (0, 0)
-        while True:
-            # everything is enqueued back to back (the kernels read the sample counts from device memory);
-            # the single host sync comes at the end and only decides whether a list overflowed
-            self._zero_fork(buf.device)
-            self._zero_grad_buffer_async(buf)
-            st = self._launch_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
-            rgb = st.keep[2]
-            check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
-                                    _stream()), "mse_loss")
-            if grad_scale != 1.0:
-                g_rgb.mul_(grad_scale)
-            self._zero_join(buf.device)
-            if not reduce_on:
-                self._run_backward(st, g_rgb, views)
-                if self._finish_forward(st, whole_stream=True):
-                    break
-                continue
-            # this rank's overflow flag (final after the forward) rides in the tail slot: the backward's first kernel
-            # writes it there (FtrfCall.overflow_out)
-            st.call.overflow_out = buf.data_ptr() + (buf.numel() - GRAD_TAIL) * 4
-            if reducer is not None:
-                # the library's own exchange (NVLink peer loads / multimem over the regions that can hold a gradient),
-                # enqueued right behind the backward: the host's one wait of the step comes after it
-                self._run_backward(st, g_rgb, views)
-                reducer.all_reduce()
-                flag = self._tail_flag(buf)
+        if reducer is not None or not reduce_on:
+            st = self._step_until_clean(rays, target, jitter, add_bg, mask, S, ndc_ray, grad_scale, buf, views, loss, g_rgb, reducer,
+                                        early=(wait == "counters"))
+        else:
+            lo, hi = self._early_grad_span()
+            while True:
+                self._zero_fork(buf.device)
+                self._zero_grad_buffer_async(buf)
+                st = self._launch_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
+                rgb = st.keep[2]
+                check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
+                                        _stream()), "mse_loss")
+                if grad_scale != 1.0:
+                    g_rgb.mul_(grad_scale)
+                self._zero_join(buf.device)
+                # this rank's overflow flag (final after the forward) rides in the tail slot: the backward's first kernel
+                # writes it there (FtrfCall.overflow_out)
+                st.call.overflow_out = buf.data_ptr() + (buf.numel() - GRAD_TAIL) * 4
+                self._run_backward(st, g_rgb, views, part=1)
+                works = [dist.all_reduce(buf[lo:], group=group, async_op=True)]
+                self._run_backward(st, g_rgb, views, part=2)
+                works.append(dist.all_reduce(buf[:lo], group=group, async_op=True))
+                for w in works:
+                    w.wait()                      # stream-level: the current stream waits for the collectives
+                flag = self._tail_flag(buf)       # async copy; _finish_forward's sync completes it
                 ok = self._finish_forward(st, whole_stream=True)
                 if float(flag[0]) == 0.0 and ok:
                     break
-                continue
-            self._run_backward(st, g_rgb, views, part=1)
-            works = [dist.all_reduce(buf[lo:], group=group, async_op=True)]
-            self._run_backward(st, g_rgb, views, part=2)
-            works.append(dist.all_reduce(buf[:lo], group=group, async_op=True))
-            for w in works:
-                w.wait()                      # stream-level: the current stream waits for the collectives
-            flag = self._tail_flag(buf)       # async copy; _finish_forward's sync completes it
-            ok = self._finish_forward(st, whole_stream=True)
-            if float(flag[0]) == 0.0 and ok:
-                break
         self._grad_gen = self.__dict__.get("_grad_gen", 0) + 1     # invalidates a pending autograd call's pre-zero
         for p, v in zip(self._all_params(), views):
             if p.grad is not v:
                 p.grad = v
         return loss[0], st.n_valid
 
-    def _tail_flag(self, buf):
-        pin = getattr(self, "_tail_pin", None)
-        if pin is None:
-            pin = self._tail_pin = torch.zeros(1, dtype=torch.float32).pin_memory()
-        pin.copy_(buf[-GRAD_TAIL:-GRAD_TAIL + 1], non_blocking=True)
-        return pin
+    def _enqueue_step(self, rays, target, jitter, add_bg, mask, S, ndc_ray, grad_scale, buf, views, loss, g_rgb, tail_flag):
+        """Everything of one step enqueued back to back, no host wait (the kernels read the sample counts from device
+        memory): gradient-buffer memset beside the forward, forward, loss, backward.  tail_flag: this rank's overflow
+        flag (final after the forward) rides in the buffer's tail slot — the backward's first kernel writes it there
+        (FtrfCall.overflow_out) — so it travels in the exchange that follows."""
+        self._zero_fork(buf.device)
+        self._zero_grad_buffer_async(buf)
+        st = self._launch_forward(rays, jitter, mask, S, True, ndc_ray, add_bg, save=True)
+        rgb = st.keep[2]
+        check(lib.ftrf_mse_loss(rgb.data_ptr(), target.data_ptr(), rgb.numel(), loss.data_ptr(), g_rgb.data_ptr(),
+                                _stream()), "mse_loss")
+        if grad_scale != 1.0:
+            g_rgb.mul_(grad_scale)
+        self._zero_join(buf.device)
+        if tail_flag:
+            st.call.overflow_out = buf.data_ptr() + (buf.numel() - GRAD_TAIL) * 4
+        self._run_backward(st, g_rgb, views)
+        return st
+
+    def _step_until_clean(self, rays, target, jitter, add_bg, mask, S, ndc_ray, grad_scale, buf, views, loss, g_rgb, reducer,
+                          early=False):
+        """One step (and, with `reducer`, the library's own gradient exchange over NVLink enqueued right behind the
+        backward); the single host sync comes at the end and only decides whether a list overflowed — on this rank or,
+        through the exchanged tail flag, on any — in which case the step is repeated with larger lists.
+        early: the host waits for the counters' copy (behind the integration stage) instead of the end of the stream;
+        see train_step(wait="counters")."""
+        while True:
+            st = self._enqueue_step(rays, target, jitter, add_bg, mask, S, ndc_ray, grad_scale, buf, views, loss, g_rgb,
+                                    reducer is not None)
+            if early and reducer is not None:
+                reducer.all_reduce()
+                seq = self.__dict__.get("_early_seq", 0)
+                self._tail_flag(buf, seq & 1)                  # lands behind the exchange, looked at by the NEXT call
+                self._finish_forward(st, whole_stream=False)   # a local overflow grows the capacities; no repeat here
+                self._settle_early()                           # the previous step's flag: its copy precedes this step's counters
+                self._early_unchecked, self._early_seq = seq & 1, seq + 1
+                return st
+            flag = None
+            if reducer is not None:
+                reducer.all_reduce()
+                flag = self._tail_flag(buf)
+            ok = self._finish_forward(st, whole_stream=not early)
+            if not early:
+                self._settle_early()
+            if ok and (flag is None or float(flag[0]) == 0.0):
+                return st
+
+    def _settle_early(self) -> None:
+        """Look at the exchanged overflow flag of the last wait="counters" step, once the stream is known to be past
+        its copy (two pinned slots, alternating, so the step after it cannot have overwritten it)."""
+        slot = self.__dict__.get("_early_unchecked")
+        if slot is not None:
+            self._early_unchecked = None
+            if float(self._tail_pins[slot]) != 0.0:
+                self.step_overflows = self.__dict__.get("step_overflows", 0) + 1
+
+    def check_steps(self) -> int:
+        """Wait for everything enqueued on the current stream and return how many wait="counters" steps with a gradient
+        exchange ran with an overflowed list on some rank since the model was built (0: every step was clean)."""
+        torch.cuda.current_stream().synchronize()
+        self._settle_early()
+        return self.__dict__.get("step_overflows", 0)
+
+    def step_buffers(self, n_rays: int, ray_cols: int = 6):
+        """(rays [n_rays, ray_cols], rgb_target [n_rays, 3]): the resident input buffers `train_step(graph=True)` reads.
+        A caller that fills them itself (a device-side ray sampler) and passes them to train_step skips the copy."""
+        bufs = self.__dict__.setdefault("_step_inputs", {})
+        k = (int(n_rays), int(ray_cols))
+        dev = self._all_params()[0].device
+        if k not in bufs or bufs[k][0].device != dev:
+            bufs[k] = (torch.zeros(k[0], k[1], dtype=torch.float32, device=dev),
+                       torch.zeros(k[0], 3, dtype=torch.float32, device=dev))
+        return bufs[k]
+
+    def _train_step_graphed(self, rays, rgb_target, S, white_bg, ndc_ray, grad_scale, reducer):
+        """train_step with the launch sequence of `_enqueue_step` (memset fork / join on the side stream, the jitter's
+        host-to-device copy from its pinned staging buffer, 16 kernels, the counters' and the loss's copies to pinned
+        memory) captured once per configuration in a CUDA graph.  A call is then: draw the jitter on the host, copy
+        the batch into the graph's input buffers (host tensors go there directly; `step_buffers` themselves are not
+        copied), one graph launch, [the gradient exchange, launched behind it], one stream sync, read the counters.
+        The graph bakes in every pointer and scalar of the call, so it is keyed on all of them (`_field_key`: parameter
+        pointers, alphaMask, derived constants; gradient buffer; batch shape; flags) and a changed key captures
+        anew; list capacities are baked in too — an overflow drops the graph, repeats the step call by call with
+        larger lists and captures again.  The first call of a configuration runs call by call (it also settles the
+        capacities and the library's lazily created streams / events) and captures afterwards."""
+        N, cols = int(rays.shape[0]), int(rays.shape[1])
+        pin, add_bg = self._draw_rng_host(N, S, True, ndc_ray, white_bg)
+        buf, views = self.grad_buffer()
+        rays_in, target_in = self.step_buffers(N, cols)
+        dev = rays_in.device
+        if not (rays.is_cuda and rays.data_ptr() == rays_in.data_ptr()):
+            rays_in.copy_(rays.detach(), non_blocking=True)
+        if not (rgb_target.is_cuda and rgb_target.data_ptr() == target_in.data_ptr()):
+            target_in.copy_(rgb_target.detach().reshape(N, 3), non_blocking=True)
+        key = (N, cols, S, bool(ndc_ray), add_bg, grad_scale, reducer is not None, pin.data_ptr(), rays_in.data_ptr(),
+               buf.data_ptr(), self._field_key(views))
+        graphs = self.__dict__.setdefault("_step_graphs", {})
+        e = graphs.get(key)
+        st = None
+        if e is not None:
+            e.graph.replay()
+            lib.ftrf_launch_count_add(e.launches)
+            flag = None
+            if reducer is not None:
+                reducer.all_reduce()
+                flag = self._tail_flag(buf)
+            ok = self._finish_forward(e.st, whole_stream=True)
+            if ok and (flag is None or float(flag[0]) == 0.0):
+                st, loss = e.st, e.loss_pin.clone()[0]
+            else:
+                del graphs[key]            # a list overflowed (here or on a peer): call by call below, then a new graph
+        if st is None:
+            jitter = pin.to(dev, non_blocking=True)
+            loss_d = torch.empty(1, dtype=torch.float32, device=dev)
+            g_rgb = torch.empty(N, 3, dtype=torch.float32, device=dev)
+            st = self._step_until_clean(rays_in, target_in, jitter, add_bg, None, S, ndc_ray, grad_scale, buf, views,
+                                        loss_d, g_rgb, reducer)
+            loss = loss_d.cpu()[0]
+            if not self.__dict__.get("_step_graph_error"):
+                if len(graphs) >= 4:
+                    graphs.clear()
+                try:
+                    graphs[key] = self._capture_step(rays_in, target_in, pin, add_bg, S, ndc_ray, grad_scale, buf, views,
+                                                     reducer is not None)
+                except Exception as err:                      # noqa: BLE001 — capture unsupported here: stay call by call
+                    self._step_graph_error = repr(err)
+                    torch.cuda.synchronize(dev)
+        self._grad_gen = self.__dict__.get("_grad_gen", 0) + 1
+        for p, v in zip(self._all_params(), views):
+            if p.grad is not v:
+                p.grad = v
+        return loss, st.n_valid
+
+    def _capture_step(self, rays_in, target_in, pin, add_bg, S, ndc_ray, grad_scale, buf, views, tail_flag):
+        dev = rays_in.device
+        e = _StepGraph()
+        e.loss_pin = torch.zeros(1, dtype=torch.float32).pin_memory()
+        e.loss = torch.empty(1, dtype=torch.float32, device=dev)
+        e.g_rgb = torch.empty(rays_in.shape[0], 3, dtype=torch.float32, device=dev)
+        e.graph = torch.cuda.CUDAGraph()
+        n0 = lib.ftrf_launch_count()
+        with torch.cuda.graph(e.graph):
+            e.jitter = pin.to(dev, non_blocking=True)
+            e.st = self._enqueue_step(rays_in, target_in, e.jitter, add_bg, None, S, ndc_ray, grad_scale, buf, views,
+                                      e.loss, e.g_rgb, tail_flag)
+            e.loss_pin.copy_(e.loss, non_blocking=True)
+        e.launches = int(lib.ftrf_launch_count() - n0)
+        lib.ftrf_launch_count_add(-e.launches)               # counted while capturing, nothing ran
+        e.keep = (rays_in, target_in, pin, buf, views)
+        return e
+
+    def step_graph_info(self):
+        """{"graphs": captured step graphs alive, "launches": kernels per replay of the latest, "error": why capture was
+        given up (None if it was not)}."""
+        graphs = self.__dict__.get("_step_graphs", {})
+        last = next(reversed(graphs.values())) if graphs else None
+        return {"graphs": len(graphs), "launches": last.launches if last else 0, "error": self.__dict__.get("_step_graph_error")}
+
+    def _tail_flag(self, buf, slot=0):
+        pins = self.__dict__.get("_tail_pins")
+        if pins is None:
+            pins = self._tail_pins = torch.zeros(2, dtype=torch.float32).pin_memory()
+        pins[slot:slot + 1].copy_(buf[-GRAD_TAIL:-GRAD_TAIL + 1], non_blocking=True)
+        return pins[slot:slot + 1]
 
     def _early_grad_span(self):
         """[lo, hi) of the flat gradient buffer holding the appearance planes / lines and basis_mat (contiguous

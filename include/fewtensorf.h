@@ -358,6 +358,9 @@ int ftrf_stream_wait_event(void* stream, void* event);
 int ftrf_zero_after(void* ptr, size_t bytes, void* side_stream, void* wait_event, void* done_event);
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py's gpu_launches). */
 unsigned long long ftrf_launch_count(void);
+/* Adjust that count by `delta`: a host that captured a launch sequence in a CUDA graph subtracts what the capture
+ * counted (nothing ran) and adds the sequence's launches on every replay, so the count stays "kernels that ran". */
+void ftrf_launch_count_add(long long delta);
 
 #ifdef __cplusplus
 }

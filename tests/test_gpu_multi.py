@@ -64,6 +64,29 @@ def _worker(rank, world, port, out):
         for _ in range(2):
             run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg)
         res["in_step"] = grads()
+        # wait="counters": the call returns behind the integration stage, the steps are enqueued back to back
+        for _ in range(3):
+            run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg, wait="counters")
+        assert model.check_steps() == 0
+        res["in_step_early"] = grads()
+        # ... and a list overflowing on ONE rank: nobody repeats alone, both ranks count the step, the next one is clean
+        if rank == 1:
+            model._cap_hint[(n, S, True)] = (64, 1 << 20)
+        for _ in range(2):
+            run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg, wait="counters")
+        assert model.check_steps() == 1, (rank, model.check_steps())
+        res["in_step_early_after_overflow"] = grads()
+        # the captured step (one graph launch) with the exchange launched behind it
+        jp = jit[rank].reshape(-1).pin_memory()
+        model._draw_rng_host = lambda n_rays, S_, is_train, ndc, wb: (jp, True)
+        try:
+            for _ in range(3):
+                model.train_step(parts[rank][0].to(dev), parts[rank][1].to(dev), None, white_bg=True, N_samples=S,
+                                 grad_scale=1.0 / world, allreduce=sg, graph=True)
+        finally:
+            del model._draw_rng_host
+        assert model.step_graph_info()["graphs"] == 1 and model.step_graph_info()["error"] is None
+        res["in_step_graph"] = grads()
     dist.barrier()
     if rank == 0:
         # one GPU, the concatenated batch (mean over 2n rays = sum of the two pre-scaled rank means)
@@ -95,3 +118,4 @@ def test_two_rank_gradients_equal_one_gpu_on_the_concatenated_batch():
     assert max(errs.values()) < 1e-5, errs
     if frac is not None:
         assert "p2p" in errs and "p2p_fused" in errs and frac < 0.6
+        assert "in_step_early" in errs and "in_step_early_after_overflow" in errs and "in_step_graph" in errs
