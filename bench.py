@@ -846,8 +846,7 @@ def run_gpu(args):
            "clocks": clocks,
            "with_prequeue": {"ms_per_step": plain_ms, "value": RAYS_PER_GPU * world / (plain_ms * 1e-3), "unit": "rays/s",
                              "note": "the same device-timed steps, each behind an untimed 0.5 ms spin kernel (+ a device-side rank alignment at N > 1) "
-                                     "so that its launches are queued ahead of it; at 8 GPUs this is SLOWER than the headline (0.78 vs 0.74 ms), "
-                                     "at 1 GPU the two agree within 1-2 %"},
+                                     "so that its launches are queued ahead of it; agrees with the headline within 1-2 % at every N"},
            "e2e": {"value": e2e_rps, "unit": "rays/s", "h2d_bytes_per_step": RAYS_PER_GPU * 10 * 4, "d2h_bytes_per_step": 4 + 32,
                    "api": "OctreeRender_trilinear_fast + torch MSE + autograd backward (reference-facing); h2d = rays, targets "
                           "and the step's jitter (drawn on the host like the reference's)",
