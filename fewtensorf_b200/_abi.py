@@ -94,7 +94,7 @@ EXPORTS = [
     "ftrf_stage_shade", "ftrf_stage_composite", "ftrf_mse_loss", "ftrf_alpha_mask_words",
     "ftrf_pack_alpha_mask", "ftrf_alpha_mask_coarse_words", "ftrf_build_coarse_mask", "ftrf_density_at", "ftrf_dense_alpha_bits", "ftrf_dilate_alpha_mask",
     "ftrf_unpack_alpha_mask", "ftrf_filter_rays", "ftrf_event_record", "ftrf_stream_wait_event", "ftrf_zero_after", "ftrf_profile_enable", "ftrf_profile_read",
-    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_launch_count_add", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce",
+    "ftrf_profile_stage_name", "ftrf_launch_count", "ftrf_launch_count_add", "ftrf_reg_factors", "ftrf_adam_step", "ftrf_adam_step_guarded", "ftrf_generate_rays", "ftrf_multimem_allreduce", "ftrf_p2p_allreduce",
     "ftrf_points_workspace_bytes", "ftrf_density_feature", "ftrf_app_feature", "ftrf_shade_points", "ftrf_shade_points_static",
     "ftrf_resample_factor", "ftrf_crop_factor", "ftrf_ortho_reg",
     "ftrf_p2p_allreduce_regions", "ftrf_multimem_allreduce_regions", "ftrf_allreduce_regions_fused",
@@ -178,6 +178,9 @@ def _load(path=LIB_PATH):
     lib.ftrf_adam_step.restype = C.c_int
     lib.ftrf_adam_step.argtypes = [C.POINTER(FtrfAdamSegment), C.c_int, C.c_float, C.c_float, C.c_float, C.c_int,
                                    C.c_void_p]
+    lib.ftrf_adam_step_guarded.restype = C.c_int
+    lib.ftrf_adam_step_guarded.argtypes = [C.POINTER(FtrfAdamSegment), C.c_int, C.c_float, C.c_float, C.c_float, C.c_int,
+                                           C.c_void_p, C.c_void_p]
     lib.ftrf_generate_rays.restype = C.c_int
     lib.ftrf_generate_rays.argtypes = [C.POINTER(FtrfCamera), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ftrf_launch_count.restype = C.c_ulonglong

@@ -193,6 +193,7 @@ struct AdamArgs {
   AdamSeg s[ADAM_MAX_SEGS];
   int n_segs;
   float beta1, beta2, eps, inv_bc2_sqrt;
+  const float* guard;        // optional device float: a non-zero value turns the whole launch into a no-op
 };
 
 __device__ __forceinline__ void adam1(float& p, float g, float& m, float& v, const AdamArgs& a, float step_size) {
@@ -204,6 +205,7 @@ __device__ __forceinline__ void adam1(float& p, float g, float& m, float& v, con
 
 __global__ void __launch_bounds__(256)
 adam_kernel(const __grid_constant__ AdamArgs a) {
+  if (a.guard && __ldg(a.guard) != 0.f) return;
   int k = 0;
   while (k + 1 < a.n_segs && (int)blockIdx.x >= a.s[k + 1].first_block) ++k;
   const AdamSeg& S = a.s[k];
@@ -251,8 +253,8 @@ extern "C" int ftrf_reg_factors(const FtrfFactorSet* fs, int model, float w_tv, 
   return launch_reg_factors(*fs, model, w_tv, w_l1, dev_scale, loss_out, with_lines, (cudaStream_t)stream);
 }
 
-extern "C" int ftrf_adam_step(const FtrfAdamSegment* segs, int n_segs, float beta1, float beta2, float eps, int step,
-                              void* stream) {
+extern "C" int ftrf_adam_step_guarded(const FtrfAdamSegment* segs, int n_segs, float beta1, float beta2, float eps, int step,
+                                      const float* skip_if_nonzero, void* stream) {
   if (!segs || n_segs <= 0 || step < 1) { set_error("adam_step: bad argument"); return FTRF_E_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
   // torch/optim/adam.py _single_tensor_adam: bias corrections on the host in double
@@ -260,6 +262,7 @@ extern "C" int ftrf_adam_step(const FtrfAdamSegment* segs, int n_segs, float bet
   for (int s0 = 0; s0 < n_segs; s0 += ADAM_MAX_SEGS) {
     AdamArgs a{};
     a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
+    a.guard = skip_if_nonzero;
     int blocks = 0;
     const int n = n_segs - s0 < ADAM_MAX_SEGS ? n_segs - s0 : ADAM_MAX_SEGS;
     int used = 0;
@@ -282,4 +285,9 @@ extern "C" int ftrf_adam_step(const FtrfAdamSegment* segs, int n_segs, float bet
     if (int e = check_launch("adam_step")) return e;
   }
   return FTRF_OK;
+}
+
+extern "C" int ftrf_adam_step(const FtrfAdamSegment* segs, int n_segs, float beta1, float beta2, float eps, int step,
+                              void* stream) {
+  return ftrf_adam_step_guarded(segs, n_segs, beta1, beta2, eps, step, nullptr, stream);
 }

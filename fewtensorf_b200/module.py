@@ -1049,6 +1049,13 @@ class TensorBase(nn.Module):
             if float(self._tail_pins[slot]) != 0.0:
                 self.step_overflows = self.__dict__.get("step_overflows", 0) + 1
 
+    def overflow_flag(self):
+        """1-element view of the gradient buffer's tail slot: 0 after a clean step, non-zero after a step with a
+        gradient exchange in which some rank's sample lists overflowed (FtrfCall.overflow_out, summed by the exchange).
+        `optim.FusedAdam(..., guard=model)` skips its update on it.  None before the first gradient buffer exists."""
+        buf = self.__dict__.get("_gradbuf")
+        return None if buf is None else buf[buf.numel() - GRAD_TAIL:buf.numel() - GRAD_TAIL + 1]
+
     def check_steps(self) -> int:
         """Wait for everything enqueued on the current stream and return how many wait="counters" steps with a gradient
         exchange ran with an overflowed list on some rank since the model was built (0: every step was clean)."""

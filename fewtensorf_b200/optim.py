@@ -40,14 +40,35 @@ def _same_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
 
 
 class FusedAdam(torch.optim.Optimizer):
-    """torch.optim.Adam (no weight decay, no amsgrad) with the whole step in one CUDA launch."""
+    """torch.optim.Adam (no weight decay, no amsgrad) with the whole step in one CUDA launch.
 
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+    guard: a model (its `overflow_flag()`), a callable returning a 1-element fp32 CUDA tensor or None, or such a tensor.
+    A non-zero value on the device turns the step into a no-op (parameters and moments untouched; the host-side step
+    count still advances, so the bias corrections of later steps are one step further than torch's would be) — what
+    makes `train_step(wait="counters", allreduce=...)` safe to follow with `step()` without looking at
+    `check_steps()`: a step whose lists overflowed on any rank is dropped on every rank."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, guard=None):
         if not 0.0 <= eps or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0:
             raise ValueError("FusedAdam: invalid betas / eps")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
         self._table = None
         self._table_key = None
+        self.guard = guard
+
+    def _guard_tensor(self):
+        g = self.guard
+        if g is None:
+            return None
+        if hasattr(g, "overflow_flag"):
+            g = g.overflow_flag()
+        elif callable(g):
+            g = g()
+        if g is None:
+            return None
+        if not (torch.is_tensor(g) and g.is_cuda and g.dtype == torch.float32 and g.numel() == 1):
+            raise RuntimeError("FusedAdam: guard must be a 1-element fp32 CUDA tensor")
+        return g
 
     def _init_state(self, p):
         st = self.state[p]
@@ -66,6 +87,7 @@ class FusedAdam(torch.optim.Optimizer):
         # one launch per distinct (betas, eps, step) combination; normally exactly one
         batches = {}
         keep = []
+        guard = self._guard_tensor()
         for group in self.param_groups:
             b1, b2 = group['betas']
             for p in group['params']:
@@ -97,5 +119,6 @@ class FusedAdam(torch.optim.Optimizer):
             for s, it in zip(table, items):
                 s.lr = it[3]
             with torch.cuda.device(items[0][0].device):        # launch where the parameters live
-                check(lib.ftrf_adam_step(table, len(items), b1, b2, eps, t, _stream()), "adam_step")
+                check(lib.ftrf_adam_step_guarded(table, len(items), b1, b2, eps, t, None if guard is None else guard.data_ptr(),
+                                                 _stream()), "adam_step")
         return loss

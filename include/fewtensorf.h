@@ -335,6 +335,12 @@ typedef struct FtrfAdamSegment {
 } FtrfAdamSegment;
 int ftrf_adam_step(const FtrfAdamSegment* segs /* host */, int n_segs, float beta1, float beta2, float eps, int step,
                    void* stream);
+/* The same step, skipped as a whole (parameters and moments untouched) when the device float `skip_if_nonzero` is not 0
+ * at launch time on the device — NULL = never.  Point it at the gradient buffer's exchanged overflow flag
+ * (FtrfCall.overflow_out) and a step whose sample lists overflowed on any rank is dropped on every rank without a host
+ * round trip; the analogue of a loss scaler's found-inf skip.  No reference counterpart (the reference has no lists). */
+int ftrf_adam_step_guarded(const FtrfAdamSegment* segs /* host */, int n_segs, float beta1, float beta2, float eps, int step,
+                           const float* skip_if_nonzero /* device, may be NULL */, void* stream);
 /* Camera rays on the device: rows row0, row0+row_step, ... (n_rows of them) of an H x W
  * pin-hole image, [n_rows*W][6] = (origin, direction).  dataLoader/ray_utils.py:24-41 get_ray_directions (pixel
  * centre + 0.5), :44-63 blender variant (y, z negated), dataLoader/blender.py:59 normalisation,

@@ -40,3 +40,25 @@ for it in range(K + 5):
         for i in range(len(names)):
             acc[i] += (t[i + 1] - t[0]) * 1e6 / K
 print("host clock, us from the start of the step:", {n: round(a, 1) for n, a in zip(names, acc)})
+
+if len(sys.argv) > 1 and sys.argv[1] == "profile":            # where the host's time goes (cProfile, 200 steps)
+    import cProfile
+    import pstats
+
+    def one():
+        r = rays_p.to(dev, non_blocking=True)
+        tg = target_p.to(dev, non_blocking=True)
+        for p in params:
+            p.grad = None
+        rgb, _, depth, _, _, nvs = ft.OctreeRender_trilinear_fast(r, model, None, chunk=bench.RAYS_PER_GPU, N_samples=bench.N_SAMPLES,
+                                                                  white_bg=True, is_train=True, device=dev)
+        loss = torch.mean((rgb - tg) ** 2)
+        loss.backward()
+        return loss.item()
+
+    pr = cProfile.Profile()
+    pr.enable()
+    for _ in range(200):
+        one()
+    pr.disable()
+    pstats.Stats(pr).sort_stats("tottime").print_stats(40)

@@ -76,6 +76,25 @@ def _worker(rank, world, port, out):
             run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg, wait="counters")
         assert model.check_steps() == 1, (rank, model.check_steps())
         res["in_step_early_after_overflow"] = grads()
+        # ... and with the guarded optimizer behind the steps: the overflowed step is dropped on BOTH ranks, the clean
+        # one is applied
+        import fewtensorf_b200 as ft
+        snap = [p.detach().clone() for p in model.parameters()]
+        opt = ft.FusedAdam(list(model.parameters()), lr=1e-3, guard=model)
+        if rank == 1:
+            model._cap_hint[(n, S, True)] = (64, 1 << 20)
+        run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg, wait="counters")
+        opt.step()
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b) for a, b in zip(snap, model.parameters())), rank
+        run(parts[rank][0], parts[rank][1], jit[rank], 1.0 / world, allreduce=sg, wait="counters")
+        opt.step()
+        torch.cuda.synchronize()
+        assert not torch.equal(snap[0], next(model.parameters())), rank
+        assert model.check_steps() == 2
+        with torch.no_grad():
+            for p, q in zip(model.parameters(), snap):
+                p.copy_(q)
         # the captured step (one graph launch) with the exchange launched behind it
         jp = jit[rank].reshape(-1).pin_memory()
         model._draw_rng_host = lambda n_rays, S_, is_train, ndc, wb: (jp, True)

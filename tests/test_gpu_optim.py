@@ -173,3 +173,41 @@ def test_full_size_reg_and_adam_vs_torch_cuda():
     for p, q in zip(mine, theirs):
         assert rel_inf(p.detach(), q.detach()) < 2e-6
     del extra
+
+
+def test_guarded_adam_drops_the_step_when_the_flag_is_set():
+    """FusedAdam(guard=...): a non-zero device flag turns the launch into a no-op, zero leaves it the plain step."""
+    import fewtensorf_b200 as ft
+    gen = torch.Generator().manual_seed(3)
+    shapes = [(1, 16, 40, 48), (1, 16, 56, 1), (27, 48), (128, 150), (128,), (5000,)]
+    base = [torch.randn(s, generator=gen) for s in shapes]
+    grads = [torch.randn(s, generator=gen) for s in shapes]
+
+    def run(flag_value):
+        ps = [torch.nn.Parameter(b.clone().cuda()) for b in base]
+        flag = None if flag_value is None else torch.full((1,), flag_value, device="cuda")
+        opt = ft.FusedAdam(ps, lr=0.01, betas=(0.9, 0.99), guard=(None if flag is None else (lambda: flag)))
+        for _ in range(2):
+            for p, g in zip(ps, grads):
+                p.grad = g.clone().cuda()
+            opt.step()
+        torch.cuda.synchronize()
+        return ps, opt
+
+    plain, _ = run(None)
+    open_, _ = run(0.0)
+    shut, opt = run(2.0)
+    for a, b, c, b0 in zip(plain, open_, shut, base):
+        assert torch.equal(a, b)
+        assert torch.equal(c.detach().cpu(), b0)
+        assert float(opt.state[c]["exp_avg"].abs().max()) == 0.0 and float(opt.state[c]["exp_avg_sq"].abs().max()) == 0.0
+    assert not torch.equal(plain[0].detach().cpu(), base[0])
+    with pytest.raises(RuntimeError):
+        ft.FusedAdam([torch.nn.Parameter(base[0].clone().cuda())], guard=lambda: torch.zeros(2, device="cuda"))._guard_tensor()
+
+
+def test_overflow_flag_is_the_gradient_buffers_tail(gm):
+    g, m = gm
+    m.grad_buffer()
+    f = m.overflow_flag()
+    assert f.numel() == 1 and f.data_ptr() == m._gradbuf.data_ptr() + (m._gradbuf.numel() - 4) * 4
