@@ -483,7 +483,9 @@ def workload_config(n_gpus):
             "rays_per_gpu": RAYS_PER_GPU, "n_samples": N_SAMPLES, "grid": GRID, "mask_grid": MASK_GRID,
             "l2": "flushed between timed steps (512 MiB write)",
             "queue": "steps are enqueued as the host gets to them (no pre-queue spin kernel in front of the timed steps: host "
-                     "launch bubbles, if any, are inside the headline; `with_prequeue` is the same measurement behind one)",
+                     "launch bubbles, if any, are inside the headline; `with_prequeue` is the same measurement behind one); "
+                     "train_step(wait='counters') returns once the step's sample counts and overflow flags are final, so "
+                     "the next step is enqueued while this one runs (`with_host_wait_per_step`: the host waits for the end of each)",
             "parallelism": f"ray-sharded x{n_gpus}"}
 
 
